@@ -1,0 +1,75 @@
+"""Sensor / algorithm parameters, field names 1:1 with the reference's compile-time constants
+(LeGO-LOAM/include/utility.h:60-136).  The reference changes sensor by editing the header and rebuilding
+(README.md:60-86); here the same names are runtime fields of `lego_params` (include/lego_b200.h)."""
+import ctypes
+import math
+
+import numpy as np
+
+
+class LegoParams(ctypes.Structure):
+    """ctypes mirror of `lego_params` in include/lego_b200.h (keep field order identical)."""
+    _fields_ = [
+        ("N_SCAN", ctypes.c_int), ("Horizon_SCAN", ctypes.c_int),
+        ("ang_res_x", ctypes.c_float), ("ang_res_y", ctypes.c_float), ("ang_bottom", ctypes.c_float),
+        ("groundScanInd", ctypes.c_int), ("useCloudRing", ctypes.c_int),
+        ("sensorMinimumRange", ctypes.c_float), ("sensorMountAngle", ctypes.c_float),
+        ("segmentTheta", ctypes.c_float), ("segmentValidPointNum", ctypes.c_int), ("segmentValidLineNum", ctypes.c_int),
+        ("segmentAlphaX", ctypes.c_float), ("segmentAlphaY", ctypes.c_float),
+        ("scanPeriod", ctypes.c_float),
+        ("edgeFeatureNum", ctypes.c_int), ("surfFeatureNum", ctypes.c_int), ("sectionsTotal", ctypes.c_int),
+        ("edgeThreshold", ctypes.c_float), ("surfThreshold", ctypes.c_float),
+        ("nearestFeatureSearchSqDist", ctypes.c_float),
+        ("surroundingKeyframeSearchRadius", ctypes.c_float),
+        ("mappingProcessInterval", ctypes.c_double),
+        ("loopClosureEnableFlag", ctypes.c_int),
+        ("device", ctypes.c_int),
+    ]
+
+
+def _f32(x):
+    return float(np.float32(x))
+
+
+# name -> (N_SCAN, Horizon_SCAN, ang_res_x, ang_res_y, ang_bottom, groundScanInd, useCloudRing); every value is
+# evaluated exactly as the C expression in the header would be (double arithmetic, then narrowed to float).
+_SENSORS = {
+    "vlp16": (16, 1800, 0.2, 2.0, 15.0 + 0.1, 7, 1),                                   # utility.h:63-68
+    "vlp16_noring": (16, 1800, 0.2, 2.0, 15.0 + 0.1, 7, 0),                            # utility.h:60 = false
+    "hdl32": (32, 1800, 360.0 / _f32(1800), 41.333 / _f32(31), 30.666666, 20, 1),      # README.md:73-82
+    "hdl64": (64, 2083, 360.0 / _f32(2083), 26.9 / _f32(63), 24.9, 50, 1),             # SURVEY.md 8c (not in reference)
+    "vls128": (128, 1800, 0.2, 0.3, 25.0, 10, 1),                                      # utility.h:79-84
+}
+
+# beam geometry used only by the synthetic generator: (elev_bottom_deg, elev_step_deg, sensor_height)
+SENSOR_GEOMETRY = {
+    "vlp16": (-15.0, 2.0, 0.7), "vlp16_noring": (-15.0, 2.0, 0.7),
+    "hdl32": (-30.67, 41.33 / 31.0, 1.2), "hdl64": (-24.9, 26.9 / 63.0, 1.73), "vls128": (-25.0, 0.3, 1.8),
+}
+
+
+def make_params(sensor="vlp16", device=0):
+    n, h, rx, ry, bottom, gsi, ring = _SENSORS[sensor]
+    p = LegoParams()
+    p.N_SCAN, p.Horizon_SCAN = n, h
+    p.ang_res_x, p.ang_res_y, p.ang_bottom = rx, ry, bottom
+    p.groundScanInd, p.useCloudRing = gsi, ring
+    p.sensorMinimumRange = 1.0                      # utility.h:111
+    p.sensorMountAngle = 0.0                        # utility.h:112
+    p.segmentTheta = 60.0 / 180.0 * math.pi         # utility.h:113
+    p.segmentValidPointNum = 5                      # utility.h:114
+    p.segmentValidLineNum = 3                       # utility.h:115
+    p.segmentAlphaX = float(p.ang_res_x) / 180.0 * math.pi   # utility.h:116 (float / double math, narrowed)
+    p.segmentAlphaY = float(p.ang_res_y) / 180.0 * math.pi   # utility.h:117
+    p.scanPeriod = 0.1                              # utility.h:107
+    p.edgeFeatureNum, p.surfFeatureNum, p.sectionsTotal = 2, 4, 6   # utility.h:120-122
+    p.edgeThreshold, p.surfThreshold = 0.1, 0.1     # utility.h:123-124
+    p.nearestFeatureSearchSqDist = 25.0             # utility.h:125
+    p.surroundingKeyframeSearchRadius = 50.0        # utility.h:129
+    p.mappingProcessInterval = 0.3                  # utility.h:105
+    p.loopClosureEnableFlag = 0                     # utility.h:104
+    p.device = device
+    return p
+
+
+SENSORS = tuple(_SENSORS)

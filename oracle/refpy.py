@@ -1,0 +1,96 @@
+"""TEST INFRASTRUCTURE ONLY.  ctypes binding for oracle/_ref/liblego_ref_<cfg>.so (the reference's own sources
+compiled verbatim against oracle/shim; see oracle/ref_harness.cpp).  Used by tests/, smoke() and bench.py's
+cpu_baseline / --impl reference arm only."""
+import ctypes
+import os
+
+import numpy as np
+
+HERE = os.path.dirname(os.path.abspath(__file__))
+
+
+def ref_so(cfg):
+    return os.path.join(HERE, "_ref", "liblego_ref_%s.so" % cfg)
+
+
+def available(cfg):
+    return os.path.exists(ref_so(cfg))
+
+
+class RefPipeline:
+    IP, FA, MO = 1, 2, 4
+
+    def __init__(self, cfg="vlp16", snapshots=True):
+        self.lib = lib = ctypes.CDLL(ref_so(cfg))
+        lib.ref_create.restype = ctypes.c_void_p
+        lib.ref_create.argtypes = [ctypes.c_int]
+        lib.ref_destroy.argtypes = [ctypes.c_void_p]
+        lib.ref_set_verbatim_drivers.argtypes = [ctypes.c_void_p, ctypes.c_int]
+        lib.ref_feed_scan.restype = ctypes.c_int
+        lib.ref_feed_scan.argtypes = [ctypes.c_void_p, ctypes.c_void_p, ctypes.c_void_p, ctypes.c_int, ctypes.c_int,
+                                      ctypes.c_double, ctypes.c_int]
+        for fn in (lib.ref_get_f32, lib.ref_get_i32):
+            fn.restype = ctypes.c_long
+            fn.argtypes = [ctypes.c_void_p, ctypes.c_char_p, ctypes.c_void_p, ctypes.c_long]
+        lib.ref_get_poses.argtypes = [ctypes.c_void_p, ctypes.c_void_p]
+        lib.ref_get_timers.argtypes = [ctypes.c_void_p, ctypes.c_void_p, ctypes.c_void_p, ctypes.c_void_p]
+        lib.ref_timer_name.restype = ctypes.c_char_p
+        lib.ref_timer_name.argtypes = [ctypes.c_int]
+        lib.ref_params.argtypes = [ctypes.c_void_p]
+        self.N_SCAN, self.Horizon_SCAN = lib.ref_n_scan(), lib.ref_horizon_scan()
+        self.groundScanInd, self.useCloudRing = lib.ref_ground_scan_ind(), lib.ref_use_cloud_ring()
+        self.h = lib.ref_create(1 if snapshots else 0)
+
+    def close(self):
+        if self.h:
+            self.lib.ref_destroy(self.h)
+            self.h = None
+
+    __del__ = close
+
+    def params(self):
+        out = np.zeros(8, np.float32)
+        self.lib.ref_params(out.ctypes.data)
+        return dict(zip(["ang_res_x", "ang_res_y", "ang_bottom", "segmentAlphaX", "segmentAlphaY", "segmentTheta",
+                         "sensorMinimumRange", "sensorMountAngle"], out))
+
+    def set_verbatim(self, on=True):
+        self.lib.ref_set_verbatim_drivers(self.h, 1 if on else 0)
+
+    def feed(self, xyzi, ring, stamp, stages=7, is_dense=True):
+        xyzi = np.ascontiguousarray(xyzi, np.float32)
+        ring_p = None
+        if ring is not None:
+            ring = np.ascontiguousarray(ring, np.uint16)
+            ring_p = ring.ctypes.data
+        return self.lib.ref_feed_scan(self.h, xyzi.ctypes.data, ring_p, int(xyzi.shape[0]), 1 if is_dense else 0,
+                                      float(stamp), stages)
+
+    def get(self, name):
+        b = name.encode()
+        n = self.lib.ref_get_f32(self.h, b, None, 0)
+        if n >= 0:
+            out = np.empty(n, np.float32)
+            self.lib.ref_get_f32(self.h, b, out.ctypes.data, n)
+            return out
+        n = self.lib.ref_get_i32(self.h, b, None, 0)
+        if n >= 0:
+            out = np.empty(n, np.int32)
+            self.lib.ref_get_i32(self.h, b, out.ctypes.data, n)
+            return out
+        raise KeyError(name)
+
+    def cloud(self, name):
+        return self.get(name).reshape(-1, 4)
+
+    def poses(self):
+        out = np.zeros(18, np.float32)
+        self.lib.ref_get_poses(self.h, out.ctypes.data)
+        return out[:6].copy(), out[6:12].copy(), out[12:].copy()
+
+    def timers(self):
+        n = self.lib.ref_num_timers()
+        ms = np.zeros(n, np.float64)
+        scans, mo = ctypes.c_long(0), ctypes.c_long(0)
+        self.lib.ref_get_timers(self.h, ms.ctypes.data, ctypes.byref(scans), ctypes.byref(mo))
+        return {self.lib.ref_timer_name(i).decode(): ms[i] for i in range(n)}, scans.value, mo.value
