@@ -1,0 +1,155 @@
+/* lego_b200.h -- C ABI of the B200-native LeGO-LOAM per-scan hot path.
+ *
+ * The reference (vigorbird/LeGO-LOAM_comment) exposes no library / plugin / FFI interface: each stage is a
+ * file-local C++ class inside a ROS node, and the boundary a maintainer can cut at is the BODY of each node's
+ * per-scan method plus the payload of the topics it consumes and produces.  Each
+ * create/process/destroy triple below replaces one such body:
+ *
+ *   lego_ip_*   <- ImageProjection::cloudHandler            LeGO-LOAM/src/imageProjection.cpp:181-197
+ *   lego_fa_*   <- FeatureAssociation::runFeatureAssociation LeGO-LOAM/src/featureAssociation.cpp:1817-1860
+ *   lego_mo_*   <- mapOptimization::run                      LeGO-LOAM/src/mapOptmization.cpp:1487-1522
+ *   lego_pipeline_* : the three stages chained on the device for `lanes` independent sequences at once (the
+ *                     throughput path; no equivalent in the reference, which pipelines the nodes over ROS topics).
+ *
+ * Conventions
+ *   - plain C types only; clouds are arrays of 4 floats per point (x, y, z, intensity) like pcl::PointXYZI's
+ *     payload (utility.h:51); the ring channel is a parallel uint16 array (PointXYZIR, utility.h:153-165).
+ *   - every function returns LEGO_OK (0) or a negative error code; nothing throws, nothing exits.
+ *   - a handle owns all its device memory; one host thread per handle; handles are independent.
+ *   - there is NO CPU fallback: every entry point runs CUDA kernels built for sm_100a and fails with
+ *     LEGO_ERR_CUDA when no usable device is present.
+ */
+#ifndef LEGO_B200_H_
+#define LEGO_B200_H_
+
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define LEGO_OK 0
+#define LEGO_ERR_ARG (-1)        /* bad argument (null pointer, size out of range)                      */
+#define LEGO_ERR_CUDA (-2)       /* CUDA runtime failure, or no device: lego_last_error() has the text  */
+#define LEGO_ERR_NOT_DENSE (-3)  /* useCloudRing with is_dense == 0: the reference logs ROS_ERROR and shuts
+                                    down (imageProjection.cpp:172-177); here it is an error code         */
+#define LEGO_ERR_CAPACITY (-4)   /* more points / keyframes than the handle was created for             */
+#define LEGO_ERR_NAME (-5)       /* unknown array name in lego_*_download / upload                      */
+
+/* Field names and meaning = the reference's compile-time constants, LeGO-LOAM/include/utility.h:60-136. */
+typedef struct lego_params {
+    int N_SCAN, Horizon_SCAN;                /* utility.h:63-64                                          */
+    float ang_res_x, ang_res_y, ang_bottom;  /* utility.h:65-67                                          */
+    int groundScanInd;                       /* utility.h:68                                             */
+    int useCloudRing;                        /* utility.h:60                                             */
+    float sensorMinimumRange;                /* utility.h:111                                            */
+    float sensorMountAngle;                  /* utility.h:112                                            */
+    float segmentTheta;                      /* utility.h:113                                            */
+    int segmentValidPointNum;                /* utility.h:114                                            */
+    int segmentValidLineNum;                 /* utility.h:115                                            */
+    float segmentAlphaX, segmentAlphaY;      /* utility.h:116-117                                        */
+    float scanPeriod;                        /* utility.h:107                                            */
+    int edgeFeatureNum, surfFeatureNum, sectionsTotal;   /* utility.h:120-122                            */
+    float edgeThreshold, surfThreshold;      /* utility.h:123-124                                        */
+    float nearestFeatureSearchSqDist;        /* utility.h:125                                            */
+    float surroundingKeyframeSearchRadius;   /* utility.h:129                                            */
+    double mappingProcessInterval;           /* utility.h:105                                            */
+    int loopClosureEnableFlag;               /* utility.h:104 (must be 0 in this release)                */
+    int device;                              /* CUDA device ordinal                                      */
+} lego_params;
+
+/* A cloud living on the device (dev) with an optional host mirror (host, may be NULL). Valid until the next
+ * process() call on the handle that produced it. */
+typedef struct lego_cloud_view {
+    const float* dev;    /* device pointer, count*4 floats */
+    const float* host;   /* host pointer or NULL           */
+    int count;
+} lego_cloud_view;
+
+/* cloud_msgs/cloud_info (cloud_msgs/msg/cloud_info.msg:1-11).  Per-ring arrays have N_SCAN entries; per-point
+ * arrays have `count` valid entries (the reference allocates N_SCAN*Horizon_SCAN and never clears them,
+ * imageProjection.cpp:125-130; only the first `count` are meaningful). Pointers are HOST pointers when the view
+ * is an input of lego_fa_process and device pointers in dev_* when handed over on the device. */
+typedef struct lego_cloud_info_view {
+    const int32_t* startRingIndex;
+    const int32_t* endRingIndex;
+    float startOrientation, endOrientation, orientationDiff;
+    const uint8_t* segmentedCloudGroundFlag;
+    const uint32_t* segmentedCloudColInd;
+    const float* segmentedCloudRange;
+    int count;
+    int on_device;       /* 0: the pointers above are host memory, 1: device memory */
+} lego_cloud_info_view;
+
+const char* lego_last_error(void);
+int lego_device_count(void);
+
+/* ---------------------------------------------------------------- ImageProjection */
+typedef struct lego_ip lego_ip;
+int lego_ip_create(const lego_params* p, lego_ip** out);
+int lego_ip_destroy(lego_ip* h);
+/* One lidar scan: xyzi = P*4 floats in sensor firing order, ring = P uint16 or NULL (required when
+ * useCloudRing), host memory.  Outputs: segmented cloud + cloud_info + outlier cloud, device-resident with host
+ * mirrors filled (payload of /segmented_cloud, /segmented_cloud_info, /outlier_cloud, imageProjection.cpp:463-478). */
+int lego_ip_process(lego_ip* h, const float* xyzi, const uint16_t* ring, int P, int is_dense, double stamp,
+                    lego_cloud_info_view* info, lego_cloud_view* segmented, lego_cloud_view* outlier);
+
+/* ---------------------------------------------------------------- FeatureAssociation */
+typedef struct lego_fa lego_fa;
+typedef struct lego_fa_outputs {
+    lego_cloud_view cornerPointsSharp, cornerPointsLessSharp, surfPointsFlat, surfPointsLessFlat; /* featureAssociation.cpp:786-817 */
+    lego_cloud_view laserCloudCornerLast, laserCloudSurfLast, outlierCloudLast;                   /* featureAssociation.cpp:1796-1813 */
+    int odometry_valid;   /* 0 on the initialisation scan (featureAssociation.cpp:1846-1849), else 1      */
+    int published;        /* 1 when the three "last" clouds were forwarded to mapping this scan           */
+    float transformCur[6];
+} lego_fa_outputs;
+int lego_fa_create(const lego_params* p, lego_fa** out);
+int lego_fa_destroy(lego_fa* h);
+/* Inputs = the three ImageProjection outputs of one scan (host or device views). transformSum_out = accumulated
+ * odometry [rx,ry,rz,tx,ty,tz] in the LOAM camera frame (featureAssociation.cpp:1697-1725). */
+int lego_fa_process(lego_fa* h, const lego_cloud_info_view* info, const lego_cloud_view* segmented,
+                    const lego_cloud_view* outlier, double stamp, float transformSum_out[6], lego_fa_outputs* out);
+
+/* ---------------------------------------------------------------- mapOptimization (scan-to-map) */
+typedef struct lego_mo lego_mo;
+int lego_mo_create(const lego_params* p, lego_mo** out);
+int lego_mo_destroy(lego_mo* h);
+/* Inputs = /laser_cloud_corner_last, /laser_cloud_surf_last, /outlier_cloud_last and the odometry pose of the
+ * same stamp.  *processed = 1 when the mapping body ran (time gate mapOptmization.cpp:1499).  Outputs follow
+ * publishTF (mapOptmization.cpp:654-673): transformAftMapped and transformBefMapped. */
+int lego_mo_process(lego_mo* h, const lego_cloud_view* corner_last, const lego_cloud_view* surf_last,
+                    const lego_cloud_view* outlier_last, const float transformSum[6], double stamp,
+                    float transformAftMapped_out[6], float transformBefMapped_out[6], int* processed);
+
+/* ---------------------------------------------------------------- chained, batched pipeline */
+typedef struct lego_pipeline lego_pipeline;
+/* lanes independent sequences processed in lock step; max_points = capacity per scan (0 = N_SCAN*Horizon_SCAN+slack) */
+int lego_pipeline_create(const lego_params* p, int lanes, int max_points, lego_pipeline** out);
+int lego_pipeline_destroy(lego_pipeline* h);
+/* One scan for every lane.  xyzi: lanes * stride_points * 4 floats, ring: lanes * stride_points, npts: lanes
+ * ints, stamps: lanes doubles.  src_on_device = 1 when xyzi/ring are device pointers (npts/stamps stay host).
+ * stage_mask: bit0 ImageProjection, bit1 FeatureAssociation, bit2 mapOptimization. */
+int lego_pipeline_step(lego_pipeline* h, const float* xyzi, const uint16_t* ring, const int* npts,
+                       int stride_points, const double* stamps, int src_on_device, int stage_mask);
+/* poses_out: lanes * 18 floats = transformSum | transformAftMapped | transformBefMapped; flags_out: lanes ints,
+ * bit1 odometry ran, bit2 clouds forwarded to mapping, bit3 mapping body ran.  Synchronises the handle's stream. */
+int lego_pipeline_get_poses(lego_pipeline* h, float* poses_out, int* flags_out);
+int lego_pipeline_sync(lego_pipeline* h);
+/* number of kernel launches issued by the handle so far (bench.py's gpu_launches) */
+long lego_pipeline_launch_count(lego_pipeline* h);
+/* Parity / debug access to named device arrays of one lane (see DESIGN.md for the name list).  Returns the
+ * element count (and copies min(count, cap) elements) or a negative error code.  elem_size_out gets 1/2/4/16. */
+long lego_pipeline_download(lego_pipeline* h, int lane, const char* name, void* dst, long cap, int* elem_size_out);
+long lego_pipeline_upload(lego_pipeline* h, int lane, const char* name, const void* src, long count);
+
+/* ---------------------------------------------------------------- device self-tests (parity suite) */
+/* out[i] = the device implementation of glibc's atan2f(y[i], x[i]) (csrc/parity_math.cuh); host pointers. */
+int lego_selftest_atan2f(const float* y, const float* x, float* out, long n);
+/* Sorts nseg independent segments (offsets has nseg+1 entries) on the device with the replayed libstdc++
+ * std::sort (csrc/std_sort_replay.cuh); inds_out receives, per segment, the original positions in sorted order. */
+int lego_selftest_std_sort(const float* values, const int* offsets, int nseg, int* inds_out);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* LEGO_B200_H_ */

@@ -1,0 +1,156 @@
+"""ctypes binding of include/lego_b200.h.  No computation happens here: every call goes straight into
+liblego_b200.so; if the library is missing it is built with nvcc, and if that fails the import raises."""
+import ctypes
+import os
+
+import numpy as np
+
+from .params import LegoParams
+
+_HERE = os.path.dirname(os.path.abspath(__file__))
+LIB_PATH = os.path.join(_HERE, "liblego_b200.so")
+
+# every extern "C" symbol declared in include/lego_b200.h (checked by tests/test_abi.py)
+EXPORTED = [
+    "lego_last_error", "lego_device_count",
+    "lego_ip_create", "lego_ip_destroy", "lego_ip_process",
+    "lego_fa_create", "lego_fa_destroy", "lego_fa_process",
+    "lego_mo_create", "lego_mo_destroy", "lego_mo_process",
+    "lego_pipeline_create", "lego_pipeline_destroy", "lego_pipeline_step", "lego_pipeline_get_poses",
+    "lego_pipeline_sync", "lego_pipeline_launch_count", "lego_pipeline_download", "lego_pipeline_upload",
+    "lego_selftest_atan2f", "lego_selftest_std_sort",
+]
+
+_lib = None
+
+
+class LegoError(RuntimeError):
+    pass
+
+
+def load():
+    global _lib
+    if _lib is None:
+        if not os.path.exists(LIB_PATH):
+            from .build import build
+            build()
+        lib = ctypes.CDLL(LIB_PATH)
+        lib.lego_last_error.restype = ctypes.c_char_p
+        lib.lego_pipeline_create.argtypes = [ctypes.POINTER(LegoParams), ctypes.c_int, ctypes.c_int, ctypes.POINTER(ctypes.c_void_p)]
+        lib.lego_pipeline_destroy.argtypes = [ctypes.c_void_p]
+        lib.lego_pipeline_step.argtypes = [ctypes.c_void_p, ctypes.c_void_p, ctypes.c_void_p, ctypes.c_void_p, ctypes.c_int,
+                                           ctypes.c_void_p, ctypes.c_int, ctypes.c_int]
+        lib.lego_pipeline_sync.argtypes = [ctypes.c_void_p]
+        lib.lego_pipeline_launch_count.argtypes = [ctypes.c_void_p]
+        lib.lego_pipeline_launch_count.restype = ctypes.c_long
+        lib.lego_pipeline_download.argtypes = [ctypes.c_void_p, ctypes.c_int, ctypes.c_char_p, ctypes.c_void_p, ctypes.c_long,
+                                               ctypes.POINTER(ctypes.c_int)]
+        lib.lego_pipeline_download.restype = ctypes.c_long
+        lib.lego_pipeline_upload.argtypes = [ctypes.c_void_p, ctypes.c_int, ctypes.c_char_p, ctypes.c_void_p, ctypes.c_long]
+        lib.lego_pipeline_upload.restype = ctypes.c_long
+        if hasattr(lib, "lego_pipeline_get_poses"):
+            lib.lego_pipeline_get_poses.argtypes = [ctypes.c_void_p, ctypes.c_void_p, ctypes.c_void_p]
+        _lib = lib
+    return _lib
+
+
+def _check(rc, what):
+    if rc < 0:
+        raise LegoError("%s failed (%d): %s" % (what, rc, load().lego_last_error().decode()))
+    return rc
+
+
+_DTYPES = {("f", 4): np.float32, ("i", 4): np.int32, ("i", 1): np.int8, ("u", 1): np.uint8, ("f", 16): np.float32}
+_INT_NAMES = {"groundMat": np.int8, "segGroundFlag": np.uint8}
+
+
+def selftest_atan2f(y, x):
+    y = np.ascontiguousarray(y, np.float32); x = np.ascontiguousarray(x, np.float32)
+    out = np.empty_like(y)
+    lib = load()
+    lib.lego_selftest_atan2f.argtypes = [ctypes.c_void_p, ctypes.c_void_p, ctypes.c_void_p, ctypes.c_long]
+    _check(lib.lego_selftest_atan2f(y.ctypes.data, x.ctypes.data, out.ctypes.data, y.size), "lego_selftest_atan2f")
+    return out
+
+
+def selftest_std_sort(values, offsets):
+    values = np.ascontiguousarray(values, np.float32); offsets = np.ascontiguousarray(offsets, np.int32)
+    out = np.empty(values.size, np.int32)
+    lib = load()
+    lib.lego_selftest_std_sort.argtypes = [ctypes.c_void_p, ctypes.c_void_p, ctypes.c_int, ctypes.c_void_p]
+    _check(lib.lego_selftest_std_sort(values.ctypes.data, offsets.ctypes.data, offsets.size - 1, out.ctypes.data), "lego_selftest_std_sort")
+    return out
+
+
+class Pipeline:
+    """`lanes` independent sequences stepped in lock step on one GPU (lego_pipeline_* in include/lego_b200.h)."""
+    IP, FA, MO = 1, 2, 4
+
+    def __init__(self, params, lanes=1, max_points=0):
+        self.lib = load()
+        self.params = params
+        self.lanes = lanes
+        self.h = ctypes.c_void_p()
+        _check(self.lib.lego_pipeline_create(ctypes.byref(params), lanes, max_points, ctypes.byref(self.h)), "lego_pipeline_create")
+        self.N = params.N_SCAN * params.Horizon_SCAN
+
+    def close(self):
+        if getattr(self, "h", None):
+            self.lib.lego_pipeline_destroy(self.h)
+            self.h = None
+
+    __del__ = close
+
+    def step(self, xyzi, ring, npts, stamps, stage_mask=7, on_device=False, stride_points=None):
+        """xyzi float32[lanes, stride, 4], ring uint16[lanes, stride], npts int32[lanes], stamps float64[lanes]
+        (numpy host arrays, or raw device pointers as ints when on_device)."""
+        npts = np.ascontiguousarray(npts, np.int32)
+        stamps = np.ascontiguousarray(stamps, np.float64)
+        if on_device:
+            xp, rp = xyzi, ring
+        else:
+            xyzi = np.ascontiguousarray(xyzi, np.float32)
+            ring = None if ring is None else np.ascontiguousarray(ring, np.uint16)
+            stride_points = xyzi.shape[1]
+            xp, rp = xyzi.ctypes.data, (None if ring is None else ring.ctypes.data)
+        _check(self.lib.lego_pipeline_step(self.h, xp, rp, npts.ctypes.data, int(stride_points), stamps.ctypes.data,
+                                           1 if on_device else 0, stage_mask), "lego_pipeline_step")
+
+    def sync(self):
+        _check(self.lib.lego_pipeline_sync(self.h), "lego_pipeline_sync")
+
+    def launch_count(self):
+        return self.lib.lego_pipeline_launch_count(self.h)
+
+    def poses(self):
+        poses = np.zeros((self.lanes, 18), np.float32)
+        flags = np.zeros(self.lanes, np.int32)
+        _check(self.lib.lego_pipeline_get_poses(self.h, poses.ctypes.data, flags.ctypes.data), "lego_pipeline_get_poses")
+        return poses, flags
+
+    def download(self, name, lane=0):
+        es = ctypes.c_int(0)
+        n = _check(self.lib.lego_pipeline_download(self.h, lane, name.encode(), None, 0, ctypes.byref(es)), "download " + name)
+        e = es.value
+        if e == 16:
+            out = np.empty((n, 4), np.float32)
+        elif e == 1:
+            out = np.empty(n, _INT_NAMES.get(name, np.uint8))
+        elif e == 8:
+            out = np.empty(n, np.float64)
+        elif name in _FLOAT_NAMES:
+            out = np.empty(n, np.float32)
+        else:
+            out = np.empty(n, np.int32)
+        if n:
+            _check(self.lib.lego_pipeline_download(self.h, lane, name.encode(), out.ctypes.data, n, ctypes.byref(es)), "download " + name)
+        return out
+
+    def upload(self, name, arr, lane=0):
+        arr = np.ascontiguousarray(arr)
+        cnt = arr.shape[0]
+        _check(self.lib.lego_pipeline_upload(self.h, lane, name.encode(), arr.ctypes.data, cnt), "upload " + name)
+
+
+_FLOAT_NAMES = {"rangeMat", "segRange", "orientation", "cloudCurvature", "transformCur", "transformSum", "slot4val",
+                "matP", "transformTobeMapped", "transformAftMapped", "transformBefMapped"}

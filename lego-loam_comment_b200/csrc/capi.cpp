@@ -1,0 +1,86 @@
+// C ABI (include/lego_b200.h) over lego::Engine.  Exceptions never cross the boundary: every entry point
+// converts them into an error code and a message retrievable with lego_last_error().
+#include <cstring>
+#include <new>
+#include <stdexcept>
+#include <vector>
+#include "engine.h"
+
+using lego::Engine;
+
+struct lego_pipeline { Engine* e; std::vector<double> stamps; };
+struct lego_ip { Engine* e; std::vector<float> h_seg, h_outlier, h_range; std::vector<int32_t> h_start, h_end; std::vector<uint8_t> h_ground; std::vector<uint32_t> h_col; };
+
+#define LEGO_TRY try {
+#define LEGO_CATCH \
+    } catch (const std::length_error& ex) { lego::set_last_error(ex.what()); return LEGO_ERR_CAPACITY; } \
+      catch (const std::bad_alloc&) { lego::set_last_error("out of host memory"); return LEGO_ERR_CUDA; } \
+      catch (const std::exception& ex) { if (lego::last_error().empty()) lego::set_last_error(ex.what()); return LEGO_ERR_CUDA; }
+
+extern "C" {
+
+const char* lego_last_error(void) { return lego::last_error().c_str(); }
+
+int lego_device_count(void) {
+    int n = 0;
+    if (cudaGetDeviceCount(&n) != cudaSuccess) { cudaGetLastError(); return 0; }
+    return n;
+}
+
+// ------------------------------------------------------------------ pipeline
+int lego_pipeline_create(const lego_params* p, int lanes, int max_points, lego_pipeline** out) {
+    if (!p || !out || lanes < 1 || p->N_SCAN < 2 || p->N_SCAN > 128 || p->Horizon_SCAN < 16) return LEGO_ERR_ARG;
+    if (p->loopClosureEnableFlag) { lego::set_last_error("loop closure is not part of this release"); return LEGO_ERR_ARG; }
+    LEGO_TRY
+    lego_pipeline* h = new lego_pipeline();
+    h->e = new Engine(*p, lanes, max_points);
+    *out = h;
+    return LEGO_OK;
+    LEGO_CATCH
+}
+int lego_pipeline_destroy(lego_pipeline* h) {
+    if (!h) return LEGO_ERR_ARG;
+    delete h->e; delete h;
+    return LEGO_OK;
+}
+int lego_pipeline_step(lego_pipeline* h, const float* xyzi, const uint16_t* ring, const int* npts, int stride_points,
+                       const double* stamps, int src_on_device, int stage_mask) {
+    if (!h || !xyzi || !npts || !stamps) return LEGO_ERR_ARG;
+    Engine& e = *h->e;
+    if (e.c.useRing && !ring) return LEGO_ERR_ARG;
+    LEGO_TRY
+    h->stamps.assign(stamps, stamps + e.c.L);
+    if (stage_mask & 1) {
+        e.uploadScan(xyzi, ring, npts, stride_points, src_on_device != 0);
+        e.projectPointCloud();
+        e.groundRemoval();
+        e.cloudSegmentation();
+    }
+    if (stage_mask & 2) {
+        e.adjustDistortionCalculateSmoothnessMarkOccluded();
+        e.extractFeatures();
+        e.updateTransformation();
+        e.integrateTransformationPublishCloudsLast();
+    }
+    lego::cuda_check(cudaGetLastError(), "kernel launch");
+    return LEGO_OK;
+    LEGO_CATCH
+}
+int lego_pipeline_sync(lego_pipeline* h) {
+    if (!h) return LEGO_ERR_ARG;
+    LEGO_TRY h->e->sync(); return LEGO_OK; LEGO_CATCH
+}
+long lego_pipeline_launch_count(lego_pipeline* h) { return h ? h->e->launches : 0; }
+long lego_pipeline_download(lego_pipeline* h, int lane, const char* name, void* dst, long cap, int* elem_size_out) {
+    if (!h || !name) return LEGO_ERR_ARG;
+    LEGO_TRY
+    if (!std::strcmp(name, "labelMat")) h->e->finalizeLabelMat();
+    return h->e->download(lane, name, dst, cap, elem_size_out);
+    LEGO_CATCH
+}
+long lego_pipeline_upload(lego_pipeline* h, int lane, const char* name, const void* src, long count) {
+    if (!h || !name || !src) return LEGO_ERR_ARG;
+    LEGO_TRY return h->e->upload(lane, name, src, count); LEGO_CATCH
+}
+
+}  // extern "C"

@@ -1,0 +1,130 @@
+// Host-side engine: owns the device buffers of `lanes` independent sequences and mirrors the reference's three
+// stage classes (ImageProjection / FeatureAssociation / mapOptimization) method for method.  Every method only
+// enqueues kernels on the engine's stream; nothing here computes on the CPU except the keyframe bookkeeping of
+// mapOptimization, which is host glue in the reference too (mapOptmization.cpp:956-1065, 1353-1454).
+#pragma once
+#include <cuda_runtime.h>
+#include <stdint.h>
+#include <string>
+#include <vector>
+#include "../../include/lego_b200.h"
+
+namespace lego {
+
+// ---- constants derived once from lego_params (host side, with the reference's float/double semantics) ----
+struct Consts {
+    int R, C, N, G, L, Pcap, Ocap;
+    int useRing;
+    float ang_res_x, ang_res_y, ang_bottom;
+    float sensorMinimumRange, sensorMountAngle, segmentTheta;
+    float sinAlphaX, cosAlphaX, sinAlphaY, cosAlphaY;   // sinf/cosf of segmentAlphaX/Y computed on the host (glibc)
+    int segmentValidPointNum, segmentValidLineNum;
+    float scanPeriod, edgeThreshold, surfThreshold, nearestFeatureSearchSqDist;
+    int rowWords;   // ceil(R/32) words of row bitmask per component
+};
+
+// ---- ImageProjection device arrays, all [lane][...] with the strides implied by Consts ----
+struct IpDev {
+    const float4* in_xyzi;     // [L][Pcap]
+    const uint16_t* in_ring;   // [L][Pcap]
+    const int* npts;           // [L]
+    int* owner;                // [L][N]   index of the last input point that fell into the cell, -1 = empty
+    float* rangeMat;           // [L][N]   FLT_MAX = empty           (imageProjection.cpp:152)
+    float4* fullCloud;         // [L][N]   NaN / intensity -1 = empty (imageProjection.cpp:157)
+    int8_t* groundMat;         // [L][N]   -1 / 0 / 1                (imageProjection.cpp:263-266)
+    int* labelMat;             // [L][N]   -1, 0 (transient), 1..K, 999999
+    int* parent;               // [L][N]   union-find forest, root = smallest cell index of the component
+    int* compSize;             // [L][N]   at roots: number of non-root members; later: the root's final label
+    uint32_t* compRows;        // [L][N][rowWords] at roots: bitmask of rows that hold a non-root member
+    int* rowCounts;            // [L][R][4] per row: valid roots, kept cells, outlier cells, unused
+    float4* segCloud;          // [L][N]
+    uint8_t* segGround;        // [L][N]   persistent, never cleared (imageProjection.cpp:125-130)
+    int* segCol;               // [L][N]
+    float* segRange;           // [L][N]
+    int* startRing; int* endRing;   // [L][R]
+    float* orient;             // [L][4]   startOrientation, endOrientation, orientationDiff
+    float4* outlier;           // [L][Ocap]
+    int* counts;               // [L][8]   0: S (segmented size) 1: O (outliers) 2: number of valid segments
+};
+
+// ---- FeatureAssociation device arrays ----
+struct FaDev {
+    float4* segAdj;            // [L][N]   segmented cloud after adjustDistortion (camera axes)
+    float* curv;               // [L][N]   cloudCurvature, persistent
+    int* picked;               // [L][N]   cloudNeighborPicked, persistent
+    int* label;                // [L][N]   cloudLabel, persistent
+    float* slot4val; int* slot4ind;   // [L] stale smoothness slot 4 (quirk Q11)
+    int* halfFirst;            // [L]      first index whose branch-A orientation passes pi (quirk Q9)
+    // ring-local feature staging, then compacted lists
+    float4* ringSharp; float4* ringLessSharp; float4* ringFlat; float4* ringLessFlat;   // [L][R][12|120|24|C]
+    int* ringCounts;           // [L][R][4]
+    float4* sharp; float4* lessSharp; float4* flat; float4* lessFlat;   // [L][12R | 120R | 24R | N]
+    int* featCounts;           // [L][4]
+    // odometry state
+    float4* cornerLast[2]; float4* surfLast[2];   // [L][120R], [L][N] double buffered
+    int* lastCounts;           // [L][4]   cornerLastNum, surfLastNum (current "last" buffer), buffer index, frameCount
+    float* transformCur;       // [L][6]
+    float* transformSum;       // [L][6]
+    float* matP;               // [L][9]
+    int* lmState;              // [L][8]   0: systemInitedLM 1: isDegenerate 2: surf phase done 3: corner phase done 4: skip 5: rows
+    int* cornerInd;            // [L][12R][2]
+    int* surfInd;              // [L][24R][3]
+    double* partials;          // [L][maxBlocks][16]
+    unsigned int* tickets;     // [L]
+    float4* outlierLast;       // [L][Ocap]
+    int* flags;                // [L]      bit1 odometry ran, bit2 clouds forwarded
+};
+
+void cuda_check(cudaError_t e, const char* what);
+void set_last_error(const std::string& s);
+
+class Engine {
+public:
+    Engine(const lego_params& p, int lanes, int max_points);
+    ~Engine();
+
+    // ---- ImageProjection (names follow imageProjection.cpp) ----
+    void uploadScan(const float* xyzi, const uint16_t* ring, const int* npts, int stride_points, bool src_on_device);
+    void projectPointCloud();     // + findStartEndAngle
+    void groundRemoval();
+    void cloudSegmentation();
+    void finalizeLabelMat();      // numeric labels for every cell (only needed for parity / visualisation)
+    // ---- FeatureAssociation (names follow featureAssociation.cpp) ----
+    void adjustDistortionCalculateSmoothnessMarkOccluded();
+    void extractFeatures();
+    void updateTransformation();
+    void integrateTransformationPublishCloudsLast();
+
+    void sync();
+    long download(int lane, const char* name, void* dst, long cap, int* elem_size);
+    long upload(int lane, const char* name, const void* src, long count);
+    bool lookup(int lane, const std::string& name, void** ptr, int* elem, long* count);
+    bool lookupFeatureAssociation(int lane, const std::string& name, void** ptr, int* elem, long* count);
+    void allocFeatureAssociation();
+
+    Consts c;
+    lego_params params;
+    cudaStream_t stream = nullptr;
+    long launches = 0;
+    IpDev ip;
+    FaDev fa;
+    std::vector<void*> allocations;
+    // host mirrors of small per-lane data
+    std::vector<int> h_counts;
+
+    template <class T> T* alloc(size_t n, bool zero = true) {
+        void* p = nullptr;
+        if (n == 0) n = 1;
+        cuda_check(cudaMalloc(&p, n * sizeof(T)), "cudaMalloc");
+        allocations.push_back(p);
+        if (zero) cuda_check(cudaMemsetAsync(p, 0, n * sizeof(T), stream), "cudaMemset");
+        return static_cast<T*>(p);
+    }
+private:
+    float4* d_in_xyzi = nullptr; uint16_t* d_in_ring = nullptr; int* d_npts = nullptr;
+    void* h_stage = nullptr;
+};
+
+const std::string& last_error();
+
+}  // namespace lego

@@ -1,0 +1,137 @@
+// FeatureAssociation, feature half: de-skew (adjustDistortion), curvature (calculateSmoothness), occlusion masks
+// (markOccludedPoints) and the sorted greedy corner / flat selection with per-ring VoxelGrid (extractFeatures).
+// Replaces featureAssociation.cpp:491-784 of the reference.  blockIdx.y = lane everywhere.
+#include <cfloat>
+#include <climits>
+#include "engine.h"
+#include "kernel_utils.cuh"
+#include "parity_math.cuh"
+#include "std_sort_replay.cuh"
+
+namespace lego {
+
+// ------------------------------------------------------------------------------------------------------------
+void Engine::allocFeatureAssociation() {
+    const size_t L = c.L, N = c.N, R = c.R, C = c.C;
+    fa.segAdj = alloc<float4>(L * N);
+    // the reference allocates these with new[] and reads parts of them before ever writing (quirks Q8/Q11);
+    // the oracle zero-fills them, and so does this allocation.  They persist across scans, never cleared.
+    fa.curv = alloc<float>(L * N); fa.picked = alloc<int>(L * N); fa.label = alloc<int>(L * N);
+    fa.slot4val = alloc<float>(L); fa.slot4ind = alloc<int>(L); fa.halfFirst = alloc<int>(L);
+    fa.ringSharp = alloc<float4>(L * R * 12); fa.ringLessSharp = alloc<float4>(L * R * 120);
+    fa.ringFlat = alloc<float4>(L * R * 24); fa.ringLessFlat = alloc<float4>(L * R * C);
+    fa.ringCounts = alloc<int>(L * R * 4);
+    fa.sharp = alloc<float4>(L * R * 12); fa.lessSharp = alloc<float4>(L * R * 120);
+    fa.flat = alloc<float4>(L * R * 24); fa.lessFlat = alloc<float4>(L * N);
+    fa.featCounts = alloc<int>(L * 4);
+    allocOdometry();
+}
+
+bool Engine::lookupFeatureAssociation(int lane, const std::string& n, void** ptr, int* elem, long* count) {
+    const size_t N = c.N, R = c.R, l = lane;
+    auto set = [&](void* p, int e, long cnt) { *ptr = p; *elem = e; *count = cnt; return true; };
+    auto cnt_of = [&](int* base, int stride, int which) {
+        int v = 0;
+        cuda_check(cudaMemcpyAsync(&v, base + l * stride + which, sizeof(int), cudaMemcpyDeviceToHost, stream), "count");
+        cuda_check(cudaStreamSynchronize(stream), "count sync");
+        return (long)v;
+    };
+    if (n == "segmentedCloudAdj") return set(fa.segAdj + l * N, 16, cnt_of(ip.counts, 8, 0));
+    if (n == "cloudCurvature") return set(fa.curv + l * N, 4, cnt_of(ip.counts, 8, 0));
+    if (n == "cloudNeighborPicked") return set(fa.picked + l * N, 4, cnt_of(ip.counts, 8, 0));
+    if (n == "cloudLabel") return set(fa.label + l * N, 4, cnt_of(ip.counts, 8, 0));
+    if (n == "slot4val") return set(fa.slot4val + l, 4, 1);
+    if (n == "slot4ind") return set(fa.slot4ind + l, 4, 1);
+    if (n == "halfFirst") return set(fa.halfFirst + l, 4, 1);
+    if (n == "cornerPointsSharp") return set(fa.sharp + l * R * 12, 16, cnt_of(fa.featCounts, 4, 0));
+    if (n == "cornerPointsLessSharp") return set(fa.lessSharp + l * R * 120, 16, cnt_of(fa.featCounts, 4, 1));
+    if (n == "surfPointsFlat") return set(fa.flat + l * R * 24, 16, cnt_of(fa.featCounts, 4, 2));
+    if (n == "surfPointsLessFlat") return set(fa.lessFlat + l * N, 16, cnt_of(fa.featCounts, 4, 3));
+    if (n == "featCounts") return set(fa.featCounts + l * 4, 4, 4);
+    return lookupOdometry(lane, n, ptr, elem, count);
+}
+
+// ------------------------------------------------------------------------------------------------------------
+// Orientation of a segmented point for the first half of the sweep ("branch A", featureAssociation.cpp:504-512):
+// returns the unwrapped ori and whether this point would flip halfPassed.
+__device__ __forceinline__ float ori_branch_a(float4 p, float startOri, bool* trigger) {
+    // camera axes: point.x = lidar y, point.z = lidar x (featureAssociation.cpp:500-502)
+    float ori = -pm::atan2f_glibc(p.y, p.x);
+    if ((double)ori < (double)startOri - M_PI / 2) ori = (float)((double)ori + 2 * M_PI);
+    else if ((double)ori > (double)startOri + M_PI * 3 / 2) ori = (float)((double)ori - 2 * M_PI);
+    *trigger = (double)PM_SUB(ori, startOri) > M_PI;
+    return ori;
+}
+__device__ __forceinline__ float ori_branch_b(float4 p, float endOri) {
+    float ori = -pm::atan2f_glibc(p.y, p.x);
+    ori = (float)((double)ori + 2 * M_PI);
+    if ((double)ori < (double)endOri - M_PI * 3 / 2) ori = (float)((double)ori + 2 * M_PI);
+    else if ((double)ori > (double)endOri + M_PI / 2) ori = (float)((double)ori - 2 * M_PI);
+    return ori;
+}
+
+// occlusion rule of one loop iteration k of markOccludedPoints (featureAssociation.cpp:647-670):
+// 1 = marks k-5..k, 2 = marks k+1..k+6, 0 = nothing.  Valid loop range is [5, S-6).
+__device__ __forceinline__ int occl_type(const float* r, const int* col, int k, int S) {
+    if (k < 5 || k >= S - 6) return 0;
+    const int cd = abs(col[k + 1] - col[k]);
+    if (cd >= 10) return 0;
+    if ((double)PM_SUB(r[k], r[k + 1]) > 0.3) return 1;
+    if ((double)PM_SUB(r[k + 1], r[k]) > 0.3) return 2;
+    return 0;
+}
+
+// calculateSmoothness + markOccludedPoints as one gather stencil per point, plus the halfPassed search of
+// adjustDistortion.  The reference's scatter writes (picked[i-5..i] = 1 ...) are all "set to 1", so gathering the
+// union of the rules that can reach index i is order-free and exact.  Entries the reference does not reset
+// (i < 5, i >= S-5) keep their previous value OR-ed with this scan's marks, exactly as its persistent arrays do.
+__global__ void __launch_bounds__(256) fa_prepare_kernel(IpDev d, FaDev f, Consts c) {
+    const int lane = blockIdx.y;
+    const int i = blockIdx.x * blockDim.x + threadIdx.x;
+    const int S = d.counts[lane * 8 + 0];
+    if (i >= S) return;
+    const size_t base = (size_t)lane * c.N;
+    const float* r = d.segRange + base;
+    const int* col = d.segCol + base;
+    int pk;
+    if (i >= 5 && i < S - 5) {
+        float s = PM_ADD(r[i - 5], r[i - 4]);
+        s = PM_ADD(s, r[i - 3]); s = PM_ADD(s, r[i - 2]); s = PM_ADD(s, r[i - 1]);
+        s = PM_SUB(s, PM_MUL(r[i], 10.0f));
+        s = PM_ADD(s, r[i + 1]); s = PM_ADD(s, r[i + 2]); s = PM_ADD(s, r[i + 3]); s = PM_ADD(s, r[i + 4]); s = PM_ADD(s, r[i + 5]);
+        f.curv[base + i] = PM_MUL(s, s);
+        f.label[base + i] = 0;
+        pk = 0;
+    } else {
+        pk = f.picked[base + i];
+    }
+    for (int k = i; k <= i + 5; ++k) if (occl_type(r, col, k, S) == 1) pk = 1;
+    for (int k = i - 6; k <= i - 1; ++k) if (occl_type(r, col, k, S) == 2) pk = 1;
+    if (i >= 5 && i < S - 6) {
+        const float d1 = fabsf(PM_SUB(r[i - 1], r[i])), d2 = fabsf(PM_SUB(r[i + 1], r[i]));
+        if ((double)d1 > 0.02 * (double)r[i] && (double)d2 > 0.02 * (double)r[i]) pk = 1;
+    }
+    f.picked[base + i] = pk;
+    // halfPassed: first index whose branch-A orientation is more than pi past the start (quirk Q9)
+    bool trig;
+    ori_branch_a(d.segCloud[base + i], d.orient[lane * 4 + 0], &trig);
+    if (trig) atomicMin(f.halfFirst + lane, i);
+}
+
+// adjustDistortion without IMU (featureAssociation.cpp:491-523, 615): axis swap and intensity = ring + 0.1*relTime.
+__global__ void __launch_bounds__(256) fa_distort_kernel(IpDev d, FaDev f, Consts c) {
+    const int lane = blockIdx.y;
+    const int i = blockIdx.x * blockDim.x + threadIdx.x;
+    const int S = d.counts[lane * 8 + 0];
+    if (i >= S) return;
+    const size_t base = (size_t)lane * c.N;
+    const float4 p = d.segCloud[base + i];
+    const float so = d.orient[lane * 4 + 0], eo = d.orient[lane * 4 + 1], od = d.orient[lane * 4 + 2];
+    bool trig;
+    float ori = (i <= f.halfFirst[lane]) ? ori_branch_a(p, so, &trig) : ori_branch_b(p, eo);
+    const float relTime = PM_DIV(PM_SUB(ori, so), od);
+    const float inten = PM_ADD((float)(int)p.w, PM_MUL(c.scanPeriod, relTime));
+    f.segAdj[base + i] = make_float4(p.y, p.z, p.x, inten);
+}
+
+}  // namespace lego

@@ -1,0 +1,335 @@
+// ImageProjection stage as sm_100a kernels: range-image projection, ground removal, connected-component
+// segmentation and the ordered compaction into the segmented cloud + cloud_info.
+// Replaces the body of ImageProjection::cloudHandler (reference LeGO-LOAM/src/imageProjection.cpp:181-197).
+// One launch covers every lane (independent sequence): blockIdx.y = lane.
+#include <cfloat>
+#include <math_constants.h>
+#include "engine.h"
+#include "parity_math.cuh"
+#include "kernel_utils.cuh"
+
+namespace lego {
+
+// ------------------------------------------------------------------------------------------------------------
+// projectPointCloud (imageProjection.cpp:211-257) + findStartEndAngle (imageProjection.cpp:199-209).
+// The reference walks the cloud in input order and lets later points overwrite earlier ones in the same cell
+// (quirk Q3); here each point does atomicMax(owner[cell], pointIndex) and a gather pass reads the winner.
+// Arithmetic mirrors the C++ expression types: atan2f * 180 is a FLOAT product, the division by M_PI and the
+// column computation are double, the result is narrowed to float on assignment.
+__global__ void __launch_bounds__(256) ip_project_kernel(IpDev d, Consts c) {
+    const int lane = blockIdx.y;
+    const int i = blockIdx.x * blockDim.x + threadIdx.x;
+    const int P = d.npts[lane];
+    const float4* __restrict__ in = d.in_xyzi + (size_t)lane * c.Pcap;
+    if (i == 0) {
+        float* o = d.orient + lane * 4;
+        if (P > 0) {
+            const float4 a = in[0], b = in[P - 1];
+            const float so = -pm::atan2f_glibc(a.y, a.x);
+            float eo = (float)((double)(-pm::atan2f_glibc(b.y, b.x)) + 2.0 * M_PI);
+            const float diff = PM_SUB(eo, so);
+            if ((double)diff > 3.0 * M_PI) eo = (float)((double)eo - 2.0 * M_PI);
+            else if ((double)diff < M_PI) eo = (float)((double)eo + 2.0 * M_PI);
+            o[0] = so; o[1] = eo; o[2] = PM_SUB(eo, so);
+        }
+    }
+    if (i >= P) return;
+    const float4 p = in[i];
+    long long row;
+    if (c.useRing) {
+        row = d.in_ring[(size_t)lane * c.Pcap + i];
+    } else {
+        const float xy = PM_SQRT(PM_ADD(PM_MUL(p.x, p.x), PM_MUL(p.y, p.y)));
+        const float va = (float)((double)PM_MUL(pm::atan2f_glibc(p.z, xy), 180.0f) / M_PI);
+        const float rf = PM_DIV(PM_ADD(va, c.ang_bottom), c.ang_res_y);
+        if (!(rf > -9.0e18f && rf < 9.0e18f)) return;
+        row = (long long)rf;   // size_t conversion of the reference truncates toward zero (quirk Q2)
+    }
+    if (row < 0 || row >= c.R) return;
+    const float ha = (float)((double)PM_MUL(pm::atan2f_glibc(p.x, p.y), 180.0f) / M_PI);
+    const double colf = -round(((double)ha - 90.0) / (double)c.ang_res_x) + (double)(c.C / 2);
+    if (!(colf > -9.0e18 && colf < 9.0e18)) return;
+    long long col = (long long)colf;
+    if (col >= c.C) col -= c.C;
+    if (col < 0 || col >= c.C) return;
+    const float range = PM_SQRT(PM_ADD(PM_ADD(PM_MUL(p.x, p.x), PM_MUL(p.y, p.y)), PM_MUL(p.z, p.z)));
+    if (range < c.sensorMinimumRange) return;
+    atomicMax(d.owner + (size_t)lane * c.N + row * c.C + col, i);
+}
+
+// Gather pass: one thread per image cell.  Writes rangeMat / fullCloud exactly as the sequential loop would
+// have left them, and resets the per-cell segmentation scratch (union-find parent, component statistics).
+__global__ void __launch_bounds__(256) ip_gather_kernel(IpDev d, Consts c) {
+    const int lane = blockIdx.y;
+    const int cell = blockIdx.x * blockDim.x + threadIdx.x;
+    if (cell >= c.N) return;
+    const size_t g = (size_t)lane * c.N + cell;
+    const int o = d.owner[g];
+    float4 out; float range;
+    if (o < 0) {
+        out = make_float4(CUDART_NAN_F, CUDART_NAN_F, CUDART_NAN_F, -1.0f);
+        range = FLT_MAX;
+    } else {
+        const float4 p = d.in_xyzi[(size_t)lane * c.Pcap + o];
+        range = PM_SQRT(PM_ADD(PM_ADD(PM_MUL(p.x, p.x), PM_MUL(p.y, p.y)), PM_MUL(p.z, p.z)));
+        const int row = cell / c.C, col = cell - row * c.C;
+        const float inten = (float)((double)(float)row + (double)(float)col / 10000.0);
+        out = make_float4(p.x, p.y, p.z, inten);
+    }
+    d.fullCloud[g] = out;
+    d.rangeMat[g] = range;
+    d.groundMat[g] = 0;
+    d.parent[g] = cell;
+    d.compSize[g] = 0;
+    for (int w = 0; w < c.rowWords; ++w) d.compRows[g * c.rowWords + w] = 0u;
+}
+
+// groundRemoval (imageProjection.cpp:260-291): the only sequential dependence is along a column (a -1 written
+// for pair i may overwrite the 1 written by pair i-1 and vice versa, quirk Q4), so one thread walks one column.
+__global__ void __launch_bounds__(128) ip_ground_kernel(IpDev d, Consts c) {
+    const int lane = blockIdx.y;
+    const int j = blockIdx.x * blockDim.x + threadIdx.x;
+    if (j >= c.C) return;
+    const size_t base = (size_t)lane * c.N;
+    const float4* fc = d.fullCloud + base;
+    int8_t* gm = d.groundMat + base;
+    float4 lower = fc[j];
+    for (int i = 0; i < c.G; ++i) {
+        if (i + 1 >= c.R) break;
+        const float4 upper = fc[j + (i + 1) * c.C];
+        if (lower.w == -1.0f || upper.w == -1.0f) {
+            gm[j + i * c.C] = -1;
+        } else {
+            const float dx = PM_SUB(upper.x, lower.x), dy = PM_SUB(upper.y, lower.y), dz = PM_SUB(upper.z, lower.z);
+            const float hyp = PM_SQRT(PM_ADD(PM_MUL(dx, dx), PM_MUL(dy, dy)));
+            const float angle = (float)((double)PM_MUL(pm::atan2f_glibc(dz, hyp), 180.0f) / M_PI);
+            if (fabsf(PM_SUB(angle, c.sensorMountAngle)) <= 10.0f) {
+                gm[j + i * c.C] = 1;
+                gm[j + (i + 1) * c.C] = 1;
+            }
+        }
+        lower = upper;
+    }
+}
+
+// A cell takes part in segmentation iff the reference would have initialised its label to 0:
+// not ground and holding a return (imageProjection.cpp:295-301).
+__device__ __forceinline__ bool seg_cell(const IpDev& d, size_t g) { return d.owner[g] >= 0 && d.groundMat[g] != 1; }
+
+__device__ __forceinline__ int uf_find(int* parent, int i) {
+    volatile int* vp = parent;
+    int p;
+    while ((p = vp[i]) != i) i = p;
+    return i;
+}
+// link by smaller index: the root of a finished component is its smallest cell index = the BFS seed the
+// reference's row-major driver would have started from (imageProjection.cpp:314-317).
+__device__ __forceinline__ void uf_union(int* parent, int a, int b) {
+    while (true) {
+        a = uf_find(parent, a); b = uf_find(parent, b);
+        if (a == b) return;
+        if (a < b) { int t = a; a = b; b = t; }
+        const int old = atomicMin(parent + a, b);
+        if (old == a) return;
+        a = old;
+    }
+}
+
+// Edge test of labelComponents (imageProjection.cpp:411-423): symmetric in the two cells, so the BFS flood fill
+// is plain connected components of the graph these edges define (validated in SURVEY.md section 8).
+__device__ __forceinline__ bool seg_edge(float r1, float r2, float sinA, float cosA, float theta) {
+    const float d1 = fmaxf(r1, r2), d2 = fminf(r1, r2);
+    const float angle = pm::atan2f_glibc(PM_MUL(d2, sinA), PM_SUB(d1, PM_MUL(d2, cosA)));
+    return angle > theta;
+}
+
+__global__ void __launch_bounds__(256) ip_ccl_union_kernel(IpDev d, Consts c) {
+    const int lane = blockIdx.y;
+    const int cell = blockIdx.x * blockDim.x + threadIdx.x;
+    if (cell >= c.N) return;
+    const size_t base = (size_t)lane * c.N;
+    if (!seg_cell(d, base + cell)) return;
+    const int row = cell / c.C, col = cell - row * c.C;
+    const float r = d.rangeMat[base + cell];
+    int* parent = d.parent + base;
+    // horizontal neighbour, columns wrap (imageProjection.cpp:403-406)
+    const int rc = row * c.C + (col + 1 == c.C ? 0 : col + 1);
+    if (rc != cell && seg_cell(d, base + rc) && seg_edge(r, d.rangeMat[base + rc], c.sinAlphaX, c.cosAlphaX, c.segmentTheta))
+        uf_union(parent, cell, rc);
+    // vertical neighbour, rows do not wrap (imageProjection.cpp:400-401)
+    if (row + 1 < c.R) {
+        const int dc = cell + c.C;
+        if (seg_cell(d, base + dc) && seg_edge(r, d.rangeMat[base + dc], c.sinAlphaY, c.cosAlphaY, c.segmentTheta))
+            uf_union(parent, cell, dc);
+    }
+}
+
+// Component statistics: size and the set of rows among NON-seed members.  The reference sets lineCountFlag only
+// for cells it pushes, never for the seed itself (imageProjection.cpp:376-384 vs 431, quirk Q5).
+__global__ void __launch_bounds__(256) ip_ccl_stats_kernel(IpDev d, Consts c) {
+    const int lane = blockIdx.y;
+    const int cell = blockIdx.x * blockDim.x + threadIdx.x;
+    if (cell >= c.N) return;
+    const size_t base = (size_t)lane * c.N;
+    if (!seg_cell(d, base + cell)) return;
+    int* parent = d.parent + base;
+    const int root = uf_find(parent, cell);
+    if (root == cell) return;
+    parent[cell] = root;
+    atomicAdd(d.compSize + base + root, 1);
+    const int row = cell / c.C;
+    atomicOr(d.compRows + (base + root) * c.rowWords + (row >> 5), 1u << (row & 31));
+}
+
+// feasibleSegment of imageProjection.cpp:441-451 for the component rooted at `root`.
+__device__ __forceinline__ bool comp_valid(const IpDev& d, const Consts& c, size_t base, int root) {
+    const int size = d.compSize[base + root] + 1;
+    if (size >= 30) return true;
+    if (size < c.segmentValidPointNum) return false;
+    int lines = 0;
+    for (int w = 0; w < c.rowWords; ++w) lines += __popc(d.compRows[(base + root) * c.rowWords + w]);
+    return lines >= c.segmentValidLineNum;
+}
+
+// Per-cell classification shared by the counting and the writing pass (imageProjection.cpp:326-351).
+// returns bit0 = cell heads a valid segment, bit1 = cell goes to segmentedCloud, bit2 = cell goes to outlierCloud
+__device__ __forceinline__ int classify_cell(const IpDev& d, const Consts& c, size_t base, int row, int col) {
+    const int cell = row * c.C + col;
+    const size_t g = base + cell;
+    const bool ground = d.groundMat[g] == 1;
+    int f = 0;
+    if (d.owner[g] >= 0 && !ground) {
+        const int root = d.parent[g];
+        const bool valid = comp_valid(d, c, base, root);
+        if (valid) { if (root == cell) f |= 1; f |= 2; }
+        else if (row > c.G && col % 5 == 0) f |= 4;
+    } else if (ground) {
+        if (!(col % 5 != 0 && col > 5 && col < c.C - 5)) f |= 2;
+    }
+    return f;
+}
+
+__global__ void __launch_bounds__(256) ip_row_count_kernel(IpDev d, Consts c) {
+    const int lane = blockIdx.y, row = blockIdx.x;
+    const size_t base = (size_t)lane * c.N;
+    int n0 = 0, n1 = 0, n2 = 0;
+    for (int col = threadIdx.x; col < c.C; col += blockDim.x) {
+        const int f = classify_cell(d, c, base, row, col);
+        n0 += f & 1; n1 += (f >> 1) & 1; n2 += (f >> 2) & 1;
+    }
+    __shared__ int sh[3][8];
+    n0 = warp_sum(n0); n1 = warp_sum(n1); n2 = warp_sum(n2);
+    const int w = threadIdx.x >> 5, l = threadIdx.x & 31;
+    if (l == 0) { sh[0][w] = n0; sh[1][w] = n1; sh[2][w] = n2; }
+    __syncthreads();
+    if (threadIdx.x < 3) {
+        int s = 0;
+        for (int k = 0; k < (int)(blockDim.x >> 5); ++k) s += sh[threadIdx.x][k];
+        d.rowCounts[((size_t)lane * c.R + row) * 4 + threadIdx.x] = s;
+    }
+}
+
+// Ordered compaction (imageProjection.cpp:319-355): row-major order is kept by giving every row block the
+// prefix of the counts of the rows before it and scanning inside the row.  Also numbers the valid segments
+// 1..K in seed order (imageProjection.cpp:453-454) and marks the rest 999999 at their root cells.
+__global__ void __launch_bounds__(256) ip_compact_kernel(IpDev d, Consts c) {
+    const int lane = blockIdx.y, row = blockIdx.x;
+    const size_t base = (size_t)lane * c.N;
+    __shared__ int pre[3];
+    __shared__ int wsum[3][8];
+    __shared__ int carry[3];
+    if (threadIdx.x < 3) {
+        int s = 0;
+        for (int r = 0; r < row; ++r) s += d.rowCounts[((size_t)lane * c.R + r) * 4 + threadIdx.x];
+        pre[threadIdx.x] = s; carry[threadIdx.x] = 0;
+    }
+    __syncthreads();
+    const int w = threadIdx.x >> 5, l = threadIdx.x & 31, nw = blockDim.x >> 5;
+    if (threadIdx.x == 0) d.startRing[lane * c.R + row] = pre[1] - 1 + 5;
+    for (int col0 = 0; col0 < c.C; col0 += blockDim.x) {
+        const int col = col0 + threadIdx.x;
+        const int f = col < c.C ? classify_cell(d, c, base, row, col) : 0;
+        int v[3] = {f & 1, (f >> 1) & 1, (f >> 2) & 1};
+        int inc[3];
+#pragma unroll
+        for (int k = 0; k < 3; ++k) { inc[k] = warp_inclusive_scan(v[k]); if (l == 31) wsum[k][w] = inc[k]; }
+        __syncthreads();
+        int off[3];
+#pragma unroll
+        for (int k = 0; k < 3; ++k) {
+            int s = 0;
+            for (int q = 0; q < w; ++q) s += wsum[k][q];
+            off[k] = pre[k] + carry[k] + s + inc[k] - v[k];
+        }
+        if (col < c.C) {
+            const size_t g = base + row * c.C + col;
+            if (v[0]) d.labelMat[g] = off[0] + 1;
+            else if (d.owner[g] >= 0 && d.groundMat[g] != 1 && d.parent[g] == row * c.C + col) d.labelMat[g] = 999999;
+            if (v[1]) {
+                const size_t o = base + off[1];
+                d.segCloud[o] = d.fullCloud[g];
+                d.segGround[o] = d.groundMat[g] == 1 ? 1 : 0;
+                d.segCol[o] = col;
+                d.segRange[o] = d.rangeMat[g];
+            }
+            if (v[2] && off[2] < c.Ocap) d.outlier[(size_t)lane * c.Ocap + off[2]] = d.fullCloud[g];
+        }
+        __syncthreads();
+        if (threadIdx.x < 3) { int s = 0; for (int q = 0; q < nw; ++q) s += wsum[threadIdx.x][q]; carry[threadIdx.x] += s; }
+        __syncthreads();
+    }
+    if (threadIdx.x == 0) {
+        d.endRing[lane * c.R + row] = pre[1] + carry[1] - 1 - 5;
+        if (row == c.R - 1) {
+            d.counts[lane * 8 + 0] = pre[1] + carry[1];
+            d.counts[lane * 8 + 1] = min(pre[2] + carry[2], c.Ocap);
+            d.counts[lane * 8 + 2] = pre[0] + carry[0];
+        }
+    }
+}
+
+// labelMat for every cell (only needed when someone looks at it: parity tests, segmentedCloudPure).
+__global__ void __launch_bounds__(256) ip_label_finalize_kernel(IpDev d, Consts c) {
+    const int lane = blockIdx.y;
+    const int cell = blockIdx.x * blockDim.x + threadIdx.x;
+    if (cell >= c.N) return;
+    const size_t base = (size_t)lane * c.N;
+    const size_t g = base + cell;
+    if (!(d.owner[g] >= 0 && d.groundMat[g] != 1)) { d.labelMat[g] = -1; return; }
+    const int root = d.parent[g];
+    if (root != cell) d.labelMat[g] = d.labelMat[base + root];
+}
+
+// ------------------------------------------------------------------------------------------------------------
+void Engine::projectPointCloud() {
+    cuda_check(cudaMemsetAsync(ip.owner, 0xFF, sizeof(int) * (size_t)c.L * c.N, stream), "memset owner");
+    dim3 g1((c.Pcap + 255) / 256, c.L);
+    ip_project_kernel<<<g1, 256, 0, stream>>>(ip, c);
+    dim3 g2((c.N + 255) / 256, c.L);
+    ip_gather_kernel<<<g2, 256, 0, stream>>>(ip, c);
+    launches += 3;
+}
+
+void Engine::groundRemoval() {
+    dim3 g((c.C + 127) / 128, c.L);
+    ip_ground_kernel<<<g, 128, 0, stream>>>(ip, c);
+    launches += 1;
+}
+
+void Engine::cloudSegmentation() {
+    dim3 g((c.N + 255) / 256, c.L);
+    ip_ccl_union_kernel<<<g, 256, 0, stream>>>(ip, c);
+    ip_ccl_stats_kernel<<<g, 256, 0, stream>>>(ip, c);
+    dim3 gr(c.R, c.L);
+    ip_row_count_kernel<<<gr, 256, 0, stream>>>(ip, c);
+    ip_compact_kernel<<<gr, 256, 0, stream>>>(ip, c);
+    launches += 4;
+}
+
+void Engine::finalizeLabelMat() {
+    dim3 g((c.N + 255) / 256, c.L);
+    ip_label_finalize_kernel<<<g, 256, 0, stream>>>(ip, c);
+    launches += 1;
+}
+
+}  // namespace lego

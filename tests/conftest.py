@@ -1,0 +1,25 @@
+import os
+import sys
+
+import pytest
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+for p in (ROOT, os.path.join(ROOT, "oracle")):
+    if p not in sys.path:
+        sys.path.insert(0, p)
+
+
+def pytest_configure(config):
+    config.addinivalue_line("markers", "gpu: needs a CUDA device (run on the B200 box with -m gpu)")
+
+
+@pytest.fixture(scope="session")
+def ref_available():
+    import refpy
+    return refpy.available
+
+
+def require_ref(cfg):
+    import refpy
+    if not refpy.available(cfg):
+        pytest.skip("oracle/_ref/liblego_ref_%s.so not built (needs /root/reference at build time)" % cfg)

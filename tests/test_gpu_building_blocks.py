@@ -1,0 +1,65 @@
+"""GPU checks of the two bit-exactness building blocks: the device atan2f (must equal glibc's atan2f of this
+image bit for bit) and the device replay of libstdc++ std::sort (must give std::sort's permutation)."""
+import ctypes
+import os
+import subprocess
+
+import numpy as np
+import pytest
+
+import lego_loam_b200  # noqa: F401
+from lego_loam_b200 import capi
+
+pytestmark = pytest.mark.gpu
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+
+
+def _libm_atan2f(y, x):
+    libm = ctypes.CDLL("libm.so.6")
+    libm.atan2f.restype = ctypes.c_float
+    libm.atan2f.argtypes = [ctypes.c_float, ctypes.c_float]
+    return np.array([libm.atan2f(float(a), float(b)) for a, b in zip(y, x)], np.float32)
+
+
+def test_device_atan2f_equals_glibc():
+    rng = np.random.default_rng(5)
+    n = 400000
+    y = rng.uniform(-100, 100, n).astype(np.float32)
+    x = rng.uniform(-100, 100, n).astype(np.float32)
+    y[::7] *= np.float32(1e-6); x[::11] *= np.float32(1e-5)
+    # segmentation form d2*sin(a), d1 - d2*cos(a)
+    d1 = rng.uniform(1, 100, n // 4).astype(np.float32); d2 = (d1 * rng.uniform(0.5, 1.0, n // 4)).astype(np.float32)
+    sa, ca = np.float32(np.sin(np.float32(0.0034906585))), np.float32(np.cos(np.float32(0.0034906585)))
+    y[: n // 4] = d2 * sa; x[: n // 4] = d1 - d2 * ca
+    sp = np.array([[0, 1], [-0.0, 1], [0, -1], [-0.0, -1], [1, 0], [-1, 0], [1, -0.0], [np.inf, 1], [1, np.inf], [1, -np.inf],
+                   [-np.inf, -np.inf], [1e30, 1e-30], [1e-30, -1e30], [3, 1]], np.float32)
+    y = np.concatenate([y, sp[:, 0]]); x = np.concatenate([x, sp[:, 1]])
+    got = capi.selftest_atan2f(y, x)
+    want = _libm_atan2f(y, x)
+    bad = np.flatnonzero(got.view(np.uint32) != want.view(np.uint32))
+    assert bad.size == 0, "%d mismatches, first: y=%r x=%r got=%r want=%r" % (bad.size, y[bad[0]], x[bad[0]], got[bad[0]], want[bad[0]])
+
+
+def test_device_std_sort_replay_equals_libstdcxx(tmp_path):
+    exe = str(tmp_path / "std_sort_cli")
+    subprocess.check_call(["g++", "-O2", os.path.join(ROOT, "tests", "native", "std_sort_cli.cpp"), "-o", exe])
+    rng = np.random.default_rng(11)
+    segs = []
+    for c in range(3000):
+        n = int(rng.integers(1, 420)) if c % 40 else int(rng.integers(1, 2100))
+        mode = c % 6
+        if mode == 0: v = rng.integers(0, 5, n).astype(np.float32)
+        elif mode == 1: v = (rng.integers(-1000, 1001, n).astype(np.float32) * np.float32(1e-3)) ** 2
+        elif mode == 2: v = np.arange(n, dtype=np.float32)
+        elif mode == 3: v = np.arange(n, 0, -1).astype(np.float32)
+        elif mode == 4:
+            k = n // 2
+            v = np.concatenate([np.where(np.arange(k) % 2 == 0, np.arange(k) + 1, k + np.arange(k)), (np.arange(n - k) + 1) * 2]).astype(np.float32)
+        else: v = rng.random(n).astype(np.float32)
+        segs.append(v)
+    offsets = np.concatenate([[0], np.cumsum([len(s) for s in segs])]).astype(np.int32)
+    values = np.concatenate(segs)
+    blob = np.int32(len(segs)).tobytes() + offsets.tobytes() + values.tobytes()
+    want = np.frombuffer(subprocess.run([exe], input=blob, stdout=subprocess.PIPE, check=True).stdout, np.int32)
+    got = capi.selftest_std_sort(values, offsets)
+    assert np.array_equal(got, want)
