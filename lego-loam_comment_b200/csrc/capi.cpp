@@ -70,6 +70,10 @@ int lego_pipeline_sync(lego_pipeline* h) {
     if (!h) return LEGO_ERR_ARG;
     LEGO_TRY h->e->sync(); return LEGO_OK; LEGO_CATCH
 }
+int lego_pipeline_get_poses(lego_pipeline* h, float* poses_out, int* flags_out) {
+    if (!h || !poses_out) return LEGO_ERR_ARG;
+    LEGO_TRY h->e->getPoses(poses_out, flags_out); return LEGO_OK; LEGO_CATCH
+}
 long lego_pipeline_launch_count(lego_pipeline* h) { return h ? h->e->launches : 0; }
 long lego_pipeline_download(lego_pipeline* h, int lane, const char* name, void* dst, long cap, int* elem_size_out) {
     if (!h || !name) return LEGO_ERR_ARG;

@@ -81,6 +81,19 @@ void Engine::uploadScan(const float* xyzi, const uint16_t* ring, const int* npts
     if (!src_on_device || true) cuda_check(cudaStreamSynchronize(stream), "upload sync");
 }
 
+void Engine::getPoses(float* poses18, int* flags) {
+    std::vector<float> sum(6 * (size_t)c.L);
+    cuda_check(cudaMemcpyAsync(sum.data(), fa.transformSum, sizeof(float) * 6 * c.L, cudaMemcpyDeviceToHost, stream), "poses");
+    std::vector<int> fl(c.L);
+    cuda_check(cudaMemcpyAsync(fl.data(), fa.flags, sizeof(int) * c.L, cudaMemcpyDeviceToHost, stream), "flags");
+    cuda_check(cudaStreamSynchronize(stream), "poses sync");
+    for (int l = 0; l < c.L; ++l) {
+        for (int k = 0; k < 6; ++k) poses18[l * 18 + k] = sum[l * 6 + k];
+        for (int k = 6; k < 18; ++k) poses18[l * 18 + k] = 0.f;
+        if (flags) flags[l] = fl[l];
+    }
+}
+
 // ---- named arrays (parity tests / debugging) ----
 struct NamedArray { void* ptr; int elem; long count; };
 

@@ -8,6 +8,7 @@
 #include <string>
 #include <vector>
 #include "../../include/lego_b200.h"
+#include "voxel_hash.cuh"
 
 namespace lego {
 
@@ -73,6 +74,7 @@ struct FaDev {
     unsigned int* tickets;     // [L]
     float4* outlierLast;       // [L][Ocap]
     int* flags;                // [L]      bit1 odometry ran, bit2 clouds forwarded
+    VoxelHash hashCorner, hashSurf;   // 1 m voxel hash over the current "last" clouds (replaces the two kd-trees)
 };
 
 void cuda_check(cudaError_t e, const char* what);
@@ -96,16 +98,21 @@ public:
     void integrateTransformationPublishCloudsLast();
 
     void sync();
+    void getPoses(float* poses18, int* flags);   // per lane: transformSum | transformAftMapped | transformBefMapped
     long download(int lane, const char* name, void* dst, long cap, int* elem_size);
     long upload(int lane, const char* name, const void* src, long count);
     bool lookup(int lane, const std::string& name, void** ptr, int* elem, long* count);
     bool lookupFeatureAssociation(int lane, const std::string& name, void** ptr, int* elem, long* count);
     void allocFeatureAssociation();
+    void allocOdometry();
+    VoxelHash allocHash(int cap, float cell);
+    bool lookupOdometry(int lane, const std::string& name, void** ptr, int* elem, long* count);
 
     Consts c;
     lego_params params;
     cudaStream_t stream = nullptr;
     long launches = 0;
+    int faBuf = 0;             // which of the double-buffered "last" clouds is current (same for every lane)
     IpDev ip;
     FaDev fa;
     std::vector<void*> allocations;

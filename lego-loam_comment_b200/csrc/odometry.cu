@@ -1,0 +1,156 @@
+// FeatureAssociation, odometry half: scan-to-scan two-step LM (featureAssociation.cpp:1044-1478, 1666-1695),
+// pose integration (featureAssociation.cpp:1697-1725) and the end-of-sweep re-projection + "last" cloud swap
+// (featureAssociation.cpp:1759-1815).  blockIdx.y / blockIdx.x = lane; the whole LM loop of one lane runs inside
+// one persistent CTA so there is no host round trip between iterations.
+#include <cfloat>
+#include "engine.h"
+#include "kernel_utils.cuh"
+#include "odometry_kernels.cuh"
+
+namespace lego {
+
+__global__ void fa_init_state_kernel(FaDev f, int L);
+
+VoxelHash Engine::allocHash(int cap, float cell) {
+    VoxelHash h;
+    int H = 1024;
+    while (H < 2 * cap) H <<= 1;
+    h.H = H; h.cap = cap; h.invCell = 1.0f / cell;
+    h.keys = alloc<unsigned long long>((size_t)c.L * H); h.count = alloc<int>((size_t)c.L * H); h.start = alloc<int>((size_t)c.L * H);
+    h.slotOf = alloc<int>((size_t)c.L * cap); h.sorted = alloc<float4>((size_t)c.L * cap);
+    return h;
+}
+
+void Engine::allocOdometry() {
+    const size_t L = c.L, N = c.N, R = c.R;
+    for (int b = 0; b < 2; ++b) { fa.cornerLast[b] = alloc<float4>(L * R * 120); fa.surfLast[b] = alloc<float4>(L * N); }
+    fa.lastCounts = alloc<int>(L * 4);
+    fa.transformCur = alloc<float>(L * 6); fa.transformSum = alloc<float>(L * 6); fa.matP = alloc<float>(L * 9);
+    fa.lmState = alloc<int>(L * 8);
+    fa.cornerInd = alloc<int>(L * R * 12 * 2); fa.surfInd = alloc<int>(L * R * 24 * 3);
+    fa.partials = alloc<double>(L * 16); fa.tickets = alloc<unsigned int>(L);
+    fa.outlierLast = alloc<float4>(L * c.Ocap); fa.flags = alloc<int>(L);
+    fa.hashCorner = allocHash(c.R * 120, 1.0f); fa.hashSurf = allocHash(c.N, 1.0f);
+    fa_init_state_kernel<<<(c.L + 63) / 64, 64, 0, stream>>>(fa, c.L);
+}
+
+bool Engine::lookupOdometry(int lane, const std::string& n, void** ptr, int* elem, long* count) {
+    const size_t N = c.N, R = c.R, l = lane;
+    auto set = [&](void* p, int e, long cnt) { *ptr = p; *elem = e; *count = cnt; return true; };
+    auto cnt_of = [&](int* base, int stride, int which) {
+        int v = 0;
+        cuda_check(cudaMemcpyAsync(&v, base + l * stride + which, sizeof(int), cudaMemcpyDeviceToHost, stream), "count");
+        cuda_check(cudaStreamSynchronize(stream), "count sync");
+        return (long)v;
+    };
+    if (n == "transformCur") return set(fa.transformCur + l * 6, 4, 6);
+    if (n == "transformSum") return set(fa.transformSum + l * 6, 4, 6);
+    if (n == "matP") return set(fa.matP + l * 9, 4, 9);
+    if (n == "lmState") return set(fa.lmState + l * 8, 4, 8);
+    if (n == "lastCounts") return set(fa.lastCounts + l * 4, 4, 4);
+    if (n == "faFlags") return set(fa.flags + l, 4, 1);
+    if (n == "laserCloudCornerLast") return set(fa.cornerLast[faBuf] + l * R * 120, 16, cnt_of(fa.lastCounts, 4, 0));
+    if (n == "laserCloudSurfLast") return set(fa.surfLast[faBuf] + l * N, 16, cnt_of(fa.lastCounts, 4, 1));
+    if (n == "outlierCloudLast") return set(fa.outlierLast + l * c.Ocap, 16, cnt_of(ip.counts, 8, 1));
+    return false;
+}
+
+// ------------------------------------------------------------------------------------------------------------
+__global__ void __launch_bounds__(ODO_THREADS) fa_odometry_kernel(IpDev d, FaDev f, Consts c, int buf) {
+    extern __shared__ __align__(16) unsigned char odo_smem[];
+    __shared__ OdoShared sh;
+    float4* sel = reinterpret_cast<float4*>(odo_smem);
+    const int lane = blockIdx.x, tid = threadIdx.x;
+    if (!f.lmState[lane * 8 + 0]) return;                       // first scan: checkSystemInitialization only
+    const int nCornerLast = f.lastCounts[lane * 4 + 0], nSurfLast = f.lastCounts[lane * 4 + 1];
+    if (nCornerLast < 10 || nSurfLast < 100) return;            // featureAssociation.cpp:1668-1669
+    if (tid < 6) sh.T[tid] = f.transformCur[lane * 6 + tid];
+    if (tid < 9) sh.matP[tid] = f.matP[lane * 9 + tid];
+    if (tid == 0) sh.isDegenerate = f.lmState[lane * 8 + 1];
+    __syncthreads();
+    const size_t R = c.R, N = c.N;
+    {
+        const VhLane vh = vh_lane(f.hashSurf, lane);
+        odo_phase<true>(sh, sel, f.flat + lane * R * 24, f.featCounts[lane * 4 + 2], f.surfLast[buf] + lane * N, nSurfLast, vh,
+                        f.surfInd + lane * R * 24 * 3, c);
+    }
+    {
+        const VhLane vh = vh_lane(f.hashCorner, lane);
+        odo_phase<false>(sh, sel, f.sharp + lane * R * 12, f.featCounts[lane * 4 + 0], f.cornerLast[buf] + lane * R * 120, nCornerLast, vh,
+                         f.cornerInd + lane * R * 12 * 2, c);
+    }
+    if (tid < 6) f.transformCur[lane * 6 + tid] = sh.T[tid];
+    if (tid < 9) f.matP[lane * 9 + tid] = sh.matP[tid];
+    if (tid == 0) f.lmState[lane * 8 + 1] = sh.isDegenerate;
+}
+
+// publishCloudsLast (featureAssociation.cpp:1759-1789) / checkSystemInitialization (featureAssociation.cpp:1605-1637):
+// the less-sharp and less-flat clouds become the next "last" clouds, re-projected to the end of the sweep except on
+// the very first scan; adjustOutlierCloud (featureAssociation.cpp:1746-1757) swaps the outliers into camera axes.
+__global__ void __launch_bounds__(256) fa_clouds_last_kernel(IpDev d, FaDev f, Consts c, int nb) {
+    const int lane = blockIdx.y;
+    const size_t R = c.R, N = c.N;
+    const bool inited = f.lmState[lane * 8 + 0] != 0;
+    float T[6];
+#pragma unroll
+    for (int k = 0; k < 6; ++k) T[k] = f.transformCur[lane * 6 + k];
+    const int nC = f.featCounts[lane * 4 + 1], nS = f.featCounts[lane * 4 + 3], nO = d.counts[lane * 8 + 1];
+    const int t0 = blockIdx.x * blockDim.x + threadIdx.x, stride = gridDim.x * blockDim.x;
+    const float4* ls = f.lessSharp + lane * R * 120; float4* cl = f.cornerLast[nb] + lane * R * 120;
+    for (int i = t0; i < nC; i += stride) { const float4 p = ls[i]; cl[i] = inited ? pose::transform_to_end(p, T) : p; }
+    const float4* lf = f.lessFlat + lane * N; float4* sl = f.surfLast[nb] + lane * N;
+    for (int i = t0; i < nS; i += stride) { const float4 p = lf[i]; sl[i] = inited ? pose::transform_to_end(p, T) : p; }
+    const float4* oc = d.outlier + (size_t)lane * c.Ocap; float4* ol = f.outlierLast + (size_t)lane * c.Ocap;
+    for (int i = t0; i < nO; i += stride) { const float4 p = oc[i]; ol[i] = make_float4(p.y, p.z, p.x, p.w); }
+}
+
+// integrateTransformation (featureAssociation.cpp:1697-1725) and the publish bookkeeping of publishCloudsLast
+// (frameCount / skipFrameNum, featureAssociation.cpp:1790-1794), one thread per lane.
+__global__ void fa_finish_scan_kernel(IpDev d, FaDev f, Consts c) {
+    const int lane = blockIdx.x * blockDim.x + threadIdx.x;
+    if (lane >= c.L) return;
+    int flags = 1;
+    if (!f.lmState[lane * 8 + 0]) {
+        f.lmState[lane * 8 + 0] = 1;
+        flags |= 16;   // corner/surf "last" clouds are published once at initialisation, without odometry
+    } else {
+        float S[6], T[6];
+        for (int k = 0; k < 6; ++k) { S[k] = f.transformSum[lane * 6 + k]; T[k] = f.transformCur[lane * 6 + k]; }
+        pose::integrate_transformation(S, T);
+        for (int k = 0; k < 6; ++k) f.transformSum[lane * 6 + k] = S[k];
+        flags |= 2;
+        int fc = f.lastCounts[lane * 4 + 3] + 1;
+        if (fc >= 2) { fc = 0; flags |= 4; }   // skipFrameNum = 1 (featureAssociation.cpp:284)
+        f.lastCounts[lane * 4 + 3] = fc;
+    }
+    f.lastCounts[lane * 4 + 0] = f.featCounts[lane * 4 + 1];
+    f.lastCounts[lane * 4 + 1] = f.featCounts[lane * 4 + 3];
+    f.flags[lane] = flags;
+}
+
+__global__ void fa_init_state_kernel(FaDev f, int L) {
+    const int lane = blockIdx.x * blockDim.x + threadIdx.x;
+    if (lane < L) f.lastCounts[lane * 4 + 3] = 1;   // frameCount = skipFrameNum (featureAssociation.cpp:314)
+}
+
+void Engine::updateTransformation() {
+    const size_t smem = sizeof(float4) * 24 * (size_t)c.R;
+    static bool attr_set = false;
+    if (!attr_set) { cuda_check(cudaFuncSetAttribute(fa_odometry_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 64 * 1024), "smem attr"); attr_set = true; }
+    fa_odometry_kernel<<<c.L, ODO_THREADS, smem, stream>>>(ip, fa, c, faBuf);
+    launches += 1;
+}
+
+void Engine::integrateTransformationPublishCloudsLast() {
+    const int nb = faBuf ^ 1;
+    dim3 g(ODO_TE_BLOCKS, c.L);
+    fa_clouds_last_kernel<<<g, 256, 0, stream>>>(ip, fa, c, nb);
+    fa_finish_scan_kernel<<<(c.L + 63) / 64, 64, 0, stream>>>(ip, fa, c);
+    faBuf = nb;
+    // the two kd-tree rebuilds of featureAssociation.cpp:1786-1787 become two voxel-hash builds
+    launches += 2;
+    launches += vh_build(fa.hashCorner, c.L, fa.cornerLast[nb], (size_t)c.R * 120, fa.lastCounts + 0, 4, stream);
+    launches += vh_build(fa.hashSurf, c.L, fa.surfLast[nb], (size_t)c.N, fa.lastCounts + 1, 4, stream);
+}
+
+}  // namespace lego

@@ -1,0 +1,143 @@
+// GPU voxel hash for exact nearest-neighbour queries: the replacement for pcl::KdTreeFLANN in the reference's
+// correspondence searches (featureAssociation.cpp:1054,1165 scan-to-scan 1-NN; mapOptmization.cpp:1099,1181
+// scan-to-map 5-NN).  Points are binned into cubic cells of edge `cell` metres; an open-addressing table maps the
+// packed cell coordinate to a contiguous run of a cell-sorted copy of the cloud (xyz + original index in w), so a
+// query walks the 27 (or, for the 5 m odometry search, growing shells of) neighbouring cells and streams their
+// points from consecutive addresses.
+//
+// Exactness: every point closer than k*cell lies in a cell whose Chebyshev distance to the query's cell is <= k,
+// so a shell search that stops once its current best is <= k*cell is exact; the acceptance thresholds of the
+// reference (5th neighbour < 1 m for mapping, nearest < 5 m for odometry) bound k.  Equal distances are resolved
+// by the lowest original index, which makes results independent of the order points land inside a cell.
+//
+// Build = 3 launches over all lanes (blockIdx.y = lane): insert+count, per-lane exclusive scan of the slot
+// counts, scatter.  Tables are sized to >= 2x the capacity of the cloud, so probe sequences stay short.
+#pragma once
+#include <cuda_runtime.h>
+#include <stdint.h>
+#include "kernel_utils.cuh"
+
+namespace lego {
+
+struct VoxelHash {
+    unsigned long long* keys;   // [L][H]  packed cell coordinate, VH_EMPTY = free
+    int* count;                 // [L][H]  points in the cell (also used as the scatter cursor, counting down)
+    int* start;                 // [L][H]  first position of the cell's run in `sorted`
+    int* slotOf;                // [L][cap] table slot of every input point
+    float4* sorted;             // [L][cap] cell-sorted copy, w = original index (int bits)
+    int H;                      // slots per lane, power of two
+    int cap;                    // points per lane
+    float invCell;              // 1 / cell edge
+};
+
+#define VH_EMPTY 0xFFFFFFFFFFFFFFFFull
+
+__host__ __device__ __forceinline__ unsigned long long vh_pack(int ix, int iy, int iz) {
+    return ((unsigned long long)(unsigned)(ix + (1 << 20)) & 0x1FFFFF) |
+           (((unsigned long long)(unsigned)(iy + (1 << 20)) & 0x1FFFFF) << 21) |
+           (((unsigned long long)(unsigned)(iz + (1 << 20)) & 0x1FFFFF) << 42);
+}
+__host__ __device__ __forceinline__ unsigned vh_hash(unsigned long long k) {
+    k ^= k >> 33; k *= 0xff51afd7ed558ccdull; k ^= k >> 33; k *= 0xc4ceb9fe1a85ec53ull; k ^= k >> 33;
+    return (unsigned)k;
+}
+__device__ __forceinline__ int vh_cell(float v, float invCell) { return (int)floorf(v * invCell); }
+
+// slot holding `key`, or -1
+__device__ __forceinline__ int vh_find(const unsigned long long* __restrict__ keys, int H, unsigned long long key) {
+    unsigned s = vh_hash(key) & (unsigned)(H - 1);
+    while (true) {
+        const unsigned long long k = keys[s];
+        if (k == key) return (int)s;
+        if (k == VH_EMPTY) return -1;
+        s = (s + 1) & (unsigned)(H - 1);
+    }
+}
+
+// ---- build (kernels live in voxel_hash.cu); n[lane * nStride] = number of points of the lane's cloud ----
+__global__ void vh_clear_kernel(VoxelHash h);
+__global__ void vh_insert_kernel(VoxelHash h, const float4* __restrict__ pts, size_t ptsStride, const int* __restrict__ n, int nStride);
+__global__ void vh_scan_kernel(VoxelHash h);
+__global__ void vh_scatter_kernel(VoxelHash h, const float4* __restrict__ pts, size_t ptsStride, const int* __restrict__ n, int nStride);
+__global__ void vh_recount_kernel(VoxelHash h, const int* __restrict__ n, int nStride);
+// Enqueues the five build launches for all lanes; returns the number of launches.
+int vh_build(const VoxelHash& h, int lanes, const float4* pts, size_t ptsStride, const int* n, int nStride, cudaStream_t stream);
+
+// ---- query helpers ----
+struct VhLane { const unsigned long long* keys; const int* start; const int* count; const float4* sorted; int H; float invCell; };
+__device__ __forceinline__ VhLane vh_lane(const VoxelHash& h, int lane) {
+    VhLane v;
+    v.keys = h.keys + (size_t)lane * h.H; v.start = h.start + (size_t)lane * h.H; v.count = h.count + (size_t)lane * h.H;
+    v.sorted = h.sorted + (size_t)lane * h.cap; v.H = h.H; v.invCell = h.invCell;
+    return v;
+}
+
+// squared distance exactly as the reference / PCL evaluate it in float32: ((dx*dx + dy*dy) + dz*dz)
+__device__ __forceinline__ float vh_dist2(float4 a, float x, float y, float z) {
+    const float dx = __fsub_rn(a.x, x), dy = __fsub_rn(a.y, y), dz = __fsub_rn(a.z, z);
+    return __fadd_rn(__fadd_rn(__fmul_rn(dx, dx), __fmul_rn(dy, dy)), __fmul_rn(dz, dz));
+}
+
+// Exact nearest neighbour within sqrt(maxD2): returns the original index or -1; *d2out = its squared distance.
+// Shells of cells are visited outwards; shell k only adds the cells at Chebyshev distance exactly k.
+__device__ inline int vh_nearest(const VhLane& v, float x, float y, float z, float maxD2, float cellEdge, float* d2out) {
+    const int cx = vh_cell(x, v.invCell), cy = vh_cell(y, v.invCell), cz = vh_cell(z, v.invCell);
+    float best = maxD2; int bestI = -1;
+    const int maxShell = (int)ceilf(sqrtf(maxD2) * v.invCell);
+    for (int k = 0; k <= maxShell; ++k) {
+        for (int dz = -k; dz <= k; ++dz)
+            for (int dy = -k; dy <= k; ++dy) {
+                const bool face = (abs(dz) == k) || (abs(dy) == k);
+                const int step = face ? 1 : (k == 0 ? 1 : 2 * k);
+                for (int dx = -k; dx <= k; dx += step) {
+                    const int s = vh_find(v.keys, v.H, vh_pack(cx + dx, cy + dy, cz + dz));
+                    if (s < 0) continue;
+                    const int b = v.start[s], e = b + v.count[s];
+                    for (int t = b; t < e; ++t) {
+                        const float4 a = v.sorted[t];
+                        const float d = vh_dist2(a, x, y, z);
+                        const int ai = __float_as_int(a.w);
+                        if (d < best || (d == best && bestI >= 0 && ai < bestI)) { best = d; bestI = ai; }
+                    }
+                }
+            }
+        // every unvisited point is farther than k * cellEdge from the query
+        const float reach = (float)k * cellEdge;
+        if (bestI >= 0 && best <= reach * reach) break;
+    }
+    *d2out = best;
+    return bestI;
+}
+
+// Exact 5 nearest neighbours among the 27 cells around the query (exact whenever the 5th is closer than one
+// cell edge, the only case the reference accepts: mapOptmization.cpp:1101, 1183).  d2[] ascending, ties by index.
+// Returns the number found (<= 5).
+__device__ inline int vh_knn5(const VhLane& v, float x, float y, float z, float* d2, int* idx) {
+    const int cx = vh_cell(x, v.invCell), cy = vh_cell(y, v.invCell), cz = vh_cell(z, v.invCell);
+    int found = 0;
+#pragma unroll
+    for (int k = 0; k < 5; ++k) { d2[k] = 3.0e38f; idx[k] = 0x7fffffff; }
+    for (int dz = -1; dz <= 1; ++dz)
+        for (int dy = -1; dy <= 1; ++dy)
+            for (int dx = -1; dx <= 1; ++dx) {
+                const int s = vh_find(v.keys, v.H, vh_pack(cx + dx, cy + dy, cz + dz));
+                if (s < 0) continue;
+                const int b = v.start[s], e = b + v.count[s];
+                for (int t = b; t < e; ++t) {
+                    const float4 a = v.sorted[t];
+                    float d = vh_dist2(a, x, y, z);
+                    int ai = __float_as_int(a.w);
+                    if (d > d2[4] || (d == d2[4] && ai > idx[4])) continue;
+                    ++found;
+                    // insertion into the sorted list of 5 (registers, fully unrolled)
+#pragma unroll
+                    for (int k = 0; k < 5; ++k) {
+                        const bool lt = d < d2[k] || (d == d2[k] && ai < idx[k]);
+                        if (lt) { const float td = d2[k]; const int ti = idx[k]; d2[k] = d; idx[k] = ai; d = td; ai = ti; }
+                    }
+                }
+            }
+    return found < 5 ? found : 5;
+}
+
+}  // namespace lego
