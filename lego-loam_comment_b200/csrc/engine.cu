@@ -41,8 +41,16 @@ Engine::Engine(const lego_params& p, int lanes, int max_points) : params(p) {
     c.rowWords = (c.R + 31) / 32;
 
     const size_t L = lanes, N = c.N, R = c.R;
-    d_in_xyzi = alloc<float4>(L * c.Pcap); d_in_ring = alloc<uint16_t>(L * c.Pcap); d_npts = alloc<int>(L);
-    ip.in_xyzi = d_in_xyzi; ip.in_ring = d_in_ring; ip.npts = d_npts;
+    cuda_check(cudaStreamCreateWithFlags(&copyStream, cudaStreamNonBlocking), "cudaStreamCreate");
+    const size_t tbl = sizeof(void*) * L;
+    for (int b = 0; b < 2; ++b) {
+        d_in_xyzi[b] = alloc<float4>(L * c.Pcap); d_in_ring[b] = alloc<uint16_t>(L * c.Pcap); d_npts[b] = alloc<int>(L);
+        d_ptr_xyzi[b] = alloc<const float4*>(L); d_ptr_ring[b] = alloc<const uint16_t*>(L);
+        cuda_check(cudaEventCreateWithFlags(&evCopied[b], cudaEventDisableTiming), "event");
+        cuda_check(cudaEventCreateWithFlags(&evConsumed[b], cudaEventDisableTiming), "event");
+        cuda_check(cudaMallocHost(reinterpret_cast<void**>(&h_pin[b]), 2 * tbl + sizeof(int) * L), "cudaMallocHost");
+    }
+    ip.in_xyzi = d_ptr_xyzi[0]; ip.in_ring = d_ptr_ring[0]; ip.npts = d_npts[0];
     ip.owner = alloc<int>(L * N); ip.rangeMat = alloc<float>(L * N); ip.fullCloud = alloc<float4>(L * N);
     ip.groundMat = alloc<int8_t>(L * N); ip.labelMat = alloc<int>(L * N); ip.parent = alloc<int>(L * N);
     ip.compSize = alloc<int>(L * N); ip.compRows = alloc<uint32_t>(L * N * c.rowWords); ip.rowCounts = alloc<int>(L * R * 4);
@@ -56,30 +64,109 @@ Engine::Engine(const lego_params& p, int lanes, int max_points) : params(p) {
 
 Engine::~Engine() {
     if (stream) cudaStreamSynchronize(stream);
+    if (copyStream) cudaStreamSynchronize(copyStream);
     for (void* p : allocations) cudaFree(p);
-    if (h_stage) cudaFreeHost(h_stage);
+    for (int b = 0; b < 2; ++b) {
+        if (h_pin[b]) cudaFreeHost(h_pin[b]);
+        if (evCopied[b]) cudaEventDestroy(evCopied[b]);
+        if (evConsumed[b]) cudaEventDestroy(evConsumed[b]);
+    }
+    if (copyStream) cudaStreamDestroy(copyStream);
     if (stream) cudaStreamDestroy(stream);
+}
+
+cudaEvent_t Engine::takeEvent() {
+    if (!evPool.empty()) { cudaEvent_t e = evPool.back(); evPool.pop_back(); return e; }
+    cudaEvent_t e; cuda_check(cudaEventCreate(&e), "event create"); return e;
+}
+void Engine::profBegin(const char* name) {
+    if (profMode == 2 && std::strstr(name, profFilter.c_str()) == nullptr) { profLog.push_back({nullptr, nullptr, nullptr}); return; }
+    ProfEntry pe{name, takeEvent(), takeEvent()};
+    cuda_check(cudaEventRecord(pe.a, stream), "event record");
+    profLog.push_back(pe);
+}
+void Engine::profEnd() {
+    ProfEntry& pe = profLog.back();
+    if (!pe.name) { profLog.pop_back(); return; }
+    cuda_check(cudaEventRecord(pe.b, stream), "event record");
+}
+void Engine::profReset() {
+    for (auto& pe : profLog) { evPool.push_back(pe.a); evPool.push_back(pe.b); }
+    profLog.clear();
+}
+// Aggregates the log per kernel name: names newline-separated, ms[k] = summed device time, counts[k] = launches.
+long Engine::profRead(char* names, long cap, double* ms, long* counts, long maxk) {
+    sync();
+    std::vector<const char*> order; std::vector<double> tot; std::vector<long> cnt;
+    for (auto& pe : profLog) {
+        float t = 0.f;
+        cuda_check(cudaEventElapsedTime(&t, pe.a, pe.b), "event elapsed");
+        size_t k = 0;
+        for (; k < order.size(); ++k) if (!std::strcmp(order[k], pe.name)) break;
+        if (k == order.size()) { order.push_back(pe.name); tot.push_back(0.0); cnt.push_back(0); }
+        tot[k] += t; cnt[k] += 1;
+    }
+    std::string joined;
+    for (size_t k = 0; k < order.size() && (long)k < maxk; ++k) { joined += order[k]; joined += "\n"; ms[k] = tot[k]; counts[k] = cnt[k]; }
+    if (names && cap > 0) { std::strncpy(names, joined.c_str(), cap - 1); names[cap - 1] = 0; }
+    return (long)order.size();
+}
+void Engine::timerRecord(int slot) {
+    if (!timerEv[slot]) cuda_check(cudaEventCreate(&timerEv[slot]), "event create");
+    cuda_check(cudaEventRecord(timerEv[slot], stream), "event record");
+}
+float Engine::timerElapsed(int a, int b) {
+    float t = 0.f;
+    cuda_check(cudaEventSynchronize(timerEv[b]), "event sync");
+    cuda_check(cudaEventElapsedTime(&t, timerEv[a], timerEv[b]), "event elapsed");
+    return t;
 }
 
 void Engine::sync() { cuda_check(cudaStreamSynchronize(stream), "stream sync"); }
 
-// copyPointCloud (imageProjection.cpp:163-179): the host message becomes device arrays; one copy per array.
+// copyPointCloud (imageProjection.cpp:163-179): the host message becomes device arrays.  Host sources are copied into
+// one of two staging buffers on a separate copy stream, so the upload of scan k+1 overlaps the processing of scan k;
+// device sources are used in place through the per-lane pointer table (no copy at all).
 void Engine::uploadScan(const float* xyzi, const uint16_t* ring, const int* npts, int stride_points, bool src_on_device) {
-    const cudaMemcpyKind kind = src_on_device ? cudaMemcpyDeviceToDevice : cudaMemcpyHostToDevice;
-    for (int l = 0; l < c.L; ++l) if (npts[l] > c.Pcap || npts[l] < 0) { set_last_error("scan larger than max_points"); throw std::length_error("capacity"); }
-    if (stride_points == c.Pcap) {
-        cuda_check(cudaMemcpyAsync(d_in_xyzi, xyzi, sizeof(float4) * (size_t)c.L * c.Pcap, kind, stream), "upload xyzi");
-        if (ring) cuda_check(cudaMemcpyAsync(d_in_ring, ring, sizeof(uint16_t) * (size_t)c.L * c.Pcap, kind, stream), "upload ring");
-    } else {
-        for (int l = 0; l < c.L; ++l) {
-            cuda_check(cudaMemcpyAsync(d_in_xyzi + (size_t)l * c.Pcap, xyzi + (size_t)l * stride_points * 4, sizeof(float4) * npts[l], kind, stream), "upload xyzi");
-            if (ring) cuda_check(cudaMemcpyAsync(d_in_ring + (size_t)l * c.Pcap, ring + (size_t)l * stride_points, sizeof(uint16_t) * npts[l], kind, stream), "upload ring");
+    for (int l = 0; l < c.L; ++l) if (npts[l] < 0 || (!src_on_device && npts[l] > c.Pcap)) { set_last_error("scan larger than max_points"); throw std::length_error("capacity"); }
+    const int b = inBuf; inBuf ^= 1;
+    const size_t tbl = sizeof(void*) * (size_t)c.L;
+    // the staging buffers / pinned tables of slot b were last used two steps ago: wait until that step consumed them
+    cuda_check(cudaEventSynchronize(evConsumed[b]), "event sync");
+    const float4** hx = reinterpret_cast<const float4**>(h_pin[b]);
+    const uint16_t** hr = reinterpret_cast<const uint16_t**>(h_pin[b] + tbl);
+    int* hn = reinterpret_cast<int*>(h_pin[b] + 2 * tbl);
+    for (int l = 0; l < c.L; ++l) {
+        hn[l] = npts[l];
+        if (src_on_device) {
+            hx[l] = reinterpret_cast<const float4*>(xyzi) + (size_t)l * stride_points;
+            hr[l] = ring ? ring + (size_t)l * stride_points : nullptr;
+        } else {
+            hx[l] = d_in_xyzi[b] + (size_t)l * c.Pcap;
+            hr[l] = d_in_ring[b] + (size_t)l * c.Pcap;
         }
     }
-    cuda_check(cudaMemcpyAsync(d_npts, npts, sizeof(int) * c.L, cudaMemcpyHostToDevice, stream), "upload npts");
-    // npts is pageable host memory that the caller may reuse: make the copy complete before returning
-    if (!src_on_device || true) cuda_check(cudaStreamSynchronize(stream), "upload sync");
+    if (!src_on_device) {
+        if (stride_points == c.Pcap) {
+            cuda_check(cudaMemcpyAsync(d_in_xyzi[b], xyzi, sizeof(float4) * (size_t)c.L * c.Pcap, cudaMemcpyHostToDevice, copyStream), "upload xyzi");
+            if (ring) cuda_check(cudaMemcpyAsync(d_in_ring[b], ring, sizeof(uint16_t) * (size_t)c.L * c.Pcap, cudaMemcpyHostToDevice, copyStream), "upload ring");
+        } else {
+            for (int l = 0; l < c.L; ++l) {
+                cuda_check(cudaMemcpyAsync(d_in_xyzi[b] + (size_t)l * c.Pcap, xyzi + (size_t)l * stride_points * 4, sizeof(float4) * npts[l], cudaMemcpyHostToDevice, copyStream), "upload xyzi");
+                if (ring) cuda_check(cudaMemcpyAsync(d_in_ring[b] + (size_t)l * c.Pcap, ring + (size_t)l * stride_points, sizeof(uint16_t) * npts[l], cudaMemcpyHostToDevice, copyStream), "upload ring");
+            }
+        }
+    }
+    cuda_check(cudaMemcpyAsync(d_ptr_xyzi[b], hx, tbl, cudaMemcpyHostToDevice, copyStream), "upload table");
+    cuda_check(cudaMemcpyAsync(d_ptr_ring[b], hr, tbl, cudaMemcpyHostToDevice, copyStream), "upload table");
+    cuda_check(cudaMemcpyAsync(d_npts[b], hn, sizeof(int) * c.L, cudaMemcpyHostToDevice, copyStream), "upload npts");
+    cuda_check(cudaEventRecord(evCopied[b], copyStream), "event record");
+    cuda_check(cudaStreamWaitEvent(stream, evCopied[b], 0), "stream wait");
+    ip.in_xyzi = d_ptr_xyzi[b]; ip.in_ring = d_ptr_ring[b]; ip.npts = d_npts[b];
+    curIn = b;
 }
+
+void Engine::inputConsumed() { cuda_check(cudaEventRecord(evConsumed[curIn], stream), "event record"); }
 
 void Engine::getPoses(float* poses18, int* flags) {
     std::vector<float> sum(6 * (size_t)c.L);

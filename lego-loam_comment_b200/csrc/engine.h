@@ -26,8 +26,8 @@ struct Consts {
 
 // ---- ImageProjection device arrays, all [lane][...] with the strides implied by Consts ----
 struct IpDev {
-    const float4* in_xyzi;     // [L][Pcap]
-    const uint16_t* in_ring;   // [L][Pcap]
+    const float4* const* in_xyzi;     // [L] per-lane pointer to the scan's points (staging buffer or caller's device memory)
+    const uint16_t* const* in_ring;   // [L] per-lane pointer to the ring channel
     const int* npts;           // [L]
     int* owner;                // [L][N]   index of the last input point that fell into the cell, -1 = empty
     float* rangeMat;           // [L][N]   FLT_MAX = empty           (imageProjection.cpp:152)
@@ -87,6 +87,7 @@ public:
 
     // ---- ImageProjection (names follow imageProjection.cpp) ----
     void uploadScan(const float* xyzi, const uint16_t* ring, const int* npts, int stride_points, bool src_on_device);
+    void inputConsumed();         // marks the point after which the current input buffers may be overwritten
     void projectPointCloud();     // + findStartEndAngle
     void groundRemoval();
     void cloudSegmentation();
@@ -98,6 +99,20 @@ public:
     void integrateTransformationPublishCloudsLast();
 
     void sync();
+    // ---- timing: CUDA events on the engine's own stream (bench.py cannot see this stream through torch) ----
+    int profMode = 0;                 // 0 off, 1 every kernel, 2 only kernels whose name contains profFilter
+    std::string profFilter;
+    struct ProfEntry { const char* name; cudaEvent_t a, b; };
+    std::vector<ProfEntry> profLog;
+    std::vector<cudaEvent_t> evPool;
+    cudaEvent_t timerEv[8] = {};
+    cudaEvent_t takeEvent();
+    void profBegin(const char* name);
+    void profEnd();
+    void profReset();
+    long profRead(char* names, long cap, double* ms, long* counts, long maxk);
+    void timerRecord(int slot);
+    float timerElapsed(int a, int b);
     void getPoses(float* poses18, int* flags);   // per lane: transformSum | transformAftMapped | transformBefMapped
     long download(int lane, const char* name, void* dst, long cap, int* elem_size);
     long upload(int lane, const char* name, const void* src, long count);
@@ -128,10 +143,22 @@ public:
         return static_cast<T*>(p);
     }
 private:
-    float4* d_in_xyzi = nullptr; uint16_t* d_in_ring = nullptr; int* d_npts = nullptr;
-    void* h_stage = nullptr;
+    // double-buffered input staging: the H2D copy of scan k+1 runs on copyStream while scan k is still being processed
+    float4* d_in_xyzi[2] = {nullptr, nullptr}; uint16_t* d_in_ring[2] = {nullptr, nullptr}; int* d_npts[2] = {nullptr, nullptr};
+    const float4** d_ptr_xyzi[2] = {nullptr, nullptr}; const uint16_t** d_ptr_ring[2] = {nullptr, nullptr};
+    cudaStream_t copyStream = nullptr;
+    cudaEvent_t evCopied[2] = {nullptr, nullptr}, evConsumed[2] = {nullptr, nullptr};
+    int inBuf = 0, curIn = 0;
+    char* h_pin[2] = {nullptr, nullptr};   // pinned: per-lane pointer tables + npts of the step in flight
 };
 
 const std::string& last_error();
+
+// times the launches enqueued during its lifetime when profiling is on
+struct ProfScope {
+    Engine* e;
+    ProfScope(Engine* eng, const char* name) : e(eng) { if (e->profMode) e->profBegin(name); }
+    ~ProfScope() { if (e->profMode) e->profEnd(); }
+};
 
 }  // namespace lego

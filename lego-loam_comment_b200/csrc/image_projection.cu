@@ -20,7 +20,7 @@ __global__ void __launch_bounds__(256) ip_project_kernel(IpDev d, Consts c) {
     const int lane = blockIdx.y;
     const int i = blockIdx.x * blockDim.x + threadIdx.x;
     const int P = d.npts[lane];
-    const float4* __restrict__ in = d.in_xyzi + (size_t)lane * c.Pcap;
+    const float4* __restrict__ in = d.in_xyzi[lane];
     if (i == 0) {
         float* o = d.orient + lane * 4;
         if (P > 0) {
@@ -37,7 +37,7 @@ __global__ void __launch_bounds__(256) ip_project_kernel(IpDev d, Consts c) {
     const float4 p = in[i];
     long long row;
     if (c.useRing) {
-        row = d.in_ring[(size_t)lane * c.Pcap + i];
+        row = d.in_ring[lane][i];
     } else {
         const float xy = PM_SQRT(PM_ADD(PM_MUL(p.x, p.x), PM_MUL(p.y, p.y)));
         const float va = (float)((double)PM_MUL(pm::atan2f_glibc(p.z, xy), 180.0f) / M_PI);
@@ -70,7 +70,7 @@ __global__ void __launch_bounds__(256) ip_gather_kernel(IpDev d, Consts c) {
         out = make_float4(CUDART_NAN_F, CUDART_NAN_F, CUDART_NAN_F, -1.0f);
         range = FLT_MAX;
     } else {
-        const float4 p = d.in_xyzi[(size_t)lane * c.Pcap + o];
+        const float4 p = d.in_xyzi[lane][o];
         range = PM_SQRT(PM_ADD(PM_ADD(PM_MUL(p.x, p.x), PM_MUL(p.y, p.y)), PM_MUL(p.z, p.z)));
         const int row = cell / c.C, col = cell - row * c.C;
         const float inten = (float)((double)(float)row + (double)(float)col / 10000.0);
@@ -307,6 +307,7 @@ void Engine::projectPointCloud() {
     ip_project_kernel<<<g1, 256, 0, stream>>>(ip, c);
     dim3 g2((c.N + 255) / 256, c.L);
     ip_gather_kernel<<<g2, 256, 0, stream>>>(ip, c);
+    inputConsumed();
     launches += 3;
 }
 
