@@ -1,0 +1,417 @@
+#!/usr/bin/env python
+"""bench.py -- throughput of the LeGO-LOAM per-scan hot path (ImageProjection -> FeatureAssociation ->
+mapOptimization scan-to-map) on B200, in scans/s, on synthetic scans of the named sensor shape.
+
+A "step" = one lidar scan for each of `lanes` independent sequences stepped in lock step through the whole
+pipeline (the reference processes one scan per ROS callback; sequences are the only data-parallel axis,
+SURVEY.md 8e).  value = lanes * steps * n_gpus / device time, inputs resident in HBM; e2e = the same through
+the C ABI with HOST buffers (pinned), H2D of every scan and D2H of the poses inside the timed region.
+
+    python bench.py [--gpus N] [--steps K] [--warmup W] [--lanes L] [--sensor vlp16] [--impl reference]
+
+--impl reference times the reference's own CPU code (oracle/_ref, the reference sources compiled verbatim) on the
+host cores, one independent sequence per core.
+"""
+import argparse
+import json
+import os
+import subprocess
+import sys
+import threading
+import time
+
+import numpy as np
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+sys.path.insert(0, ROOT)
+sys.path.insert(0, os.path.join(ROOT, "oracle"))
+
+METRIC = "scans_per_sec"
+UNIT = "scans/s"
+
+
+def parse_args():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=20)
+    ap.add_argument("--warmup", type=int, default=4)
+    ap.add_argument("--lanes", type=int, default=64, help="independent sequences per GPU stepped in lock step")
+    ap.add_argument("--sensor", default="vlp16")
+    ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
+    ap.add_argument("--stages", type=int, default=7, help="bit0 ImageProjection, bit1 FeatureAssociation, bit2 mapOptimization")
+    ap.add_argument("--speed", type=float, default=4.0)
+    ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--no-e2e", action="store_true")
+    ap.add_argument("--profile-json", default="", help="write the per-kernel CUDA-event breakdown to this file")
+    return ap.parse_args()
+
+
+def dist_env():
+    rank = int(os.environ.get("RANK", "0"))
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    local = int(os.environ.get("LOCAL_RANK", "0"))
+    return rank, world, local
+
+
+# ------------------------------------------------------------------------------------------------ clocks
+class ClockSampler:
+    """Samples nvidia-smi clocks / throttle reasons of one GPU while the timed region runs."""
+    Q = "clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.hw_slowdown,clocks_event_reasons.hw_thermal_slowdown," \
+        "clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap"
+
+    def __init__(self, gpu_index):
+        self.rows = []
+        self.proc = None
+        self.gpu = gpu_index
+
+    def start(self):
+        try:
+            self.proc = subprocess.Popen(["nvidia-smi", "-i", str(self.gpu), "--query-gpu=" + self.Q, "--format=csv,noheader,nounits",
+                                          "-lms", "100"], stdout=subprocess.PIPE, stderr=subprocess.DEVNULL, text=True)
+            self.t = threading.Thread(target=self._read, daemon=True)
+            self.t.start()
+        except OSError:
+            self.proc = None
+
+    def _read(self):
+        for line in self.proc.stdout:
+            self.rows.append([c.strip() for c in line.split(",")])
+
+    def stop(self):
+        if not self.proc:
+            return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["nvidia-smi unavailable"]}
+        time.sleep(0.15)
+        self.proc.terminate()
+        try:
+            self.proc.wait(timeout=2)
+        except subprocess.TimeoutExpired:
+            self.proc.kill()
+        sm, mx, reasons = [], [], set()
+        names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
+        for r in self.rows:
+            if len(r) < 7:
+                continue
+            try:
+                sm.append(float(r[0])); mx.append(float(r[1]))
+            except ValueError:
+                continue
+            for k, nm in enumerate(names):
+                if r[3 + k].lower().startswith("active"):
+                    reasons.add(nm)
+        return {"sm_mhz": float(np.median(sm)) if sm else None, "sm_max_mhz": max(mx) if mx else None,
+                "reasons": sorted(reasons), "samples": len(sm)}
+
+
+# ------------------------------------------------------------------------------------------------ inputs
+def gen_inputs(sensor, lanes, n_scans, seed0, speed):
+    """Synthetic scans (tools/synth_scan.cpp): lane l = sequence with seed seed0+l, scans 0..n_scans-1.
+    -> xyzi float32[T, L, cap, 4], ring uint16[T, L, cap], npts int32[T, L], stamps float64[T]"""
+    import lego_loam_b200  # noqa: F401
+    from lego_loam_b200.synth import SynthSequence
+    seqs = [SynthSequence(sensor, seed=seed0 + l, scene="street", speed=speed, n_scans=max(n_scans, 64)) for l in range(lanes)]
+    cap = seqs[0].cap
+    xyzi = np.zeros((n_scans, lanes, cap, 4), np.float32)
+    ring = np.zeros((n_scans, lanes, cap), np.uint16)
+    npts = np.zeros((n_scans, lanes), np.int32)
+    for l, s in enumerate(seqs):
+        x, r, n = s.batch(0, n_scans)
+        xyzi[:, l] = x; ring[:, l] = r; npts[:, l] = n
+    stamps = np.arange(n_scans, dtype=np.float64) * 0.1
+    return xyzi, ring, npts, stamps, cap
+
+
+# ------------------------------------------------------------------------------------------------ roofline
+def algorithmic_bytes(name, c):
+    """Compulsory HBM bytes of ONE launch of kernel `name` (every input read once, every output written once;
+    formulas of SURVEY.md 8d / DESIGN.md, evaluated with the run's own counts, summed over the lanes of the launch).
+    c: dict of per-step totals over lanes (P, N, S, O, Fs, Fl, Ff, Flf, R, C, G, L, ...)."""
+    N, P, S, O, L = c["N"], c["P"], c["S"], c["O"], c["L"]
+    F3 = c["Fs"] + c["Fl"] + c["Ff"]
+    t = {
+        "memset_owner": 4 * N,
+        "ip_project_kernel": 18 * P + 4 * P,
+        "ip_gather_kernel": 4 * N + 16 * P + 20 * N,
+        "ip_ground_kernel": 16 * (c["G"] + 1) * c["C"] * L + N,
+        "ip_ccl_union_kernel": 8 * N,
+        "ip_ccl_stats_kernel": 4 * N,
+        "ip_row_count_kernel": 9 * N,
+        "ip_compact_kernel": 9 * N + 41 * S + 16 * O + 8 * c["R"] * L,
+        "fa_prepare_kernel": 20 * S,
+        "fa_distort_kernel": 32 * S,
+        "fa_extract_kernel": 33 * S + 16 * F3 + 32 * S + 16 * c["Flf"],
+        "fa_gather_features_kernel": 32 * (F3 + c["Flf"]),
+        "fa_odometry_kernel": c.get("odo_bytes", 0),
+        "fa_clouds_last_kernel": 32 * (c["Fl"] + c["Flf"]) + 32 * O,
+        "fa_finish_scan_kernel": 64 * L,
+        "vh_build(cornerLast)": 36 * c["Fl"],
+        "vh_build(surfLast)": 36 * c["Flf"],
+    }
+    t.update(c.get("mo_bytes", {}))
+    return float(t.get(name, 0))
+
+
+def gather_counts(pl, params, lanes):
+    """Per-step workload counts summed over lanes, read back from the device counters after the run."""
+    c = dict(N=params.N_SCAN * params.Horizon_SCAN * lanes, R=params.N_SCAN, C=params.Horizon_SCAN, G=params.groundScanInd, L=lanes,
+             P=0, S=0, O=0, Fs=0, Fl=0, Ff=0, Flf=0)
+    odo = 0
+    for l in range(lanes):
+        ipc = pl.download("ipCounts", l)
+        fc = pl.download("featCounts", l)
+        lc = pl.download("lastCounts", l)
+        st = pl.download("lmState", l)
+        c["S"] += int(ipc[0]); c["O"] += int(ipc[1])
+        c["Fs"] += int(fc[0]); c["Fl"] += int(fc[1]); c["Ff"] += int(fc[2]); c["Flf"] += int(fc[3])
+        # K10 + K11 of SURVEY.md 8d: per correspondence refresh 24*Q + 16*M, per LM iteration 96 bytes per row
+        it_s, it_c = max(int(st[6]), 1), max(int(st[7]), 1)
+        odo += ((it_s + 4) // 5) * (24 * int(fc[2]) + 16 * int(lc[1])) + it_s * 96 * int(fc[2])
+        odo += ((it_c + 4) // 5) * (24 * int(fc[0]) + 16 * int(lc[0])) + it_c * 96 * int(fc[0])
+    c["odo_bytes"] = odo
+    return c
+
+
+def load_peaks():
+    p = os.path.join(ROOT, "MEASURED_PEAKS.json")
+    if os.path.exists(p):
+        with open(p) as f:
+            return float(json.load(f)["hbm_gbs"]), "measured (MEASURED_PEAKS.json hbm_gbs)"
+    return 6650.0, "fallback (B200_PROFILING.md)"
+
+
+# ------------------------------------------------------------------------------------------------ B200 arm
+def run_b200(args):
+    import torch
+    import torch.distributed as dist
+    import lego_loam_b200  # noqa: F401
+    from lego_loam_b200.capi import Pipeline
+    from lego_loam_b200.params import make_params
+
+    rank, world, local = dist_env()
+    if not torch.cuda.is_available():
+        raise SystemExit("bench.py: no CUDA device (the product has no CPU fallback)")
+    torch.cuda.set_device(local)
+    if world > 1:
+        dist.init_process_group("nccl", device_id=torch.device("cuda", local))
+    L, K, W = args.lanes, args.steps, args.warmup
+    T = W + K
+    params = make_params(args.sensor, device=local)
+    xyzi, ring, npts, stamps, cap = gen_inputs(args.sensor, L, T, seed0=1000 * rank, speed=args.speed)
+
+    def barrier():
+        torch.cuda.synchronize()
+        if world > 1:
+            dist.barrier()
+        torch.cuda.synchronize()
+
+    def stamps_of(t):
+        return np.full(L, stamps[t])
+
+    # ---- device-resident inputs (value) -------------------------------------------------------------
+    d_xyzi = torch.from_numpy(xyzi).cuda()
+    d_ring = torch.from_numpy(ring).cuda()
+    torch.cuda.synchronize()
+    xs, rs = d_xyzi.stride(0) * 4, d_ring.stride(0) * 2
+
+    def device_step(pl, t):
+        pl.step(d_xyzi.data_ptr() + t * xs, d_ring.data_ptr() + t * rs, npts[t], stamps_of(t), stage_mask=args.stages,
+                on_device=True, stride_points=cap)
+
+    # pass 1 (untimed): per-kernel CUDA-event breakdown, finds the dominant kernel
+    pl = Pipeline(params, lanes=L, max_points=cap)
+    for t in range(W):
+        device_step(pl, t)
+    pl.sync()
+    pl.profile(1)
+    for t in range(W, T):
+        device_step(pl, t)
+    prof = pl.profile_read()
+    pl.profile(0)
+    counts = gather_counts(pl, params, L)
+    counts["P"] = int(npts[T - 1].sum())
+    pl.close()
+    tot_ms = sum(v[0] for v in prof.values()) or 1.0
+    dominant = max(prof, key=lambda k: prof[k][0])
+
+    # pass 2 (timed): K steps, events on the pipeline's stream; only the dominant kernel stays bracketed
+    pl = Pipeline(params, lanes=L, max_points=cap)
+    for t in range(W):
+        device_step(pl, t)
+    pl.sync()
+    pl.profile(2, dominant)
+    launches0 = pl.launch_count()
+    clk = ClockSampler(local)
+    clk.start()
+    barrier()
+    pl.timer_record(0)
+    for t in range(W, T):
+        device_step(pl, t)
+    pl.timer_record(1)
+    pl.sync()
+    barrier()
+    ms = pl.timer_elapsed_ms(0, 1)
+    clocks = clk.stop()
+    launches = pl.launch_count() - launches0
+    dom = pl.profile_read().get(dominant, (0.0, 0))
+    pl.profile(0)
+    poses_dev, _ = pl.poses()
+    pl.close()
+
+    # ---- host buffers through the C ABI (e2e) --------------------------------------------------------
+    e2e = None
+    if not args.no_e2e:
+        h_xyzi = torch.from_numpy(xyzi).pin_memory()
+        h_ring = torch.from_numpy(ring).pin_memory()
+        hx, hr = h_xyzi.numpy(), h_ring.numpy()
+        pl = Pipeline(params, lanes=L, max_points=cap)
+        for t in range(W):
+            pl.step(hx[t], hr[t], npts[t], stamps_of(t), stage_mask=args.stages)
+            pl.poses()
+        barrier()
+        t0 = time.perf_counter()
+        for t in range(W, T):
+            pl.step(hx[t], hr[t], npts[t], stamps_of(t), stage_mask=args.stages)
+            poses_host, _ = pl.poses()        # D2H of the step's result, synchronises
+        barrier()
+        e2e_s = time.perf_counter() - t0
+        pl.close()
+        if world > 1:
+            tt = torch.tensor([e2e_s], device="cuda"); dist.all_reduce(tt, op=dist.ReduceOp.MAX); e2e_s = float(tt.item())
+        assert np.allclose(poses_host, poses_dev, atol=1e-6), "host-buffer and device-buffer runs disagree"
+        e2e = {"value": L * K * world / e2e_s, "unit": UNIT,
+               "h2d_bytes_per_step": int(hx[0].nbytes + hr[0].nbytes + npts[0].nbytes), "d2h_bytes_per_step": int(L * (18 * 4 + 4))}
+
+    if world > 1:
+        tt = torch.tensor([ms], device="cuda"); dist.all_reduce(tt, op=dist.ReduceOp.MAX); ms = float(tt.item())
+    return dict(rank=rank, world=world, ms=ms, L=L, K=K, W=W, e2e=e2e, clocks=clocks, launches=launches, prof=prof, tot_ms=tot_ms,
+                dominant=dominant, dom=dom, counts=counts, cap=cap, params=params,
+                step_bytes=int(xyzi[0].nbytes + ring[0].nbytes), inputs=(xyzi, ring, npts, stamps))
+
+
+# ------------------------------------------------------------------------------------------------ CPU reference
+def _ref_worker(q, sensor, seed, n_scans, speed, stages, pin_core):
+    """One process = one sequence through the reference's own code (oracle/_ref), timed without scan generation."""
+    try:
+        if pin_core is not None and hasattr(os, "sched_setaffinity"):
+            os.sched_setaffinity(0, {pin_core})
+        import lego_loam_b200  # noqa: F401
+        from lego_loam_b200.synth import SynthSequence
+        import refpy
+        seq = SynthSequence(sensor, seed=seed, scene="street", speed=speed, n_scans=max(n_scans, 64))
+        x, r, n = seq.batch(0, n_scans, threads=1)
+        ref = refpy.RefPipeline(sensor, snapshots=False)
+        t0 = time.perf_counter()
+        for k in range(n_scans):
+            ref.feed(x[k, :n[k]], r[k, :n[k]], k * 0.1, stages)
+        dt = time.perf_counter() - t0
+        timers, scans, mo_calls = ref.timers()
+        ref.close()
+        q.put((n_scans, dt, {k: v / max(scans, 1) for k, v in timers.items()}, mo_calls))
+    except Exception as ex:  # noqa: BLE001
+        q.put((0, 0.0, {"error": repr(ex)}, 0))
+
+
+def run_reference_cpu(sensor, n_procs, scans_per_proc, speed, stages, seed0=0, pin=False):
+    """-> (scans/s over all processes, per-stage ms of process 0, mapping calls of process 0, wall seconds)"""
+    import multiprocessing as mp
+    ctx = mp.get_context("spawn")
+    q = ctx.Queue()
+    procs = [ctx.Process(target=_ref_worker, args=(q, sensor, seed0 + i, scans_per_proc, speed, stages, i if pin else None))
+             for i in range(n_procs)]
+    for p in procs:
+        p.start()
+    res = [q.get() for _ in procs]
+    for p in procs:
+        p.join()
+    total = sum(r[0] for r in res)
+    slowest = max(r[1] for r in res) or 1e-9
+    return total / slowest, res[0][2], res[0][3], slowest
+
+
+def reference_available(sensor):
+    import refpy
+    return refpy.available(sensor)
+
+
+def run_reference_arm(args):
+    rank, world, _ = dist_env()
+    if rank != 0:
+        return None
+    cores = os.cpu_count() or 1
+    per_step = 25 if args.sensor.startswith("vlp16") else 8          # scans per process per "step": bounded sample
+    n_scans = per_step * (args.steps + args.warmup)
+    rate, stages_ms, mo_calls, wall = run_reference_cpu(args.sensor, cores, n_scans, args.speed, args.stages)
+    line = {
+        "impl": "reference", "metric": METRIC, "value": rate, "unit": UNIT, "n_gpus": args.gpus, "steps": args.steps, "warmup": args.warmup,
+        "ms_per_step": 1000.0 * wall / (args.steps + args.warmup), "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
+        "dtype": "f32", "data": "synthetic",
+        "config": {"workload": workload_name(args), "sensor": args.sensor, "stages": args.stages,
+                   "note": "reference sources compiled verbatim (oracle/_ref), one independent sequence per host core"},
+        "cpu_baseline": {"value": rate, "unit": UNIT, "cores": cores, "kind": "reference",
+                         "sample": "%d processes x %d scans of the street sequence, all stages" % (cores, n_scans)},
+        "e2e": {"value": rate, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
+        "gpu_launches": 0,
+    }
+    return line
+
+
+def workload_name(args):
+    shape = {"vlp16": "VLP-16 16x1800", "vlp16_noring": "VLP-16 16x1800 (no ring channel)", "hdl32": "HDL-32E 32x1800",
+             "hdl64": "64-beam 64x2083", "vls128": "VLS-128 128x1800"}[args.sensor]
+    st = "+".join(n for b, n in ((1, "imageProjection"), (2, "featureAssociation"), (4, "mapOptimization")) if args.stages & b)
+    return "%s synthetic street trajectories, %s" % (shape, st)
+
+
+# ------------------------------------------------------------------------------------------------ main
+def main():
+    args = parse_args()
+    if args.impl == "reference":
+        if not reference_available(args.sensor):
+            # the oracle restatement always exists in the repo; only the verbatim-compiled .so can be missing
+            print(json.dumps({"impl": "reference", "unavailable": "oracle/_ref/liblego_ref_%s.so not built" % args.sensor}))
+            return
+        line = run_reference_arm(args)
+        if line is not None:
+            print(json.dumps(line))
+        return
+
+    r = run_b200(args)
+    if r["rank"] != 0:
+        return
+    L, K, world = r["L"], r["K"], r["world"]
+    value = L * K * world / (r["ms"] * 1e-3)
+    peak, peak_src = load_peaks()
+    dom_ms, dom_n = r["dom"]
+    abytes = algorithmic_bytes(r["dominant"], r["counts"])
+    achieved = (abytes / (dom_ms * 1e-3 / max(dom_n, 1)) / 1e9) if dom_ms > 0 else 0.0
+    roofline = {"bound": "hbm", "kernel": r["dominant"], "achieved": achieved, "peak": peak, "unit": "GB/s",
+                "frac": achieved / peak, "traffic": None, "peak_source": peak_src,
+                "algorithmic_bytes_per_launch": abytes, "avg_launch_ms": dom_ms / max(dom_n, 1),
+                "share_of_step": r["prof"][r["dominant"]][0] / r["tot_ms"]}
+    line = {
+        "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": K, "warmup": r["W"],
+        "ms_per_step": r["ms"] / K, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
+        "dtype": "f32", "data": "synthetic",
+        "config": {"workload": workload_name(args), "sensor": args.sensor, "lanes_per_gpu": L, "stages": args.stages,
+                   "points_per_scan": r["cap"],
+                   "l2": "per-step inputs %.0f MB + per-lane state exceed the 126 MB L2 (no flush needed)" % (r["step_bytes"] / 1e6)},
+        "roofline": roofline, "clocks": r["clocks"], "gpu_launches": int(r["launches"]),
+    }
+    if r["e2e"]:
+        line["e2e"] = r["e2e"]
+    if not args.no_cpu_baseline and reference_available(args.sensor):
+        n = 400 if args.sensor.startswith("vlp16") else 120
+        rate, stages_ms, mo_calls, wall = run_reference_cpu(args.sensor, 1, n, args.speed, args.stages, pin=False)
+        line["cpu_baseline"] = {"value": rate, "unit": UNIT, "cores": 1, "kind": "reference",
+                                "sample": "%d scans of one street sequence, reference sources compiled verbatim (oracle/_ref), %.1f s" % (n, wall),
+                                "per_stage_ms": {k: round(v, 4) for k, v in stages_ms.items() if isinstance(v, float)}}
+    if args.profile_json:
+        with open(args.profile_json, "w") as f:
+            json.dump({"per_kernel_ms_over_timed_steps": {k: {"ms": v[0], "launches": v[1],
+                                                             "algorithmic_bytes_per_launch": algorithmic_bytes(k, r["counts"])}
+                                                         for k, v in r["prof"].items()},
+                       "counts": {k: v for k, v in r["counts"].items() if not isinstance(v, dict)}, "line": line}, f, indent=1)
+    print(json.dumps(line))
+
+
+if __name__ == "__main__":
+    main()

@@ -137,6 +137,14 @@ int lego_pipeline_get_poses(lego_pipeline* h, float* poses_out, int* flags_out);
 int lego_pipeline_sync(lego_pipeline* h);
 /* number of kernel launches issued by the handle so far (bench.py's gpu_launches) */
 long lego_pipeline_launch_count(lego_pipeline* h);
+/* Timing on the handle's own stream (CUDA events; a caller's torch.cuda.Event cannot see this stream).
+ * timer_record(slot) records event `slot` (0..7); timer_elapsed waits for slot_b and returns the device time between
+ * the two.  profile(mode): 0 off, 1 bracket every kernel launch with events, 2 only kernels whose name contains
+ * `filter`; profile_read sums the brackets per kernel name (names newline-separated) and returns the number of names. */
+int lego_pipeline_timer_record(lego_pipeline* h, int slot);
+int lego_pipeline_timer_elapsed(lego_pipeline* h, int slot_a, int slot_b, float* ms_out);
+int lego_pipeline_profile(lego_pipeline* h, int mode, const char* filter);
+long lego_pipeline_profile_read(lego_pipeline* h, char* names, long names_cap, double* ms, long* counts, long max_kernels);
 /* Parity / debug access to named device arrays of one lane (see DESIGN.md for the name list).  Returns the
  * element count (and copies min(count, cap) elements) or a negative error code.  elem_size_out gets 1/2/4/16. */
 long lego_pipeline_download(lego_pipeline* h, int lane, const char* name, void* dst, long cap, int* elem_size_out);

@@ -18,6 +18,7 @@ EXPORTED = [
     "lego_mo_create", "lego_mo_destroy", "lego_mo_process",
     "lego_pipeline_create", "lego_pipeline_destroy", "lego_pipeline_step", "lego_pipeline_get_poses",
     "lego_pipeline_sync", "lego_pipeline_launch_count", "lego_pipeline_download", "lego_pipeline_upload",
+    "lego_pipeline_timer_record", "lego_pipeline_timer_elapsed", "lego_pipeline_profile", "lego_pipeline_profile_read",
     "lego_selftest_atan2f", "lego_selftest_std_sort",
 ]
 
@@ -48,8 +49,12 @@ def load():
         lib.lego_pipeline_download.restype = ctypes.c_long
         lib.lego_pipeline_upload.argtypes = [ctypes.c_void_p, ctypes.c_int, ctypes.c_char_p, ctypes.c_void_p, ctypes.c_long]
         lib.lego_pipeline_upload.restype = ctypes.c_long
-        if hasattr(lib, "lego_pipeline_get_poses"):
-            lib.lego_pipeline_get_poses.argtypes = [ctypes.c_void_p, ctypes.c_void_p, ctypes.c_void_p]
+        lib.lego_pipeline_get_poses.argtypes = [ctypes.c_void_p, ctypes.c_void_p, ctypes.c_void_p]
+        lib.lego_pipeline_timer_record.argtypes = [ctypes.c_void_p, ctypes.c_int]
+        lib.lego_pipeline_timer_elapsed.argtypes = [ctypes.c_void_p, ctypes.c_int, ctypes.c_int, ctypes.POINTER(ctypes.c_float)]
+        lib.lego_pipeline_profile.argtypes = [ctypes.c_void_p, ctypes.c_int, ctypes.c_char_p]
+        lib.lego_pipeline_profile_read.argtypes = [ctypes.c_void_p, ctypes.c_char_p, ctypes.c_long, ctypes.c_void_p, ctypes.c_void_p, ctypes.c_long]
+        lib.lego_pipeline_profile_read.restype = ctypes.c_long
         _lib = lib
     return _lib
 
@@ -121,6 +126,25 @@ class Pipeline:
 
     def launch_count(self):
         return self.lib.lego_pipeline_launch_count(self.h)
+
+    def timer_record(self, slot):
+        _check(self.lib.lego_pipeline_timer_record(self.h, slot), "lego_pipeline_timer_record")
+
+    def timer_elapsed_ms(self, a, b):
+        ms = ctypes.c_float(0)
+        _check(self.lib.lego_pipeline_timer_elapsed(self.h, a, b, ctypes.byref(ms)), "lego_pipeline_timer_elapsed")
+        return ms.value
+
+    def profile(self, mode, name_filter=""):
+        _check(self.lib.lego_pipeline_profile(self.h, mode, name_filter.encode()), "lego_pipeline_profile")
+
+    def profile_read(self, max_kernels=128):
+        names = ctypes.create_string_buffer(8192)
+        ms = np.zeros(max_kernels, np.float64)
+        counts = np.zeros(max_kernels, np.int64)
+        n = _check(self.lib.lego_pipeline_profile_read(self.h, names, 8192, ms.ctypes.data, counts.ctypes.data, max_kernels), "profile_read")
+        keys = names.value.decode().split("\n")[:n]
+        return {k: (float(ms[i]), int(counts[i])) for i, k in enumerate(keys)}
 
     def poses(self):
         poses = np.zeros((self.lanes, 18), np.float32)

@@ -75,6 +75,28 @@ int lego_pipeline_get_poses(lego_pipeline* h, float* poses_out, int* flags_out) 
     LEGO_TRY h->e->getPoses(poses_out, flags_out); return LEGO_OK; LEGO_CATCH
 }
 long lego_pipeline_launch_count(lego_pipeline* h) { return h ? h->e->launches : 0; }
+int lego_pipeline_profile(lego_pipeline* h, int mode, const char* filter) {
+    if (!h || mode < 0 || mode > 2) return LEGO_ERR_ARG;
+    LEGO_TRY
+    h->e->sync();
+    h->e->profReset();
+    h->e->profMode = mode;
+    h->e->profFilter = filter ? filter : "";
+    return LEGO_OK;
+    LEGO_CATCH
+}
+long lego_pipeline_profile_read(lego_pipeline* h, char* names, long names_cap, double* ms, long* counts, long max_kernels) {
+    if (!h || !ms || !counts) return LEGO_ERR_ARG;
+    LEGO_TRY return h->e->profRead(names, names_cap, ms, counts, max_kernels); LEGO_CATCH
+}
+int lego_pipeline_timer_record(lego_pipeline* h, int slot) {
+    if (!h || slot < 0 || slot >= 8) return LEGO_ERR_ARG;
+    LEGO_TRY h->e->timerRecord(slot); return LEGO_OK; LEGO_CATCH
+}
+int lego_pipeline_timer_elapsed(lego_pipeline* h, int slot_a, int slot_b, float* ms_out) {
+    if (!h || !ms_out || slot_a < 0 || slot_a >= 8 || slot_b < 0 || slot_b >= 8) return LEGO_ERR_ARG;
+    LEGO_TRY *ms_out = h->e->timerElapsed(slot_a, slot_b); return LEGO_OK; LEGO_CATCH
+}
 long lego_pipeline_download(lego_pipeline* h, int lane, const char* name, void* dst, long cap, int* elem_size_out) {
     if (!h || !name) return LEGO_ERR_ARG;
     LEGO_TRY

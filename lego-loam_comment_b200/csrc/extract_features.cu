@@ -316,8 +316,8 @@ __global__ void fa_distort_kernel(IpDev d, FaDev f, Consts c);
 void Engine::adjustDistortionCalculateSmoothnessMarkOccluded() {
     cuda_check(cudaMemsetAsync(fa.halfFirst, 0x7F, sizeof(int) * c.L, stream), "memset halfFirst");
     dim3 g((c.N + 255) / 256, c.L);
-    fa_prepare_kernel<<<g, 256, 0, stream>>>(ip, fa, c);
-    fa_distort_kernel<<<g, 256, 0, stream>>>(ip, fa, c);
+    { ProfScope ps(this, "fa_prepare_kernel"); fa_prepare_kernel<<<g, 256, 0, stream>>>(ip, fa, c); }
+    { ProfScope ps(this, "fa_distort_kernel"); fa_distort_kernel<<<g, 256, 0, stream>>>(ip, fa, c); }
     launches += 3;
 }
 
@@ -329,8 +329,8 @@ void Engine::extractFeatures() {
         attr_set = true;
     }
     dim3 g(c.R, c.L);
-    fa_extract_kernel<<<g, 256, smem, stream>>>(ip, fa, c, 0.2f);   // downSizeFilter.setLeafSize(0.2,...) featureAssociation.cpp:225
-    fa_gather_features_kernel<<<c.L, 256, 0, stream>>>(fa, c);
+    { ProfScope ps(this, "fa_extract_kernel"); fa_extract_kernel<<<g, 256, smem, stream>>>(ip, fa, c, 0.2f); }   // downSizeFilter.setLeafSize(0.2,...) featureAssociation.cpp:225
+    { ProfScope ps(this, "fa_gather_features_kernel"); fa_gather_features_kernel<<<c.L, 256, 0, stream>>>(fa, c); }
     launches += 2;
 }
 

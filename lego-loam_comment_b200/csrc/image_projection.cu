@@ -302,28 +302,28 @@ __global__ void __launch_bounds__(256) ip_label_finalize_kernel(IpDev d, Consts 
 
 // ------------------------------------------------------------------------------------------------------------
 void Engine::projectPointCloud() {
-    cuda_check(cudaMemsetAsync(ip.owner, 0xFF, sizeof(int) * (size_t)c.L * c.N, stream), "memset owner");
+    { ProfScope ps(this, "memset_owner"); cuda_check(cudaMemsetAsync(ip.owner, 0xFF, sizeof(int) * (size_t)c.L * c.N, stream), "memset owner"); }
     dim3 g1((c.Pcap + 255) / 256, c.L);
-    ip_project_kernel<<<g1, 256, 0, stream>>>(ip, c);
+    { ProfScope ps(this, "ip_project_kernel"); ip_project_kernel<<<g1, 256, 0, stream>>>(ip, c); }
     dim3 g2((c.N + 255) / 256, c.L);
-    ip_gather_kernel<<<g2, 256, 0, stream>>>(ip, c);
+    { ProfScope ps(this, "ip_gather_kernel"); ip_gather_kernel<<<g2, 256, 0, stream>>>(ip, c); }
     inputConsumed();
     launches += 3;
 }
 
 void Engine::groundRemoval() {
     dim3 g((c.C + 127) / 128, c.L);
-    ip_ground_kernel<<<g, 128, 0, stream>>>(ip, c);
+    { ProfScope ps(this, "ip_ground_kernel"); ip_ground_kernel<<<g, 128, 0, stream>>>(ip, c); }
     launches += 1;
 }
 
 void Engine::cloudSegmentation() {
     dim3 g((c.N + 255) / 256, c.L);
-    ip_ccl_union_kernel<<<g, 256, 0, stream>>>(ip, c);
-    ip_ccl_stats_kernel<<<g, 256, 0, stream>>>(ip, c);
+    { ProfScope ps(this, "ip_ccl_union_kernel"); ip_ccl_union_kernel<<<g, 256, 0, stream>>>(ip, c); }
+    { ProfScope ps(this, "ip_ccl_stats_kernel"); ip_ccl_stats_kernel<<<g, 256, 0, stream>>>(ip, c); }
     dim3 gr(c.R, c.L);
-    ip_row_count_kernel<<<gr, 256, 0, stream>>>(ip, c);
-    ip_compact_kernel<<<gr, 256, 0, stream>>>(ip, c);
+    { ProfScope ps(this, "ip_row_count_kernel"); ip_row_count_kernel<<<gr, 256, 0, stream>>>(ip, c); }
+    { ProfScope ps(this, "ip_compact_kernel"); ip_compact_kernel<<<gr, 256, 0, stream>>>(ip, c); }
     launches += 4;
 }
 

@@ -69,19 +69,20 @@ __global__ void __launch_bounds__(ODO_THREADS) fa_odometry_kernel(IpDev d, FaDev
     if (tid == 0) sh.isDegenerate = f.lmState[lane * 8 + 1];
     __syncthreads();
     const size_t R = c.R, N = c.N;
+    int itS = 0, itC = 0;
     {
         const VhLane vh = vh_lane(f.hashSurf, lane);
-        odo_phase<true>(sh, sel, f.flat + lane * R * 24, f.featCounts[lane * 4 + 2], f.surfLast[buf] + lane * N, nSurfLast, vh,
+        itS = odo_phase<true>(sh, sel, f.flat + lane * R * 24, f.featCounts[lane * 4 + 2], f.surfLast[buf] + lane * N, nSurfLast, vh,
                         f.surfInd + lane * R * 24 * 3, c);
     }
     {
         const VhLane vh = vh_lane(f.hashCorner, lane);
-        odo_phase<false>(sh, sel, f.sharp + lane * R * 12, f.featCounts[lane * 4 + 0], f.cornerLast[buf] + lane * R * 120, nCornerLast, vh,
+        itC = odo_phase<false>(sh, sel, f.sharp + lane * R * 12, f.featCounts[lane * 4 + 0], f.cornerLast[buf] + lane * R * 120, nCornerLast, vh,
                          f.cornerInd + lane * R * 12 * 2, c);
     }
     if (tid < 6) f.transformCur[lane * 6 + tid] = sh.T[tid];
     if (tid < 9) f.matP[lane * 9 + tid] = sh.matP[tid];
-    if (tid == 0) f.lmState[lane * 8 + 1] = sh.isDegenerate;
+    if (tid == 0) { f.lmState[lane * 8 + 1] = sh.isDegenerate; f.lmState[lane * 8 + 6] = itS; f.lmState[lane * 8 + 7] = itC; }
 }
 
 // publishCloudsLast (featureAssociation.cpp:1759-1789) / checkSystemInitialization (featureAssociation.cpp:1605-1637):
@@ -137,20 +138,20 @@ void Engine::updateTransformation() {
     const size_t smem = sizeof(float4) * 24 * (size_t)c.R;
     static bool attr_set = false;
     if (!attr_set) { cuda_check(cudaFuncSetAttribute(fa_odometry_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 64 * 1024), "smem attr"); attr_set = true; }
-    fa_odometry_kernel<<<c.L, ODO_THREADS, smem, stream>>>(ip, fa, c, faBuf);
+    { ProfScope ps(this, "fa_odometry_kernel"); fa_odometry_kernel<<<c.L, ODO_THREADS, smem, stream>>>(ip, fa, c, faBuf); }
     launches += 1;
 }
 
 void Engine::integrateTransformationPublishCloudsLast() {
     const int nb = faBuf ^ 1;
     dim3 g(ODO_TE_BLOCKS, c.L);
-    fa_clouds_last_kernel<<<g, 256, 0, stream>>>(ip, fa, c, nb);
-    fa_finish_scan_kernel<<<(c.L + 63) / 64, 64, 0, stream>>>(ip, fa, c);
+    { ProfScope ps(this, "fa_clouds_last_kernel"); fa_clouds_last_kernel<<<g, 256, 0, stream>>>(ip, fa, c, nb); }
+    { ProfScope ps(this, "fa_finish_scan_kernel"); fa_finish_scan_kernel<<<(c.L + 63) / 64, 64, 0, stream>>>(ip, fa, c); }
     faBuf = nb;
     // the two kd-tree rebuilds of featureAssociation.cpp:1786-1787 become two voxel-hash builds
     launches += 2;
-    launches += vh_build(fa.hashCorner, c.L, fa.cornerLast[nb], (size_t)c.R * 120, fa.lastCounts + 0, 4, stream);
-    launches += vh_build(fa.hashSurf, c.L, fa.surfLast[nb], (size_t)c.N, fa.lastCounts + 1, 4, stream);
+    { ProfScope ps(this, "vh_build(cornerLast)"); launches += vh_build(fa.hashCorner, c.L, fa.cornerLast[nb], (size_t)c.R * 120, fa.lastCounts + 0, 4, stream); }
+    { ProfScope ps(this, "vh_build(surfLast)"); launches += vh_build(fa.hashSurf, c.L, fa.surfLast[nb], (size_t)c.N, fa.lastCounts + 1, 4, stream); }
 }
 
 }  // namespace lego

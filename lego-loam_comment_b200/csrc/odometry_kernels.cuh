@@ -57,13 +57,15 @@ __device__ inline void build_ring_offsets(const float4* __restrict__ cloud, int 
 // One LM phase.  SURF: features = surfPointsFlat, unknowns [rx, rz, ty] (featureAssociation.cpp:1155-1377);
 // otherwise features = cornerPointsSharp, unknowns [ry, tx, tz] (featureAssociation.cpp:1044-1153, 1379-1478).
 template <bool SURF>
-__device__ void odo_phase(OdoShared& sh, float4* sel, const float4* __restrict__ feats, int Q,
+__device__ int odo_phase(OdoShared& sh, float4* sel, const float4* __restrict__ feats, int Q,
                           const float4* __restrict__ last, int M, const VhLane& vh, int* ind, const Consts& c) {
     constexpr int K = SURF ? 3 : 2;
     const int tid = threadIdx.x, lid = tid & 31, warp = tid >> 5;
     const float maxD2 = c.nearestFeatureSearchSqDist;
     build_ring_offsets(last, M, c.R, sh.ringOff);
+    int itersDone = 0;
     for (int iter = 0; iter < 25; ++iter) {
+        itersDone = iter + 1;
         for (int q = tid; q < Q; q += ODO_THREADS) sel[q] = pose::transform_to_start(feats[q], sh.T);
         __syncthreads();
         if (iter % 5 == 0) {
@@ -207,6 +209,7 @@ __device__ void odo_phase(OdoShared& sh, float4* sel, const float4* __restrict__
         if (!sh.keepGoing) break;
     }
     __syncthreads();
+    return itersDone;
 }
 
 }  // namespace lego
