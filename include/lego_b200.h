@@ -157,6 +157,10 @@ int lego_selftest_atan2f(const float* y, const float* x, float* out, long n);
  * std::sort (csrc/std_sort_replay.cuh); inds_out receives, per segment, the original positions in sorted order. */
 int lego_selftest_std_sort(const float* values, const int* offsets, int nseg, int* inds_out);
 
+/* Batched pcl::VoxelGrid (csrc/voxel_grid.cu) on nseg independent clouds: offsets has nseg+1 entries (in points);
+ * out receives the filtered clouds back to back in segment order, out_counts[s] their sizes.  Host pointers. */
+int lego_selftest_voxel_grid(const float* xyzi, const int* offsets, int nseg, float leaf, float* out, int* out_counts);
+
 #ifdef __cplusplus
 }
 #endif

@@ -19,7 +19,7 @@ EXPORTED = [
     "lego_pipeline_create", "lego_pipeline_destroy", "lego_pipeline_step", "lego_pipeline_get_poses",
     "lego_pipeline_sync", "lego_pipeline_launch_count", "lego_pipeline_download", "lego_pipeline_upload",
     "lego_pipeline_timer_record", "lego_pipeline_timer_elapsed", "lego_pipeline_profile", "lego_pipeline_profile_read",
-    "lego_selftest_atan2f", "lego_selftest_std_sort",
+    "lego_selftest_atan2f", "lego_selftest_std_sort", "lego_selftest_voxel_grid",
 ]
 
 _lib = None
@@ -85,6 +85,22 @@ def selftest_std_sort(values, offsets):
     lib.lego_selftest_std_sort.argtypes = [ctypes.c_void_p, ctypes.c_void_p, ctypes.c_int, ctypes.c_void_p]
     _check(lib.lego_selftest_std_sort(values.ctypes.data, offsets.ctypes.data, offsets.size - 1, out.ctypes.data), "lego_selftest_std_sort")
     return out
+
+
+def selftest_voxel_grid(clouds, leaf):
+    """clouds: list of float32[n_i, 4] -> list of filtered float32[m_i, 4] (device VoxelGrid, one segment per cloud)."""
+    offsets = np.concatenate([[0], np.cumsum([len(c) for c in clouds])]).astype(np.int32)
+    xyzi = np.ascontiguousarray(np.concatenate(clouds) if len(clouds) else np.zeros((0, 4)), np.float32)
+    out = np.empty((max(int(offsets[-1]), 1), 4), np.float32)
+    counts = np.zeros(len(clouds), np.int32)
+    lib = load()
+    lib.lego_selftest_voxel_grid.argtypes = [ctypes.c_void_p, ctypes.c_void_p, ctypes.c_int, ctypes.c_float, ctypes.c_void_p, ctypes.c_void_p]
+    _check(lib.lego_selftest_voxel_grid(xyzi.ctypes.data, offsets.ctypes.data, len(clouds), leaf, out.ctypes.data, counts.ctypes.data),
+           "lego_selftest_voxel_grid")
+    res, w = [], 0
+    for c in counts:
+        res.append(out[w:w + c].copy()); w += c
+    return res
 
 
 class Pipeline:
@@ -177,4 +193,4 @@ class Pipeline:
 
 
 _FLOAT_NAMES = {"rangeMat", "segRange", "orientation", "cloudCurvature", "transformCur", "transformSum", "slot4val",
-                "matP", "transformTobeMapped", "transformAftMapped", "transformBefMapped"}
+                "matP", "moTransformSum", "transformTobeMapped", "transformAftMapped", "transformBefMapped"}

@@ -59,6 +59,7 @@ Engine::Engine(const lego_params& p, int lanes, int max_points) : params(p) {
     ip.orient = alloc<float>(L * 4); ip.outlier = alloc<float4>(L * c.Ocap); ip.counts = alloc<int>(L * 8);
 
     allocFeatureAssociation();
+    allocMapOptimization();
     cuda_check(cudaStreamSynchronize(stream), "init sync");
 }
 
@@ -71,6 +72,13 @@ Engine::~Engine() {
         if (evCopied[b]) cudaEventDestroy(evCopied[b]);
         if (evConsumed[b]) cudaEventDestroy(evConsumed[b]);
     }
+    if (moPinned) cudaFreeHost(moPinned);
+    if (moRecordsHost) cudaFreeHost(moRecordsHost);
+    for (int b = 0; b < 2; ++b) if (moStaged[b]) cudaEventDestroy(moStaged[b]);
+    if (moRecordsReady) cudaEventDestroy(moRecordsReady);
+    for (auto& pe : profLog) { if (pe.a) cudaEventDestroy(pe.a); if (pe.b) cudaEventDestroy(pe.b); }
+    for (cudaEvent_t e : evPool) cudaEventDestroy(e);
+    for (cudaEvent_t e : timerEv) if (e) cudaEventDestroy(e);
     if (copyStream) cudaStreamDestroy(copyStream);
     if (stream) cudaStreamDestroy(stream);
 }
@@ -169,15 +177,17 @@ void Engine::uploadScan(const float* xyzi, const uint16_t* ring, const int* npts
 void Engine::inputConsumed() { cuda_check(cudaEventRecord(evConsumed[curIn], stream), "event record"); }
 
 void Engine::getPoses(float* poses18, int* flags) {
-    std::vector<float> sum(6 * (size_t)c.L);
+    std::vector<float> sum(6 * (size_t)c.L), aft(6 * (size_t)c.L), bef(6 * (size_t)c.L);
     cuda_check(cudaMemcpyAsync(sum.data(), fa.transformSum, sizeof(float) * 6 * c.L, cudaMemcpyDeviceToHost, stream), "poses");
+    cuda_check(cudaMemcpyAsync(aft.data(), mo.transformAftMapped, sizeof(float) * 6 * c.L, cudaMemcpyDeviceToHost, stream), "poses");
+    cuda_check(cudaMemcpyAsync(bef.data(), mo.transformBefMapped, sizeof(float) * 6 * c.L, cudaMemcpyDeviceToHost, stream), "poses");
     std::vector<int> fl(c.L);
     cuda_check(cudaMemcpyAsync(fl.data(), fa.flags, sizeof(int) * c.L, cudaMemcpyDeviceToHost, stream), "flags");
     cuda_check(cudaStreamSynchronize(stream), "poses sync");
     for (int l = 0; l < c.L; ++l) {
         for (int k = 0; k < 6; ++k) poses18[l * 18 + k] = sum[l * 6 + k];
-        for (int k = 6; k < 18; ++k) poses18[l * 18 + k] = 0.f;
-        if (flags) flags[l] = fl[l];
+        for (int k = 0; k < 6; ++k) { poses18[l * 18 + 6 + k] = aft[l * 6 + k]; poses18[l * 18 + 12 + k] = bef[l * 6 + k]; }
+        if (flags) flags[l] = (fl[l] & 7) | (moActiveLast.size() == (size_t)c.L && moActiveLast[l] ? 8 : 0);
     }
 }
 

@@ -8,6 +8,7 @@
 #include <string>
 #include <vector>
 #include "../../include/lego_b200.h"
+#include "voxel_grid.cuh"
 #include "voxel_hash.cuh"
 
 namespace lego {
@@ -77,6 +78,62 @@ struct FaDev {
     VoxelHash hashCorner, hashSurf;   // 1 m voxel hash over the current "last" clouds (replaces the two kd-trees)
 };
 
+// ---- mapOptimization ----
+// One surrounding key frame of this mapping call, prepared by the host bookkeeping (extractSurroundingKeyFrames,
+// mapOptmization.cpp:1001-1056): where its three down-sampled clouds live in the key-frame pool, where they go in
+// the local map, and the sin/cos/translation of its key pose (updateTransformPointCloudSinCos, mapOptmization.cpp:529-543).
+struct MoKfEntry {
+    int srcC, nC, dstC;       // corner cloud: pool offset, size, offset in laserCloudCornerFromMap
+    int srcS, nS, dstS;       // surf cloud -> laserCloudSurfFromMap
+    int srcO, nO, dstO;       // outlier cloud -> laserCloudSurfFromMap (right behind the surf cloud of the same key frame)
+    float ctRoll, stRoll, ctPitch, stPitch, ctYaw, stYaw, tInX, tInY, tInZ;
+};
+// What saveKeyFramesAndFactor (mapOptmization.cpp:1353-1454) decided on the device, read back asynchronously by the
+// host bookkeeping before the next mapping call.
+struct MoRecord {
+    int ran;                  // the mapping body ran for this lane in this step
+    int saved;                // a key frame was appended
+    int poolOff, nC, nS, nO;  // its clouds in the pool
+    int error;                // capacity overflow bits
+    int iters;                // LM iterations of scan2MapOptimization
+    float robotPos[3];        // currentRobotPosPoint
+    float pose6D[6];          // x, y, z, roll, pitch, yaw of cloudKeyPoses6D
+};
+
+struct MoDev {
+    float* transformSum;       // [L][6]  odometry pose after the message round trip (laserOdometryHandler, mapOptmization.cpp:608-621)
+    float* transformIncre; float* transformTobeMapped; float* transformBefMapped; float* transformAftMapped; float* transformLast;   // [L][6]
+    float* matP;               // [L][36]
+    int* state;                // [L][16] 0 isDegenerate, 1 number of key frames, 2 pool points used, 3 LM iterations, 4 rows of the last iteration, 5 error bits
+    float* prevRobotPos;       // [L][4]  previousRobotPosPoint
+    int* active;               // [L]     host gate decision of this step (mapOptmization.cpp:1489-1499)
+    float4* pool;              // [L][poolCap] corner | surf | outlier cloud of every key frame, sensor frame
+    MoKfEntry* entries;        // [L][maxSel]
+    int* nEntries;             // [L]
+    float4* cornerFromMap; float4* surfFromMap;        // [L][cornerRawCap], [L][surfRawCap]
+    float4* cornerFromMapDS; float4* surfFromMapDS;    // [L][cornerDSCap], [L][surfDSCap]
+    int* mapCounts;            // [L][4]  cornerFromMap, surfFromMap, cornerFromMapDS, surfFromMapDS sizes
+    float4* cornerLastDS; float4* surfLastDS; float4* outlierLastDS; float4* surfTotalLast; float4* surfTotalLastDS;
+    int* scanCounts;           // [L][8]  cornerLastDS, surfLastDS, outlierLastDS, surfTotalLast, surfTotalLastDS sizes
+    VoxelHash hashCornerMap, hashSurfMap;
+    MoRecord* records;         // [L]
+    int poolCap, maxSel, cornerRawCap, surfRawCap, cornerDSCap, surfDSCap, scanCornerCap, scanSurfCap, scanOutlierCap, maxKeyFrames;
+};
+
+// host side of one lane's mapOptimization: the key-frame list and the message gates
+struct MoKeyFrame { float x, y, z, roll, pitch, yaw; int poolOff, nC, nS, nO; };
+struct MoLaneHost {
+    std::vector<MoKeyFrame> keyFrames;                // cloudKeyPoses3D / 6D + where the clouds live
+    std::vector<int> surroundingExistingKeyPosesID;   // mapOptmization.cpp:90
+    float currentRobotPos[3] = {0.f, 0.f, 0.f};       // PointType default = 0 (mapOptmization.cpp:96)
+    double timeLastProcessing = -1.0;                 // mapOptmization.cpp:331
+    bool newCorner = false, newSurf = false, newOutlier = false, newOdometry = false;
+    double timeCorner = 0, timeSurf = 0, timeOutlier = 0, timeOdometry = 0;
+    // FeatureAssociation's publish cadence mirrored on the host (featureAssociation.cpp:284, 314, 1790-1794)
+    bool faInited = false; int faFrameCount = 1;
+    int lastError = 0;
+};
+
 void cuda_check(cudaError_t e, const char* what);
 void set_last_error(const std::string& s);
 
@@ -97,6 +154,15 @@ public:
     void extractFeatures();
     void updateTransformation();
     void integrateTransformationPublishCloudsLast();
+
+    // ---- mapOptimization (names follow mapOptmization.cpp) ----
+    void allocMapOptimization();
+    void mapOptimizationRun(const double* stamps);   // gates + the body of mapOptimization::run for every lane that passes them
+    bool mapOptimizationGates(const double* stamps, std::vector<int>& active);
+    void mapOptimizationBody(const std::vector<int>& active);
+    bool lookupMapOptimization(int lane, const std::string& name, void** ptr, int* elem, long* count);
+    void consumeMapRecords();                        // host bookkeeping of saveKeyFramesAndFactor from the device records
+    void selectSurroundingKeyFrames(int lane, std::vector<MoKfEntry>& out, int* nCorner, int* nSurf);
 
     void sync();
     // ---- timing: CUDA events on the engine's own stream (bench.py cannot see this stream through torch) ----
@@ -130,6 +196,20 @@ public:
     int faBuf = 0;             // which of the double-buffered "last" clouds is current (same for every lane)
     IpDev ip;
     FaDev fa;
+    MoDev mo;
+    std::vector<MoLaneHost> moHost;
+    VgBatch vgMap;             // 2 segments per lane: local corner / surf map
+    VgBatch vgScan[2];         // per value of faBuf, 3 segments per lane: corner / surf / outlier cloud of the current scan
+    VgBatch vgSurfTotal;       // 1 segment per lane
+    char* moPinned = nullptr;  // pinned staging: entries | nEntries | mapCounts | active, double buffered
+    size_t moPinnedStride = 0;
+    int moPinnedSlot = 0;
+    cudaEvent_t moStaged[2] = {nullptr, nullptr};
+    MoRecord* moRecordsHost = nullptr;   // pinned [L]
+    cudaEvent_t moRecordsReady = nullptr;
+    bool moRecordsPending = false;
+    bool moLastAny = false;
+    std::vector<int> moActiveLast;   // per lane: the mapping body ran in the last step
     std::vector<void*> allocations;
     // host mirrors of small per-lane data
     std::vector<int> h_counts;

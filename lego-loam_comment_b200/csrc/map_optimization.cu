@@ -1,0 +1,296 @@
+// mapOptimization scan-to-map as sm_100a kernels (reference LeGO-LOAM/src/mapOptmization.cpp:1487-1522, the body of
+// mapOptimization::run with loop closure off).  blockIdx.y (or blockIdx.x for the per-lane kernels) = lane; lanes whose
+// gates did not open this step (mo.active[lane] == 0) return at once.
+//   mo_begin_kernel        laserOdometryHandler + transformAssociateToMap                      (608-621, 376-461)
+//   mo_assemble_map_kernel extractSurroundingKeyFrames: transform + concatenate key-frame clouds (1041-1056, 545-575)
+//   vg_filter              downSizeFilterCorner/Surf/Outlier on the local map and the current scan (1058-1089)
+//   mo_concat_kernel       laserCloudSurfTotalLast = surfLastDS + outlierLastDS                   (1083-1086)
+//   vh_build               the two kd-tree builds of scan2MapOptimization                         (1333-1334)
+//   mo_scan2map_kernel     <= 10 x {cornerOptimization, surfOptimization, LMOptimization} + transformUpdate, one
+//                          persistent CTA per lane, no host round trip                            (1093-1350)
+//   mo_save_keyframe_kernel saveKeyFramesAndFactor: 0.3 m gate, key pose, clouds into the pool     (1353-1454)
+#include <cfloat>
+#include "engine.h"
+#include "map_kernels.cuh"
+
+namespace lego {
+
+__global__ void mo_begin_kernel(FaDev f, MoDev m, int L) {
+    const int lane = blockIdx.x * blockDim.x + threadIdx.x;
+    if (lane >= L) return;
+    MoRecord& rec = m.records[lane];
+    rec.ran = 0; rec.saved = 0; rec.error = 0; rec.iters = 0;
+    if (!m.active[lane]) return;
+    rec.ran = 1;
+    float S[6], T[6], I[6];
+    odometry_message_round_trip(f.transformSum + lane * 6, S);
+    for (int k = 0; k < 6; ++k) { m.transformSum[lane * 6 + k] = S[k]; T[k] = m.transformTobeMapped[lane * 6 + k]; I[k] = m.transformIncre[lane * 6 + k]; }
+    transform_associate_to_map(S, m.transformBefMapped + lane * 6, m.transformAftMapped + lane * 6, I, T);
+    for (int k = 0; k < 6; ++k) { m.transformTobeMapped[lane * 6 + k] = T[k]; m.transformIncre[lane * 6 + k] = I[k]; }
+}
+
+// One CTA per (entry slice, lane): entry e = one surrounding key frame; its corner cloud goes to laserCloudCornerFromMap,
+// its surf and outlier clouds to laserCloudSurfFromMap, transformed by the key pose (mapOptmization.cpp:1041-1056).
+__global__ void __launch_bounds__(256) mo_assemble_map_kernel(MoDev m) {
+    const int lane = blockIdx.y;
+    if (!m.active[lane]) return;
+    const int nE = m.nEntries[lane];
+    const float4* pool = m.pool + (size_t)lane * m.poolCap;
+    float4* cm = m.cornerFromMap + (size_t)lane * m.cornerRawCap;
+    float4* sm_ = m.surfFromMap + (size_t)lane * m.surfRawCap;
+    for (int e = blockIdx.x; e < nE; e += gridDim.x) {
+        const MoKfEntry en = m.entries[(size_t)lane * m.maxSel + e];
+        MapSinCos t;
+        t.cRoll = en.ctRoll; t.sRoll = en.stRoll; t.cPitch = en.ctPitch; t.sPitch = en.stPitch; t.cYaw = en.ctYaw; t.sYaw = en.stYaw;
+        t.tX = en.tInX; t.tY = en.tInY; t.tZ = en.tInZ;
+        for (int i = threadIdx.x; i < en.nC; i += blockDim.x) cm[en.dstC + i] = map_transform(t, pool[en.srcC + i]);
+        for (int i = threadIdx.x; i < en.nS; i += blockDim.x) sm_[en.dstS + i] = map_transform(t, pool[en.srcS + i]);
+        for (int i = threadIdx.x; i < en.nO; i += blockDim.x) sm_[en.dstO + i] = map_transform(t, pool[en.srcO + i]);
+    }
+}
+
+__global__ void __launch_bounds__(256) mo_concat_kernel(MoDev m, int surfCap, int outlierCap, int totalCap) {
+    const int lane = blockIdx.y;
+    if (!m.active[lane]) return;
+    const int nS = m.scanCounts[lane * 8 + 1], nO = m.scanCounts[lane * 8 + 2];
+    const float4* s = m.surfLastDS + (size_t)lane * surfCap;
+    const float4* o = m.outlierLastDS + (size_t)lane * outlierCap;
+    float4* t = m.surfTotalLast + (size_t)lane * totalCap;
+    for (int i = blockIdx.x * blockDim.x + threadIdx.x; i < nS + nO; i += gridDim.x * blockDim.x) t[i] = i < nS ? s[i] : o[i - nS];
+    if (blockIdx.x == 0 && threadIdx.x == 0) m.scanCounts[lane * 8 + 3] = nS + nO;
+}
+
+struct MoShared {
+    float T[6];
+    float matP[36];
+    int isDegenerate;
+    int done;
+    double red[MO_WARPS][MO_ACC];
+};
+
+__device__ __forceinline__ void mo_accumulate(double* acc, const MapSinCos& sc, float4 o, float cx, float cy, float cz, float cd) {
+    const float srx = sc.sRoll, crx = sc.cRoll, sry = sc.sPitch, cry = sc.cPitch, srz = sc.sYaw, crz = sc.cYaw;
+    const float arx = (crx * sry * srz * o.x + crx * crz * sry * o.y - srx * sry * o.z) * cx
+                    + (-srx * srz * o.x - crz * srx * o.y - crx * o.z) * cy
+                    + (crx * cry * srz * o.x + crx * cry * crz * o.y - cry * srx * o.z) * cz;
+    const float ary = ((cry * srx * srz - crz * sry) * o.x + (sry * srz + cry * crz * srx) * o.y + crx * cry * o.z) * cx
+                    + ((-cry * crz - srx * sry * srz) * o.x + (cry * srz - crz * srx * sry) * o.y - crx * sry * o.z) * cz;
+    const float arz = ((crz * srx * sry - cry * srz) * o.x + (-cry * crz - srx * sry * srz) * o.y) * cx
+                    + (crx * crz * o.x - crx * srz * o.y) * cy
+                    + ((sry * srz + cry * crz * srx) * o.x + (crz * sry - cry * srx * srz) * o.y) * cz;
+    const double A[6] = {(double)arx, (double)ary, (double)arz, (double)cx, (double)cy, (double)cz};
+    const double B = (double)(-cd);
+    int k = 0;
+#pragma unroll
+    for (int i = 0; i < 6; ++i)
+#pragma unroll
+        for (int j = i; j < 6; ++j) acc[k++] += A[i] * A[j];
+#pragma unroll
+    for (int i = 0; i < 6; ++i) acc[21 + i] += A[i] * B;
+    acc[27] += 1.0;
+}
+
+// cornerOptimization for one point (mapOptmization.cpp:1096-1172): returns true and the weighted coefficients when
+// the point yields a residual row.
+__device__ inline bool mo_corner_residual(const VhLane& vh, const float4* __restrict__ map, const MapSinCos& sc, float4 ori, float* cx_, float* cy_, float* cz_, float* cd_) {
+    const float4 ps = map_transform(sc, ori);
+    float d2[5]; int idx[5];
+    const int found = vh_knn5(vh, ps.x, ps.y, ps.z, d2, idx);
+    if (found < 5 || !((double)d2[4] < 1.0)) return false;
+    float px[5], py[5], pz[5];
+    float cx = 0.f, cy = 0.f, cz = 0.f;
+#pragma unroll
+    for (int j = 0; j < 5; ++j) { const float4 q = map[idx[j]]; px[j] = q.x; py[j] = q.y; pz[j] = q.z; cx += q.x; cy += q.y; cz += q.z; }
+    cx /= 5; cy /= 5; cz /= 5;
+    float a11 = 0, a12 = 0, a13 = 0, a22 = 0, a23 = 0, a33 = 0;
+#pragma unroll
+    for (int j = 0; j < 5; ++j) {
+        const float ax = px[j] - cx, ay = py[j] - cy, az = pz[j] - cz;
+        a11 += ax * ax; a12 += ax * ay; a13 += ax * az; a22 += ay * ay; a23 += ay * az; a33 += az * az;
+    }
+    a11 /= 5; a12 /= 5; a13 /= 5; a22 /= 5; a23 /= 5; a33 /= 5;
+    const float A1[9] = {a11, a12, a13, a12, a22, a23, a13, a23, a33};
+    float D1[3], V1[9];
+    sm::eigen_sym<3>(A1, D1, V1);
+    if (!(D1[0] > 3 * D1[1])) return false;
+    const float x0 = ps.x, y0 = ps.y, z0 = ps.z;
+    const float x1 = (float)((double)cx + 0.1 * (double)V1[0]), y1 = (float)((double)cy + 0.1 * (double)V1[1]), z1 = (float)((double)cz + 0.1 * (double)V1[2]);
+    const float x2 = (float)((double)cx - 0.1 * (double)V1[0]), y2 = (float)((double)cy - 0.1 * (double)V1[1]), z2 = (float)((double)cz - 0.1 * (double)V1[2]);
+    const float m11 = (x0 - x1) * (y0 - y2) - (x0 - x2) * (y0 - y1);
+    const float m22 = (x0 - x1) * (z0 - z2) - (x0 - x2) * (z0 - z1);
+    const float m33 = (y0 - y1) * (z0 - z2) - (y0 - y2) * (z0 - z1);
+    const float a012 = sqrtf(m11 * m11 + m22 * m22 + m33 * m33);
+    const float l12 = sqrtf((x1 - x2) * (x1 - x2) + (y1 - y2) * (y1 - y2) + (z1 - z2) * (z1 - z2));
+    const float la = ((y1 - y2) * m11 + (z1 - z2) * m22) / a012 / l12;
+    const float lb = -((x1 - x2) * m11 - (z1 - z2) * m33) / a012 / l12;
+    const float lc = -((x1 - x2) * m22 + (y1 - y2) * m33) / a012 / l12;
+    const float ld2 = a012 / l12;
+    const float s = (float)(1.0 - 0.9 * (double)fabsf(ld2));
+    if (!((double)s > 0.1)) return false;
+    *cx_ = s * la; *cy_ = s * lb; *cz_ = s * lc; *cd_ = s * ld2;
+    return true;
+}
+
+// surfOptimization for one point (mapOptmization.cpp:1179-1225)
+__device__ inline bool mo_surf_residual(const VhLane& vh, const float4* __restrict__ map, const MapSinCos& sc, float4 ori, float* cx_, float* cy_, float* cz_, float* cd_) {
+    const float4 ps = map_transform(sc, ori);
+    float d2[5]; int idx[5];
+    const int found = vh_knn5(vh, ps.x, ps.y, ps.z, d2, idx);
+    if (found < 5 || !((double)d2[4] < 1.0)) return false;
+    float A0[15];
+#pragma unroll
+    for (int j = 0; j < 5; ++j) { const float4 q = map[idx[j]]; A0[j * 3] = q.x; A0[j * 3 + 1] = q.y; A0[j * 3 + 2] = q.z; }
+    const float B0[5] = {-1.f, -1.f, -1.f, -1.f, -1.f};
+    float X0[3];
+    sm::solve_qr<5, 3>(A0, B0, X0);
+    float pa = X0[0], pb = X0[1], pc = X0[2], pd = 1.f;
+    const float ps_ = sqrtf(pa * pa + pb * pb + pc * pc);
+    pa /= ps_; pb /= ps_; pc /= ps_; pd /= ps_;
+#pragma unroll
+    for (int j = 0; j < 5; ++j)
+        if ((double)fabsf(pa * A0[j * 3] + pb * A0[j * 3 + 1] + pc * A0[j * 3 + 2] + pd) > 0.2) return false;
+    const float pd2 = pa * ps.x + pb * ps.y + pc * ps.z + pd;
+    const float s = (float)(1.0 - 0.9 * (double)fabsf(pd2) / (double)sqrtf(sqrtf(ps.x * ps.x + ps.y * ps.y + ps.z * ps.z)));
+    if (!((double)s > 0.1)) return false;
+    *cx_ = s * pa; *cy_ = s * pb; *cz_ = s * pc; *cd_ = s * pd2;
+    return true;
+}
+
+// scan2MapOptimization (mapOptmization.cpp:1329-1350): one persistent CTA per lane.
+__global__ void __launch_bounds__(MO_THREADS) mo_scan2map_kernel(MoDev m) {
+    __shared__ MoShared sh;
+    const int lane = blockIdx.x, tid = threadIdx.x, lid = tid & 31, warp = tid >> 5;
+    if (!m.active[lane]) return;
+    const int nCornerMap = m.mapCounts[lane * 4 + 2], nSurfMap = m.mapCounts[lane * 4 + 3];
+    if (!(nCornerMap > 10 && nSurfMap > 100)) return;
+    const int nCorner = m.scanCounts[lane * 8 + 0], nSurf = m.scanCounts[lane * 8 + 4];
+    if (tid < 6) sh.T[tid] = m.transformTobeMapped[lane * 6 + tid];
+    if (tid < 36) sh.matP[tid] = m.matP[lane * 36 + tid];
+    if (tid == 0) { sh.isDegenerate = m.state[lane * 16 + 0]; sh.done = 0; }
+    __syncthreads();
+    const VhLane vhC = vh_lane(m.hashCornerMap, lane), vhS = vh_lane(m.hashSurfMap, lane);
+    const float4* cornerMap = m.cornerFromMapDS + (size_t)lane * m.cornerDSCap;
+    const float4* surfMap = m.surfFromMapDS + (size_t)lane * m.surfDSCap;
+    const float4* corner = m.cornerLastDS + (size_t)lane * m.scanCornerCap;
+    const float4* surf = m.surfTotalLastDS + (size_t)lane * (m.scanSurfCap + m.scanOutlierCap);
+    int iters = 0, rows = 0;
+    for (int iter = 0; iter < 10; ++iter) {
+        iters = iter + 1;
+        const MapSinCos sc = map_sincos(sh.T);
+        double acc[MO_ACC];
+#pragma unroll
+        for (int k = 0; k < MO_ACC; ++k) acc[k] = 0.0;
+        for (int q = tid; q < nCorner + nSurf; q += MO_THREADS) {
+            float cx, cy, cz, cd; bool ok; float4 o;
+            if (q < nCorner) { o = corner[q]; ok = mo_corner_residual(vhC, cornerMap, sc, o, &cx, &cy, &cz, &cd); }
+            else { o = surf[q - nCorner]; ok = mo_surf_residual(vhS, surfMap, sc, o, &cx, &cy, &cz, &cd); }
+            if (ok) mo_accumulate(acc, sc, o, cx, cy, cz, cd);
+        }
+#pragma unroll
+        for (int k = 0; k < MO_ACC; ++k) { const double v = warp_sum_d(acc[k]); if (lid == 0) sh.red[warp][k] = v; }
+        __syncthreads();
+        if (tid == 0) {
+            double s[MO_ACC];
+            for (int k = 0; k < MO_ACC; ++k) { s[k] = 0.0; for (int w = 0; w < MO_WARPS; ++w) s[k] += sh.red[w][k]; }
+            rows = (int)s[27];
+            int done = 0;
+            if (rows < 50) {
+                done = 1;   // LMOptimization returns false without touching the pose: every further iteration would repeat this one
+            } else {
+                float AtA[36], AtB[6], X[6];
+                int k = 0;
+                for (int i = 0; i < 6; ++i) for (int j = i; j < 6; ++j) { AtA[i * 6 + j] = (float)s[k]; AtA[j * 6 + i] = (float)s[k]; ++k; }
+                for (int i = 0; i < 6; ++i) AtB[i] = (float)s[21 + i];
+                sm::solve_qr<6, 6>(AtA, AtB, X);
+                if (iter == 0) sh.isDegenerate = sm::degeneracy_projector<6>(AtA, 100.f, sh.matP) ? 1 : 0;
+                if (sh.isDegenerate) {
+                    float X2[6];
+                    for (int i = 0; i < 6; ++i) { double t = 0.0; for (int j = 0; j < 6; ++j) t += (double)sh.matP[i * 6 + j] * (double)X[j]; X2[i] = (float)t; }
+                    for (int i = 0; i < 6; ++i) X[i] = X2[i];
+                }
+                for (int i = 0; i < 6; ++i) sh.T[i] += X[i];
+                const float r2d = 57.29577951308232f;   // pcl::rad2deg(float)
+                double dr = 0.0, dt = 0.0;
+                for (int i = 0; i < 3; ++i) { const double a = (double)(X[i] * r2d), b = (double)(X[3 + i] * 100); dr += a * a; dt += b * b; }
+                const float deltaR = (float)sqrt(dr), deltaT = (float)sqrt(dt);
+                if ((double)deltaR < 0.05 && (double)deltaT < 0.05) done = 1;
+            }
+            sh.done = done;
+        }
+        __syncthreads();
+        if (sh.done) break;
+    }
+    // transformUpdate without IMU (mapOptmization.cpp:463-496)
+    if (tid < 6) {
+        m.transformTobeMapped[lane * 6 + tid] = sh.T[tid];
+        m.transformBefMapped[lane * 6 + tid] = m.transformSum[lane * 6 + tid];
+        m.transformAftMapped[lane * 6 + tid] = sh.T[tid];
+    }
+    if (tid < 36) m.matP[lane * 36 + tid] = sh.matP[tid];
+    if (tid == 0) { m.state[lane * 16 + 0] = sh.isDegenerate; m.state[lane * 16 + 3] = iters; m.state[lane * 16 + 4] = rows; m.records[lane].iters = iters; }
+}
+
+// Rot3::RzRyRx(x, y, z) then .roll() / .pitch() / .yaw() (the GTSAM calls of mapOptmization.cpp:1376-1440), in double.
+__device__ inline void rzryrx_round_trip(double x, double y, double z, double* roll, double* pitch, double* yaw) {
+    const double cx = cos(x), sx = sin(x), cy = cos(y), sy = sin(y), cz = cos(z), sz = sin(z);
+    const double r00 = cz * cy, r10 = sz * cy, r20 = -sy, r21 = cy * sx, r22 = cy * cx;
+    *roll = atan2(r21, r22);
+    *pitch = atan2(-r20, sqrt(r21 * r21 + r22 * r22));
+    *yaw = atan2(r10, r00);
+}
+
+// saveKeyFramesAndFactor (mapOptmization.cpp:1353-1454) with a chain-only pose graph: without loop closures the iSAM2
+// estimate of the newest pose is the value that was inserted, so the update reduces to the Rot3 round trip.
+__global__ void __launch_bounds__(256) mo_save_keyframe_kernel(MoDev m) {
+    const int lane = blockIdx.x, tid = threadIdx.x;
+    if (!m.active[lane]) return;
+    __shared__ int s_save, s_off, s_err;
+    MoRecord& rec = m.records[lane];
+    const int nC = m.scanCounts[lane * 8 + 0], nS = m.scanCounts[lane * 8 + 1], nO = m.scanCounts[lane * 8 + 2];
+    if (tid == 0) {
+        float* Aft = m.transformAftMapped + lane * 6; float* T = m.transformTobeMapped + lane * 6; float* Last = m.transformLast + lane * 6;
+        float* prev = m.prevRobotPos + lane * 4;
+        const float cx = Aft[3], cy = Aft[4], cz = Aft[5];
+        rec.robotPos[0] = cx; rec.robotPos[1] = cy; rec.robotPos[2] = cz;
+        const int nKF = m.state[lane * 16 + 1];
+        const float dist = sqrtf((prev[0] - cx) * (prev[0] - cx) + (prev[1] - cy) * (prev[1] - cy) + (prev[2] - cz) * (prev[2] - cz));
+        bool save = !((double)dist < 0.3);
+        int err = 0;
+        if (!save && nKF > 0) { s_save = 0; }
+        else {
+            const int used = m.state[lane * 16 + 2];
+            if (nKF >= m.maxKeyFrames || used + nC + nS + nO > m.poolCap) { err = 1; s_save = 0; }
+            else {
+                prev[0] = cx; prev[1] = cy; prev[2] = cz;
+                const float* P = nKF == 0 ? T : Aft;   // first key frame is built from transformTobeMapped (1375-1382)
+                if (nKF == 0) for (int i = 0; i < 6; ++i) Last[i] = T[i];
+                double roll, pitch, yaw;
+                rzryrx_round_trip((double)P[2], (double)P[0], (double)P[1], &roll, &pitch, &yaw);
+                const float kx = P[3], ky = P[4], kz = P[5];   // translation (z, x, y) -> thisPose3D (y, z, x) of it
+                const float kroll = (float)pitch, kpitch = (float)yaw, kyaw = (float)roll;
+                rec.pose6D[0] = kx; rec.pose6D[1] = ky; rec.pose6D[2] = kz; rec.pose6D[3] = kroll; rec.pose6D[4] = kpitch; rec.pose6D[5] = kyaw;
+                if (nKF + 1 > 1) {
+                    Aft[0] = kroll; Aft[1] = kpitch; Aft[2] = kyaw; Aft[3] = kx; Aft[4] = ky; Aft[5] = kz;
+                    for (int i = 0; i < 6; ++i) { Last[i] = Aft[i]; T[i] = Aft[i]; }
+                }
+                m.state[lane * 16 + 1] = nKF + 1;
+                m.state[lane * 16 + 2] = used + nC + nS + nO;
+                s_save = 1; s_off = used;
+                rec.saved = 1; rec.poolOff = used; rec.nC = nC; rec.nS = nS; rec.nO = nO;
+            }
+        }
+        s_err = err;
+        if (err) { m.state[lane * 16 + 5] |= err; rec.error |= err; }
+    }
+    __syncthreads();
+    if (!s_save) return;
+    float4* dst = m.pool + (size_t)lane * m.poolCap + s_off;
+    const float4* c = m.cornerLastDS + (size_t)lane * m.scanCornerCap;
+    const float4* s = m.surfLastDS + (size_t)lane * m.scanSurfCap;
+    const float4* o = m.outlierLastDS + (size_t)lane * m.scanOutlierCap;
+    for (int i = tid; i < nC; i += blockDim.x) dst[i] = c[i];
+    for (int i = tid; i < nS; i += blockDim.x) dst[nC + i] = s[i];
+    for (int i = tid; i < nO; i += blockDim.x) dst[nC + nS + i] = o[i];
+}
+
+}  // namespace lego

@@ -52,7 +52,7 @@ bool Engine::lookupOdometry(int lane, const std::string& n, void** ptr, int* ele
     if (n == "laserCloudCornerLast") return set(fa.cornerLast[faBuf] + l * R * 120, 16, cnt_of(fa.lastCounts, 4, 0));
     if (n == "laserCloudSurfLast") return set(fa.surfLast[faBuf] + l * N, 16, cnt_of(fa.lastCounts, 4, 1));
     if (n == "outlierCloudLast") return set(fa.outlierLast + l * c.Ocap, 16, cnt_of(ip.counts, 8, 1));
-    return false;
+    return lookupMapOptimization(lane, n, ptr, elem, count);
 }
 
 // ------------------------------------------------------------------------------------------------------------

@@ -1,9 +1,12 @@
 // Device self-tests exported through the C ABI so the parity suite can check the two building blocks whose
 // bit-exactness everything else rests on, directly on the GPU: the glibc atan2f model and the std::sort replay.
+#include <algorithm>
+#include <cstring>
 #include <vector>
 #include "engine.h"
 #include "parity_math.cuh"
 #include "std_sort_replay.cuh"
+#include "voxel_grid.cuh"
 
 namespace lego {
 
@@ -48,6 +51,49 @@ int lego_selftest_std_sort(const float* values, const int* offsets, int nseg, in
         lego::cuda_check(cudaMemcpy(h.data(), d, sizeof(ssr::Item) * total, cudaMemcpyDeviceToHost), "selftest copy");
         cudaFree(d); cudaFree(doff);
         for (int i = 0; i < total; ++i) inds_out[i] = h[i].ind;
+        return LEGO_OK;
+    } catch (...) { return LEGO_ERR_CUDA; }
+}
+
+// Batched VoxelGrid on nseg independent clouds (offsets has nseg+1 entries, in points): out gets the filtered
+// clouds back to back in segment order, out_counts[s] their sizes.
+int lego_selftest_voxel_grid(const float* xyzi, const int* offsets, int nseg, float leaf, float* out, int* out_counts) {
+    try {
+        using lego::VgSeg;
+        const int total = offsets[nseg];
+        int maxCap = 1;
+        for (int s = 0; s < nseg; ++s) maxCap = std::max(maxCap, offsets[s + 1] - offsets[s]);
+        lego::VgBatch b; b.nSeg = nseg; b.maxBlocks = (maxCap + lego::VG_TILE - 1) / lego::VG_TILE;
+        float4 *din, *dout; int *dn, *dno, *dhist, *dheads, *dstate; unsigned* dscratch;
+        const size_t tot = (size_t)std::max(total, 1);
+        lego::cuda_check(cudaMalloc(&din, tot * 16), "malloc"); lego::cuda_check(cudaMalloc(&dout, tot * 16), "malloc");
+        lego::cuda_check(cudaMalloc(&dn, nseg * 4), "malloc"); lego::cuda_check(cudaMalloc(&dno, nseg * 4), "malloc");
+        lego::cuda_check(cudaMalloc(&dhist, (size_t)nseg * 256 * b.maxBlocks * 4), "malloc");
+        lego::cuda_check(cudaMalloc(&dheads, (size_t)nseg * b.maxBlocks * 4), "malloc");
+        lego::cuda_check(cudaMalloc(&dstate, (size_t)nseg * 16 * 4), "malloc");
+        lego::cuda_check(cudaMalloc(&dscratch, tot * 4 * 4), "malloc");
+        lego::cuda_check(cudaMalloc(&b.segs, sizeof(VgSeg) * nseg), "malloc");
+        std::vector<VgSeg> segs(nseg); std::vector<int> n(nseg);
+        for (int s = 0; s < nseg; ++s) {
+            VgSeg& g = segs[s];
+            n[s] = offsets[s + 1] - offsets[s];
+            g.in = din + offsets[s]; g.nIn = dn + s; g.out = dout + offsets[s]; g.nOut = dno + s; g.active = nullptr;
+            g.leaf = leaf; g.cap = n[s]; g.outCap = n[s];
+            g.keys[0] = dscratch + offsets[s]; g.keys[1] = dscratch + tot + offsets[s];
+            g.vals[0] = dscratch + 2 * tot + offsets[s]; g.vals[1] = dscratch + 3 * tot + offsets[s];
+            g.blockHist = dhist + (size_t)s * 256 * b.maxBlocks; g.blockHeads = dheads + (size_t)s * b.maxBlocks; g.state = dstate + s * 16;
+        }
+        cudaMemcpy(din, xyzi, (size_t)total * 16, cudaMemcpyHostToDevice);
+        cudaMemcpy(dn, n.data(), nseg * 4, cudaMemcpyHostToDevice);
+        cudaMemcpy(b.segs, segs.data(), sizeof(VgSeg) * nseg, cudaMemcpyHostToDevice);
+        lego::vg_filter(b, 0);
+        lego::cuda_check(cudaDeviceSynchronize(), "voxel grid selftest");
+        lego::cuda_check(cudaMemcpy(out_counts, dno, nseg * 4, cudaMemcpyDeviceToHost), "selftest copy");
+        std::vector<float> tmp((size_t)tot * 4);
+        cudaMemcpy(tmp.data(), dout, (size_t)total * 16, cudaMemcpyDeviceToHost);
+        size_t w = 0;
+        for (int s = 0; s < nseg; ++s) { std::memcpy(out + w * 4, tmp.data() + (size_t)offsets[s] * 4, (size_t)out_counts[s] * 16); w += out_counts[s]; }
+        cudaFree(din); cudaFree(dout); cudaFree(dn); cudaFree(dno); cudaFree(dhist); cudaFree(dheads); cudaFree(dstate); cudaFree(dscratch); cudaFree(b.segs);
         return LEGO_OK;
     } catch (...) { return LEGO_ERR_CUDA; }
 }

@@ -94,3 +94,40 @@ class RefPipeline:
         scans, mo = ctypes.c_long(0), ctypes.c_long(0)
         self.lib.ref_get_timers(self.h, ms.ctypes.data, ctypes.byref(scans), ctypes.byref(mo))
         return {self.lib.ref_timer_name(i).decode(): ms[i] for i in range(n)}, scans.value, mo.value
+
+
+# ---------------------------------------------------------------- third-party restatements (oracle/port.cpp)
+_port = None
+
+
+def port():
+    """oracle/_build/liblego_oracle.so (built by `make -C oracle port`; needs no /root/reference)."""
+    global _port
+    if _port is None:
+        so = os.path.join(HERE, "_build", "liblego_oracle.so")
+        if not os.path.exists(so):
+            import subprocess
+            subprocess.check_call(["make", "-s", "-C", HERE, "port"])
+        lib = ctypes.CDLL(so)
+        lib.oracle_voxel_grid.restype = ctypes.c_long
+        lib.oracle_voxel_grid.argtypes = [ctypes.c_void_p, ctypes.c_long, ctypes.c_float, ctypes.c_void_p, ctypes.c_long]
+        lib.oracle_knn.argtypes = [ctypes.c_void_p, ctypes.c_long, ctypes.c_void_p, ctypes.c_long, ctypes.c_int, ctypes.c_void_p, ctypes.c_void_p]
+        lib.oracle_solve_qr.argtypes = [ctypes.c_void_p, ctypes.c_void_p, ctypes.c_void_p, ctypes.c_int, ctypes.c_int]
+        lib.oracle_eigen_sym.argtypes = [ctypes.c_void_p, ctypes.c_void_p, ctypes.c_void_p, ctypes.c_int]
+        _port = lib
+    return _port
+
+
+def voxel_grid(xyzi, leaf):
+    xyzi = np.ascontiguousarray(xyzi, np.float32).reshape(-1, 4)
+    out = np.empty((max(len(xyzi), 1), 4), np.float32)
+    m = port().oracle_voxel_grid(xyzi.ctypes.data, len(xyzi), leaf, out.ctypes.data, len(out))
+    return out[:m].copy()
+
+
+def knn(pts, queries, k):
+    pts = np.ascontiguousarray(pts, np.float32).reshape(-1, 4)
+    queries = np.ascontiguousarray(queries, np.float32).reshape(-1, 4)
+    idx = np.empty((len(queries), k), np.int32); d2 = np.empty((len(queries), k), np.float32)
+    port().oracle_knn(pts.ctypes.data, len(pts), queries.ctypes.data, len(queries), k, idx.ctypes.data, d2.ctypes.data)
+    return idx, d2
