@@ -167,6 +167,26 @@ def gather_counts(pl, params, lanes):
         odo += ((it_s + 4) // 5) * (24 * int(fc[2]) + 16 * int(lc[1])) + it_s * 96 * int(fc[2])
         odo += ((it_c + 4) // 5) * (24 * int(fc[0]) + 16 * int(lc[0])) + it_c * 96 * int(fc[0])
     c["odo_bytes"] = odo
+    # mapOptimization (counts of the last mapping call of every lane; K13..K18 of SURVEY.md 8d)
+    mc = np.zeros(4, np.int64); sc = np.zeros(8, np.int64); s2m = 0
+    for l in range(lanes):
+        m_, s_, st = pl.download("mapCounts", l), pl.download("scanCounts", l), pl.download("moState", l)
+        mc += m_; sc += s_
+        s2m += int(st[3]) * (128 * (int(s_[0]) + int(s_[4])) + 32 * int(st[4]))
+    c["mo_bytes"] = {
+        "mo_begin_kernel": 200 * lanes,
+        "mo_assemble_map_kernel": 32 * int(mc[0] + mc[1]),
+        "vg_filter(localMap)": 16 * int(mc.sum()),
+        "vg_filter(currentScan)": 16 * (c["Fl"] + c["Flf"] + c["O"] + int(sc[0] + sc[1] + sc[2])),
+        "mo_concat_kernel": 32 * int(sc[3]),
+        "vg_filter(surfTotal)": 16 * int(sc[3] + sc[4]),
+        "vh_build(cornerMap)": 36 * int(mc[2]),
+        "vh_build(surfMap)": 36 * int(mc[3]),
+        "mo_scan2map_kernel": s2m,
+        "mo_save_keyframe_kernel": 32 * int(sc[0] + sc[1] + sc[2]),
+    }
+    c["map"] = {"cornerFromMap": int(mc[0]), "surfFromMap": int(mc[1]), "cornerFromMapDS": int(mc[2]), "surfFromMapDS": int(mc[3]),
+                "cornerLastDS": int(sc[0]), "surfLastDS": int(sc[1]), "outlierLastDS": int(sc[2]), "surfTotalLastDS": int(sc[4])}
     return c
 
 
@@ -409,7 +429,7 @@ def main():
             json.dump({"per_kernel_ms_over_timed_steps": {k: {"ms": v[0], "launches": v[1],
                                                              "algorithmic_bytes_per_launch": algorithmic_bytes(k, r["counts"])}
                                                          for k, v in r["prof"].items()},
-                       "counts": {k: v for k, v in r["counts"].items() if not isinstance(v, dict)}, "line": line}, f, indent=1)
+                       "counts": {k: v for k, v in r["counts"].items() if k != "mo_bytes"}, "line": line}, f, indent=1)
     print(json.dumps(line))
 
 

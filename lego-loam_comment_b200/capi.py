@@ -194,3 +194,95 @@ class Pipeline:
 
 _FLOAT_NAMES = {"rangeMat", "segRange", "orientation", "cloudCurvature", "transformCur", "transformSum", "slot4val",
                 "matP", "moTransformSum", "transformTobeMapped", "transformAftMapped", "transformBefMapped"}
+
+
+# ---------------------------------------------------------------------------------------------- per-stage handles
+class CloudView(ctypes.Structure):
+    _fields_ = [("dev", ctypes.c_void_p), ("host", ctypes.c_void_p), ("count", ctypes.c_int)]
+
+    def numpy(self):
+        if not self.count:
+            return np.zeros((0, 4), np.float32)
+        return np.ctypeslib.as_array(ctypes.cast(self.host, ctypes.POINTER(ctypes.c_float)), (self.count, 4)).copy()
+
+
+class CloudInfoView(ctypes.Structure):
+    """cloud_msgs/cloud_info (cloud_msgs/msg/cloud_info.msg:1-11)"""
+    _fields_ = [("startRingIndex", ctypes.c_void_p), ("endRingIndex", ctypes.c_void_p),
+                ("startOrientation", ctypes.c_float), ("endOrientation", ctypes.c_float), ("orientationDiff", ctypes.c_float),
+                ("segmentedCloudGroundFlag", ctypes.c_void_p), ("segmentedCloudColInd", ctypes.c_void_p),
+                ("segmentedCloudRange", ctypes.c_void_p), ("count", ctypes.c_int), ("on_device", ctypes.c_int)]
+
+
+class FaOutputs(ctypes.Structure):
+    _fields_ = [("cornerPointsSharp", CloudView), ("cornerPointsLessSharp", CloudView), ("surfPointsFlat", CloudView),
+                ("surfPointsLessFlat", CloudView), ("laserCloudCornerLast", CloudView), ("laserCloudSurfLast", CloudView),
+                ("outlierCloudLast", CloudView), ("odometry_valid", ctypes.c_int), ("published", ctypes.c_int),
+                ("transformCur", ctypes.c_float * 6)]
+
+
+class _Stage:
+    _prefix = ""
+
+    def __init__(self, params):
+        self.lib = load()
+        self.h = ctypes.c_void_p()
+        create = getattr(self.lib, self._prefix + "_create")
+        create.argtypes = [ctypes.POINTER(LegoParams), ctypes.POINTER(ctypes.c_void_p)]
+        _check(create(ctypes.byref(params), ctypes.byref(self.h)), self._prefix + "_create")
+
+    def close(self):
+        if getattr(self, "h", None):
+            d = getattr(self.lib, self._prefix + "_destroy")
+            d.argtypes = [ctypes.c_void_p]
+            d(self.h)
+            self.h = None
+
+    __del__ = close
+
+
+class ImageProjection(_Stage):
+    """lego_ip_* : drop-in for ImageProjection::cloudHandler (imageProjection.cpp:181-197)."""
+    _prefix = "lego_ip"
+
+    def process(self, xyzi, ring, stamp, is_dense=True):
+        xyzi = np.ascontiguousarray(xyzi, np.float32)
+        ring = None if ring is None else np.ascontiguousarray(ring, np.uint16)
+        info, seg, outl = CloudInfoView(), CloudView(), CloudView()
+        f = self.lib.lego_ip_process
+        f.argtypes = [ctypes.c_void_p, ctypes.c_void_p, ctypes.c_void_p, ctypes.c_int, ctypes.c_int, ctypes.c_double,
+                      ctypes.POINTER(CloudInfoView), ctypes.POINTER(CloudView), ctypes.POINTER(CloudView)]
+        rc = f(self.h, xyzi.ctypes.data, None if ring is None else ring.ctypes.data, len(xyzi), 1 if is_dense else 0, stamp,
+               ctypes.byref(info), ctypes.byref(seg), ctypes.byref(outl))
+        _check(rc, "lego_ip_process")
+        return info, seg, outl
+
+
+class FeatureAssociation(_Stage):
+    """lego_fa_* : drop-in for FeatureAssociation::runFeatureAssociation (featureAssociation.cpp:1817-1860)."""
+    _prefix = "lego_fa"
+
+    def process(self, info, seg, outl, stamp):
+        out = FaOutputs()
+        ts = (ctypes.c_float * 6)()
+        f = self.lib.lego_fa_process
+        f.argtypes = [ctypes.c_void_p, ctypes.POINTER(CloudInfoView), ctypes.POINTER(CloudView), ctypes.POINTER(CloudView),
+                      ctypes.c_double, ctypes.c_void_p, ctypes.POINTER(FaOutputs)]
+        _check(f(self.h, ctypes.byref(info), ctypes.byref(seg), ctypes.byref(outl), stamp, ts, ctypes.byref(out)), "lego_fa_process")
+        return np.array(ts[:], np.float32), out
+
+
+class MapOptimization(_Stage):
+    """lego_mo_* : drop-in for mapOptimization::run (mapOptmization.cpp:1487-1522)."""
+    _prefix = "lego_mo"
+
+    def process(self, corner_last, surf_last, outlier_last, transform_sum, stamp):
+        aft, bef = (ctypes.c_float * 6)(), (ctypes.c_float * 6)()
+        done = ctypes.c_int(0)
+        ts = np.ascontiguousarray(transform_sum, np.float32)
+        f = self.lib.lego_mo_process
+        f.argtypes = [ctypes.c_void_p, ctypes.POINTER(CloudView), ctypes.POINTER(CloudView), ctypes.POINTER(CloudView), ctypes.c_void_p,
+                      ctypes.c_double, ctypes.c_void_p, ctypes.c_void_p, ctypes.POINTER(ctypes.c_int)]
+        _check(f(self.h, ctypes.byref(corner_last), ctypes.byref(surf_last), ctypes.byref(outlier_last), ts.ctypes.data, stamp, aft, bef,
+                 ctypes.byref(done)), "lego_mo_process")
+        return np.array(aft[:], np.float32), np.array(bef[:], np.float32), bool(done.value)
