@@ -182,7 +182,7 @@ def gather_counts(pl, params, lanes):
         "vg_filter(surfTotal)": 16 * int(sc[3] + sc[4]),
         "vh_build(cornerMap)": 36 * int(mc[2]),
         "vh_build(surfMap)": 36 * int(mc[3]),
-        "mo_scan2map_kernel": s2m,
+        "mo_scan2map(lm loop)": s2m,
         "mo_save_keyframe_kernel": 32 * int(sc[0] + sc[1] + sc[2]),
     }
     c["map"] = {"cornerFromMap": int(mc[0]), "surfFromMap": int(mc[1]), "cornerFromMapDS": int(mc[2]), "surfFromMapDS": int(mc[3]),

@@ -15,7 +15,9 @@ namespace lego {
 __global__ void mo_begin_kernel(FaDev f, MoDev m, int L);
 __global__ void mo_assemble_map_kernel(MoDev m);
 __global__ void mo_concat_kernel(MoDev m, int surfCap, int outlierCap, int totalCap);
-__global__ void mo_scan2map_kernel(MoDev m);
+__global__ void mo_lm_begin_kernel(MoDev m, int L);
+__global__ void mo_residual_kernel(MoDev m);
+__global__ void mo_solve_kernel(MoDev m, int iter);
 __global__ void mo_save_keyframe_kernel(MoDev m);
 
 static int env_int(const char* name, int dflt) {
@@ -47,6 +49,8 @@ void Engine::allocMapOptimization() {
     mo.scanCounts = alloc<int>(L * 8);
     mo.hashCornerMap = allocHash(mo.cornerDSCap, 1.0f); mo.hashSurfMap = allocHash(mo.surfDSCap, 1.0f);
     mo.records = alloc<MoRecord>(L);
+    mo.resBlocks = (mo.scanCornerCap + mo.scanSurfCap + mo.scanOutlierCap + 255) / 256;
+    mo.partials = alloc<double>(L * mo.resBlocks * 28);
     moHost.assign(c.L, MoLaneHost());
 
     // ---- VoxelGrid segment tables ----
@@ -320,9 +324,18 @@ void Engine::mapOptimizationBody(const std::vector<int>& active) {
     { ProfScope ps(this, "vg_filter(surfTotal)"); launches += vg_filter(vgSurfTotal, stream); }
     { ProfScope ps(this, "vh_build(cornerMap)"); launches += vh_build(mo.hashCornerMap, c.L, mo.cornerFromMapDS, (size_t)mo.cornerDSCap, mo.mapCounts + 2, 4, stream); }
     { ProfScope ps(this, "vh_build(surfMap)"); launches += vh_build(mo.hashSurfMap, c.L, mo.surfFromMapDS, (size_t)mo.surfDSCap, mo.mapCounts + 3, 4, stream); }
-    { ProfScope ps(this, "mo_scan2map_kernel"); mo_scan2map_kernel<<<c.L, 512, 0, stream>>>(mo); }
+    {
+        ProfScope ps(this, "mo_scan2map(lm loop)");
+        mo_lm_begin_kernel<<<(c.L + 63) / 64, 64, 0, stream>>>(mo, c.L);
+        dim3 g(mo.resBlocks, c.L);
+        for (int iter = 0; iter < 10; ++iter) {
+            mo_residual_kernel<<<g, 256, 0, stream>>>(mo);
+            mo_solve_kernel<<<c.L, 32, 0, stream>>>(mo, iter);
+        }
+        launches += 21;
+    }
     { ProfScope ps(this, "mo_save_keyframe_kernel"); mo_save_keyframe_kernel<<<c.L, 256, 0, stream>>>(mo); }
-    launches += 4;
+    launches += 3;
     cuda_check(cudaMemcpyAsync(moRecordsHost, mo.records, sizeof(MoRecord) * c.L, cudaMemcpyDeviceToHost, stream), "records");
     cuda_check(cudaEventRecord(moRecordsReady, stream), "event record");
     moRecordsPending = true;

@@ -6,8 +6,8 @@
 //   vg_filter              downSizeFilterCorner/Surf/Outlier on the local map and the current scan (1058-1089)
 //   mo_concat_kernel       laserCloudSurfTotalLast = surfLastDS + outlierLastDS                   (1083-1086)
 //   vh_build               the two kd-tree builds of scan2MapOptimization                         (1333-1334)
-//   mo_scan2map_kernel     <= 10 x {cornerOptimization, surfOptimization, LMOptimization} + transformUpdate, one
-//                          persistent CTA per lane, no host round trip                            (1093-1350)
+//   mo_residual_kernel /   <= 10 x {cornerOptimization + surfOptimization rows over the whole GPU, LMOptimization in one
+//   mo_solve_kernel        warp per lane}, convergence decided on the device, then transformUpdate   (1093-1350, 463-496)
 //   mo_save_keyframe_kernel saveKeyFramesAndFactor: 0.3 m gate, key pose, clouds into the pool     (1353-1454)
 #include <cfloat>
 #include "engine.h"
@@ -59,14 +59,6 @@ __global__ void __launch_bounds__(256) mo_concat_kernel(MoDev m, int surfCap, in
     for (int i = blockIdx.x * blockDim.x + threadIdx.x; i < nS + nO; i += gridDim.x * blockDim.x) t[i] = i < nS ? s[i] : o[i - nS];
     if (blockIdx.x == 0 && threadIdx.x == 0) m.scanCounts[lane * 8 + 3] = nS + nO;
 }
-
-struct MoShared {
-    float T[6];
-    float matP[36];
-    int isDegenerate;
-    int done;
-    double red[MO_WARPS][MO_ACC];
-};
 
 __device__ __forceinline__ void mo_accumulate(double* acc, const MapSinCos& sc, float4 o, float cx, float cy, float cz, float cd) {
     const float srx = sc.sRoll, crx = sc.cRoll, sry = sc.sPitch, cry = sc.cPitch, srz = sc.sYaw, crz = sc.cYaw;
@@ -156,78 +148,103 @@ __device__ inline bool mo_surf_residual(const VhLane& vh, const float4* __restri
     return true;
 }
 
-// scan2MapOptimization (mapOptmization.cpp:1329-1350): one persistent CTA per lane.
-__global__ void __launch_bounds__(MO_THREADS) mo_scan2map_kernel(MoDev m) {
-    __shared__ MoShared sh;
-    const int lane = blockIdx.x, tid = threadIdx.x, lid = tid & 31, warp = tid >> 5;
-    if (!m.active[lane]) return;
-    const int nCornerMap = m.mapCounts[lane * 4 + 2], nSurfMap = m.mapCounts[lane * 4 + 3];
-    if (!(nCornerMap > 10 && nSurfMap > 100)) return;
+// ---- scan2MapOptimization (mapOptmization.cpp:1329-1350) as <= 10 x {mo_residual_kernel, mo_solve_kernel} -------------
+// A lane's residual rows are independent, so they are spread over as many CTAs as there are queries (grid.x covers the
+// capacity, CTAs past the live query count leave at once); every CTA writes its 28 partial sums and a one-warp kernel
+// per lane adds them in block order (deterministic), solves the 6x6 system and decides convergence on the device.
+// state[6] = 1 while the lane is iterating; a finished lane makes the remaining launches of the call no-ops.
+__global__ void mo_lm_begin_kernel(MoDev m, int L) {
+    const int lane = blockIdx.x * blockDim.x + threadIdx.x;
+    if (lane >= L) return;
+    int go = 0;
+    if (m.active[lane]) {
+        const int nCornerMap = m.mapCounts[lane * 4 + 2], nSurfMap = m.mapCounts[lane * 4 + 3];
+        go = (nCornerMap > 10 && nSurfMap > 100) ? 1 : 0;   // guard of mapOptmization.cpp:1331
+        m.state[lane * 16 + 3] = 0; m.state[lane * 16 + 4] = 0;
+    }
+    m.state[lane * 16 + 6] = go;
+}
+
+__global__ void __launch_bounds__(MO_RES_THREADS) mo_residual_kernel(MoDev m) {
+    const int lane = blockIdx.y, tid = threadIdx.x, lid = tid & 31, warp = tid >> 5;
+    if (!m.state[lane * 16 + 6]) return;
     const int nCorner = m.scanCounts[lane * 8 + 0], nSurf = m.scanCounts[lane * 8 + 4];
-    if (tid < 6) sh.T[tid] = m.transformTobeMapped[lane * 6 + tid];
-    if (tid < 36) sh.matP[tid] = m.matP[lane * 36 + tid];
-    if (tid == 0) { sh.isDegenerate = m.state[lane * 16 + 0]; sh.done = 0; }
+    const int q = blockIdx.x * MO_RES_THREADS + tid;
+    if (blockIdx.x * MO_RES_THREADS >= nCorner + nSurf) return;
+    __shared__ double red[MO_RES_THREADS / 32][MO_ACC];
+    const MapSinCos sc = map_sincos(m.transformTobeMapped + lane * 6);
+    double acc[MO_ACC];
+#pragma unroll
+    for (int k = 0; k < MO_ACC; ++k) acc[k] = 0.0;
+    if (q < nCorner + nSurf) {
+        float cx, cy, cz, cd; bool ok; float4 o;
+        if (q < nCorner) {
+            o = m.cornerLastDS[(size_t)lane * m.scanCornerCap + q];
+            ok = mo_corner_residual(vh_lane(m.hashCornerMap, lane), m.cornerFromMapDS + (size_t)lane * m.cornerDSCap, sc, o, &cx, &cy, &cz, &cd);
+        } else {
+            o = m.surfTotalLastDS[(size_t)lane * (m.scanSurfCap + m.scanOutlierCap) + (q - nCorner)];
+            ok = mo_surf_residual(vh_lane(m.hashSurfMap, lane), m.surfFromMapDS + (size_t)lane * m.surfDSCap, sc, o, &cx, &cy, &cz, &cd);
+        }
+        if (ok) mo_accumulate(acc, sc, o, cx, cy, cz, cd);
+    }
+#pragma unroll
+    for (int k = 0; k < MO_ACC; ++k) { const double v = warp_sum_d(acc[k]); if (lid == 0) red[warp][k] = v; }
     __syncthreads();
-    const VhLane vhC = vh_lane(m.hashCornerMap, lane), vhS = vh_lane(m.hashSurfMap, lane);
-    const float4* cornerMap = m.cornerFromMapDS + (size_t)lane * m.cornerDSCap;
-    const float4* surfMap = m.surfFromMapDS + (size_t)lane * m.surfDSCap;
-    const float4* corner = m.cornerLastDS + (size_t)lane * m.scanCornerCap;
-    const float4* surf = m.surfTotalLastDS + (size_t)lane * (m.scanSurfCap + m.scanOutlierCap);
-    int iters = 0, rows = 0;
-    for (int iter = 0; iter < 10; ++iter) {
-        iters = iter + 1;
-        const MapSinCos sc = map_sincos(sh.T);
-        double acc[MO_ACC];
-#pragma unroll
-        for (int k = 0; k < MO_ACC; ++k) acc[k] = 0.0;
-        for (int q = tid; q < nCorner + nSurf; q += MO_THREADS) {
-            float cx, cy, cz, cd; bool ok; float4 o;
-            if (q < nCorner) { o = corner[q]; ok = mo_corner_residual(vhC, cornerMap, sc, o, &cx, &cy, &cz, &cd); }
-            else { o = surf[q - nCorner]; ok = mo_surf_residual(vhS, surfMap, sc, o, &cx, &cy, &cz, &cd); }
-            if (ok) mo_accumulate(acc, sc, o, cx, cy, cz, cd);
-        }
-#pragma unroll
-        for (int k = 0; k < MO_ACC; ++k) { const double v = warp_sum_d(acc[k]); if (lid == 0) sh.red[warp][k] = v; }
-        __syncthreads();
-        if (tid == 0) {
-            double s[MO_ACC];
-            for (int k = 0; k < MO_ACC; ++k) { s[k] = 0.0; for (int w = 0; w < MO_WARPS; ++w) s[k] += sh.red[w][k]; }
-            rows = (int)s[27];
-            int done = 0;
-            if (rows < 50) {
-                done = 1;   // LMOptimization returns false without touching the pose: every further iteration would repeat this one
-            } else {
-                float AtA[36], AtB[6], X[6];
-                int k = 0;
-                for (int i = 0; i < 6; ++i) for (int j = i; j < 6; ++j) { AtA[i * 6 + j] = (float)s[k]; AtA[j * 6 + i] = (float)s[k]; ++k; }
-                for (int i = 0; i < 6; ++i) AtB[i] = (float)s[21 + i];
-                sm::solve_qr<6, 6>(AtA, AtB, X);
-                if (iter == 0) sh.isDegenerate = sm::degeneracy_projector<6>(AtA, 100.f, sh.matP) ? 1 : 0;
-                if (sh.isDegenerate) {
-                    float X2[6];
-                    for (int i = 0; i < 6; ++i) { double t = 0.0; for (int j = 0; j < 6; ++j) t += (double)sh.matP[i * 6 + j] * (double)X[j]; X2[i] = (float)t; }
-                    for (int i = 0; i < 6; ++i) X[i] = X2[i];
-                }
-                for (int i = 0; i < 6; ++i) sh.T[i] += X[i];
-                const float r2d = 57.29577951308232f;   // pcl::rad2deg(float)
-                double dr = 0.0, dt = 0.0;
-                for (int i = 0; i < 3; ++i) { const double a = (double)(X[i] * r2d), b = (double)(X[3 + i] * 100); dr += a * a; dt += b * b; }
-                const float deltaR = (float)sqrt(dr), deltaT = (float)sqrt(dt);
-                if ((double)deltaR < 0.05 && (double)deltaT < 0.05) done = 1;
-            }
-            sh.done = done;
-        }
-        __syncthreads();
-        if (sh.done) break;
+    if (tid < MO_ACC) {
+        double s = 0.0;
+        for (int w = 0; w < MO_RES_THREADS / 32; ++w) s += red[w][tid];
+        m.partials[((size_t)lane * m.resBlocks + blockIdx.x) * MO_ACC + tid] = s;
     }
-    // transformUpdate without IMU (mapOptmization.cpp:463-496)
-    if (tid < 6) {
-        m.transformTobeMapped[lane * 6 + tid] = sh.T[tid];
-        m.transformBefMapped[lane * 6 + tid] = m.transformSum[lane * 6 + tid];
-        m.transformAftMapped[lane * 6 + tid] = sh.T[tid];
+}
+
+// LMOptimization (mapOptmization.cpp:1229-1327) + the loop control of scan2MapOptimization + transformUpdate (463-496)
+__global__ void __launch_bounds__(32) mo_solve_kernel(MoDev m, int iter) {
+    const int lane = blockIdx.x, lid = threadIdx.x;
+    if (!m.state[lane * 16 + 6]) return;
+    __shared__ double s[MO_ACC];
+    const int nQ = m.scanCounts[lane * 8 + 0] + m.scanCounts[lane * 8 + 4];
+    const int nb = (nQ + MO_RES_THREADS - 1) / MO_RES_THREADS;
+    if (lid < MO_ACC) {
+        double t = 0.0;
+        const double* p = m.partials + (size_t)lane * m.resBlocks * MO_ACC + lid;
+        for (int b = 0; b < nb; ++b) t += p[(size_t)b * MO_ACC];
+        s[lid] = t;
     }
-    if (tid < 36) m.matP[lane * 36 + tid] = sh.matP[tid];
-    if (tid == 0) { m.state[lane * 16 + 0] = sh.isDegenerate; m.state[lane * 16 + 3] = iters; m.state[lane * 16 + 4] = rows; m.records[lane].iters = iters; }
+    __syncwarp();
+    if (lid != 0) return;
+    float* T = m.transformTobeMapped + lane * 6;
+    float* matP = m.matP + lane * 36;
+    const int rows = (int)s[27];
+    int done = 0;
+    if (rows < 50) {
+        done = 1;   // LMOptimization returns false without touching the pose: every further iteration would repeat this one
+    } else {
+        float AtA[36], AtB[6], X[6];
+        int k = 0;
+        for (int i = 0; i < 6; ++i) for (int j = i; j < 6; ++j) { AtA[i * 6 + j] = (float)s[k]; AtA[j * 6 + i] = (float)s[k]; ++k; }
+        for (int i = 0; i < 6; ++i) AtB[i] = (float)s[21 + i];
+        sm::solve_qr<6, 6>(AtA, AtB, X);
+        int degenerate = m.state[lane * 16 + 0];
+        if (iter == 0) { degenerate = sm::degeneracy_projector<6>(AtA, 100.f, matP) ? 1 : 0; m.state[lane * 16 + 0] = degenerate; }
+        if (degenerate) {
+            float X2[6];
+            for (int i = 0; i < 6; ++i) { double t = 0.0; for (int j = 0; j < 6; ++j) t += (double)matP[i * 6 + j] * (double)X[j]; X2[i] = (float)t; }
+            for (int i = 0; i < 6; ++i) X[i] = X2[i];
+        }
+        for (int i = 0; i < 6; ++i) T[i] += X[i];
+        const float r2d = 57.29577951308232f;   // pcl::rad2deg(float)
+        double dr = 0.0, dt = 0.0;
+        for (int i = 0; i < 3; ++i) { const double a = (double)(X[i] * r2d), b = (double)(X[3 + i] * 100); dr += a * a; dt += b * b; }
+        const float deltaR = (float)sqrt(dr), deltaT = (float)sqrt(dt);
+        if ((double)deltaR < 0.05 && (double)deltaT < 0.05) done = 1;
+    }
+    m.state[lane * 16 + 3] = iter + 1; m.state[lane * 16 + 4] = rows;
+    if (done || iter == 9) {
+        m.state[lane * 16 + 6] = 0;
+        m.records[lane].iters = iter + 1;
+        // transformUpdate without IMU (mapOptmization.cpp:463-496)
+        for (int i = 0; i < 6; ++i) { m.transformBefMapped[lane * 6 + i] = m.transformSum[lane * 6 + i]; m.transformAftMapped[lane * 6 + i] = T[i]; }
+    }
 }
 
 // Rot3::RzRyRx(x, y, z) then .roll() / .pitch() / .yaw() (the GTSAM calls of mapOptmization.cpp:1376-1440), in double.

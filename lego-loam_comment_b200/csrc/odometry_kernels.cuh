@@ -69,14 +69,11 @@ __device__ int odo_phase(OdoShared& sh, float4* sel, const float4* __restrict__ 
         for (int q = tid; q < Q; q += ODO_THREADS) sel[q] = pose::transform_to_start(feats[q], sh.T);
         __syncthreads();
         if (iter % 5 == 0) {
-            for (int q = tid; q < Q; q += ODO_THREADS) {
-                float d2;
-                const float4 p = sel[q];
-                ind[q * K] = vh_nearest(vh, p.x, p.y, p.z, maxD2, 1.0f, &d2);
-            }
-            __syncthreads();
             for (int q = warp; q < Q; q += ODO_WARPS) {
-                const int closest = ind[q * K];
+                float d2near;
+                const float4 pq = sel[q];
+                const int closest = vh_nearest_warp(vh, pq.x, pq.y, pq.z, maxD2, 1.0f, &d2near);
+                if (lid == 0) ind[q * K] = closest;
                 Cand b2 = {maxD2, 0x7fffffff, -1}, b3 = {maxD2, 0x7fffffff, -1};
                 if (closest >= 0) {
                     const float4 p = sel[q];

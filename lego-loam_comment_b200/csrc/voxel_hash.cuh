@@ -109,6 +109,44 @@ __device__ inline int vh_nearest(const VhLane& v, float x, float y, float z, flo
     return bestI;
 }
 
+// Warp-cooperative form of vh_nearest: all 32 lanes of a warp call it with the SAME query; the cells of each shell are
+// dealt out to the lanes, so the 27-cell common case costs one probe per lane and the rare 5 m miss (1331 cells) 42.
+// Same result as vh_nearest: minimum of (distance, original index) in lexicographic order.
+__device__ inline int vh_nearest_warp(const VhLane& v, float x, float y, float z, float maxD2, float cellEdge, float* d2out) {
+    const int lid = threadIdx.x & 31;
+    const int cx = vh_cell(x, v.invCell), cy = vh_cell(y, v.invCell), cz = vh_cell(z, v.invCell);
+    float best = maxD2; int bestI = 0x7fffffff;
+    const int maxShell = (int)ceilf(sqrtf(maxD2) * v.invCell);
+    for (int k = 1; k <= max(maxShell, 1); ++k) {
+        const int side = 2 * k + 1, ncell = side * side * side;
+        for (int c = lid; c < ncell; c += 32) {
+            const int dz = c / (side * side) - k, r = c % (side * side), dy = r / side - k, dx = r % side - k;
+            // shell k adds the cells at Chebyshev distance exactly k; the first round (k = 1) also covers the centre cell
+            if (k > 1 && max(abs(dx), max(abs(dy), abs(dz))) < k) continue;
+            const int s = vh_find(v.keys, v.H, vh_pack(cx + dx, cy + dy, cz + dz));
+            if (s < 0) continue;
+            const int b = v.start[s], e = b + v.count[s];
+            for (int t = b; t < e; ++t) {
+                const float4 a = v.sorted[t];
+                const float d = vh_dist2(a, x, y, z);
+                const int ai = __float_as_int(a.w);
+                if (d < best || (d == best && bestI != 0x7fffffff && ai < bestI)) { best = d; bestI = ai; }
+            }
+        }
+        // warp minimum of (best, bestI); lanes that found nothing carry (maxD2, INT_MAX)
+#pragma unroll
+        for (int o = 16; o > 0; o >>= 1) {
+            const float od = __shfl_xor_sync(0xffffffffu, best, o);
+            const int oi = __shfl_xor_sync(0xffffffffu, bestI, o);
+            if (od < best || (od == best && oi < bestI)) { best = od; bestI = oi; }
+        }
+        const float reach = (float)k * cellEdge;
+        if (bestI != 0x7fffffff && best <= reach * reach) break;   // every unvisited point is farther than k cells
+    }
+    *d2out = best;
+    return bestI == 0x7fffffff ? -1 : bestI;
+}
+
 // Exact 5 nearest neighbours among the 27 cells around the query (exact whenever the 5th is closer than one
 // cell edge, the only case the reference accepts: mapOptmization.cpp:1101, 1183).  d2[] ascending, ties by index.
 // Returns the number found (<= 5).
