@@ -102,13 +102,33 @@ class ClockSampler:
                 "reasons": sorted(reasons), "samples": len(sm)}
 
 
+# ------------------------------------------------------------------------------------------------ sharding
+def lane_seeds(rank, lanes):
+    """Sequences are the only axis the path shards on: rank r owns sequences r*1000 .. r*1000+lanes-1,
+    no sequence is shared, nothing is exchanged on the data path."""
+    assert lanes <= 1000
+    return [1000 * rank + l for l in range(lanes)]
+
+
+def max_over_ranks(x, world, device=None):
+    """Timing reduction of the contract: the slowest rank defines the step time."""
+    if world <= 1:
+        return float(x)
+    import torch
+    import torch.distributed as dist
+    t = torch.tensor([float(x)], dtype=torch.float64, device=device or "cpu")
+    dist.all_reduce(t, op=dist.ReduceOp.MAX)
+    return float(t.item())
+
+
 # ------------------------------------------------------------------------------------------------ inputs
-def gen_inputs(sensor, lanes, n_scans, seed0, speed):
-    """Synthetic scans (tools/synth_scan.cpp): lane l = sequence with seed seed0+l, scans 0..n_scans-1.
+def gen_inputs(sensor, seeds, n_scans, speed):
+    """Synthetic scans (tools/synth_scan.cpp): lane l = sequence with seed seeds[l], scans 0..n_scans-1.
     -> xyzi float32[T, L, cap, 4], ring uint16[T, L, cap], npts int32[T, L], stamps float64[T]"""
     import lego_loam_b200  # noqa: F401
     from lego_loam_b200.synth import SynthSequence
-    seqs = [SynthSequence(sensor, seed=seed0 + l, scene="street", speed=speed, n_scans=max(n_scans, 64)) for l in range(lanes)]
+    seqs = [SynthSequence(sensor, seed=sd, scene="street", speed=speed, n_scans=max(n_scans, 64)) for sd in seeds]
+    lanes = len(seeds)
     cap = seqs[0].cap
     xyzi = np.zeros((n_scans, lanes, cap, 4), np.float32)
     ring = np.zeros((n_scans, lanes, cap), np.uint16)
@@ -215,7 +235,7 @@ def run_b200(args):
     L, K, W = args.lanes, args.steps, args.warmup
     T = W + K
     params = make_params(args.sensor, device=local)
-    xyzi, ring, npts, stamps, cap = gen_inputs(args.sensor, L, T, seed0=1000 * rank, speed=args.speed)
+    xyzi, ring, npts, stamps, cap = gen_inputs(args.sensor, lane_seeds(rank, L), T, speed=args.speed)
 
     def barrier():
         torch.cuda.synchronize()
@@ -294,14 +314,12 @@ def run_b200(args):
         barrier()
         e2e_s = time.perf_counter() - t0
         pl.close()
-        if world > 1:
-            tt = torch.tensor([e2e_s], device="cuda"); dist.all_reduce(tt, op=dist.ReduceOp.MAX); e2e_s = float(tt.item())
+        e2e_s = max_over_ranks(e2e_s, world, "cuda")
         assert np.allclose(poses_host, poses_dev, atol=1e-6), "host-buffer and device-buffer runs disagree"
         e2e = {"value": L * K * world / e2e_s, "unit": UNIT,
                "h2d_bytes_per_step": int(hx[0].nbytes + hr[0].nbytes + npts[0].nbytes), "d2h_bytes_per_step": int(L * (18 * 4 + 4))}
 
-    if world > 1:
-        tt = torch.tensor([ms], device="cuda"); dist.all_reduce(tt, op=dist.ReduceOp.MAX); ms = float(tt.item())
+    ms = max_over_ranks(ms, world, "cuda")
     return dict(rank=rank, world=world, ms=ms, L=L, K=K, W=W, e2e=e2e, clocks=clocks, launches=launches, prof=prof, tot_ms=tot_ms,
                 dominant=dominant, dom=dom, counts=counts, cap=cap, params=params,
                 step_bytes=int(xyzi[0].nbytes + ring[0].nbytes), inputs=(xyzi, ring, npts, stamps))

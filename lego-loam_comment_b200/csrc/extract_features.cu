@@ -74,7 +74,8 @@ __global__ void __launch_bounds__(256) fa_extract_kernel(IpDev d, FaDev f, Const
     signed char* s_picked = reinterpret_cast<signed char*>(tail);
     signed char* s_label = reinterpret_cast<signed char*>(tail + Cw);
     unsigned char* s_ground = tail + 2 * Cw;
-    __shared__ int s_sp[6], s_ep[6];
+    __shared__ int s_sp[6], s_ep[6], s_tie[6];
+    __shared__ int s_pickSharp[12], s_pickLess[120], s_pickFlat[24], s_nPick[3];
     __shared__ float s_red[6][8];
     __shared__ int s_scan[8];
     __shared__ int s_carry;
@@ -94,13 +95,49 @@ __global__ void __launch_bounds__(256) fa_extract_kernel(IpDev d, FaDev f, Const
         else { it.value = w.gcurv[k]; it.ind = k; }
         items[k - start] = it;
     }
-    if (tid < 6) { int sp, ep; sector_bounds(start, end, tid, &sp, &ep); s_sp[tid] = sp; s_ep[tid] = ep; }
+    if (tid < 6) { int sp, ep; sector_bounds(start, end, tid, &sp, &ep); s_sp[tid] = sp; s_ep[tid] = ep; s_tie[tid] = 0; }
+    if (tid < 3) s_nPick[tid] = 0;
     __syncthreads();
 
     // ---- phase 1: std::sort(cloudSmoothness.begin()+sp, cloudSmoothness.begin()+ep) per sector ----
-    if (lid == 0 && warp < 6) {
-        const int sp = s_sp[warp], ep = s_ep[warp];
-        if (sp < ep) ssr::std_sort(items + (sp - start), ep - sp);
+    // A sector whose curvatures are all distinct has exactly one sorted order, so it is sorted in parallel by ranking
+    // (every thread counts the smaller keys of its items).  Equal curvatures are common (quirk Q17) and their final
+    // order depends on libstdc++'s introsort path: those sectors keep their original arrangement and one thread replays
+    // std::sort on it.
+    {
+        constexpr int MAXI = 9;                     // items per thread: covers Horizon_SCAN <= 2304
+        const bool rankable = end - start <= MAXI * 256;
+        ssr::Item mine[MAXI]; int dst[MAXI], sec[MAXI];
+#pragma unroll
+        for (int u = 0; u < MAXI; ++u) {
+            const int k = start + tid + u * 256;
+            dst[u] = -1; sec[u] = 0;
+            if (rankable && k < end) {
+                int j = -1;
+#pragma unroll
+                for (int t = 0; t < 6; ++t) if (k >= s_sp[t] && k < s_ep[t]) j = t;
+                if (j >= 0) {
+                    const ssr::Item it = items[k - start];
+                    const int sp = s_sp[j], ep = s_ep[j];
+                    int rank = 0; bool tie = false;
+                    for (int q = sp; q < ep; ++q) {
+                        const float v = items[q - start].value;
+                        rank += ((v < it.value) || (v == it.value && q < k)) ? 1 : 0;
+                        tie |= (v == it.value && q != k);
+                    }
+                    if (tie) s_tie[j] = 1;
+                    mine[u] = it; dst[u] = sp - start + rank; sec[u] = j;
+                }
+            }
+        }
+        if (!rankable && tid < 6) s_tie[tid] = 1;
+        __syncthreads();
+#pragma unroll
+        for (int u = 0; u < MAXI; ++u) if (dst[u] >= 0 && !s_tie[sec[u]]) items[dst[u]] = mine[u];
+        if (lid == 0 && warp < 6 && s_tie[warp]) {
+            const int sp = s_sp[warp], ep = s_ep[warp];
+            if (sp < ep) ssr::std_sort(items + (sp - start), ep - sp);
+        }
     }
     __syncthreads();
     if (tid == 0 && start == 4 && s_sp[0] < s_ep[0]) { f.slot4val[lane] = items[0].value; f.slot4ind[lane] = items[0].ind; }
@@ -108,10 +145,6 @@ __global__ void __launch_bounds__(256) fa_extract_kernel(IpDev d, FaDev f, Const
     // ---- phase 2: greedy selection, sectors in order, one warp ----
     if (warp == 0) {
         int nSharp = 0, nLess = 0, nFlat = 0;
-        float4* oSharp = f.ringSharp + ((size_t)lane * c.R + ring) * 12;
-        float4* oLess = f.ringLessSharp + ((size_t)lane * c.R + ring) * 120;
-        float4* oFlat = f.ringFlat + ((size_t)lane * c.R + ring) * 24;
-        const float4* adj = f.segAdj + base;
         for (int j = 0; j < 6; ++j) {
             const int sp = s_sp[j], ep = s_ep[j];
             if (sp >= ep) continue;
@@ -130,10 +163,9 @@ __global__ void __launch_bounds__(256) fa_extract_kernel(IpDev d, FaDev f, Const
                     const int pind = __shfl_sync(0xffffffffu, ind, first);
                     ++picks;
                     if (picks > 20) { stop = true; break; }
-                    if (lid == 0) {
-                        const float4 p = adj[pind];
-                        if (picks <= 2) { w_set_label(w, pind, 2); oSharp[nSharp] = p; oLess[nLess] = p; }
-                        else { w_set_label(w, pind, 1); oLess[nLess] = p; }
+                    if (lid == 0) {   // the points themselves are copied by the whole CTA after the selection
+                        if (picks <= 2) { w_set_label(w, pind, 2); s_pickSharp[nSharp] = pind; s_pickLess[nLess] = pind; }
+                        else { w_set_label(w, pind, 1); s_pickLess[nLess] = pind; }
                         suppress(w, pind);
                     }
                     if (picks <= 2) ++nSharp;
@@ -158,7 +190,7 @@ __global__ void __launch_bounds__(256) fa_extract_kernel(IpDev d, FaDev f, Const
                     ++picks;
                     if (lid == 0) {
                         w_set_label(w, pind, -1);
-                        oFlat[nFlat] = adj[pind];
+                        s_pickFlat[nFlat] = pind;
                         if (picks < 4) suppress(w, pind);
                     }
                     ++nFlat;
@@ -168,9 +200,18 @@ __global__ void __launch_bounds__(256) fa_extract_kernel(IpDev d, FaDev f, Const
                 }
             }
         }
-        if (lid == 0) { rc[0] = nSharp; rc[1] = nLess; rc[2] = nFlat; }
+        if (lid == 0) { rc[0] = nSharp; rc[1] = nLess; rc[2] = nFlat; s_nPick[0] = nSharp; s_nPick[1] = nLess; s_nPick[2] = nFlat; }
     }
     __syncthreads();
+    {
+        const float4* adjp = f.segAdj + base;
+        float4* oSharp = f.ringSharp + ((size_t)lane * c.R + ring) * 12;
+        float4* oLess = f.ringLessSharp + ((size_t)lane * c.R + ring) * 120;
+        float4* oFlat = f.ringFlat + ((size_t)lane * c.R + ring) * 24;
+        if (tid < s_nPick[0]) oSharp[tid] = adjp[s_pickSharp[tid]];
+        if (tid >= 32 && tid - 32 < s_nPick[2]) oFlat[tid - 32] = adjp[s_pickFlat[tid - 32]];
+        if (tid >= 64 && tid - 64 < s_nPick[1]) oLess[tid - 64] = adjp[s_pickLess[tid - 64]];
+    }
 
     // ---- write back this ring's share of the persistent arrays ([lo, hi-1): the last slot is never modified here
     //      but may be by the next ring's CTA) ----

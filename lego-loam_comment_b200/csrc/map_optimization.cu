@@ -87,7 +87,7 @@ __device__ __forceinline__ void mo_accumulate(double* acc, const MapSinCos& sc, 
 __device__ inline bool mo_corner_residual(const VhLane& vh, const float4* __restrict__ map, const MapSinCos& sc, float4 ori, float* cx_, float* cy_, float* cz_, float* cd_) {
     const float4 ps = map_transform(sc, ori);
     float d2[5]; int idx[5];
-    const int found = vh_knn5(vh, ps.x, ps.y, ps.z, d2, idx);
+    const int found = vh_knn5(vh, ps.x, ps.y, ps.z, 1.0f, d2, idx);
     if (found < 5 || !((double)d2[4] < 1.0)) return false;
     float px[5], py[5], pz[5];
     float cx = 0.f, cy = 0.f, cz = 0.f;
@@ -127,7 +127,7 @@ __device__ inline bool mo_corner_residual(const VhLane& vh, const float4* __rest
 __device__ inline bool mo_surf_residual(const VhLane& vh, const float4* __restrict__ map, const MapSinCos& sc, float4 ori, float* cx_, float* cy_, float* cz_, float* cd_) {
     const float4 ps = map_transform(sc, ori);
     float d2[5]; int idx[5];
-    const int found = vh_knn5(vh, ps.x, ps.y, ps.z, d2, idx);
+    const int found = vh_knn5(vh, ps.x, ps.y, ps.z, 1.0f, d2, idx);
     if (found < 5 || !((double)d2[4] < 1.0)) return false;
     float A0[15];
 #pragma unroll

@@ -147,34 +147,50 @@ __device__ inline int vh_nearest_warp(const VhLane& v, float x, float y, float z
     return bestI == 0x7fffffff ? -1 : bestI;
 }
 
-// Exact 5 nearest neighbours among the 27 cells around the query (exact whenever the 5th is closer than one
-// cell edge, the only case the reference accepts: mapOptmization.cpp:1101, 1183).  d2[] ascending, ties by index.
-// Returns the number found (<= 5).
-__device__ inline int vh_knn5(const VhLane& v, float x, float y, float z, float* d2, int* idx) {
-    const int cx = vh_cell(x, v.invCell), cy = vh_cell(y, v.invCell), cz = vh_cell(z, v.invCell);
+// Exact 5 nearest neighbours among the 27 cells around the query, restricted to squared distances <= bound (callers
+// pass the reference's acceptance limit: the 5th neighbour must be closer than 1 m, mapOptmization.cpp:1101, 1183, so
+// farther points can never matter and one cell edge of reach is exact).  d2[] ascending, ties by original index.
+// The centre cell is scanned first; a neighbouring cell is skipped when the distance from the query to its box already
+// exceeds the current 5th best (a lower bound on every point inside, taken with a safety margin for rounding), which
+// leaves 2-4 of the 27 cells in the common case.  Returns the number of candidates kept (<= 5).
+__device__ inline int vh_knn5(const VhLane& v, float x, float y, float z, float bound, float* d2, int* idx) {
+    const float ux = x * v.invCell, uy = y * v.invCell, uz = z * v.invCell;
+    const float flx = floorf(ux), fly = floorf(uy), flz = floorf(uz);
+    const int cx = (int)flx, cy = (int)fly, cz = (int)flz;
+    const float cell = 1.0f / v.invCell;
+    // distance from the query to the lower / upper face of its own cell, per axis
+    const float lo[3] = {(ux - flx) * cell, (uy - fly) * cell, (uz - flz) * cell};
+    const float hi[3] = {cell - lo[0], cell - lo[1], cell - lo[2]};
     int found = 0;
 #pragma unroll
-    for (int k = 0; k < 5; ++k) { d2[k] = 3.0e38f; idx[k] = 0x7fffffff; }
-    for (int dz = -1; dz <= 1; ++dz)
-        for (int dy = -1; dy <= 1; ++dy)
-            for (int dx = -1; dx <= 1; ++dx) {
-                const int s = vh_find(v.keys, v.H, vh_pack(cx + dx, cy + dy, cz + dz));
-                if (s < 0) continue;
-                const int b = v.start[s], e = b + v.count[s];
-                for (int t = b; t < e; ++t) {
-                    const float4 a = v.sorted[t];
-                    float d = vh_dist2(a, x, y, z);
-                    int ai = __float_as_int(a.w);
-                    if (d > d2[4] || (d == d2[4] && ai > idx[4])) continue;
-                    ++found;
-                    // insertion into the sorted list of 5 (registers, fully unrolled)
+    for (int k = 0; k < 5; ++k) { d2[k] = bound; idx[k] = 0x7fffffff; }
+    // visiting order: centre, 6 faces, 12 edges, 8 corners (nearest boxes first, so the bound tightens early)
+    for (int pass = 0; pass < 4; ++pass)
+        for (int code = 0; code < 27; ++code) {
+            const int dx = code % 3 - 1, dy = (code / 3) % 3 - 1, dz = code / 9 - 1;
+            if (abs(dx) + abs(dy) + abs(dz) != pass) continue;
+            const float gx = dx < 0 ? lo[0] : (dx > 0 ? hi[0] : 0.f);
+            const float gy = dy < 0 ? lo[1] : (dy > 0 ? hi[1] : 0.f);
+            const float gz = dz < 0 ? lo[2] : (dz > 0 ? hi[2] : 0.f);
+            const float boxD2 = gx * gx + gy * gy + gz * gz;
+            if (boxD2 > d2[4] * 1.0001f + 1e-5f) continue;
+            const int s = vh_find(v.keys, v.H, vh_pack(cx + dx, cy + dy, cz + dz));
+            if (s < 0) continue;
+            const int b = v.start[s], e = b + v.count[s];
+            for (int t = b; t < e; ++t) {
+                const float4 a = v.sorted[t];
+                float d = vh_dist2(a, x, y, z);
+                int ai = __float_as_int(a.w);
+                if (d > d2[4] || (d == d2[4] && ai > idx[4])) continue;
+                ++found;
+                // insertion into the sorted list of 5 (registers, fully unrolled)
 #pragma unroll
-                    for (int k = 0; k < 5; ++k) {
-                        const bool lt = d < d2[k] || (d == d2[k] && ai < idx[k]);
-                        if (lt) { const float td = d2[k]; const int ti = idx[k]; d2[k] = d; idx[k] = ai; d = td; ai = ti; }
-                    }
+                for (int k = 0; k < 5; ++k) {
+                    const bool lt = d < d2[k] || (d == d2[k] && ai < idx[k]);
+                    if (lt) { const float td = d2[k]; const int ti = idx[k]; d2[k] = d; idx[k] = ai; d = td; ai = ti; }
                 }
             }
+        }
     return found < 5 ? found : 5;
 }
 
