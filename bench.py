@@ -36,6 +36,7 @@ def parse_args():
     ap.add_argument("--steps", type=int, default=20)
     ap.add_argument("--warmup", type=int, default=4)
     ap.add_argument("--lanes", type=int, default=64, help="independent sequences per GPU stepped in lock step")
+    ap.add_argument("--handles", type=int, default=1, help="pipeline handles (CUDA streams) the lanes of one GPU are split over")
     ap.add_argument("--sensor", default="vlp16")
     ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
     ap.add_argument("--stages", type=int, default=7, help="bit0 ImageProjection, bit1 FeatureAssociation, bit2 mapOptimization")
@@ -210,6 +211,15 @@ def gather_counts(pl, params, lanes):
     return c
 
 
+def merge_counts(a, b):
+    out = dict(a)
+    for k in ("N", "L", "S", "O", "Fs", "Fl", "Ff", "Flf", "odo_bytes"):
+        out[k] = a[k] + b[k]
+    out["mo_bytes"] = {k: a["mo_bytes"][k] + b["mo_bytes"][k] for k in a["mo_bytes"]}
+    out["map"] = {k: a["map"][k] + b["map"][k] for k in a["map"]}
+    return out
+
+
 def load_peaks():
     p = os.path.join(ROOT, "MEASURED_PEAKS.json")
     if os.path.exists(p):
@@ -247,54 +257,86 @@ def run_b200(args):
         return np.full(L, stamps[t])
 
     # ---- device-resident inputs (value) -------------------------------------------------------------
+    # The lanes are split over `handles` pipeline handles = CUDA streams: while one handle sits in its latency-bound LM
+    # kernels (one CTA per lane) the others' streaming kernels fill the rest of the GPU.
+    H = max(1, min(args.handles, L))
+    bounds = [(h * L) // H for h in range(H + 1)]
     d_xyzi = torch.from_numpy(xyzi).cuda()
     d_ring = torch.from_numpy(ring).cuda()
     torch.cuda.synchronize()
     xs, rs = d_xyzi.stride(0) * 4, d_ring.stride(0) * 2
 
-    def device_step(pl, t):
-        pl.step(d_xyzi.data_ptr() + t * xs, d_ring.data_ptr() + t * rs, npts[t], stamps_of(t), stage_mask=args.stages,
-                on_device=True, stride_points=cap)
+    def make_group():
+        return [Pipeline(params, lanes=bounds[h + 1] - bounds[h], max_points=cap) for h in range(H)]
+
+    def device_step(group, t):
+        for h, pl in enumerate(group):
+            l0, l1 = bounds[h], bounds[h + 1]
+            pl.step(d_xyzi.data_ptr() + t * xs + l0 * cap * 16, d_ring.data_ptr() + t * rs + l0 * cap * 2, npts[t, l0:l1], stamps_of(t)[l0:l1],
+                    stage_mask=args.stages, on_device=True, stride_points=cap)
+
+    def sync_group(group):
+        for pl in group:
+            pl.sync()
+
+    def close_group(group):
+        for pl in group:
+            pl.close()
 
     # pass 1 (untimed): per-kernel CUDA-event breakdown, finds the dominant kernel
-    pl = Pipeline(params, lanes=L, max_points=cap)
+    group = make_group()
     for t in range(W):
-        device_step(pl, t)
-    pl.sync()
-    pl.profile(1)
+        device_step(group, t)
+    sync_group(group)
+    for pl in group:
+        pl.profile(1)
     for t in range(W, T):
-        device_step(pl, t)
-    prof = pl.profile_read()
-    pl.profile(0)
-    counts = gather_counts(pl, params, L)
+        device_step(group, t)
+    prof = {}
+    for pl in group:
+        for k, (ms_k, n_k) in pl.profile_read().items():
+            a_ms, a_n = prof.get(k, (0.0, 0))
+            prof[k] = (a_ms + ms_k, a_n + n_k)
+        pl.profile(0)
+    counts = None
+    for h, pl in enumerate(group):
+        ch = gather_counts(pl, params, bounds[h + 1] - bounds[h])
+        counts = ch if counts is None else merge_counts(counts, ch)
     counts["P"] = int(npts[T - 1].sum())
-    pl.close()
+    close_group(group)
     tot_ms = sum(v[0] for v in prof.values()) or 1.0
     dominant = max(prof, key=lambda k: prof[k][0])
 
-    # pass 2 (timed): K steps, events on the pipeline's stream; only the dominant kernel stays bracketed
-    pl = Pipeline(params, lanes=L, max_points=cap)
+    # pass 2 (timed): K steps, events on the pipelines' streams; only the dominant kernel stays bracketed
+    group = make_group()
     for t in range(W):
-        device_step(pl, t)
-    pl.sync()
-    pl.profile(2, dominant)
-    launches0 = pl.launch_count()
+        device_step(group, t)
+    sync_group(group)
+    for pl in group:
+        pl.profile(2, dominant)
+    launches0 = sum(pl.launch_count() for pl in group)
     clk = ClockSampler(local)
     clk.start()
     barrier()
-    pl.timer_record(0)
+    for pl in group:
+        pl.timer_record(0)
     for t in range(W, T):
-        device_step(pl, t)
-    pl.timer_record(1)
-    pl.sync()
+        device_step(group, t)
+    for pl in group:
+        pl.timer_record(1)
+    sync_group(group)
     barrier()
-    ms = pl.timer_elapsed_ms(0, 1)
+    ms = max(group[0].timer_elapsed_to(0, pl, 1) for pl in group)
     clocks = clk.stop()
-    launches = pl.launch_count() - launches0
-    dom = pl.profile_read().get(dominant, (0.0, 0))
-    pl.profile(0)
-    poses_dev, _ = pl.poses()
-    pl.close()
+    launches = sum(pl.launch_count() for pl in group) - launches0
+    dom_ms, dom_n = 0.0, 0
+    for pl in group:
+        d_ms, d_n = pl.profile_read().get(dominant, (0.0, 0))
+        dom_ms += d_ms; dom_n += d_n
+        pl.profile(0)
+    dom = (dom_ms, dom_n)
+    poses_dev = np.concatenate([pl.poses()[0] for pl in group])
+    close_group(group)
 
     # ---- host buffers through the C ABI (e2e) --------------------------------------------------------
     e2e = None
@@ -302,18 +344,23 @@ def run_b200(args):
         h_xyzi = torch.from_numpy(xyzi).pin_memory()
         h_ring = torch.from_numpy(ring).pin_memory()
         hx, hr = h_xyzi.numpy(), h_ring.numpy()
-        pl = Pipeline(params, lanes=L, max_points=cap)
+        group = make_group()
+
+        def host_step(t):
+            for h, pl in enumerate(group):
+                l0, l1 = bounds[h], bounds[h + 1]
+                pl.step(hx[t, l0:l1], hr[t, l0:l1], npts[t, l0:l1], stamps_of(t)[l0:l1], stage_mask=args.stages)
+            return np.concatenate([pl.poses()[0] for pl in group])   # D2H of the step's result, synchronises
+
         for t in range(W):
-            pl.step(hx[t], hr[t], npts[t], stamps_of(t), stage_mask=args.stages)
-            pl.poses()
+            host_step(t)
         barrier()
         t0 = time.perf_counter()
         for t in range(W, T):
-            pl.step(hx[t], hr[t], npts[t], stamps_of(t), stage_mask=args.stages)
-            poses_host, _ = pl.poses()        # D2H of the step's result, synchronises
+            poses_host = host_step(t)
         barrier()
         e2e_s = time.perf_counter() - t0
-        pl.close()
+        close_group(group)
         e2e_s = max_over_ranks(e2e_s, world, "cuda")
         assert np.allclose(poses_host, poses_dev, atol=1e-6), "host-buffer and device-buffer runs disagree"
         e2e = {"value": L * K * world / e2e_s, "unit": UNIT,
@@ -429,7 +476,7 @@ def main():
         "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": K, "warmup": r["W"],
         "ms_per_step": r["ms"] / K, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
         "dtype": "f32", "data": "synthetic",
-        "config": {"workload": workload_name(args), "sensor": args.sensor, "lanes_per_gpu": L, "stages": args.stages,
+        "config": {"workload": workload_name(args), "sensor": args.sensor, "lanes_per_gpu": L, "handles_per_gpu": args.handles, "stages": args.stages,
                    "points_per_scan": r["cap"],
                    "l2": "per-step inputs %.0f MB + per-lane state exceed the 126 MB L2 (no flush needed)" % (r["step_bytes"] / 1e6)},
         "roofline": roofline, "clocks": r["clocks"], "gpu_launches": int(r["launches"]),

@@ -143,6 +143,9 @@ long lego_pipeline_launch_count(lego_pipeline* h);
  * `filter`; profile_read sums the brackets per kernel name (names newline-separated) and returns the number of names. */
 int lego_pipeline_timer_record(lego_pipeline* h, int slot);
 int lego_pipeline_timer_elapsed(lego_pipeline* h, int slot_a, int slot_b, float* ms_out);
+/* device time from event slot_a of handle ha to event slot_b of handle hb (handles of one device; several handles =
+ * several streams whose kernels overlap on the GPU) */
+int lego_pipeline_timer_elapsed_between(lego_pipeline* ha, int slot_a, lego_pipeline* hb, int slot_b, float* ms_out);
 int lego_pipeline_profile(lego_pipeline* h, int mode, const char* filter);
 long lego_pipeline_profile_read(lego_pipeline* h, char* names, long names_cap, double* ms, long* counts, long max_kernels);
 /* Parity / debug access to named device arrays of one lane (see DESIGN.md for the name list).  Returns the

@@ -18,7 +18,7 @@ EXPORTED = [
     "lego_mo_create", "lego_mo_destroy", "lego_mo_process",
     "lego_pipeline_create", "lego_pipeline_destroy", "lego_pipeline_step", "lego_pipeline_get_poses",
     "lego_pipeline_sync", "lego_pipeline_launch_count", "lego_pipeline_download", "lego_pipeline_upload",
-    "lego_pipeline_timer_record", "lego_pipeline_timer_elapsed", "lego_pipeline_profile", "lego_pipeline_profile_read",
+    "lego_pipeline_timer_record", "lego_pipeline_timer_elapsed", "lego_pipeline_timer_elapsed_between", "lego_pipeline_profile", "lego_pipeline_profile_read",
     "lego_selftest_atan2f", "lego_selftest_std_sort", "lego_selftest_voxel_grid",
 ]
 
@@ -149,6 +149,14 @@ class Pipeline:
     def timer_elapsed_ms(self, a, b):
         ms = ctypes.c_float(0)
         _check(self.lib.lego_pipeline_timer_elapsed(self.h, a, b, ctypes.byref(ms)), "lego_pipeline_timer_elapsed")
+        return ms.value
+
+    def timer_elapsed_to(self, a, other, b):
+        """device ms from this handle's event a to `other`'s event b"""
+        ms = ctypes.c_float(0)
+        f = self.lib.lego_pipeline_timer_elapsed_between
+        f.argtypes = [ctypes.c_void_p, ctypes.c_int, ctypes.c_void_p, ctypes.c_int, ctypes.POINTER(ctypes.c_float)]
+        _check(f(self.h, a, other.h, b, ctypes.byref(ms)), "lego_pipeline_timer_elapsed_between")
         return ms.value
 
     def profile(self, mode, name_filter=""):

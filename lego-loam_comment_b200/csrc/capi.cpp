@@ -99,6 +99,15 @@ int lego_pipeline_timer_elapsed(lego_pipeline* h, int slot_a, int slot_b, float*
     if (!h || !ms_out || slot_a < 0 || slot_a >= 8 || slot_b < 0 || slot_b >= 8) return LEGO_ERR_ARG;
     LEGO_TRY *ms_out = h->e->timerElapsed(slot_a, slot_b); return LEGO_OK; LEGO_CATCH
 }
+int lego_pipeline_timer_elapsed_between(lego_pipeline* ha, int slot_a, lego_pipeline* hb, int slot_b, float* ms_out) {
+    if (!ha || !hb || !ms_out || slot_a < 0 || slot_a >= 8 || slot_b < 0 || slot_b >= 8) return LEGO_ERR_ARG;
+    LEGO_TRY
+    if (!ha->e->timerEv[slot_a] || !hb->e->timerEv[slot_b]) { lego::set_last_error("timer slot was never recorded"); return LEGO_ERR_ARG; }
+    lego::cuda_check(cudaEventSynchronize(hb->e->timerEv[slot_b]), "event sync");
+    lego::cuda_check(cudaEventElapsedTime(ms_out, ha->e->timerEv[slot_a], hb->e->timerEv[slot_b]), "event elapsed");
+    return LEGO_OK;
+    LEGO_CATCH
+}
 long lego_pipeline_download(lego_pipeline* h, int lane, const char* name, void* dst, long cap, int* elem_size_out) {
     if (!h || !name) return LEGO_ERR_ARG;
     LEGO_TRY

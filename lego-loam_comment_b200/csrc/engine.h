@@ -188,7 +188,7 @@ public:
     bool lookupFeatureAssociation(int lane, const std::string& name, void** ptr, int* elem, long* count);
     void allocFeatureAssociation();
     void allocOdometry();
-    VoxelHash allocHash(int cap, float cell);
+    VoxelHash allocHash(int cap, float cell, const int* n, int nStride);
     bool lookupOdometry(int lane, const std::string& name, void** ptr, int* elem, long* count);
 
     Consts c;

@@ -34,19 +34,26 @@ __device__ __forceinline__ bool w_ground(const RingWin& w, int i) { return (in_w
 __device__ __forceinline__ void w_set_picked(RingWin& w, int i) { if (in_win(w, i)) w.picked[i - w.lo] = 1; else w.gpicked[i] = 1; }
 __device__ __forceinline__ void w_set_label(RingWin& w, int i, int v) { if (in_win(w, i)) w.label[i - w.lo] = (signed char)v; else w.glabel[i] = v; }
 
-// suppression of the picked point's neighbourhood (featureAssociation.cpp:720-732 and 751-767).  An index below 0
-// ends the walk: the reference reads out of bounds there (quirk Q11) and the oracle defines it as "stop".
-__device__ __forceinline__ void suppress(RingWin& w, int ind) {
-    w_set_picked(w, ind);
-    for (int l = 1; l <= 5; ++l) {
-        if (abs(w_col(w, ind + l) - w_col(w, ind + l - 1)) > 10) break;
-        w_set_picked(w, ind + l);
+// Suppression of the picked point's neighbourhood (featureAssociation.cpp:720-732 and 751-767): the point and up to
+// five slots on either side are marked, each walk stopping at the first column gap > 10.  An index below 0 ends the
+// backward walk: the reference reads out of bounds there (quirk Q11) and the oracle defines it as "stop".
+// The same walk done by a whole warp: lanes 0-4 test the five forward steps, lanes 5-9 the five backward steps, a
+// ballot finds where each walk stops, and the lanes before the stop mark their slot.
+__device__ __forceinline__ void suppress_warp(RingWin& w, int ind, int lid) {
+    bool bad = false; int slot = ind;
+    if (lid < 5) {
+        const int l = lid + 1;
+        slot = ind + l;
+        bad = abs(w_col(w, ind + l) - w_col(w, ind + l - 1)) > 10;
+    } else if (lid < 10) {
+        const int l = -(lid - 4);
+        slot = ind + l;
+        bad = (ind + l < 0) || abs(w_col(w, ind + l) - w_col(w, ind + l + 1)) > 10;
     }
-    for (int l = -1; l >= -5; --l) {
-        if (ind + l < 0) break;
-        if (abs(w_col(w, ind + l) - w_col(w, ind + l + 1)) > 10) break;
-        w_set_picked(w, ind + l);
-    }
+    const unsigned m = __ballot_sync(0xffffffffu, bad);
+    const int nF = (m & 0x1fu) ? __ffs(m & 0x1fu) - 1 : 5;
+    const int nB = ((m >> 5) & 0x1fu) ? __ffs((m >> 5) & 0x1fu) - 1 : 5;
+    if (lid < nF || (lid >= 5 && lid - 5 < nB) || lid == 10) w_set_picked(w, slot);
 }
 
 __device__ __forceinline__ void sector_bounds(int start, int end, int j, int* sp, int* ep) {
@@ -166,8 +173,8 @@ __global__ void __launch_bounds__(256) fa_extract_kernel(IpDev d, FaDev f, Const
                     if (lid == 0) {   // the points themselves are copied by the whole CTA after the selection
                         if (picks <= 2) { w_set_label(w, pind, 2); s_pickSharp[nSharp] = pind; s_pickLess[nLess] = pind; }
                         else { w_set_label(w, pind, 1); s_pickLess[nLess] = pind; }
-                        suppress(w, pind);
                     }
+                    suppress_warp(w, pind, lid);
                     if (picks <= 2) ++nSharp;
                     ++nLess;
                     __syncwarp();
@@ -191,8 +198,8 @@ __global__ void __launch_bounds__(256) fa_extract_kernel(IpDev d, FaDev f, Const
                     if (lid == 0) {
                         w_set_label(w, pind, -1);
                         s_pickFlat[nFlat] = pind;
-                        if (picks < 4) suppress(w, pind);
                     }
+                    if (picks < 4) suppress_warp(w, pind, lid);
                     ++nFlat;
                     __syncwarp();
                     if (picks >= 4) { stop = true; break; }

@@ -47,7 +47,7 @@ void Engine::allocMapOptimization() {
     const size_t totCap = (size_t)mo.scanSurfCap + mo.scanOutlierCap;
     mo.surfTotalLast = alloc<float4>(L * totCap); mo.surfTotalLastDS = alloc<float4>(L * totCap);
     mo.scanCounts = alloc<int>(L * 8);
-    mo.hashCornerMap = allocHash(mo.cornerDSCap, 1.0f); mo.hashSurfMap = allocHash(mo.surfDSCap, 1.0f);
+    mo.hashCornerMap = allocHash(mo.cornerDSCap, 1.0f, mo.mapCounts + 2, 4); mo.hashSurfMap = allocHash(mo.surfDSCap, 1.0f, mo.mapCounts + 3, 4);
     mo.records = alloc<MoRecord>(L);
     mo.resBlocks = (mo.scanCornerCap + mo.scanSurfCap + mo.scanOutlierCap + 255) / 256;
     mo.partials = alloc<double>(L * mo.resBlocks * 28);
@@ -322,8 +322,8 @@ void Engine::mapOptimizationBody(const std::vector<int>& active) {
         mo_concat_kernel<<<g, 256, 0, stream>>>(mo, mo.scanSurfCap, mo.scanOutlierCap, mo.scanSurfCap + mo.scanOutlierCap);
     }
     { ProfScope ps(this, "vg_filter(surfTotal)"); launches += vg_filter(vgSurfTotal, stream); }
-    { ProfScope ps(this, "vh_build(cornerMap)"); launches += vh_build(mo.hashCornerMap, c.L, mo.cornerFromMapDS, (size_t)mo.cornerDSCap, mo.mapCounts + 2, 4, stream); }
-    { ProfScope ps(this, "vh_build(surfMap)"); launches += vh_build(mo.hashSurfMap, c.L, mo.surfFromMapDS, (size_t)mo.surfDSCap, mo.mapCounts + 3, 4, stream); }
+    { ProfScope ps(this, "vh_build(cornerMap)"); launches += vh_build(mo.hashCornerMap, c.L, mo.cornerFromMapDS, (size_t)mo.cornerDSCap, stream); }
+    { ProfScope ps(this, "vh_build(surfMap)"); launches += vh_build(mo.hashSurfMap, c.L, mo.surfFromMapDS, (size_t)mo.surfDSCap, stream); }
     {
         ProfScope ps(this, "mo_scan2map(lm loop)");
         mo_lm_begin_kernel<<<(c.L + 63) / 64, 64, 0, stream>>>(mo, c.L);

@@ -2,7 +2,9 @@
 // pose integration (featureAssociation.cpp:1697-1725) and the end-of-sweep re-projection + "last" cloud swap
 // (featureAssociation.cpp:1759-1815).  blockIdx.y / blockIdx.x = lane; the whole LM loop of one lane runs inside
 // one persistent CTA so there is no host round trip between iterations.
+#include <algorithm>
 #include <cfloat>
+#include <cstdlib>
 #include "engine.h"
 #include "kernel_utils.cuh"
 #include "odometry_kernels.cuh"
@@ -11,11 +13,12 @@ namespace lego {
 
 __global__ void fa_init_state_kernel(FaDev f, int L);
 
-VoxelHash Engine::allocHash(int cap, float cell) {
+VoxelHash Engine::allocHash(int cap, float cell, const int* n, int nStride) {
     VoxelHash h;
     int H = 1024;
     while (H < 2 * cap) H <<= 1;
-    h.H = H; h.cap = cap; h.invCell = 1.0f / cell;
+    h.H = H; h.cap = cap; h.invCell = 1.0f / cell; h.n = n; h.nStride = nStride;
+    { const char* e = std::getenv("LEGO_VH_MIN"); h.minH = e && *e ? std::min(H, std::max(1024, std::atoi(e))) : 1024; }
     h.keys = alloc<unsigned long long>((size_t)c.L * H); h.count = alloc<int>((size_t)c.L * H); h.start = alloc<int>((size_t)c.L * H);
     h.slotOf = alloc<int>((size_t)c.L * cap); h.sorted = alloc<float4>((size_t)c.L * cap);
     return h;
@@ -30,7 +33,7 @@ void Engine::allocOdometry() {
     fa.cornerInd = alloc<int>(L * R * 12 * 2); fa.surfInd = alloc<int>(L * R * 24 * 3);
     fa.partials = alloc<double>(L * 16); fa.tickets = alloc<unsigned int>(L);
     fa.outlierLast = alloc<float4>(L * c.Ocap); fa.flags = alloc<int>(L);
-    fa.hashCorner = allocHash(c.R * 120, 1.0f); fa.hashSurf = allocHash(c.N, 1.0f);
+    fa.hashCorner = allocHash(c.R * 120, 1.0f, fa.lastCounts + 0, 4); fa.hashSurf = allocHash(c.N, 1.0f, fa.lastCounts + 1, 4);
     fa_init_state_kernel<<<(c.L + 63) / 64, 64, 0, stream>>>(fa, c.L);
 }
 
@@ -150,8 +153,8 @@ void Engine::integrateTransformationPublishCloudsLast() {
     faBuf = nb;
     // the two kd-tree rebuilds of featureAssociation.cpp:1786-1787 become two voxel-hash builds
     launches += 2;
-    { ProfScope ps(this, "vh_build(cornerLast)"); launches += vh_build(fa.hashCorner, c.L, fa.cornerLast[nb], (size_t)c.R * 120, fa.lastCounts + 0, 4, stream); }
-    { ProfScope ps(this, "vh_build(surfLast)"); launches += vh_build(fa.hashSurf, c.L, fa.surfLast[nb], (size_t)c.N, fa.lastCounts + 1, 4, stream); }
+    { ProfScope ps(this, "vh_build(cornerLast)"); launches += vh_build(fa.hashCorner, c.L, fa.cornerLast[nb], (size_t)c.R * 120, stream); }
+    { ProfScope ps(this, "vh_build(surfLast)"); launches += vh_build(fa.hashSurf, c.L, fa.surfLast[nb], (size_t)c.N, stream); }
 }
 
 }  // namespace lego

@@ -25,12 +25,25 @@ struct VoxelHash {
     int* start;                 // [L][H]  first position of the cell's run in `sorted`
     int* slotOf;                // [L][cap] table slot of every input point
     float4* sorted;             // [L][cap] cell-sorted copy, w = original index (int bits)
-    int H;                      // slots per lane, power of two
+    int H;                      // slots ALLOCATED per lane, power of two; a build uses only vh_table_size(n, H) of them
+    const int* n;               // [lane * nStride] live size of the indexed cloud (device counter)
+    int nStride;
+    int minH;                   // lower limit of the table size in use (= H switches the live sizing off)
     int cap;                    // points per lane
     float invCell;              // 1 / cell edge
 };
 
 #define VH_EMPTY 0xFFFFFFFFFFFFFFFFull
+
+// the 27 cells around a query ordered by box distance class: centre, 6 faces, 12 edges, 8 corners;
+// entry = (dx+1) | (dy+1) << 2 | (dz+1) << 4
+#define VH_C(dx, dy, dz) (((dx) + 1) | (((dy) + 1) << 2) | (((dz) + 1) << 4))
+static __device__ __constant__ unsigned char VH_ORDER27[27] = {
+    VH_C(0, 0, 0),
+    VH_C(-1, 0, 0), VH_C(1, 0, 0), VH_C(0, -1, 0), VH_C(0, 1, 0), VH_C(0, 0, -1), VH_C(0, 0, 1),
+    VH_C(-1, -1, 0), VH_C(1, -1, 0), VH_C(-1, 1, 0), VH_C(1, 1, 0), VH_C(-1, 0, -1), VH_C(1, 0, -1), VH_C(-1, 0, 1), VH_C(1, 0, 1),
+    VH_C(0, -1, -1), VH_C(0, 1, -1), VH_C(0, -1, 1), VH_C(0, 1, 1),
+    VH_C(-1, -1, -1), VH_C(1, -1, -1), VH_C(-1, 1, -1), VH_C(1, 1, -1), VH_C(-1, -1, 1), VH_C(1, -1, 1), VH_C(-1, 1, 1), VH_C(1, 1, 1)};
 
 __host__ __device__ __forceinline__ unsigned long long vh_pack(int ix, int iy, int iz) {
     return ((unsigned long long)(unsigned)(ix + (1 << 20)) & 0x1FFFFF) |
@@ -40,6 +53,15 @@ __host__ __device__ __forceinline__ unsigned long long vh_pack(int ix, int iy, i
 __host__ __device__ __forceinline__ unsigned vh_hash(unsigned long long k) {
     k ^= k >> 33; k *= 0xff51afd7ed558ccdull; k ^= k >> 33; k *= 0xc4ceb9fe1a85ec53ull; k ^= k >> 33;
     return (unsigned)k;
+}
+// Table size actually used for a cloud of n points: the smallest power of two >= 4n (at least 1024, at most the
+// allocation).  Sizing by the live count instead of the capacity keeps the clear / scan / recount passes proportional
+// to the data; 4n keeps the load factor below 1/4 so that look-ups of EMPTY neighbour cells -- the common case of the
+// shell searches -- end after ~1.2 probes.
+__host__ __device__ __forceinline__ int vh_table_size(int n, int Hmax, int Hmin = 1024) {
+    int H = Hmin;
+    while (H < 4 * n && H < Hmax) H <<= 1;
+    return H;
 }
 __device__ __forceinline__ int vh_cell(float v, float invCell) { return (int)floorf(v * invCell); }
 
@@ -56,19 +78,19 @@ __device__ __forceinline__ int vh_find(const unsigned long long* __restrict__ ke
 
 // ---- build (kernels live in voxel_hash.cu); n[lane * nStride] = number of points of the lane's cloud ----
 __global__ void vh_clear_kernel(VoxelHash h);
-__global__ void vh_insert_kernel(VoxelHash h, const float4* __restrict__ pts, size_t ptsStride, const int* __restrict__ n, int nStride);
+__global__ void vh_insert_kernel(VoxelHash h, const float4* __restrict__ pts, size_t ptsStride);
 __global__ void vh_scan_kernel(VoxelHash h);
-__global__ void vh_scatter_kernel(VoxelHash h, const float4* __restrict__ pts, size_t ptsStride, const int* __restrict__ n, int nStride);
-__global__ void vh_recount_kernel(VoxelHash h, const int* __restrict__ n, int nStride);
-// Enqueues the five build launches for all lanes; returns the number of launches.
-int vh_build(const VoxelHash& h, int lanes, const float4* pts, size_t ptsStride, const int* n, int nStride, cudaStream_t stream);
+__global__ void vh_scatter_kernel(VoxelHash h, const float4* __restrict__ pts, size_t ptsStride);
+__global__ void vh_recount_kernel(VoxelHash h);
+// Enqueues the five build launches for all lanes (cloud sizes come from h.n); returns the number of launches.
+int vh_build(const VoxelHash& h, int lanes, const float4* pts, size_t ptsStride, cudaStream_t stream);
 
 // ---- query helpers ----
 struct VhLane { const unsigned long long* keys; const int* start; const int* count; const float4* sorted; int H; float invCell; };
 __device__ __forceinline__ VhLane vh_lane(const VoxelHash& h, int lane) {
     VhLane v;
     v.keys = h.keys + (size_t)lane * h.H; v.start = h.start + (size_t)lane * h.H; v.count = h.count + (size_t)lane * h.H;
-    v.sorted = h.sorted + (size_t)lane * h.cap; v.H = h.H; v.invCell = h.invCell;
+    v.sorted = h.sorted + (size_t)lane * h.cap; v.H = vh_table_size(min(h.n[lane * h.nStride], h.cap), h.H, h.minH); v.invCell = h.invCell;
     return v;
 }
 
@@ -165,10 +187,9 @@ __device__ inline int vh_knn5(const VhLane& v, float x, float y, float z, float 
 #pragma unroll
     for (int k = 0; k < 5; ++k) { d2[k] = bound; idx[k] = 0x7fffffff; }
     // visiting order: centre, 6 faces, 12 edges, 8 corners (nearest boxes first, so the bound tightens early)
-    for (int pass = 0; pass < 4; ++pass)
-        for (int code = 0; code < 27; ++code) {
-            const int dx = code % 3 - 1, dy = (code / 3) % 3 - 1, dz = code / 9 - 1;
-            if (abs(dx) + abs(dy) + abs(dz) != pass) continue;
+    for (int o = 0; o < 27; ++o) {
+            const int code = VH_ORDER27[o];
+            const int dx = (code & 3) - 1, dy = ((code >> 2) & 3) - 1, dz = ((code >> 4) & 3) - 1;
             const float gx = dx < 0 ? lo[0] : (dx > 0 ? hi[0] : 0.f);
             const float gy = dy < 0 ? lo[1] : (dy > 0 ? hi[1] : 0.f);
             const float gz = dz < 0 ? lo[2] : (dz > 0 ? hi[2] : 0.f);
