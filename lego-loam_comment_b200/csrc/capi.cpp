@@ -111,6 +111,14 @@ int lego_pipeline_timer_elapsed_between(lego_pipeline* ha, int slot_a, lego_pipe
 long lego_pipeline_download(lego_pipeline* h, int lane, const char* name, void* dst, long cap, int* elem_size_out) {
     if (!h || !name) return LEGO_ERR_ARG;
     LEGO_TRY
+    if (!std::strcmp(name, "surroundingExistingKeyPosesID")) {   // host-side list of the key-frame bookkeeping
+        if (lane < 0 || lane >= h->e->c.L) return LEGO_ERR_NAME;
+        const std::vector<int>& v = h->e->moHost[lane].surroundingExistingKeyPosesID;
+        if (elem_size_out) *elem_size_out = 4;
+        const long n = (long)v.size();
+        if (dst && n > 0) std::memcpy(dst, v.data(), sizeof(int) * (size_t)(n < cap ? n : cap));
+        return n;
+    }
     if (!std::strcmp(name, "labelMat")) h->e->finalizeLabelMat();
     return h->e->download(lane, name, dst, cap, elem_size_out);
     LEGO_CATCH

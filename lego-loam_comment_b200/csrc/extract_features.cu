@@ -126,13 +126,25 @@ __global__ void __launch_bounds__(256) fa_extract_kernel(IpDev d, FaDev f, Const
                 if (j >= 0) {
                     const ssr::Item it = items[k - start];
                     const int sp = s_sp[j], ep = s_ep[j];
-                    int rank = 0; bool tie = false;
-                    for (int q = sp; q < ep; ++q) {
-                        const float v = items[q - start].value;
-                        rank += ((v < it.value) || (v == it.value && q < k)) ? 1 : 0;
-                        tie |= (v == it.value && q != k);
+                    // rank = number of smaller curvatures in the sector, eq = number of equal ones (itself included).
+                    // The curvatures are read from the staged cloudCurvature window (contiguous floats, 4 per load);
+                    // slot 4 of cloudSmoothness is the one entry that is NOT cloudCurvature (quirk Q11), patched below.
+                    const float x = it.value;
+                    const float* vp = s_curv + (sp - w.lo);
+                    const int n = ep - sp;
+                    int rank = 0, eq = 0, q = 0;
+                    for (; q < n && ((size_t)(vp + q) & 15); ++q) { const float v = vp[q]; rank += v < x; eq += v == x; }
+                    for (; q + 4 <= n; q += 4) {
+                        const float4 v = *reinterpret_cast<const float4*>(vp + q);
+                        rank += (v.x < x) + (v.y < x) + (v.z < x) + (v.w < x);
+                        eq += (v.x == x) + (v.y == x) + (v.z == x) + (v.w == x);
                     }
-                    if (tie) s_tie[j] = 1;
+                    for (; q < n; ++q) { const float v = vp[q]; rank += v < x; eq += v == x; }
+                    if (start == 4 && j == 0) {
+                        const float c4 = s_curv[4 - w.lo], t4 = items[0].value;
+                        rank += (t4 < x) - (c4 < x); eq += (t4 == x) - (c4 == x);
+                    }
+                    if (eq > 1) s_tie[j] = 1;
                     mine[u] = it; dst[u] = sp - start + rank; sec[u] = j;
                 }
             }
@@ -334,27 +346,30 @@ __global__ void __launch_bounds__(256) fa_extract_kernel(IpDev d, FaDev f, Const
     if (tid == 0) rc[3] = s_carry;
 }
 
-// Concatenate the ring-local lists in ring order (the reference appends ring by ring, featureAssociation.cpp:782).
-__global__ void __launch_bounds__(256) fa_gather_features_kernel(FaDev f, Consts c) {
-    const int lane = blockIdx.x, tid = threadIdx.x;
-    __shared__ int off[4][129];
+// Concatenate the ring-local lists in ring order (the reference appends ring by ring, featureAssociation.cpp:782):
+// one CTA per (ring, lane) sums the counts of the rings before it and copies its own four lists.
+__global__ void __launch_bounds__(128) fa_gather_features_kernel(FaDev f, Consts c) {
+    const int ring = blockIdx.x, lane = blockIdx.y, tid = threadIdx.x;
+    __shared__ int off[4], cnt[4], tot[4];
     if (tid < 4) {
-        int s = 0;
-        for (int r = 0; r < c.R; ++r) { off[tid][r] = s; s += f.ringCounts[((size_t)lane * c.R + r) * 4 + tid]; }
-        off[tid][c.R] = s;
-        f.featCounts[lane * 4 + tid] = s;
+        int s = 0, all = 0;
+        for (int r = 0; r < c.R; ++r) {
+            const int n = f.ringCounts[((size_t)lane * c.R + r) * 4 + tid];
+            if (r < ring) s += n;
+            all += n;
+        }
+        off[tid] = s; tot[tid] = all; cnt[tid] = f.ringCounts[((size_t)lane * c.R + ring) * 4 + tid];
+        if (ring == 0) f.featCounts[lane * 4 + tid] = all;
     }
     __syncthreads();
     const int cap[4] = {12, 120, 24, c.C};
-    float4* src[4] = {f.ringSharp + (size_t)lane * c.R * 12, f.ringLessSharp + (size_t)lane * c.R * 120,
-                      f.ringFlat + (size_t)lane * c.R * 24, f.ringLessFlat + (size_t)lane * c.R * c.C};
+    const float4* src[4] = {f.ringSharp + (size_t)lane * c.R * 12, f.ringLessSharp + (size_t)lane * c.R * 120,
+                            f.ringFlat + (size_t)lane * c.R * 24, f.ringLessFlat + (size_t)lane * c.R * c.C};
     float4* dst[4] = {f.sharp + (size_t)lane * c.R * 12, f.lessSharp + (size_t)lane * c.R * 120,
                       f.flat + (size_t)lane * c.R * 24, f.lessFlat + (size_t)lane * c.N};
+#pragma unroll
     for (int t = 0; t < 4; ++t)
-        for (int r = 0; r < c.R; ++r) {
-            const int n = off[t][r + 1] - off[t][r];
-            for (int i = tid; i < n; i += blockDim.x) dst[t][off[t][r] + i] = src[t][(size_t)r * cap[t] + i];
-        }
+        for (int i = tid; i < cnt[t]; i += blockDim.x) dst[t][off[t] + i] = src[t][(size_t)ring * cap[t] + i];
 }
 
 // Kernels defined in feature_association.cu
@@ -378,7 +393,7 @@ void Engine::extractFeatures() {
     }
     dim3 g(c.R, c.L);
     { ProfScope ps(this, "fa_extract_kernel"); fa_extract_kernel<<<g, 256, smem, stream>>>(ip, fa, c, 0.2f); }   // downSizeFilter.setLeafSize(0.2,...) featureAssociation.cpp:225
-    { ProfScope ps(this, "fa_gather_features_kernel"); fa_gather_features_kernel<<<c.L, 256, 0, stream>>>(fa, c); }
+    { ProfScope ps(this, "fa_gather_features_kernel"); fa_gather_features_kernel<<<dim3(c.R, c.L), 128, 0, stream>>>(fa, c); }
     launches += 2;
 }
 
