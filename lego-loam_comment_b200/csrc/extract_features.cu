@@ -2,18 +2,25 @@
 //
 // Rings are independent in the reference's loop (suppression reaches +-5 slots, the ring margins are 5+5 slots;
 // validated in SURVEY.md section 8), so each CTA owns one ring and walks its six sectors in order:
-//   phase 1  six warps replay libstdc++'s std::sort on their sector's {curvature, index} slots (std_sort_replay.cuh);
+//   phase 0  the ring's window of cloudNeighborPicked / cloudLabel is staged in shared memory together with two
+//            derived bytes per point: the static part of the pick conditions (curvature vs threshold, ground flag)
+//            and how far the +-5 suppression walk of featureAssociation.cpp:720-732 gets before a column gap > 10;
+//   phase 1  six warps sort their sector's {curvature, index} slots: a warp-local stable LSD radix sort gives the
+//            order whenever the curvatures are distinct; a sector that holds equal curvatures keeps its arrangement
+//            and one thread replays libstdc++'s std::sort on it (std_sort_replay.cuh, quirk Q17);
 //            the sort range is [sp, ep) while the scans below include slot ep (quirk Q10);
 //   phase 2  warp 0 does the greedy picks with warp ballots: 32 candidates are tested at once, the first eligible
-//            one is taken, its +-5 neighbourhood is suppressed (stopping at column gaps > 10), and the remaining
-//            lanes are re-tested -- identical to the sequential scan because suppression only ever removes
-//            candidates;
+//            one is taken, its neighbourhood is suppressed in registers (and in the shared window for later chunks)
+//            and the remaining lanes are re-tested -- identical to the sequential scan because suppression only
+//            ever removes candidates;
 //   phase 3  the ring's less-flat candidates go through pcl::VoxelGrid(0.2) semantics: bounding box, voxel keys,
-//            block-wide bitonic sort by (key, position), one thread per voxel averages its members in order.
-// cloudNeighborPicked / cloudLabel live in persistent global arrays exactly like the reference's (never cleared);
-// the CTA stages its ring's window in shared memory and writes it back.
+//            block-wide stable radix sort by key (input order kept inside a voxel), one thread per voxel averages
+//            its members in order.
+// cloudNeighborPicked / cloudLabel live in persistent global arrays exactly like the reference's (never cleared).
 #include <cfloat>
 #include <climits>
+#include <cstdlib>
+#include <stdexcept>
 #include "engine.h"
 #include "kernel_utils.cuh"
 #include "parity_math.cuh"
@@ -23,32 +30,38 @@ namespace lego {
 
 struct RingWin {
     int lo, hi;                       // window [lo, hi) of cloud indices staged in shared memory
-    int* col; float* curv; signed char* picked; signed char* label; unsigned char* ground;   // shared
+    signed char* picked; signed char* label; unsigned char* stat;                            // shared
     const int* gcol; const float* gcurv; int* gpicked; int* glabel; const uint8_t* gground;  // global (lane base)
+    float edgeThreshold, surfThreshold;
 };
 __device__ __forceinline__ bool in_win(const RingWin& w, int i) { return i >= w.lo && i < w.hi; }
-__device__ __forceinline__ int w_col(const RingWin& w, int i) { return in_win(w, i) ? w.col[i - w.lo] : w.gcol[i]; }
-__device__ __forceinline__ float w_curv(const RingWin& w, int i) { return in_win(w, i) ? w.curv[i - w.lo] : w.gcurv[i]; }
+// bit 0: may become an edge point (curvature > edgeThreshold, not ground); bit 1: may become a flat point
+__device__ __forceinline__ unsigned char pick_stat(float curv, bool ground, float edgeT, float surfT) {
+    return (unsigned char)(((curv > edgeT && !ground) ? 1 : 0) | ((curv < surfT && ground) ? 2 : 0));
+}
+__device__ __forceinline__ int w_stat(const RingWin& w, int i) {
+    return in_win(w, i) ? (int)w.stat[i - w.lo] : (int)pick_stat(w.gcurv[i], w.gground[i] != 0, w.edgeThreshold, w.surfThreshold);
+}
 __device__ __forceinline__ int w_picked(const RingWin& w, int i) { return in_win(w, i) ? (int)w.picked[i - w.lo] : w.gpicked[i]; }
-__device__ __forceinline__ bool w_ground(const RingWin& w, int i) { return (in_win(w, i) ? w.ground[i - w.lo] : w.gground[i]) != 0; }
 __device__ __forceinline__ void w_set_picked(RingWin& w, int i) { if (in_win(w, i)) w.picked[i - w.lo] = 1; else w.gpicked[i] = 1; }
 __device__ __forceinline__ void w_set_label(RingWin& w, int i, int v) { if (in_win(w, i)) w.label[i - w.lo] = (signed char)v; else w.glabel[i] = v; }
 
 // Suppression of the picked point's neighbourhood (featureAssociation.cpp:720-732 and 751-767): the point and up to
 // five slots on either side are marked, each walk stopping at the first column gap > 10.  An index below 0 ends the
 // backward walk: the reference reads out of bounds there (quirk Q11) and the oracle defines it as "stop".
-// The same walk done by a whole warp: lanes 0-4 test the five forward steps, lanes 5-9 the five backward steps, a
-// ballot finds where each walk stops, and the lanes before the stop mark their slot.
+// General version for a point anywhere in the cloud (only the stale slot-4 entry of quirk Q11 can be outside its own
+// ring): lanes 0-4 test the five forward steps, lanes 5-9 the five backward steps, a ballot finds where each walk
+// stops, and the lanes before the stop mark their slot.
 __device__ __forceinline__ void suppress_warp(RingWin& w, int ind, int lid) {
     bool bad = false; int slot = ind;
     if (lid < 5) {
         const int l = lid + 1;
         slot = ind + l;
-        bad = abs(w_col(w, ind + l) - w_col(w, ind + l - 1)) > 10;
+        bad = abs(w.gcol[ind + l] - w.gcol[ind + l - 1]) > 10;
     } else if (lid < 10) {
         const int l = -(lid - 4);
         slot = ind + l;
-        bad = (ind + l < 0) || abs(w_col(w, ind + l) - w_col(w, ind + l + 1)) > 10;
+        bad = (ind + l < 0) || abs(w.gcol[ind + l] - w.gcol[ind + l + 1]) > 10;
     }
     const unsigned m = __ballot_sync(0xffffffffu, bad);
     const int nF = (m & 0x1fu) ? __ffs(m & 0x1fu) - 1 : 5;
@@ -61,7 +74,55 @@ __device__ __forceinline__ void sector_bounds(int start, int end, int j, int* sp
     *ep = (start * (5 - j) + end * (j + 1)) / 6 - 1;
 }
 
-__global__ void __launch_bounds__(256) fa_extract_kernel(IpDev d, FaDev f, Consts c, float leaf) {
+// ---- stable LSD radix sort pieces (8-bit digits) over lists of 16-bit entries; key(e) is the 32-bit key of entry e.
+// One warp owns `n` consecutive entries and 256 private counters; ranks inside a 32-entry chunk come from
+// __match_any_sync, so there are no shared-memory atomics and equal digits keep their order.
+__device__ __forceinline__ unsigned float_sort_key(float v) {
+    const unsigned b = __float_as_uint(v);
+    return b ^ ((unsigned)((int)b >> 31) | 0x80000000u);
+}
+template <class KeyF>
+__device__ __forceinline__ void warp_radix_count(const unsigned short* in, int n, int shift, unsigned short* h, int lid, KeyF key) {
+    for (int q0 = 0; q0 < n; q0 += 32) {
+        const int q = q0 + lid;
+        const bool valid = q < n;
+        const unsigned dg = valid ? ((key(in[q]) >> shift) & 255u) : 256u;
+        const unsigned peers = __match_any_sync(0xffffffffu, dg);
+        if (valid && lid == __ffs(peers) - 1) h[dg] = (unsigned short)(h[dg] + __popc(peers));
+        __syncwarp();
+    }
+}
+template <class KeyF>
+__device__ __forceinline__ void warp_radix_scatter(const unsigned short* in, unsigned short* out, int n, int shift, unsigned short* h, int lid, KeyF key) {
+    for (int q0 = 0; q0 < n; q0 += 32) {
+        const int q = q0 + lid;
+        const bool valid = q < n;
+        const unsigned short e = valid ? in[q] : (unsigned short)0;
+        const unsigned dg = valid ? ((key(e) >> shift) & 255u) : 256u;
+        const unsigned peers = __match_any_sync(0xffffffffu, dg);
+        const int leader = __ffs(peers) - 1;
+        int old = 0;
+        if (valid && lid == leader) { old = h[dg]; h[dg] = (unsigned short)(old + __popc(peers)); }
+        old = __shfl_sync(0xffffffffu, old, leader);
+        if (valid) out[old + __popc(peers & ((1u << lid) - 1u))] = e;
+        __syncwarp();
+    }
+}
+// exclusive scan of a warp's 256 counters, in place
+__device__ __forceinline__ void warp_scan256(unsigned short* h, int lid) {
+    int v[8], s = 0;
+#pragma unroll
+    for (int i = 0; i < 8; ++i) { v[i] = h[8 * lid + i]; s += v[i]; }
+    int run = warp_inclusive_scan(s) - s;
+#pragma unroll
+    for (int i = 0; i < 8; ++i) { h[8 * lid + i] = (unsigned short)run; run += v[i]; }
+    __syncwarp();
+}
+
+constexpr int FX_MAX_SECTOR = 13 * 32;   // entries one warp permutes from registers (Horizon_SCAN <= 2496)
+constexpr int FX_MAX_ITERS = 16;         // 256-wide sweeps over one ring (Horizon_SCAN <= 4096)
+
+__global__ void __launch_bounds__(256) fa_extract_kernel(IpDev d, FaDev f, Consts c, float leaf, int dbg) {
     extern __shared__ __align__(16) unsigned char smem[];
     const int lane = blockIdx.y, ring = blockIdx.x, tid = threadIdx.x;
     const int warp = tid >> 5, lid = tid & 31;
@@ -71,30 +132,40 @@ __global__ void __launch_bounds__(256) fa_extract_kernel(IpDev d, FaDev f, Const
     int* rc = f.ringCounts + ((size_t)lane * c.R + ring) * 4;
     if (rowEnd - rowStart <= 0) { if (tid < 4) rc[tid] = 0; return; }
 
-    // ---- shared memory carve-up; region A (items | col | curv) is reused for the voxel keys in phase 3 ----
+    // ---- shared memory carve-up ----
+    //   region A  8*C bytes   cloudSmoothness slots of the ring (phases 1-2), then voxel keys + positions (phase 3)
+    //   region B  4*Cw bytes  column indices while the derived bytes are computed, then the two sort index lists
+    //   region C  4*Cw bytes  picked | label | stat | reach, one byte per window slot each
     const int Cw = c.C + 8;
     ssr::Item* items = reinterpret_cast<ssr::Item*>(smem);
+    unsigned* vkey = reinterpret_cast<unsigned*>(smem);
+    unsigned short* cpos = reinterpret_cast<unsigned short*>(smem + (size_t)4 * c.C);
     int* s_col = reinterpret_cast<int*>(smem + (size_t)8 * c.C);
-    float* s_curv = reinterpret_cast<float*>(smem + (size_t)8 * c.C + (size_t)4 * Cw);
-    unsigned long long* vkeys = reinterpret_cast<unsigned long long*>(smem);
-    unsigned char* tail = smem + (size_t)8 * c.C + (size_t)8 * Cw;
+    unsigned short* ordA = reinterpret_cast<unsigned short*>(smem + (size_t)8 * c.C);
+    unsigned short* ordB = ordA + Cw;
+    unsigned char* tail = smem + (size_t)8 * c.C + (size_t)4 * Cw;
     signed char* s_picked = reinterpret_cast<signed char*>(tail);
     signed char* s_label = reinterpret_cast<signed char*>(tail + Cw);
-    unsigned char* s_ground = tail + 2 * Cw;
-    __shared__ int s_sp[6], s_ep[6], s_tie[6];
+    unsigned char* s_stat = tail + 2 * Cw;
+    unsigned char* s_reach = tail + 3 * Cw;   // forward steps | backward steps << 4 of the suppression walk
+    __shared__ unsigned short s_hist[8 * 256];
+    __shared__ int s_sp[6], s_ep[6];
     __shared__ int s_pickSharp[12], s_pickLess[120], s_pickFlat[24], s_nPick[3];
     __shared__ float s_red[6][8];
     __shared__ int s_scan[8];
-    __shared__ int s_carry;
+    __shared__ int s_cnt[FX_MAX_ITERS * 8 + 1];
 
     RingWin w;
     w.lo = max(rowStart - 1, 0); w.hi = rowEnd;
-    w.col = s_col; w.curv = s_curv; w.picked = s_picked; w.label = s_label; w.ground = s_ground;
+    w.picked = s_picked; w.label = s_label; w.stat = s_stat;
     w.gcol = d.segCol + base; w.gcurv = f.curv + base; w.gpicked = f.picked + base; w.glabel = f.label + base; w.gground = d.segGround + base;
+    w.edgeThreshold = c.edgeThreshold; w.surfThreshold = c.surfThreshold;
 
+    // ---- phase 0: stage the window ----
     for (int k = w.lo + tid; k < w.hi; k += blockDim.x) {
-        s_col[k - w.lo] = w.gcol[k]; s_curv[k - w.lo] = w.gcurv[k];
-        s_picked[k - w.lo] = (signed char)w.gpicked[k]; s_label[k - w.lo] = (signed char)w.glabel[k]; s_ground[k - w.lo] = w.gground[k];
+        s_col[k - w.lo] = w.gcol[k];
+        s_picked[k - w.lo] = (signed char)w.gpicked[k]; s_label[k - w.lo] = (signed char)w.glabel[k];
+        s_stat[k - w.lo] = pick_stat(w.gcurv[k], w.gground[k] != 0, c.edgeThreshold, c.surfThreshold);
     }
     for (int k = start + tid; k < end; k += blockDim.x) {
         ssr::Item it;
@@ -102,120 +173,107 @@ __global__ void __launch_bounds__(256) fa_extract_kernel(IpDev d, FaDev f, Const
         else { it.value = w.gcurv[k]; it.ind = k; }
         items[k - start] = it;
     }
-    if (tid < 6) { int sp, ep; sector_bounds(start, end, tid, &sp, &ep); s_sp[tid] = sp; s_ep[tid] = ep; s_tie[tid] = 0; }
+    if (tid < 6) { int sp, ep; sector_bounds(start, end, tid, &sp, &ep); s_sp[tid] = sp; s_ep[tid] = ep; }
     if (tid < 3) s_nPick[tid] = 0;
     __syncthreads();
+    // reach of the suppression walk from every slot a sector can pick, [start, end): slots k-5 .. k+5 are inside the window
+    for (int k = start + tid; k < end; k += blockDim.x) {
+        const int* cc = s_col + (k - w.lo);
+        int nF = 0, nB = 0;
+        while (nF < 5 && abs(cc[nF + 1] - cc[nF]) <= 10) ++nF;
+        while (nB < 5 && k - nB - 1 >= 0 && abs(cc[-nB - 1] - cc[-nB]) <= 10) ++nB;
+        s_reach[k - w.lo] = (unsigned char)(nF | (nB << 4));
+    }
+    __syncthreads();   // region B becomes the sort index lists
 
-    // ---- phase 1: std::sort(cloudSmoothness.begin()+sp, cloudSmoothness.begin()+ep) per sector ----
-    // A sector whose curvatures are all distinct has exactly one sorted order, so it is sorted in parallel by ranking
-    // (every thread counts the smaller keys of its items).  Equal curvatures are common (quirk Q17) and their final
-    // order depends on libstdc++'s introsort path: those sectors keep their original arrangement and one thread replays
-    // std::sort on it.
-    {
-        constexpr int MAXI = 9;                     // items per thread: covers Horizon_SCAN <= 2304
-        const bool rankable = end - start <= MAXI * 256;
-        ssr::Item mine[MAXI]; int dst[MAXI], sec[MAXI];
+    // ---- phase 1: std::sort(cloudSmoothness.begin()+sp, cloudSmoothness.begin()+ep) per sector, one warp each ----
+    // A sector whose curvatures are all distinct has exactly one sorted order, which the radix sort finds.  Equal
+    // curvatures do occur (quirk Q17) and their final order depends on libstdc++'s introsort path: such a sector is
+    // left in its original arrangement and one thread replays std::sort on it.
+    if (warp < 6) {
+        const int sp = s_sp[warp], ep = s_ep[warp];
+        const int n = ep - sp, b = sp - start;
+        bool replay = n > FX_MAX_SECTOR || (dbg & 1);
+        if (!replay && n > 1) {
+            unsigned short* in = ordA + b; unsigned short* out = ordB + b;
+            unsigned short* h = s_hist + warp * 256;
+            auto key = [&](unsigned short e) -> unsigned { return float_sort_key(items[b + e].value); };
+            for (int q = lid; q < n; q += 32) in[q] = (unsigned short)q;
+            __syncwarp();
+            for (int shift = 0; shift < 32; shift += 8) {
 #pragma unroll
-        for (int u = 0; u < MAXI; ++u) {
-            const int k = start + tid + u * 256;
-            dst[u] = -1; sec[u] = 0;
-            if (rankable && k < end) {
-                int j = -1;
+                for (int i = 0; i < 8; ++i) h[lid + 32 * i] = 0;
+                __syncwarp();
+                warp_radix_count(in, n, shift, h, lid, key);
+                warp_scan256(h, lid);
+                warp_radix_scatter(in, out, n, shift, h, lid, key);
+                unsigned short* t = in; in = out; out = t;
+            }
+            bool tie = false;
+            for (int q = lid; q + 1 < n; q += 32) tie |= items[b + in[q]].value == items[b + in[q + 1]].value;
+            if (__any_sync(0xffffffffu, tie)) replay = true;
+            else {
+                ssr::Item mine[FX_MAX_SECTOR / 32];
 #pragma unroll
-                for (int t = 0; t < 6; ++t) if (k >= s_sp[t] && k < s_ep[t]) j = t;
-                if (j >= 0) {
-                    const ssr::Item it = items[k - start];
-                    const int sp = s_sp[j], ep = s_ep[j];
-                    // rank = number of smaller curvatures in the sector, eq = number of equal ones (itself included).
-                    // The curvatures are read from the staged cloudCurvature window (contiguous floats, 4 per load);
-                    // slot 4 of cloudSmoothness is the one entry that is NOT cloudCurvature (quirk Q11), patched below.
-                    const float x = it.value;
-                    const float* vp = s_curv + (sp - w.lo);
-                    const int n = ep - sp;
-                    int rank = 0, eq = 0, q = 0;
-                    for (; q < n && ((size_t)(vp + q) & 15); ++q) { const float v = vp[q]; rank += v < x; eq += v == x; }
-                    for (; q + 4 <= n; q += 4) {
-                        const float4 v = *reinterpret_cast<const float4*>(vp + q);
-                        rank += (v.x < x) + (v.y < x) + (v.z < x) + (v.w < x);
-                        eq += (v.x == x) + (v.y == x) + (v.z == x) + (v.w == x);
-                    }
-                    for (; q < n; ++q) { const float v = vp[q]; rank += v < x; eq += v == x; }
-                    if (start == 4 && j == 0) {
-                        const float c4 = s_curv[4 - w.lo], t4 = items[0].value;
-                        rank += (t4 < x) - (c4 < x); eq += (t4 == x) - (c4 == x);
-                    }
-                    if (eq > 1) s_tie[j] = 1;
-                    mine[u] = it; dst[u] = sp - start + rank; sec[u] = j;
-                }
+                for (int u = 0; u < FX_MAX_SECTOR / 32; ++u) { const int q = lid + 32 * u; if (q < n) mine[u] = items[b + in[q]]; }
+                __syncwarp();
+#pragma unroll
+                for (int u = 0; u < FX_MAX_SECTOR / 32; ++u) { const int q = lid + 32 * u; if (q < n) items[b + q] = mine[u]; }
             }
         }
-        if (!rankable && tid < 6) s_tie[tid] = 1;
-        __syncthreads();
-#pragma unroll
-        for (int u = 0; u < MAXI; ++u) if (dst[u] >= 0 && !s_tie[sec[u]]) items[dst[u]] = mine[u];
-        if (lid == 0 && warp < 6 && s_tie[warp]) {
-            const int sp = s_sp[warp], ep = s_ep[warp];
-            if (sp < ep) ssr::std_sort(items + (sp - start), ep - sp);
-        }
+        if (replay && lid == 0 && n > 1 && !(dbg & 1)) ssr::std_sort(items + b, n);
     }
     __syncthreads();
     if (tid == 0 && start == 4 && s_sp[0] < s_ep[0]) { f.slot4val[lane] = items[0].value; f.slot4ind[lane] = items[0].ind; }
 
     // ---- phase 2: greedy selection, sectors in order, one warp ----
+    // Every lane keeps its candidate's state in registers: index + reach (packed), static eligibility, picked flag.
+    // A pick is broadcast with one shuffle; the lanes inside its reach drop out by comparing indices, and lanes
+    // 0..10 mark the shared window for the chunks that follow.
     if (warp == 0) {
         int nSharp = 0, nLess = 0, nFlat = 0;
-        for (int j = 0; j < 6; ++j) {
+        for (int j = 0; j < ((dbg & 2) ? 0 : 6); ++j) {
             const int sp = s_sp[j], ep = s_ep[j];
             if (sp >= ep) continue;
-            // corner pass, k = ep down to sp (featureAssociation.cpp:701-734)
-            int picks = 0; bool stop = false;
-            for (int top = ep; top >= sp && !stop; top -= 32) {
-                const int k = top - lid;
-                const bool inr = k >= sp;
-                const int ind = inr ? items[k - start].ind : 0;
-                unsigned done = 0u;
-                while (true) {
-                    const bool elig = inr && !((done >> lid) & 1u) && w_picked(w, ind) == 0 && w_curv(w, ind) > c.edgeThreshold && !w_ground(w, ind);
-                    const unsigned m = __ballot_sync(0xffffffffu, elig);
-                    if (!m) break;
-                    const int first = __ffs(m) - 1;
-                    const int pind = __shfl_sync(0xffffffffu, ind, first);
-                    ++picks;
-                    if (picks > 20) { stop = true; break; }
-                    if (lid == 0) {   // the points themselves are copied by the whole CTA after the selection
-                        if (picks <= 2) { w_set_label(w, pind, 2); s_pickSharp[nSharp] = pind; s_pickLess[nLess] = pind; }
-                        else { w_set_label(w, pind, 1); s_pickLess[nLess] = pind; }
+            for (int pass = 0; pass < 2; ++pass) {
+                // pass 0: corner points, k = ep down to sp (featureAssociation.cpp:701-734)
+                // pass 1: flat points, k = sp up to ep (featureAssociation.cpp:736-769); its 4th pick breaks BEFORE suppression (Q12)
+                int picks = 0; bool stop = false;
+                for (int c0 = 0; c0 <= ep - sp && !stop; c0 += 32) {
+                    const int k = pass == 0 ? ep - c0 - lid : sp + c0 + lid;
+                    const bool inr = k >= sp && k <= ep;
+                    const int ind = inr ? items[k - start].ind : 0;
+                    const bool fastp = inr && ind >= start && ind < end;
+                    const int packed = ind | ((fastp ? (int)s_reach[ind - w.lo] : 0xff) << 24);
+                    const bool cand = inr && ((w_stat(w, ind) >> pass) & 1);
+                    bool pk = inr ? w_picked(w, ind) != 0 : true;
+                    while (true) {
+                        const unsigned m = __ballot_sync(0xffffffffu, cand && !pk);
+                        if (!m) break;
+                        const int first = __ffs(m) - 1;
+                        const int pp = __shfl_sync(0xffffffffu, packed, first);
+                        const int pind = pp & 0xffffff, reach = (pp >> 24) & 0xff;
+                        ++picks;
+                        if (pass == 0 && picks > 20) { stop = true; break; }
+                        if (lid == 0) {   // the points themselves are copied by the whole CTA after the selection
+                            if (pass == 1) { w_set_label(w, pind, -1); s_pickFlat[nFlat] = pind; }
+                            else if (picks <= 2) { w_set_label(w, pind, 2); s_pickSharp[nSharp] = pind; s_pickLess[nLess] = pind; }
+                            else { w_set_label(w, pind, 1); s_pickLess[nLess] = pind; }
+                        }
+                        if (pass == 1) ++nFlat; else { ++nLess; if (picks <= 2) ++nSharp; }
+                        if (pass == 1 && picks >= 4) { stop = true; break; }
+                        if (reach != 0xff) {
+                            const int nF = reach & 15, nB = reach >> 4;
+                            const int o = lid - 5;
+                            if (lid <= 10 && o >= -nB && o <= nF) s_picked[pind + o - w.lo] = 1;
+                            if (ind >= pind - nB && ind <= pind + nF) pk = true;
+                        } else {
+                            suppress_warp(w, pind, lid);
+                            __syncwarp();
+                            pk = inr ? w_picked(w, ind) != 0 : true;
+                        }
                     }
-                    suppress_warp(w, pind, lid);
-                    if (picks <= 2) ++nSharp;
-                    ++nLess;
-                    __syncwarp();
-                    done |= (first == 31) ? 0xffffffffu : ((2u << first) - 1u);
-                }
-            }
-            // flat pass, k = sp up to ep (featureAssociation.cpp:736-769); the 4th pick breaks BEFORE suppression (Q12)
-            picks = 0; stop = false;
-            for (int bot = sp; bot <= ep && !stop; bot += 32) {
-                const int k = bot + lid;
-                const bool inr = k <= ep;
-                const int ind = inr ? items[k - start].ind : 0;
-                unsigned done = 0u;
-                while (true) {
-                    const bool elig = inr && !((done >> lid) & 1u) && w_picked(w, ind) == 0 && w_curv(w, ind) < c.surfThreshold && w_ground(w, ind);
-                    const unsigned m = __ballot_sync(0xffffffffu, elig);
-                    if (!m) break;
-                    const int first = __ffs(m) - 1;
-                    const int pind = __shfl_sync(0xffffffffu, ind, first);
-                    ++picks;
-                    if (lid == 0) {
-                        w_set_label(w, pind, -1);
-                        s_pickFlat[nFlat] = pind;
-                    }
-                    if (picks < 4) suppress_warp(w, pind, lid);
-                    ++nFlat;
-                    __syncwarp();
-                    if (picks >= 4) { stop = true; break; }
-                    done |= (first == 31) ? 0xffffffffu : ((2u << first) - 1u);
+                    __syncwarp();   // marks of this chunk are visible to the loads of the next one
                 }
             }
         }
@@ -237,6 +295,7 @@ __global__ void __launch_bounds__(256) fa_extract_kernel(IpDev d, FaDev f, Const
     for (int k = w.lo + tid; k < w.hi - 1; k += blockDim.x) { w.gpicked[k] = s_picked[k - w.lo]; w.glabel[k] = s_label[k - w.lo]; }
 
     // ---- phase 3: less-flat candidates of this ring -> VoxelGrid(leaf) (featureAssociation.cpp:771-782) ----
+    if (dbg & 4) { if (tid == 0) rc[3] = 0; return; }
     const float4* adj = f.segAdj + base;
     auto is_cand = [&](int k) -> bool {
         bool in_sector = false;
@@ -244,23 +303,38 @@ __global__ void __launch_bounds__(256) fa_extract_kernel(IpDev d, FaDev f, Const
         for (int j = 0; j < 6; ++j) in_sector |= (s_sp[j] < s_ep[j] && k >= s_sp[j] && k <= s_ep[j]);
         return in_sector && s_label[k - w.lo] <= 0;
     };
+    // exclusive scan of the per-(sweep, warp) counts in s_cnt[0 .. nSlots) by warp 0; the total lands in s_cnt[nSlots]
+    auto scan_counts = [&](int nSlots) {
+        if (warp == 0) {
+            int v[FX_MAX_ITERS * 8 / 32], s = 0;
+#pragma unroll
+            for (int i = 0; i < FX_MAX_ITERS * 8 / 32; ++i) { const int q = lid * (FX_MAX_ITERS * 8 / 32) + i; v[i] = q < nSlots ? s_cnt[q] : 0; s += v[i]; }
+            int run = warp_inclusive_scan(s) - s;
+#pragma unroll
+            for (int i = 0; i < FX_MAX_ITERS * 8 / 32; ++i) { const int q = lid * (FX_MAX_ITERS * 8 / 32) + i; if (q < nSlots) s_cnt[q] = run; run += v[i]; }
+            if (lid == 31) s_cnt[nSlots] = run;
+        }
+    };
+    const int nSweep = (end - start + 255) >> 8;      // <= FX_MAX_ITERS (checked on the host)
     float mn[3] = {FLT_MAX, FLT_MAX, FLT_MAX}, mx[3] = {-FLT_MAX, -FLT_MAX, -FLT_MAX};
-    int myCount = 0;
-    for (int k = start + tid; k < end; k += blockDim.x) if (is_cand(k)) {
-        const float4 p = adj[k];
-        mn[0] = fminf(mn[0], p.x); mn[1] = fminf(mn[1], p.y); mn[2] = fminf(mn[2], p.z);
-        mx[0] = fmaxf(mx[0], p.x); mx[1] = fmaxf(mx[1], p.y); mx[2] = fmaxf(mx[2], p.z);
-        ++myCount;
+    for (int it = 0; it < nSweep; ++it) {
+        const int k = start + it * 256 + tid;
+        const bool flag = k < end && is_cand(k);
+        if (flag) {
+            const float4 p = adj[k];
+            mn[0] = fminf(mn[0], p.x); mn[1] = fminf(mn[1], p.y); mn[2] = fminf(mn[2], p.z);
+            mx[0] = fmaxf(mx[0], p.x); mx[1] = fmaxf(mx[1], p.y); mx[2] = fmaxf(mx[2], p.z);
+        }
+        const unsigned bal = __ballot_sync(0xffffffffu, flag);
+        if (lid == 0) s_cnt[it * 8 + warp] = __popc(bal);
     }
-    __syncthreads();   // everyone is done with items / col / curv before region A becomes vkeys
 #pragma unroll
     for (int a = 0; a < 3; ++a) { mn[a] = warp_min_f(mn[a]); mx[a] = warp_max_f(mx[a]); }
     if (lid == 0) { for (int a = 0; a < 3; ++a) { s_red[a][warp] = mn[a]; s_red[3 + a][warp] = mx[a]; } }
-    myCount = warp_sum(myCount);
-    if (lid == 0) s_scan[warp] = myCount;
+    __syncthreads();   // also: everyone is done with the cloudSmoothness slots before region A becomes vkey / cpos
+    scan_counts(nSweep * 8);
     __syncthreads();
-    int nCand = 0;
-    for (int q = 0; q < 8; ++q) nCand += s_scan[q];
+    const int nCand = s_cnt[nSweep * 8];
     if (nCand == 0) { if (tid == 0) rc[3] = 0; return; }
 #pragma unroll
     for (int a = 0; a < 3; ++a) {
@@ -276,74 +350,91 @@ __global__ void __launch_bounds__(256) fa_extract_kernel(IpDev d, FaDev f, Const
         minb[a] = (int)floorf(PM_MUL(mn[a], inv));
         divb[a] = (int)floorf(PM_MUL(mx[a], inv)) - minb[a] + 1;
     }
+    // pcl::VoxelGrid refuses a grid whose index would overflow an int and passes the cloud through unfiltered
     const bool overflow = dd[0] * dd[1] * dd[2] > (long long)INT_MAX;
+    const long long cells = (long long)divb[0] * divb[1] * divb[2];
+    const int keyBits = (overflow || cells <= 1) ? 0 : min(32, 64 - __clzll(cells - 1));
     float4* out = f.ringLessFlat + ((size_t)lane * c.R + ring) * c.C;
-    int n2 = 1; while (n2 < nCand) n2 <<= 1;
-    __syncthreads();
-    // ordered list of candidates with their voxel keys: key << 12 | (k - start)
-    if (tid == 0) s_carry = 0;
-    __syncthreads();
-    for (int k0 = start; k0 < end; k0 += blockDim.x) {
-        const int k = k0 + tid;
-        const int flag = (k < end && is_cand(k)) ? 1 : 0;
-        const int inc = warp_inclusive_scan(flag);
-        if (lid == 31) s_scan[warp] = inc;
-        __syncthreads();
-        int off = s_carry + inc - flag;
-        for (int q = 0; q < warp; ++q) off += s_scan[q];
+    // ordered list of candidates: voxel index, position in the ring, identity permutation
+    for (int it = 0; it < nSweep; ++it) {
+        const int k = start + it * 256 + tid;
+        const bool flag = k < end && is_cand(k);
+        const unsigned bal = __ballot_sync(0xffffffffu, flag);
         if (flag) {
+            const int off = s_cnt[it * 8 + warp] + __popc(bal & ((1u << lid) - 1u));
             const float4 p = adj[k];
             const int i0 = (int)PM_SUB(floorf(PM_MUL(p.x, inv)), (float)minb[0]);
             const int i1 = (int)PM_SUB(floorf(PM_MUL(p.y, inv)), (float)minb[1]);
             const int i2 = (int)PM_SUB(floorf(PM_MUL(p.z, inv)), (float)minb[2]);
-            const long long key = overflow ? (long long)off : ((long long)i0 + (long long)i1 * divb[0] + (long long)i2 * divb[0] * divb[1]);
-            vkeys[off] = ((unsigned long long)key << 12) | (unsigned long long)(k - start);
+            vkey[off] = overflow ? (unsigned)off : (unsigned)((long long)i0 + (long long)i1 * divb[0] + (long long)i2 * divb[0] * divb[1]);
+            cpos[off] = (unsigned short)(k - start);
+            ordA[off] = (unsigned short)off;
         }
-        __syncthreads();
-        if (tid == 0) { int s = 0; for (int q = 0; q < 8; ++q) s += s_scan[q]; s_carry += s; }
-        __syncthreads();
     }
-    for (int i = nCand + tid; i < n2; i += blockDim.x) vkeys[i] = ~0ull;
     __syncthreads();
-    for (int kk = 2; kk <= n2; kk <<= 1)
-        for (int jj = kk >> 1; jj > 0; jj >>= 1) {
-            for (int i = tid; i < n2; i += blockDim.x) {
-                const int p = i ^ jj;
-                if (p > i) {
-                    const unsigned long long a = vkeys[i], b = vkeys[p];
-                    const bool asc = (i & kk) == 0;
-                    if ((a > b) == asc) { vkeys[i] = b; vkeys[p] = a; }
-                }
+    // block-wide stable radix sort of the permutation by voxel index: warp w owns a contiguous share of the list
+    unsigned short* ord = ordA;
+    {
+        unsigned short* in = ordA; unsigned short* outl = ordB;
+        const int per = ((nCand + 255) >> 8) << 5;
+        const int wb = min(warp * per, nCand), nw = min(wb + per, nCand) - wb;
+        unsigned short* h = s_hist + warp * 256;
+        auto key = [&](unsigned short e) -> unsigned { return vkey[e]; };
+        for (int shift = 0; shift < keyBits; shift += 8) {
+#pragma unroll
+            for (int q = 0; q < 8; ++q) s_hist[q * 256 + tid] = 0;
+            __syncthreads();
+            warp_radix_count(in + wb, nw, shift, h, lid, key);
+            __syncthreads();
+            {   // digit-major, warp-minor exclusive scan of the 8 x 256 counters: thread = digit
+                int run = 0;
+#pragma unroll
+                for (int q = 0; q < 8; ++q) { const int t = s_hist[q * 256 + tid]; s_hist[q * 256 + tid] = (unsigned short)run; run += t; }
+                const int inc = warp_inclusive_scan(run);
+                if (lid == 31) s_scan[warp] = inc;
+                __syncthreads();
+                int basep = inc - run;
+                for (int q = 0; q < warp; ++q) basep += s_scan[q];
+#pragma unroll
+                for (int q = 0; q < 8; ++q) s_hist[q * 256 + tid] = (unsigned short)(s_hist[q * 256 + tid] + basep);
             }
             __syncthreads();
+            warp_radix_scatter(in + wb, outl, nw, shift, h, lid, key);
+            __syncthreads();
+            unsigned short* t = in; in = outl; outl = t;
         }
-    // one output per distinct key, mean of the members in sorted order (float32 sums, then divide)
-    if (tid == 0) s_carry = 0;
+        ord = in;
+    }
+    // one output per distinct voxel, mean of the members in sorted order (float32 sums, then divide)
+    const int nHeadSweep = (nCand + 255) >> 8;
+    for (int it = 0; it < nHeadSweep; ++it) {
+        const int i = it * 256 + tid;
+        const bool head = i < nCand && (i == 0 || vkey[ord[i - 1]] != vkey[ord[i]]);
+        const unsigned bal = __ballot_sync(0xffffffffu, head);
+        if (lid == 0) s_cnt[it * 8 + warp] = __popc(bal);
+    }
     __syncthreads();
-    for (int i0 = 0; i0 < nCand; i0 += blockDim.x) {
-        const int i = i0 + tid;
-        int head = 0;
-        if (i < nCand) head = (i == 0 || (vkeys[i - 1] >> 12) != (vkeys[i] >> 12)) ? 1 : 0;
-        const int inc = warp_inclusive_scan(head);
-        if (lid == 31) s_scan[warp] = inc;
-        __syncthreads();
-        int off = s_carry + inc - head;
-        for (int q = 0; q < warp; ++q) off += s_scan[q];
+    scan_counts(nHeadSweep * 8);
+    __syncthreads();
+    for (int it = 0; it < nHeadSweep; ++it) {
+        const int i = it * 256 + tid;
+        const bool head = i < nCand && (i == 0 || vkey[ord[i - 1]] != vkey[ord[i]]);
+        const unsigned bal = __ballot_sync(0xffffffffu, head);
         if (head) {
-            const unsigned long long key = vkeys[i] >> 12;
+            const int off = s_cnt[it * 8 + warp] + __popc(bal & ((1u << lid) - 1u));
+            const unsigned key = vkey[ord[i]];
             float sx = 0.f, sy = 0.f, sz = 0.f, sw = 0.f; int cnt = 0;
-            for (int m = i; m < nCand && (vkeys[m] >> 12) == key; ++m) {
-                const float4 p = adj[start + (int)(vkeys[m] & 0xfffull)];
+            for (int m = i; m < nCand; ++m) {
+                const int e = ord[m];
+                if (vkey[e] != key) break;
+                const float4 p = adj[start + (int)cpos[e]];
                 sx = PM_ADD(sx, p.x); sy = PM_ADD(sy, p.y); sz = PM_ADD(sz, p.z); sw = PM_ADD(sw, p.w); ++cnt;
             }
             const float fc = (float)cnt;
             out[off] = make_float4(PM_DIV(sx, fc), PM_DIV(sy, fc), PM_DIV(sz, fc), PM_DIV(sw, fc));
         }
-        __syncthreads();
-        if (tid == 0) { int s = 0; for (int q = 0; q < 8; ++q) s += s_scan[q]; s_carry += s; }
-        __syncthreads();
     }
-    if (tid == 0) rc[3] = s_carry;
+    if (tid == 0) rc[3] = s_cnt[nHeadSweep * 8];
 }
 
 // Concatenate the ring-local lists in ring order (the reference appends ring by ring, featureAssociation.cpp:782):
@@ -385,14 +476,16 @@ void Engine::adjustDistortionCalculateSmoothnessMarkOccluded() {
 }
 
 void Engine::extractFeatures() {
-    const size_t smem = (size_t)8 * c.C + (size_t)8 * (c.C + 8) + (size_t)3 * (c.C + 8);
+    const size_t smem = (size_t)8 * c.C + (size_t)8 * (c.C + 8);   // regions A, B, C of fa_extract_kernel
+    if (c.C > 4096 - 8) { set_last_error("Horizon_SCAN > 4088 is not supported by fa_extract_kernel"); throw std::length_error("capacity"); }
     static bool attr_set = false;
     if (!attr_set) {
         cuda_check(cudaFuncSetAttribute(fa_extract_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 160 * 1024), "smem attr");
         attr_set = true;
     }
+    static const int dbg = getenv("LEGO_DBG_SKIP") ? atoi(getenv("LEGO_DBG_SKIP")) : 0;
     dim3 g(c.R, c.L);
-    { ProfScope ps(this, "fa_extract_kernel"); fa_extract_kernel<<<g, 256, smem, stream>>>(ip, fa, c, 0.2f); }   // downSizeFilter.setLeafSize(0.2,...) featureAssociation.cpp:225
+    { ProfScope ps(this, "fa_extract_kernel"); fa_extract_kernel<<<g, 256, smem, stream>>>(ip, fa, c, 0.2f, dbg); }   // downSizeFilter.setLeafSize(0.2,...) featureAssociation.cpp:225
     { ProfScope ps(this, "fa_gather_features_kernel"); fa_gather_features_kernel<<<dim3(c.R, c.L), 128, 0, stream>>>(fa, c); }
     launches += 2;
 }
