@@ -19,7 +19,7 @@ EXPORTED = [
     "lego_pipeline_create", "lego_pipeline_destroy", "lego_pipeline_step", "lego_pipeline_get_poses",
     "lego_pipeline_sync", "lego_pipeline_launch_count", "lego_pipeline_download", "lego_pipeline_upload",
     "lego_pipeline_timer_record", "lego_pipeline_timer_elapsed", "lego_pipeline_timer_elapsed_between", "lego_pipeline_profile", "lego_pipeline_profile_read",
-    "lego_selftest_atan2f", "lego_selftest_std_sort", "lego_selftest_voxel_grid",
+    "lego_selftest_atan2f", "lego_selftest_std_sort", "lego_selftest_warp_sort", "lego_selftest_voxel_grid",
 ]
 
 _lib = None
@@ -84,6 +84,15 @@ def selftest_std_sort(values, offsets):
     lib = load()
     lib.lego_selftest_std_sort.argtypes = [ctypes.c_void_p, ctypes.c_void_p, ctypes.c_int, ctypes.c_void_p]
     _check(lib.lego_selftest_std_sort(values.ctypes.data, offsets.ctypes.data, offsets.size - 1, out.ctypes.data), "lego_selftest_std_sort")
+    return out
+
+
+def selftest_warp_sort(values, offsets):
+    values = np.ascontiguousarray(values, np.float32); offsets = np.ascontiguousarray(offsets, np.int32)
+    out = np.empty(values.size, np.int32)
+    lib = load()
+    lib.lego_selftest_warp_sort.argtypes = [ctypes.c_void_p, ctypes.c_void_p, ctypes.c_int, ctypes.c_void_p]
+    _check(lib.lego_selftest_warp_sort(values.ctypes.data, offsets.ctypes.data, offsets.size - 1, out.ctypes.data), "lego_selftest_warp_sort")
     return out
 
 

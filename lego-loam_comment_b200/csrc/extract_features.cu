@@ -25,6 +25,7 @@
 #include "kernel_utils.cuh"
 #include "parity_math.cuh"
 #include "std_sort_replay.cuh"
+#include "warp_sort.cuh"
 
 namespace lego {
 
@@ -74,52 +75,7 @@ __device__ __forceinline__ void sector_bounds(int start, int end, int j, int* sp
     *ep = (start * (5 - j) + end * (j + 1)) / 6 - 1;
 }
 
-// ---- stable LSD radix sort pieces (8-bit digits) over lists of 16-bit entries; key(e) is the 32-bit key of entry e.
-// One warp owns `n` consecutive entries and 256 private counters; ranks inside a 32-entry chunk come from
-// __match_any_sync, so there are no shared-memory atomics and equal digits keep their order.
-__device__ __forceinline__ unsigned float_sort_key(float v) {
-    const unsigned b = __float_as_uint(v);
-    return b ^ ((unsigned)((int)b >> 31) | 0x80000000u);
-}
-template <class KeyF>
-__device__ __forceinline__ void warp_radix_count(const unsigned short* in, int n, int shift, unsigned short* h, int lid, KeyF key) {
-    for (int q0 = 0; q0 < n; q0 += 32) {
-        const int q = q0 + lid;
-        const bool valid = q < n;
-        const unsigned dg = valid ? ((key(in[q]) >> shift) & 255u) : 256u;
-        const unsigned peers = __match_any_sync(0xffffffffu, dg);
-        if (valid && lid == __ffs(peers) - 1) h[dg] = (unsigned short)(h[dg] + __popc(peers));
-        __syncwarp();
-    }
-}
-template <class KeyF>
-__device__ __forceinline__ void warp_radix_scatter(const unsigned short* in, unsigned short* out, int n, int shift, unsigned short* h, int lid, KeyF key) {
-    for (int q0 = 0; q0 < n; q0 += 32) {
-        const int q = q0 + lid;
-        const bool valid = q < n;
-        const unsigned short e = valid ? in[q] : (unsigned short)0;
-        const unsigned dg = valid ? ((key(e) >> shift) & 255u) : 256u;
-        const unsigned peers = __match_any_sync(0xffffffffu, dg);
-        const int leader = __ffs(peers) - 1;
-        int old = 0;
-        if (valid && lid == leader) { old = h[dg]; h[dg] = (unsigned short)(old + __popc(peers)); }
-        old = __shfl_sync(0xffffffffu, old, leader);
-        if (valid) out[old + __popc(peers & ((1u << lid) - 1u))] = e;
-        __syncwarp();
-    }
-}
-// exclusive scan of a warp's 256 counters, in place
-__device__ __forceinline__ void warp_scan256(unsigned short* h, int lid) {
-    int v[8], s = 0;
-#pragma unroll
-    for (int i = 0; i < 8; ++i) { v[i] = h[8 * lid + i]; s += v[i]; }
-    int run = warp_inclusive_scan(s) - s;
-#pragma unroll
-    for (int i = 0; i < 8; ++i) { h[8 * lid + i] = (unsigned short)run; run += v[i]; }
-    __syncwarp();
-}
-
-constexpr int FX_MAX_SECTOR = 13 * 32;   // entries one warp permutes from registers (Horizon_SCAN <= 2496)
+constexpr int FX_MAX_SECTOR = WS_MAX_SORT; // sector sizes the warp sort takes (Horizon_SCAN <= 2496); larger ones use the serial replay
 constexpr int FX_MAX_ITERS = 16;         // 256-wide sweeps over one ring (Horizon_SCAN <= 4096)
 
 __global__ void __launch_bounds__(256) fa_extract_kernel(IpDev d, FaDev f, Consts c, float leaf, int dbg) {
@@ -188,40 +144,16 @@ __global__ void __launch_bounds__(256) fa_extract_kernel(IpDev d, FaDev f, Const
 
     // ---- phase 1: std::sort(cloudSmoothness.begin()+sp, cloudSmoothness.begin()+ep) per sector, one warp each ----
     // A sector whose curvatures are all distinct has exactly one sorted order, which the radix sort finds.  Equal
-    // curvatures do occur (quirk Q17) and their final order depends on libstdc++'s introsort path: such a sector is
-    // left in its original arrangement and one thread replays std::sort on it.
+    // curvatures do occur (quirk Q17) and their final order depends on libstdc++'s introsort path: for such a sector
+    // the warp replays introsort's partitions first (warp_sort.cuh).
     if (warp < 6) {
         const int sp = s_sp[warp], ep = s_ep[warp];
         const int n = ep - sp, b = sp - start;
-        bool replay = n > FX_MAX_SECTOR || (dbg & 1);
-        if (!replay && n > 1) {
-            unsigned short* in = ordA + b; unsigned short* out = ordB + b;
-            unsigned short* h = s_hist + warp * 256;
-            auto key = [&](unsigned short e) -> unsigned { return float_sort_key(items[b + e].value); };
-            for (int q = lid; q < n; q += 32) in[q] = (unsigned short)q;
-            __syncwarp();
-            for (int shift = 0; shift < 32; shift += 8) {
-#pragma unroll
-                for (int i = 0; i < 8; ++i) h[lid + 32 * i] = 0;
-                __syncwarp();
-                warp_radix_count(in, n, shift, h, lid, key);
-                warp_scan256(h, lid);
-                warp_radix_scatter(in, out, n, shift, h, lid, key);
-                unsigned short* t = in; in = out; out = t;
-            }
-            bool tie = false;
-            for (int q = lid; q + 1 < n; q += 32) tie |= items[b + in[q]].value == items[b + in[q + 1]].value;
-            if (__any_sync(0xffffffffu, tie)) replay = true;
-            else {
-                ssr::Item mine[FX_MAX_SECTOR / 32];
-#pragma unroll
-                for (int u = 0; u < FX_MAX_SECTOR / 32; ++u) { const int q = lid + 32 * u; if (q < n) mine[u] = items[b + in[q]]; }
-                __syncwarp();
-#pragma unroll
-                for (int u = 0; u < FX_MAX_SECTOR / 32; ++u) { const int q = lid + 32 * u; if (q < n) items[b + q] = mine[u]; }
-            }
+        if (n > FX_MAX_SECTOR) {
+            if (lid == 0) ssr::std_sort(items + b, n);
+        } else if (!(dbg & 1)) {
+            warp_std_sort(items + b, n, ordA + b, ordB + b, s_hist + warp * 256, lid);
         }
-        if (replay && lid == 0 && n > 1 && !(dbg & 1)) ssr::std_sort(items + b, n);
     }
     __syncthreads();
     if (tid == 0 && start == 4 && s_sp[0] < s_ep[0]) { f.slot4val[lane] = items[0].value; f.slot4ind[lane] = items[0].ind; }

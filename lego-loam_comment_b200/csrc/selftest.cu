@@ -6,6 +6,7 @@
 #include "engine.h"
 #include "parity_math.cuh"
 #include "std_sort_replay.cuh"
+#include "warp_sort.cuh"
 #include "voxel_grid.cuh"
 
 namespace lego {
@@ -19,6 +20,20 @@ __global__ void selftest_atan2f_kernel(const float* y, const float* x, float* ou
 __global__ void selftest_sort_kernel(ssr::Item* items, const int* offsets, int nseg) {
     int s = blockIdx.x * blockDim.x + threadIdx.x;
     if (s < nseg) ssr::std_sort(items + offsets[s], offsets[s + 1] - offsets[s]);
+}
+
+// one warp per segment (<= WS_MAX_SORT entries): slice staged in shared memory, sorted with warp_std_sort
+__global__ void __launch_bounds__(32) selftest_warp_sort_kernel(ssr::Item* items, const int* offsets, int nseg) {
+    __shared__ ssr::Item a[WS_MAX_SORT];
+    __shared__ unsigned short oA[WS_MAX_SORT], oB[WS_MAX_SORT], h[256];
+    const int s = blockIdx.x, lid = threadIdx.x;
+    const int n = offsets[s + 1] - offsets[s];
+    ssr::Item* g = items + offsets[s];
+    for (int i = lid; i < n; i += 32) a[i] = g[i];
+    __syncwarp();
+    warp_std_sort(a, n, oA, oB, h, lid);
+    __syncwarp();
+    for (int i = lid; i < n; i += 32) g[i] = a[i];
 }
 
 }  // namespace lego
@@ -48,6 +63,25 @@ int lego_selftest_std_sort(const float* values, const int* offsets, int nseg, in
         lego::cuda_check(cudaMalloc(&d, sizeof(ssr::Item) * (total + 1)), "malloc"); lego::cuda_check(cudaMalloc(&doff, 4 * (nseg + 1)), "malloc");
         cudaMemcpy(d, h.data(), sizeof(ssr::Item) * total, cudaMemcpyHostToDevice); cudaMemcpy(doff, offsets, 4 * (nseg + 1), cudaMemcpyHostToDevice);
         lego::selftest_sort_kernel<<<(nseg + 63) / 64, 64>>>(d, doff, nseg);
+        lego::cuda_check(cudaMemcpy(h.data(), d, sizeof(ssr::Item) * total, cudaMemcpyDeviceToHost), "selftest copy");
+        cudaFree(d); cudaFree(doff);
+        for (int i = 0; i < total; ++i) inds_out[i] = h[i].ind;
+        return LEGO_OK;
+    } catch (...) { return LEGO_ERR_CUDA; }
+}
+
+// Same contract as lego_selftest_std_sort, sorted by one warp per segment (csrc/warp_sort.cuh); every segment must
+// hold at most 416 values.
+int lego_selftest_warp_sort(const float* values, const int* offsets, int nseg, int* inds_out) {
+    try {
+        const int total = offsets[nseg];
+        for (int s = 0; s < nseg; ++s) if (offsets[s + 1] - offsets[s] > lego::WS_MAX_SORT) { lego::set_last_error("segment larger than 416"); return LEGO_ERR_ARG; }
+        std::vector<ssr::Item> h(total);
+        for (int s = 0; s < nseg; ++s) for (int i = offsets[s]; i < offsets[s + 1]; ++i) { h[i].value = values[i]; h[i].ind = i - offsets[s]; }
+        ssr::Item* d; int* doff;
+        lego::cuda_check(cudaMalloc(&d, sizeof(ssr::Item) * (total + 1)), "malloc"); lego::cuda_check(cudaMalloc(&doff, 4 * (nseg + 1)), "malloc");
+        cudaMemcpy(d, h.data(), sizeof(ssr::Item) * total, cudaMemcpyHostToDevice); cudaMemcpy(doff, offsets, 4 * (nseg + 1), cudaMemcpyHostToDevice);
+        if (nseg > 0) lego::selftest_warp_sort_kernel<<<nseg, 32>>>(d, doff, nseg);
         lego::cuda_check(cudaMemcpy(h.data(), d, sizeof(ssr::Item) * total, cudaMemcpyDeviceToHost), "selftest copy");
         cudaFree(d); cudaFree(doff);
         for (int i = 0; i < total; ++i) inds_out[i] = h[i].ind;
