@@ -60,6 +60,9 @@ struct FaDev {
     // ring-local feature staging, then compacted lists
     float4* ringSharp; float4* ringLessSharp; float4* ringFlat; float4* ringLessFlat;   // [L][R][12|120|24|C]
     int* ringCounts;           // [L][R][4]
+    int* cand;                 // [L][N]   per sector: edge candidates from slot sp upward, flat candidates from slot ep downward (index | reach << 24)
+    int* candCounts;           // [L][R][6][2]
+    void* sortScratch;         // [L][N] {float, int}, only when a sector can exceed what one warp sorts (Horizon_SCAN > 2496)
     float4* sharp; float4* lessSharp; float4* flat; float4* lessFlat;   // [L][12R | 120R | 24R | N]
     int* featCounts;           // [L][4]
     // odometry state

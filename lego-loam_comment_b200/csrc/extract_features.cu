@@ -1,21 +1,20 @@
-// extractFeatures (reference featureAssociation.cpp:680-784) as one CTA per (ring, lane).
-//
-// Rings are independent in the reference's loop (suppression reaches +-5 slots, the ring margins are 5+5 slots;
-// validated in SURVEY.md section 8), so each CTA owns one ring and walks its six sectors in order:
-//   phase 0  the ring's window of cloudNeighborPicked / cloudLabel is staged in shared memory together with two
-//            derived bytes per point: the static part of the pick conditions (curvature vs threshold, ground flag)
-//            and how far the +-5 suppression walk of featureAssociation.cpp:720-732 gets before a column gap > 10;
-//   phase 1  six warps sort their sector's {curvature, index} slots: a warp-local stable LSD radix sort gives the
-//            order whenever the curvatures are distinct; a sector that holds equal curvatures keeps its arrangement
-//            and one thread replays libstdc++'s std::sort on it (std_sort_replay.cuh, quirk Q17);
-//            the sort range is [sp, ep) while the scans below include slot ep (quirk Q10);
-//   phase 2  warp 0 does the greedy picks with warp ballots: 32 candidates are tested at once, the first eligible
-//            one is taken, its neighbourhood is suppressed in registers (and in the shared window for later chunks)
-//            and the remaining lanes are re-tested -- identical to the sequential scan because suppression only
-//            ever removes candidates;
-//   phase 3  the ring's less-flat candidates go through pcl::VoxelGrid(0.2) semantics: bounding box, voxel keys,
-//            block-wide stable radix sort by key (input order kept inside a voxel), one thread per voxel averages
-//            its members in order.
+// extractFeatures (reference featureAssociation.cpp:680-784) as three kernels, each shaped after the parallelism its
+// step has.  Rings are independent in the reference's loop (suppression reaches +-5 slots, the ring margins are 5+5
+// slots; validated in SURVEY.md section 8) and so are the sorts of the six sectors of a ring.
+//   fa_sort_sectors_kernel   one warp per (sector, ring, lane): std::sort of the sector's {curvature, index} slots
+//            with exactly libstdc++'s permutation (warp_sort.cuh: radix sort when the curvatures are distinct,
+//            introsort partition replay + stable radix sort when some are equal, quirk Q17).  The sort range is
+//            [sp, ep) while the scans include slot ep (quirk Q10).  The warp then writes the two lists the greedy
+//            selection walks: edge candidates (curvature > edgeThreshold, not ground) in descending order and flat
+//            candidates (curvature < surfThreshold, ground) in ascending order, each with the reach of the
+//            suppression walk of featureAssociation.cpp:720-732 from that point (steps before a column gap > 10).
+//   fa_select_kernel         one warp per (ring, lane): the greedy picks, sectors in order.  32 candidates are tested
+//            at once, the first one not yet suppressed is taken, the lanes inside its reach drop out by comparing
+//            indices and lanes 0..10 mark cloudNeighborPicked -- identical to the sequential scan because
+//            suppression only ever removes candidates.
+//   fa_voxel_ring_kernel     one CTA per (ring, lane): the ring's less-flat candidates through pcl::VoxelGrid(0.2)
+//            semantics: bounding box, voxel keys, block-wide stable radix sort by key (input order kept inside a
+//            voxel), one thread per voxel averages its members in order.
 // cloudNeighborPicked / cloudLabel live in persistent global arrays exactly like the reference's (never cleared).
 #include <cfloat>
 #include <climits>
@@ -29,45 +28,20 @@
 
 namespace lego {
 
-struct RingWin {
-    int lo, hi;                       // window [lo, hi) of cloud indices staged in shared memory
-    signed char* picked; signed char* label; unsigned char* stat;                            // shared
-    const int* gcol; const float* gcurv; int* gpicked; int* glabel; const uint8_t* gground;  // global (lane base)
-    float edgeThreshold, surfThreshold;
-};
-__device__ __forceinline__ bool in_win(const RingWin& w, int i) { return i >= w.lo && i < w.hi; }
 // bit 0: may become an edge point (curvature > edgeThreshold, not ground); bit 1: may become a flat point
-__device__ __forceinline__ unsigned char pick_stat(float curv, bool ground, float edgeT, float surfT) {
-    return (unsigned char)(((curv > edgeT && !ground) ? 1 : 0) | ((curv < surfT && ground) ? 2 : 0));
+__device__ __forceinline__ int pick_stat(float curv, bool ground, float edgeT, float surfT) {
+    return ((curv > edgeT && !ground) ? 1 : 0) | ((curv < surfT && ground) ? 2 : 0);
 }
-__device__ __forceinline__ int w_stat(const RingWin& w, int i) {
-    return in_win(w, i) ? (int)w.stat[i - w.lo] : (int)pick_stat(w.gcurv[i], w.gground[i] != 0, w.edgeThreshold, w.surfThreshold);
-}
-__device__ __forceinline__ int w_picked(const RingWin& w, int i) { return in_win(w, i) ? (int)w.picked[i - w.lo] : w.gpicked[i]; }
-__device__ __forceinline__ void w_set_picked(RingWin& w, int i) { if (in_win(w, i)) w.picked[i - w.lo] = 1; else w.gpicked[i] = 1; }
-__device__ __forceinline__ void w_set_label(RingWin& w, int i, int v) { if (in_win(w, i)) w.label[i - w.lo] = (signed char)v; else w.glabel[i] = v; }
 
 // Suppression of the picked point's neighbourhood (featureAssociation.cpp:720-732 and 751-767): the point and up to
 // five slots on either side are marked, each walk stopping at the first column gap > 10.  An index below 0 ends the
 // backward walk: the reference reads out of bounds there (quirk Q11) and the oracle defines it as "stop".
-// General version for a point anywhere in the cloud (only the stale slot-4 entry of quirk Q11 can be outside its own
-// ring): lanes 0-4 test the five forward steps, lanes 5-9 the five backward steps, a ballot finds where each walk
-// stops, and the lanes before the stop mark their slot.
-__device__ __forceinline__ void suppress_warp(RingWin& w, int ind, int lid) {
-    bool bad = false; int slot = ind;
-    if (lid < 5) {
-        const int l = lid + 1;
-        slot = ind + l;
-        bad = abs(w.gcol[ind + l] - w.gcol[ind + l - 1]) > 10;
-    } else if (lid < 10) {
-        const int l = -(lid - 4);
-        slot = ind + l;
-        bad = (ind + l < 0) || abs(w.gcol[ind + l] - w.gcol[ind + l + 1]) > 10;
-    }
-    const unsigned m = __ballot_sync(0xffffffffu, bad);
-    const int nF = (m & 0x1fu) ? __ffs(m & 0x1fu) - 1 : 5;
-    const int nB = ((m >> 5) & 0x1fu) ? __ffs((m >> 5) & 0x1fu) - 1 : 5;
-    if (lid < nF || (lid >= 5 && lid - 5 < nB) || lid == 10) w_set_picked(w, slot);
+// reach = forward steps | backward steps << 4.
+__device__ __forceinline__ int suppression_reach(const int* col, int ind) {
+    int nF = 0, nB = 0;
+    while (nF < 5 && abs(col[ind + nF + 1] - col[ind + nF]) <= 10) ++nF;
+    while (nB < 5 && ind - nB - 1 >= 0 && abs(col[ind - nB - 1] - col[ind - nB]) <= 10) ++nB;
+    return nF | (nB << 4);
 }
 
 __device__ __forceinline__ void sector_bounds(int start, int end, int j, int* sp, int* ep) {
@@ -75,165 +49,201 @@ __device__ __forceinline__ void sector_bounds(int start, int end, int j, int* sp
     *ep = (start * (5 - j) + end * (j + 1)) / 6 - 1;
 }
 
-constexpr int FX_MAX_SECTOR = WS_MAX_SORT; // sector sizes the warp sort takes (Horizon_SCAN <= 2496); larger ones use the serial replay
-constexpr int FX_MAX_ITERS = 16;         // 256-wide sweeps over one ring (Horizon_SCAN <= 4096)
+constexpr int FS_WARPS = 4;          // sectors per CTA of fa_sort_sectors_kernel
+constexpr int SEL_WARPS = 4;         // rings per CTA of fa_select_kernel
+constexpr int FX_MAX_ITERS = 16;     // 256-wide sweeps over one ring (Horizon_SCAN <= 4096)
+constexpr int CAND_SLOW = 0xff;      // reach marker: the point is outside its ring's [start, end) (stale slot 4, quirk Q11)
 
-__global__ void __launch_bounds__(256) fa_extract_kernel(IpDev d, FaDev f, Consts c, float leaf, int dbg) {
+struct SortSmem { ssr::Item a[WS_MAX_SORT]; unsigned short oA[WS_MAX_SORT], oB[WS_MAX_SORT], h[256]; };
+
+__global__ void __launch_bounds__(32 * FS_WARPS) fa_sort_sectors_kernel(IpDev d, FaDev f, Consts c) {
+    __shared__ __align__(16) SortSmem sm[FS_WARPS];
+    const int lane = blockIdx.y, warp = threadIdx.x >> 5, lid = threadIdx.x & 31;
+    const int sec = blockIdx.x * FS_WARPS + warp;
+    if (sec >= c.R * 6) return;
+    const int ring = sec / 6, j = sec - ring * 6;
+    const size_t base = (size_t)lane * c.N;
+    const int start = d.startRing[lane * c.R + ring], end = d.endRing[lane * c.R + ring];
+    int* cnt = f.candCounts + (((size_t)lane * c.R + ring) * 6 + j) * 2;
+    int sp, ep;
+    sector_bounds(start, end, j, &sp, &ep);
+    if (end + 6 - (start - 4) <= 0 || sp >= ep) { if (lid < 2) cnt[lid] = 0; return; }   // featureAssociation.cpp:696-697
+    const int n = ep - sp;
+    const float* gcurv = f.curv + base;
+    const int* gcol = d.segCol + base;
+    const uint8_t* gground = d.segGround + base;
+    SortSmem& S = sm[warp];
+
+    // ---- std::sort(cloudSmoothness.begin()+sp, cloudSmoothness.begin()+ep) ----
+    const bool big = n > WS_MAX_SORT;
+    ssr::Item* a = big ? reinterpret_cast<ssr::Item*>(f.sortScratch) + base + sp : S.a;
+    for (int q = lid; q < n; q += 32) {
+        const int k = sp + q;
+        ssr::Item it;
+        if (k == 4) { it.value = f.slot4val[lane]; it.ind = f.slot4ind[lane]; }   // stale slot, quirk Q11
+        else { it.value = gcurv[k]; it.ind = k; }
+        a[q] = it;
+    }
+    __syncwarp();
+    const unsigned short* ord = nullptr;
+    if (!big) ord = warp_std_sort_order(a, n, S.oA, S.oB, S.h, lid);
+    else { if (lid == 0) ssr::std_sort(a, n); __syncwarp(); }
+    auto sorted_item = [&](int q) -> ssr::Item { return big ? a[q] : a[ord[q]]; };
+    if (sp == 4 && lid == 0) { const ssr::Item it = sorted_item(0); f.slot4val[lane] = it.value; f.slot4ind[lane] = it.ind; }
+
+    // ---- candidate lists of the two scans (featureAssociation.cpp:701-769) ----
+    int* cand = f.cand + base;
+    const unsigned lt = (1u << lid) - 1u;
+    auto packed_of = [&](int ind) -> int {
+        const int reach = (ind >= start && ind < end) ? suppression_reach(gcol, ind) : CAND_SLOW;
+        return ind | (reach << 24);
+    };
+    int nEdge = 0, nFlat = 0;
+    for (int c0 = 0; c0 <= n; c0 += 32) {          // k = ep down to sp
+        const int t = c0 + lid;
+        const bool valid = t <= n;
+        const int ind = !valid ? 0 : (t == 0 ? ep : sorted_item(n - t).ind);
+        const bool is = valid && (pick_stat(gcurv[ind], gground[ind] != 0, c.edgeThreshold, c.surfThreshold) & 1);
+        const unsigned m = __ballot_sync(0xffffffffu, is);
+        if (is) cand[sp + nEdge + __popc(m & lt)] = packed_of(ind);
+        nEdge += __popc(m);
+    }
+    for (int c0 = 0; c0 <= n; c0 += 32) {          // k = sp up to ep
+        const int t = c0 + lid;
+        const bool valid = t <= n;
+        const int ind = !valid ? 0 : (t == n ? ep : sorted_item(t).ind);
+        const bool is = valid && (pick_stat(gcurv[ind], gground[ind] != 0, c.edgeThreshold, c.surfThreshold) & 2);
+        const unsigned m = __ballot_sync(0xffffffffu, is);
+        if (is) cand[ep - (nFlat + __popc(m & lt))] = packed_of(ind);
+        nFlat += __popc(m);
+    }
+    if (lid == 0) { cnt[0] = nEdge; cnt[1] = nFlat; }
+}
+
+// General suppression for a point anywhere in the cloud (only the stale slot-4 entry of quirk Q11 can be outside its
+// own ring): lanes 0-4 test the five forward steps, lanes 5-9 the five backward steps, a ballot finds where each
+// walk stops, and the lanes before the stop mark their slot.
+__device__ __forceinline__ void suppress_warp(const int* gcol, int* gpicked, int ind, int lid) {
+    bool bad = false; int slot = ind;
+    if (lid < 5) {
+        const int l = lid + 1;
+        slot = ind + l;
+        bad = abs(gcol[ind + l] - gcol[ind + l - 1]) > 10;
+    } else if (lid < 10) {
+        const int l = -(lid - 4);
+        slot = ind + l;
+        bad = (ind + l < 0) || abs(gcol[ind + l] - gcol[ind + l + 1]) > 10;
+    }
+    const unsigned m = __ballot_sync(0xffffffffu, bad);
+    const int nF = (m & 0x1fu) ? __ffs(m & 0x1fu) - 1 : 5;
+    const int nB = ((m >> 5) & 0x1fu) ? __ffs((m >> 5) & 0x1fu) - 1 : 5;
+    if (lid < nF || (lid >= 5 && lid - 5 < nB) || lid == 10) gpicked[slot] = 1;
+}
+
+__global__ void __launch_bounds__(32 * SEL_WARPS) fa_select_kernel(IpDev d, FaDev f, Consts c) {
+    __shared__ int s_pick[SEL_WARPS][12 + 120 + 24];
+    const int lane = blockIdx.y, warp = threadIdx.x >> 5, lid = threadIdx.x & 31;
+    const int ring = blockIdx.x * SEL_WARPS + warp;
+    if (ring >= c.R) return;
+    const size_t base = (size_t)lane * c.N;
+    const int start = d.startRing[lane * c.R + ring], end = d.endRing[lane * c.R + ring];
+    int* rc = f.ringCounts + ((size_t)lane * c.R + ring) * 4;
+    if (end + 6 - (start - 4) <= 0) { if (lid < 3) rc[lid] = 0; return; }
+    const int* gcol = d.segCol + base;
+    int* gpicked = f.picked + base;
+    int* glabel = f.label + base;
+    const int* cand = f.cand + base;
+    const int* cnt = f.candCounts + ((size_t)lane * c.R + ring) * 12;
+    int* pickSharp = s_pick[warp]; int* pickLess = pickSharp + 12; int* pickFlat = pickLess + 120;
+
+    int nSharp = 0, nLess = 0, nFlat = 0;
+    for (int j = 0; j < 6; ++j) {
+        int sp, ep;
+        sector_bounds(start, end, j, &sp, &ep);
+        if (sp >= ep) continue;
+        for (int pass = 0; pass < 2; ++pass) {
+            // pass 0: edge points, largest curvature first (featureAssociation.cpp:701-734)
+            // pass 1: flat points, smallest curvature first (featureAssociation.cpp:736-769); its 4th pick breaks BEFORE suppression (Q12)
+            const int len = cnt[j * 2 + pass];
+            int picks = 0; bool stop = false;
+            for (int c0 = 0; c0 < len && !stop; c0 += 32) {
+                const int t = c0 + lid;
+                const bool valid = t < len;
+                const int packed = valid ? cand[pass == 0 ? sp + t : ep - t] : 0;
+                const int ind = packed & 0xffffff;
+                bool pk = valid ? gpicked[ind] != 0 : true;
+                while (true) {
+                    const unsigned m = __ballot_sync(0xffffffffu, !pk);
+                    if (!m) break;
+                    const int first = __ffs(m) - 1;
+                    const int pp = __shfl_sync(0xffffffffu, packed, first);
+                    const int pind = pp & 0xffffff, reach = (pp >> 24) & 0xff;
+                    ++picks;
+                    if (pass == 0 && picks > 20) { stop = true; break; }
+                    if (lid == 0) {   // the points themselves are copied after the selection
+                        if (pass == 1) { glabel[pind] = -1; pickFlat[nFlat] = pind; }
+                        else if (picks <= 2) { glabel[pind] = 2; pickSharp[nSharp] = pind; pickLess[nLess] = pind; }
+                        else { glabel[pind] = 1; pickLess[nLess] = pind; }
+                    }
+                    if (pass == 1) ++nFlat; else { ++nLess; if (picks <= 2) ++nSharp; }
+                    if (pass == 1 && picks >= 4) { stop = true; break; }
+                    if (reach != CAND_SLOW) {
+                        const int nF = reach & 15, nB = reach >> 4;
+                        const int o = lid - 5;
+                        if (lid <= 10 && o >= -nB && o <= nF) gpicked[pind + o] = 1;
+                        if (ind >= pind - nB && ind <= pind + nF) pk = true;
+                    } else {
+                        suppress_warp(gcol, gpicked, pind, lid);
+                        __syncwarp();
+                        pk = valid ? gpicked[ind] != 0 : true;
+                    }
+                }
+                __syncwarp();   // marks of this chunk are visible to the loads of the next one
+            }
+        }
+    }
+    if (lid == 0) { rc[0] = nSharp; rc[1] = nLess; rc[2] = nFlat; }
+    __syncwarp();
+    const float4* adj = f.segAdj + base;
+    float4* oSharp = f.ringSharp + ((size_t)lane * c.R + ring) * 12;
+    float4* oLess = f.ringLessSharp + ((size_t)lane * c.R + ring) * 120;
+    float4* oFlat = f.ringFlat + ((size_t)lane * c.R + ring) * 24;
+    if (lid < nSharp) oSharp[lid] = adj[pickSharp[lid]];
+    if (lid < nFlat) oFlat[lid] = adj[pickFlat[lid]];
+    for (int i = lid; i < nLess; i += 32) oLess[i] = adj[pickLess[i]];
+}
+
+// Less-flat candidates of one ring -> pcl::VoxelGrid(leaf) (featureAssociation.cpp:771-782).
+__global__ void __launch_bounds__(256) fa_voxel_ring_kernel(IpDev d, FaDev f, Consts c, float leaf) {
     extern __shared__ __align__(16) unsigned char smem[];
     const int lane = blockIdx.y, ring = blockIdx.x, tid = threadIdx.x;
     const int warp = tid >> 5, lid = tid & 31;
     const size_t base = (size_t)lane * c.N;
     const int start = d.startRing[lane * c.R + ring], end = d.endRing[lane * c.R + ring];
-    const int rowStart = start - 4, rowEnd = end + 6;
     int* rc = f.ringCounts + ((size_t)lane * c.R + ring) * 4;
-    if (rowEnd - rowStart <= 0) { if (tid < 4) rc[tid] = 0; return; }
+    if (end + 6 - (start - 4) <= 0) { if (tid == 0) rc[3] = 0; return; }
 
-    // ---- shared memory carve-up ----
-    //   region A  8*C bytes   cloudSmoothness slots of the ring (phases 1-2), then voxel keys + positions (phase 3)
-    //   region B  4*Cw bytes  column indices while the derived bytes are computed, then the two sort index lists
-    //   region C  4*Cw bytes  picked | label | stat | reach, one byte per window slot each
+    // shared memory: voxel index and ring position per candidate, two index lists for the sort
     const int Cw = c.C + 8;
-    ssr::Item* items = reinterpret_cast<ssr::Item*>(smem);
     unsigned* vkey = reinterpret_cast<unsigned*>(smem);
     unsigned short* cpos = reinterpret_cast<unsigned short*>(smem + (size_t)4 * c.C);
-    int* s_col = reinterpret_cast<int*>(smem + (size_t)8 * c.C);
-    unsigned short* ordA = reinterpret_cast<unsigned short*>(smem + (size_t)8 * c.C);
+    unsigned short* ordA = reinterpret_cast<unsigned short*>(smem + (size_t)6 * c.C);
     unsigned short* ordB = ordA + Cw;
-    unsigned char* tail = smem + (size_t)8 * c.C + (size_t)4 * Cw;
-    signed char* s_picked = reinterpret_cast<signed char*>(tail);
-    signed char* s_label = reinterpret_cast<signed char*>(tail + Cw);
-    unsigned char* s_stat = tail + 2 * Cw;
-    unsigned char* s_reach = tail + 3 * Cw;   // forward steps | backward steps << 4 of the suppression walk
-    __shared__ unsigned short s_hist[8 * 256];
+    __shared__ __align__(16) unsigned short s_hist[8 * 256];
     __shared__ int s_sp[6], s_ep[6];
-    __shared__ int s_pickSharp[12], s_pickLess[120], s_pickFlat[24], s_nPick[3];
     __shared__ float s_red[6][8];
     __shared__ int s_scan[8];
     __shared__ int s_cnt[FX_MAX_ITERS * 8 + 1];
-
-    RingWin w;
-    w.lo = max(rowStart - 1, 0); w.hi = rowEnd;
-    w.picked = s_picked; w.label = s_label; w.stat = s_stat;
-    w.gcol = d.segCol + base; w.gcurv = f.curv + base; w.gpicked = f.picked + base; w.glabel = f.label + base; w.gground = d.segGround + base;
-    w.edgeThreshold = c.edgeThreshold; w.surfThreshold = c.surfThreshold;
-
-    // ---- phase 0: stage the window ----
-    for (int k = w.lo + tid; k < w.hi; k += blockDim.x) {
-        s_col[k - w.lo] = w.gcol[k];
-        s_picked[k - w.lo] = (signed char)w.gpicked[k]; s_label[k - w.lo] = (signed char)w.glabel[k];
-        s_stat[k - w.lo] = pick_stat(w.gcurv[k], w.gground[k] != 0, c.edgeThreshold, c.surfThreshold);
-    }
-    for (int k = start + tid; k < end; k += blockDim.x) {
-        ssr::Item it;
-        if (k == 4) { it.value = f.slot4val[lane]; it.ind = f.slot4ind[lane]; }   // stale slot, quirk Q11
-        else { it.value = w.gcurv[k]; it.ind = k; }
-        items[k - start] = it;
-    }
     if (tid < 6) { int sp, ep; sector_bounds(start, end, tid, &sp, &ep); s_sp[tid] = sp; s_ep[tid] = ep; }
-    if (tid < 3) s_nPick[tid] = 0;
     __syncthreads();
-    // reach of the suppression walk from every slot a sector can pick, [start, end): slots k-5 .. k+5 are inside the window
-    for (int k = start + tid; k < end; k += blockDim.x) {
-        const int* cc = s_col + (k - w.lo);
-        int nF = 0, nB = 0;
-        while (nF < 5 && abs(cc[nF + 1] - cc[nF]) <= 10) ++nF;
-        while (nB < 5 && k - nB - 1 >= 0 && abs(cc[-nB - 1] - cc[-nB]) <= 10) ++nB;
-        s_reach[k - w.lo] = (unsigned char)(nF | (nB << 4));
-    }
-    __syncthreads();   // region B becomes the sort index lists
 
-    // ---- phase 1: std::sort(cloudSmoothness.begin()+sp, cloudSmoothness.begin()+ep) per sector, one warp each ----
-    // A sector whose curvatures are all distinct has exactly one sorted order, which the radix sort finds.  Equal
-    // curvatures do occur (quirk Q17) and their final order depends on libstdc++'s introsort path: for such a sector
-    // the warp replays introsort's partitions first (warp_sort.cuh).
-    if (warp < 6) {
-        const int sp = s_sp[warp], ep = s_ep[warp];
-        const int n = ep - sp, b = sp - start;
-        if (n > FX_MAX_SECTOR) {
-            if (lid == 0) ssr::std_sort(items + b, n);
-        } else if (!(dbg & 1)) {
-            warp_std_sort(items + b, n, ordA + b, ordB + b, s_hist + warp * 256, lid);
-        }
-    }
-    __syncthreads();
-    if (tid == 0 && start == 4 && s_sp[0] < s_ep[0]) { f.slot4val[lane] = items[0].value; f.slot4ind[lane] = items[0].ind; }
-
-    // ---- phase 2: greedy selection, sectors in order, one warp ----
-    // Every lane keeps its candidate's state in registers: index + reach (packed), static eligibility, picked flag.
-    // A pick is broadcast with one shuffle; the lanes inside its reach drop out by comparing indices, and lanes
-    // 0..10 mark the shared window for the chunks that follow.
-    if (warp == 0) {
-        int nSharp = 0, nLess = 0, nFlat = 0;
-        for (int j = 0; j < ((dbg & 2) ? 0 : 6); ++j) {
-            const int sp = s_sp[j], ep = s_ep[j];
-            if (sp >= ep) continue;
-            for (int pass = 0; pass < 2; ++pass) {
-                // pass 0: corner points, k = ep down to sp (featureAssociation.cpp:701-734)
-                // pass 1: flat points, k = sp up to ep (featureAssociation.cpp:736-769); its 4th pick breaks BEFORE suppression (Q12)
-                int picks = 0; bool stop = false;
-                for (int c0 = 0; c0 <= ep - sp && !stop; c0 += 32) {
-                    const int k = pass == 0 ? ep - c0 - lid : sp + c0 + lid;
-                    const bool inr = k >= sp && k <= ep;
-                    const int ind = inr ? items[k - start].ind : 0;
-                    const bool fastp = inr && ind >= start && ind < end;
-                    const int packed = ind | ((fastp ? (int)s_reach[ind - w.lo] : 0xff) << 24);
-                    const bool cand = inr && ((w_stat(w, ind) >> pass) & 1);
-                    bool pk = inr ? w_picked(w, ind) != 0 : true;
-                    while (true) {
-                        const unsigned m = __ballot_sync(0xffffffffu, cand && !pk);
-                        if (!m) break;
-                        const int first = __ffs(m) - 1;
-                        const int pp = __shfl_sync(0xffffffffu, packed, first);
-                        const int pind = pp & 0xffffff, reach = (pp >> 24) & 0xff;
-                        ++picks;
-                        if (pass == 0 && picks > 20) { stop = true; break; }
-                        if (lid == 0) {   // the points themselves are copied by the whole CTA after the selection
-                            if (pass == 1) { w_set_label(w, pind, -1); s_pickFlat[nFlat] = pind; }
-                            else if (picks <= 2) { w_set_label(w, pind, 2); s_pickSharp[nSharp] = pind; s_pickLess[nLess] = pind; }
-                            else { w_set_label(w, pind, 1); s_pickLess[nLess] = pind; }
-                        }
-                        if (pass == 1) ++nFlat; else { ++nLess; if (picks <= 2) ++nSharp; }
-                        if (pass == 1 && picks >= 4) { stop = true; break; }
-                        if (reach != 0xff) {
-                            const int nF = reach & 15, nB = reach >> 4;
-                            const int o = lid - 5;
-                            if (lid <= 10 && o >= -nB && o <= nF) s_picked[pind + o - w.lo] = 1;
-                            if (ind >= pind - nB && ind <= pind + nF) pk = true;
-                        } else {
-                            suppress_warp(w, pind, lid);
-                            __syncwarp();
-                            pk = inr ? w_picked(w, ind) != 0 : true;
-                        }
-                    }
-                    __syncwarp();   // marks of this chunk are visible to the loads of the next one
-                }
-            }
-        }
-        if (lid == 0) { rc[0] = nSharp; rc[1] = nLess; rc[2] = nFlat; s_nPick[0] = nSharp; s_nPick[1] = nLess; s_nPick[2] = nFlat; }
-    }
-    __syncthreads();
-    {
-        const float4* adjp = f.segAdj + base;
-        float4* oSharp = f.ringSharp + ((size_t)lane * c.R + ring) * 12;
-        float4* oLess = f.ringLessSharp + ((size_t)lane * c.R + ring) * 120;
-        float4* oFlat = f.ringFlat + ((size_t)lane * c.R + ring) * 24;
-        if (tid < s_nPick[0]) oSharp[tid] = adjp[s_pickSharp[tid]];
-        if (tid >= 32 && tid - 32 < s_nPick[2]) oFlat[tid - 32] = adjp[s_pickFlat[tid - 32]];
-        if (tid >= 64 && tid - 64 < s_nPick[1]) oLess[tid - 64] = adjp[s_pickLess[tid - 64]];
-    }
-
-    // ---- write back this ring's share of the persistent arrays ([lo, hi-1): the last slot is never modified here
-    //      but may be by the next ring's CTA) ----
-    for (int k = w.lo + tid; k < w.hi - 1; k += blockDim.x) { w.gpicked[k] = s_picked[k - w.lo]; w.glabel[k] = s_label[k - w.lo]; }
-
-    // ---- phase 3: less-flat candidates of this ring -> VoxelGrid(leaf) (featureAssociation.cpp:771-782) ----
-    if (dbg & 4) { if (tid == 0) rc[3] = 0; return; }
     const float4* adj = f.segAdj + base;
+    const int* glabel = f.label + base;
     auto is_cand = [&](int k) -> bool {
         bool in_sector = false;
 #pragma unroll
         for (int j = 0; j < 6; ++j) in_sector |= (s_sp[j] < s_ep[j] && k >= s_sp[j] && k <= s_ep[j]);
-        return in_sector && s_label[k - w.lo] <= 0;
+        return in_sector && glabel[k] <= 0;
     };
     // exclusive scan of the per-(sweep, warp) counts in s_cnt[0 .. nSlots) by warp 0; the total lands in s_cnt[nSlots]
     auto scan_counts = [&](int nSlots) {
@@ -263,7 +273,7 @@ __global__ void __launch_bounds__(256) fa_extract_kernel(IpDev d, FaDev f, Const
 #pragma unroll
     for (int a = 0; a < 3; ++a) { mn[a] = warp_min_f(mn[a]); mx[a] = warp_max_f(mx[a]); }
     if (lid == 0) { for (int a = 0; a < 3; ++a) { s_red[a][warp] = mn[a]; s_red[3 + a][warp] = mx[a]; } }
-    __syncthreads();   // also: everyone is done with the cloudSmoothness slots before region A becomes vkey / cpos
+    __syncthreads();
     scan_counts(nSweep * 8);
     __syncthreads();
     const int nCand = s_cnt[nSweep * 8];
@@ -310,13 +320,18 @@ __global__ void __launch_bounds__(256) fa_extract_kernel(IpDev d, FaDev f, Const
         unsigned short* in = ordA; unsigned short* outl = ordB;
         const int per = ((nCand + 255) >> 8) << 5;
         const int wb = min(warp * per, nCand), nw = min(wb + per, nCand) - wb;
-        unsigned short* h = s_hist + warp * 256;
+        constexpr int U3 = 5;   // entries per lane held in registers at a time
+        unsigned* h32 = reinterpret_cast<unsigned*>(s_hist + warp * 256);
         auto key = [&](unsigned short e) -> unsigned { return vkey[e]; };
         for (int shift = 0; shift < keyBits; shift += 8) {
 #pragma unroll
             for (int q = 0; q < 8; ++q) s_hist[q * 256 + tid] = 0;
             __syncthreads();
-            warp_radix_count(in + wb, nw, shift, h, lid, key);
+            RadixBatch<U3> r;
+            for (int q0 = 0; q0 < nw; q0 += 32 * U3) {
+                radix_batch_load(r, in + wb + q0, min(nw - q0, 32 * U3), shift, lid, key);
+                radix_batch_count(r, min(nw - q0, 32 * U3), h32, lid);
+            }
             __syncthreads();
             {   // digit-major, warp-minor exclusive scan of the 8 x 256 counters: thread = digit
                 int run = 0;
@@ -331,7 +346,10 @@ __global__ void __launch_bounds__(256) fa_extract_kernel(IpDev d, FaDev f, Const
                 for (int q = 0; q < 8; ++q) s_hist[q * 256 + tid] = (unsigned short)(s_hist[q * 256 + tid] + basep);
             }
             __syncthreads();
-            warp_radix_scatter(in + wb, outl, nw, shift, h, lid, key);
+            for (int q0 = 0; q0 < nw; q0 += 32 * U3) {
+                if (nw > 32 * U3) radix_batch_load(r, in + wb + q0, min(nw - q0, 32 * U3), shift, lid, key);
+                radix_batch_scatter(r, min(nw - q0, 32 * U3), h32, outl, lid);
+            }
             __syncthreads();
             unsigned short* t = in; in = outl; outl = t;
         }
@@ -408,18 +426,18 @@ void Engine::adjustDistortionCalculateSmoothnessMarkOccluded() {
 }
 
 void Engine::extractFeatures() {
-    const size_t smem = (size_t)8 * c.C + (size_t)8 * (c.C + 8);   // regions A, B, C of fa_extract_kernel
-    if (c.C > 4096 - 8) { set_last_error("Horizon_SCAN > 4088 is not supported by fa_extract_kernel"); throw std::length_error("capacity"); }
+    if (c.C > 4096 - 8) { set_last_error("Horizon_SCAN > 4088 is not supported by fa_voxel_ring_kernel"); throw std::length_error("capacity"); }
+    const size_t smem = (size_t)6 * c.C + (size_t)4 * (c.C + 8);   // vkey | cpos | two index lists
     static bool attr_set = false;
     if (!attr_set) {
-        cuda_check(cudaFuncSetAttribute(fa_extract_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 160 * 1024), "smem attr");
+        cuda_check(cudaFuncSetAttribute(fa_voxel_ring_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 64 * 1024), "smem attr");
         attr_set = true;
     }
-    static const int dbg = getenv("LEGO_DBG_SKIP") ? atoi(getenv("LEGO_DBG_SKIP")) : 0;
-    dim3 g(c.R, c.L);
-    { ProfScope ps(this, "fa_extract_kernel"); fa_extract_kernel<<<g, 256, smem, stream>>>(ip, fa, c, 0.2f, dbg); }   // downSizeFilter.setLeafSize(0.2,...) featureAssociation.cpp:225
+    { ProfScope ps(this, "fa_sort_sectors_kernel"); fa_sort_sectors_kernel<<<dim3((c.R * 6 + FS_WARPS - 1) / FS_WARPS, c.L), 32 * FS_WARPS, 0, stream>>>(ip, fa, c); }
+    { ProfScope ps(this, "fa_select_kernel"); fa_select_kernel<<<dim3((c.R + SEL_WARPS - 1) / SEL_WARPS, c.L), 32 * SEL_WARPS, 0, stream>>>(ip, fa, c); }
+    { ProfScope ps(this, "fa_voxel_ring_kernel"); fa_voxel_ring_kernel<<<dim3(c.R, c.L), 256, smem, stream>>>(ip, fa, c, 0.2f); }   // downSizeFilter.setLeafSize(0.2,...) featureAssociation.cpp:225
     { ProfScope ps(this, "fa_gather_features_kernel"); fa_gather_features_kernel<<<dim3(c.R, c.L), 128, 0, stream>>>(fa, c); }
-    launches += 2;
+    launches += 4;
 }
 
 }  // namespace lego

@@ -21,6 +21,8 @@ void Engine::allocFeatureAssociation() {
     fa.ringSharp = alloc<float4>(L * R * 12); fa.ringLessSharp = alloc<float4>(L * R * 120);
     fa.ringFlat = alloc<float4>(L * R * 24); fa.ringLessFlat = alloc<float4>(L * R * C);
     fa.ringCounts = alloc<int>(L * R * 4);
+    fa.cand = alloc<int>(L * N); fa.candCounts = alloc<int>(L * R * 12);
+    fa.sortScratch = C > 6 * 416 ? (void*)alloc<double>(L * N) : nullptr;
     fa.sharp = alloc<float4>(L * R * 12); fa.lessSharp = alloc<float4>(L * R * 120);
     fa.flat = alloc<float4>(L * R * 24); fa.lessFlat = alloc<float4>(L * N);
     fa.featCounts = alloc<int>(L * 4);

@@ -16,31 +16,44 @@ __device__ __forceinline__ unsigned float_sort_key(float v) {
     const unsigned b = __float_as_uint(v);
     return b ^ ((unsigned)((int)b >> 31) | 0x80000000u);
 }
-template <class KeyF>
-__device__ __forceinline__ void warp_radix_count(const unsigned short* in, int n, int shift, unsigned short* h, int lid, KeyF key) {
-    for (int q0 = 0; q0 < n; q0 += 32) {
-        const int q = q0 + lid;
-        const bool valid = q < n;
-        const unsigned dg = valid ? ((key(in[q]) >> shift) & 255u) : 256u;
-        const unsigned peers = __match_any_sync(0xffffffffu, dg);
-        if (valid && lid == __ffs(peers) - 1) h[dg] = (unsigned short)(h[dg] + __popc(peers));
-        __syncwarp();
+// A batch of up to 32*U consecutive entries of one warp's list, held in registers between the counting and the
+// scattering half of a pass: entry, digit and the lanes holding the same digit in the same 32-entry chunk.
+template <int U>
+struct RadixBatch { unsigned ed[U]; unsigned peers[U]; };   // ed = entry | digit << 16
+
+template <int U, class KeyF>
+__device__ __forceinline__ void radix_batch_load(RadixBatch<U>& r, const unsigned short* in, int n, int shift, int lid, KeyF key) {
+#pragma unroll
+    for (int u = 0; u < U; ++u) { const int q = lid + 32 * u; r.ed[u] = q < n ? (unsigned)in[q] : 0u; }
+#pragma unroll
+    for (int u = 0; u < U; ++u) { const int q = lid + 32 * u; r.ed[u] |= (q < n ? ((key((unsigned short)r.ed[u]) >> shift) & 255u) : 256u) << 16; }
+#pragma unroll
+    for (int u = 0; u < U; ++u) r.peers[u] = (32 * u < n) ? __match_any_sync(0xffffffffu, r.ed[u] >> 16) : 0u;
+}
+// counters are 16 bit, two per 32-bit word, so a chunk's leader can add its group with one shared-memory atomic
+template <int U>
+__device__ __forceinline__ void radix_batch_count(const RadixBatch<U>& r, int n, unsigned* h32, int lid) {
+#pragma unroll
+    for (int u = 0; u < U; ++u) {
+        const int q = lid + 32 * u;
+        const unsigned dg = r.ed[u] >> 16;
+        if (q < n && lid == __ffs(r.peers[u]) - 1) atomicAdd(&h32[dg >> 1], (unsigned)__popc(r.peers[u]) << ((dg & 1) * 16));
     }
 }
-template <class KeyF>
-__device__ __forceinline__ void warp_radix_scatter(const unsigned short* in, unsigned short* out, int n, int shift, unsigned short* h, int lid, KeyF key) {
-    for (int q0 = 0; q0 < n; q0 += 32) {
-        const int q = q0 + lid;
-        const bool valid = q < n;
-        const unsigned short e = valid ? in[q] : (unsigned short)0;
-        const unsigned dg = valid ? ((key(e) >> shift) & 255u) : 256u;
-        const unsigned peers = __match_any_sync(0xffffffffu, dg);
-        const int leader = __ffs(peers) - 1;
-        int old = 0;
-        if (valid && lid == leader) { old = h[dg]; h[dg] = (unsigned short)(old + __popc(peers)); }
-        old = __shfl_sync(0xffffffffu, old, leader);
-        if (valid) out[old + __popc(peers & ((1u << lid) - 1u))] = e;
-        __syncwarp();
+template <int U>
+__device__ __forceinline__ void radix_batch_scatter(const RadixBatch<U>& r, int n, unsigned* h32, unsigned short* out, int lid) {
+#pragma unroll
+    for (int u = 0; u < U; ++u) {
+        if (32 * u < n) {   // warp-uniform
+            const int q = lid + 32 * u;
+            const int leader = __ffs(r.peers[u]) - 1;
+            const unsigned dg = r.ed[u] >> 16;
+            unsigned old = 0;
+            if (q < n && lid == leader) old = atomicAdd(&h32[dg >> 1], (unsigned)__popc(r.peers[u]) << ((dg & 1) * 16));
+            __syncwarp();   // chunk u's update is ordered before chunk u+1's
+            old = (__shfl_sync(0xffffffffu, old, leader) >> ((dg & 1) * 16)) & 0xffffu;
+            if (q < n) out[old + __popc(r.peers[u] & ((1u << lid) - 1u))] = (unsigned short)r.ed[u];
+        }
     }
 }
 // exclusive scan of a warp's 256 counters, in place
@@ -117,38 +130,56 @@ __device__ __forceinline__ void warp_introsort_partitions(ssr::Item* a, int n, u
 
 // std::sort(a, a + n) with the reference's comparator (value only, utility.h:139-148), n <= WS_MAX_SORT, by one warp.
 // Distinct values have one sorted order and the radix sort finds it; if equal values exist, introsort's partitions
-// are replayed first and the radix sort (stable, like std::sort's closing insertion sort) finishes the job.
-// ordA / ordB: n entries of scratch each, h: 256 counters.
-__device__ __forceinline__ void warp_std_sort(ssr::Item* a, int n, unsigned short* ordA, unsigned short* ordB, unsigned short* h, int lid) {
-    if (n <= 1) return;
+// are replayed first (permuting a) and the radix sort (stable, like std::sort's closing insertion sort) finishes the
+// job.  Returns the sorted order as a list of positions into a: element q of the result is a[order[q]].
+// ordA / ordB: n entries of scratch each (the result is one of them), h: 256 counters (4-byte aligned).
+__device__ __forceinline__ const unsigned short* warp_std_sort_order(ssr::Item* a, int n, unsigned short* ordA, unsigned short* ordB,
+                                                                     unsigned short* h, int lid) {
     auto key = [&](unsigned short e) -> unsigned { return float_sort_key(a[e].value); };
+    unsigned short* in = ordA;
     for (int attempt = 0; attempt < 2; ++attempt) {
-        unsigned short* in = ordA; unsigned short* out = ordB;
+        in = ordA; unsigned short* out = ordB;
         for (int q = lid; q < n; q += 32) in[q] = (unsigned short)q;
         __syncwarp();
         for (int shift = 0; shift < 32; shift += 8) {
 #pragma unroll
             for (int i = 0; i < 8; ++i) h[lid + 32 * i] = 0;
             __syncwarp();
-            warp_radix_count(in, n, shift, h, lid, key);
+            constexpr int U = 5;
+            RadixBatch<U> r;
+            for (int q0 = 0; q0 < n; q0 += 32 * U) {
+                radix_batch_load(r, in + q0, min(n - q0, 32 * U), shift, lid, key);
+                radix_batch_count(r, min(n - q0, 32 * U), reinterpret_cast<unsigned*>(h), lid);
+            }
+            __syncwarp();
             warp_scan256(h, lid);
-            warp_radix_scatter(in, out, n, shift, h, lid, key);
+            for (int q0 = 0; q0 < n; q0 += 32 * U) {
+                if (n > 32 * U) radix_batch_load(r, in + q0, min(n - q0, 32 * U), shift, lid, key);
+                radix_batch_scatter(r, min(n - q0, 32 * U), reinterpret_cast<unsigned*>(h), out, lid);
+            }
+            __syncwarp();
             unsigned short* t = in; in = out; out = t;
         }
-        if (attempt == 0) {
-            bool tie = false;
-            for (int q = lid; q + 1 < n; q += 32) tie |= a[in[q]].value == a[in[q + 1]].value;
-            if (__any_sync(0xffffffffu, tie)) { warp_introsort_partitions(a, n, ordA, ordB, lid); continue; }
-        }
-        ssr::Item mine[WS_MAX_SORT / 32];
-#pragma unroll
-        for (int u = 0; u < WS_MAX_SORT / 32; ++u) { const int q = lid + 32 * u; if (q < n) mine[u] = a[in[q]]; }
-        __syncwarp();
-#pragma unroll
-        for (int u = 0; u < WS_MAX_SORT / 32; ++u) { const int q = lid + 32 * u; if (q < n) a[q] = mine[u]; }
-        __syncwarp();
-        return;
+        if (attempt == 1) break;
+        bool tie = false;
+        for (int q = lid; q + 1 < n; q += 32) tie |= a[in[q]].value == a[in[q + 1]].value;
+        if (!__any_sync(0xffffffffu, tie)) break;
+        warp_introsort_partitions(a, n, ordA, ordB, lid);
     }
+    return in;
+}
+
+// In-place form (self test).
+__device__ __forceinline__ void warp_std_sort(ssr::Item* a, int n, unsigned short* ordA, unsigned short* ordB, unsigned short* h, int lid) {
+    if (n <= 1) return;
+    const unsigned short* in = warp_std_sort_order(a, n, ordA, ordB, h, lid);
+    ssr::Item mine[WS_MAX_SORT / 32];
+#pragma unroll
+    for (int u = 0; u < WS_MAX_SORT / 32; ++u) { const int q = lid + 32 * u; if (q < n) mine[u] = a[in[q]]; }
+    __syncwarp();
+#pragma unroll
+    for (int u = 0; u < WS_MAX_SORT / 32; ++u) { const int q = lid + 32 * u; if (q < n) a[q] = mine[u]; }
+    __syncwarp();
 }
 
 }  // namespace lego
