@@ -54,7 +54,7 @@ constexpr int SEL_WARPS = 4;         // rings per CTA of fa_select_kernel
 constexpr int FX_MAX_ITERS = 16;     // 256-wide sweeps over one ring (Horizon_SCAN <= 4096)
 constexpr int CAND_SLOW = 0xff;      // reach marker: the point is outside its ring's [start, end) (stale slot 4, quirk Q11)
 
-struct SortSmem { ssr::Item a[WS_MAX_SORT]; unsigned short oA[WS_MAX_SORT], oB[WS_MAX_SORT], h[256]; };
+struct SortSmem { ssr::Item a[WS_MAX_SORT]; unsigned short oA[WS_MAX_SORT], oB[WS_MAX_SORT], h[512]; };
 
 __global__ void __launch_bounds__(32 * FS_WARPS) fa_sort_sectors_kernel(IpDev d, FaDev f, Consts c) {
     __shared__ __align__(16) SortSmem sm[FS_WARPS];

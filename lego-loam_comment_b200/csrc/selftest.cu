@@ -25,7 +25,7 @@ __global__ void selftest_sort_kernel(ssr::Item* items, const int* offsets, int n
 // one warp per segment (<= WS_MAX_SORT entries): slice staged in shared memory, sorted with warp_std_sort
 __global__ void __launch_bounds__(32) selftest_warp_sort_kernel(ssr::Item* items, const int* offsets, int nseg) {
     __shared__ ssr::Item a[WS_MAX_SORT];
-    __shared__ unsigned short oA[WS_MAX_SORT], oB[WS_MAX_SORT], h[256];
+    __shared__ unsigned short oA[WS_MAX_SORT], oB[WS_MAX_SORT], h[512];
     const int s = blockIdx.x, lid = threadIdx.x;
     const int n = offsets[s + 1] - offsets[s];
     ssr::Item* g = items + offsets[s];

@@ -67,6 +67,43 @@ __device__ __forceinline__ void warp_scan256(unsigned short* h, int lid) {
     __syncwarp();
 }
 
+// Stable LSD radix sort of one warp's list with 4-bit digits and lane-private counters: lane l owns the l-th block
+// of ceil(n/32) consecutive entries and one column of the 16 x 32 counter table, so counting and ranking need no
+// votes or atomics (MATCH / VOTE share the ADU pipe, which saturates long before anything else when every warp of
+// the SM sorts).  The exclusive scan runs over (digit, lane), which keeps equal digits in list order.
+// cnt: 512 counters.  Returns the list that holds the result (in or out).
+template <class KeyF>
+__device__ __forceinline__ unsigned short* warp_radix_sort_blocked(unsigned short* in, unsigned short* out, int n, int keyBits,
+                                                                   unsigned short* cnt, int lid, KeyF key) {
+    const int m = (n + 31) >> 5;
+    const int b0 = min(lid * m, n), b1 = min(b0 + m, n);
+    for (int shift = 0; shift < keyBits; shift += 4) {
+#pragma unroll
+        for (int b = 0; b < 16; ++b) cnt[b * 32 + lid] = 0;
+        for (int q = b0; q < b1; ++q) { const unsigned dg = (key(in[q]) >> shift) & 15u; cnt[dg * 32 + lid] = (unsigned short)(cnt[dg * 32 + lid] + 1); }
+        __syncwarp();
+        {
+            int v[16], s = 0;
+#pragma unroll
+            for (int i = 0; i < 16; ++i) { v[i] = cnt[16 * lid + i]; s += v[i]; }
+            int run = warp_inclusive_scan(s) - s;
+#pragma unroll
+            for (int i = 0; i < 16; ++i) { cnt[16 * lid + i] = (unsigned short)run; run += v[i]; }
+        }
+        __syncwarp();
+        for (int q = b0; q < b1; ++q) {
+            const unsigned short e = in[q];
+            const unsigned dg = (key(e) >> shift) & 15u;
+            const int pos = cnt[dg * 32 + lid];
+            cnt[dg * 32 + lid] = (unsigned short)(pos + 1);
+            out[pos] = e;
+        }
+        __syncwarp();
+        unsigned short* t = in; in = out; out = t;
+    }
+    return in;
+}
+
 // The partition phase of libstdc++'s introsort (std_sort_replay.cuh has the single-thread statement) done by one warp.
 // Hoare's unguarded partition is sequential as written, but its outcome has a closed form on the arrangement it
 // starts from: with L_1 < L_2 < ... the positions whose value is not below the pivot and R_1 > R_2 > ... the
@@ -132,34 +169,15 @@ __device__ __forceinline__ void warp_introsort_partitions(ssr::Item* a, int n, u
 // Distinct values have one sorted order and the radix sort finds it; if equal values exist, introsort's partitions
 // are replayed first (permuting a) and the radix sort (stable, like std::sort's closing insertion sort) finishes the
 // job.  Returns the sorted order as a list of positions into a: element q of the result is a[order[q]].
-// ordA / ordB: n entries of scratch each (the result is one of them), h: 256 counters (4-byte aligned).
+// ordA / ordB: n entries of scratch each (the result is one of them), h: 512 counters.
 __device__ __forceinline__ const unsigned short* warp_std_sort_order(ssr::Item* a, int n, unsigned short* ordA, unsigned short* ordB,
                                                                      unsigned short* h, int lid) {
     auto key = [&](unsigned short e) -> unsigned { return float_sort_key(a[e].value); };
     unsigned short* in = ordA;
     for (int attempt = 0; attempt < 2; ++attempt) {
-        in = ordA; unsigned short* out = ordB;
-        for (int q = lid; q < n; q += 32) in[q] = (unsigned short)q;
+        for (int q = lid; q < n; q += 32) ordA[q] = (unsigned short)q;
         __syncwarp();
-        for (int shift = 0; shift < 32; shift += 8) {
-#pragma unroll
-            for (int i = 0; i < 8; ++i) h[lid + 32 * i] = 0;
-            __syncwarp();
-            constexpr int U = 5;
-            RadixBatch<U> r;
-            for (int q0 = 0; q0 < n; q0 += 32 * U) {
-                radix_batch_load(r, in + q0, min(n - q0, 32 * U), shift, lid, key);
-                radix_batch_count(r, min(n - q0, 32 * U), reinterpret_cast<unsigned*>(h), lid);
-            }
-            __syncwarp();
-            warp_scan256(h, lid);
-            for (int q0 = 0; q0 < n; q0 += 32 * U) {
-                if (n > 32 * U) radix_batch_load(r, in + q0, min(n - q0, 32 * U), shift, lid, key);
-                radix_batch_scatter(r, min(n - q0, 32 * U), reinterpret_cast<unsigned*>(h), out, lid);
-            }
-            __syncwarp();
-            unsigned short* t = in; in = out; out = t;
-        }
+        in = warp_radix_sort_blocked(ordA, ordB, n, 32, h, lid, key);
         if (attempt == 1) break;
         bool tie = false;
         for (int q = lid; q + 1 < n; q += 32) tie |= a[in[q]].value == a[in[q + 1]].value;
