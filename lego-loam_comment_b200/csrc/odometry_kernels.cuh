@@ -22,6 +22,7 @@ struct OdoShared {
     int isDegenerate;
     int keepGoing;
     int ringOff[132];
+    int nextQuery;             // dynamic distribution of the correspondence searches over the warps
     double red[ODO_WARPS][10];
 };
 
@@ -67,9 +68,15 @@ __device__ int odo_phase(OdoShared& sh, float4* sel, const float4* __restrict__ 
     for (int iter = 0; iter < 25; ++iter) {
         itersDone = iter + 1;
         for (int q = tid; q < Q; q += ODO_THREADS) sel[q] = pose::transform_to_start(feats[q], sh.T);
+        if (tid == 0) sh.nextQuery = 0;
         __syncthreads();
         if (iter % 5 == 0) {
-            for (int q = warp; q < Q; q += ODO_WARPS) {
+            // one query per warp at a time, handed out dynamically: the searches differ a lot in length
+            while (true) {
+                int q = 0;
+                if (lid == 0) q = atomicAdd(&sh.nextQuery, 1);
+                q = __shfl_sync(0xffffffffu, q, 0);
+                if (q >= Q) break;
                 float d2near;
                 const float4 pq = sel[q];
                 const int closest = vh_nearest_warp(vh, pq.x, pq.y, pq.z, maxD2, 1.0f, &d2near);
@@ -81,21 +88,33 @@ __device__ int odo_phase(OdoShared& sh, float4* sel, const float4* __restrict__ 
                     // forward scan: the reference bounds it by the CURRENT feature count (quirk Q13)
                     const int hiF = min(min(Q, M), sh.ringOff[min(scan + 3, c.R + 2)]);
                     const int nF = max(hiF - (closest + 1), 0);
-                    for (int j = closest + 1 + lid; j < hiF; j += 32) {
-                        const float4 a = last[j];
+                    auto offerF = [&](const float4& a, int j) {
                         const float d = vh_dist2(a, p.x, p.y, p.z);
                         const int ring = (int)a.w, ord = j - (closest + 1);
                         if (SURF) { if (ring <= scan) cand_offer(b2, d, ord, j, maxD2); else cand_offer(b3, d, ord, j, maxD2); }
                         else if (ring > scan) cand_offer(b2, d, ord, j, maxD2);
-                    }
-                    const int loB = sh.ringOff[max(scan - 2, 0)];
-                    for (int j = closest - 1 - lid; j >= loB; j -= 32) {
-                        const float4 a = last[j];
+                    };
+                    auto offerB = [&](const float4& a, int j) {
                         const float d = vh_dist2(a, p.x, p.y, p.z);
                         const int ring = (int)a.w, ord = nF + (closest - 1 - j);
                         if (SURF) { if (ring >= scan) cand_offer(b2, d, ord, j, maxD2); else cand_offer(b3, d, ord, j, maxD2); }
                         else if (ring < scan) cand_offer(b2, d, ord, j, maxD2);
+                    };
+                    // four loads in flight per lane; cand_offer keeps the lexicographic minimum of (distance, order),
+                    // so the order in which a lane meets its candidates does not matter
+                    int j = closest + 1 + lid;
+                    for (; j + 96 < hiF; j += 128) {
+                        const float4 a0 = last[j], a1 = last[j + 32], a2 = last[j + 64], a3 = last[j + 96];
+                        offerF(a0, j); offerF(a1, j + 32); offerF(a2, j + 64); offerF(a3, j + 96);
                     }
+                    for (; j < hiF; j += 32) offerF(last[j], j);
+                    const int loB = sh.ringOff[max(scan - 2, 0)];
+                    j = closest - 1 - lid;
+                    for (; j - 96 >= loB; j -= 128) {
+                        const float4 a0 = last[j], a1 = last[j - 32], a2 = last[j - 64], a3 = last[j - 96];
+                        offerB(a0, j); offerB(a1, j - 32); offerB(a2, j - 64); offerB(a3, j - 96);
+                    }
+                    for (; j >= loB; j -= 32) offerB(last[j], j);
                 }
                 b2 = cand_warp_min(b2);
                 if (SURF) b3 = cand_warp_min(b3);

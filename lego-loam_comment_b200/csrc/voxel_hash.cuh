@@ -148,12 +148,17 @@ __device__ inline int vh_nearest_warp(const VhLane& v, float x, float y, float z
             const int s = vh_find(v.keys, v.H, vh_pack(cx + dx, cy + dy, cz + dz));
             if (s < 0) continue;
             const int b = v.start[s], e = b + v.count[s];
-            for (int t = b; t < e; ++t) {
-                const float4 a = v.sorted[t];
+            auto offer = [&](const float4& a) {
                 const float d = vh_dist2(a, x, y, z);
                 const int ai = __float_as_int(a.w);
                 if (d < best || (d == best && bestI != 0x7fffffff && ai < bestI)) { best = d; bestI = ai; }
+            };
+            int t = b;
+            for (; t + 3 < e; t += 4) {   // four loads in flight
+                const float4 a0 = v.sorted[t], a1 = v.sorted[t + 1], a2 = v.sorted[t + 2], a3 = v.sorted[t + 3];
+                offer(a0); offer(a1); offer(a2); offer(a3);
             }
+            for (; t < e; ++t) offer(v.sorted[t]);
         }
         // warp minimum of (best, bestI); lanes that found nothing carry (maxD2, INT_MAX)
 #pragma unroll
