@@ -16,7 +16,7 @@ EXPORTED = [
     "lego_ip_create", "lego_ip_destroy", "lego_ip_process",
     "lego_fa_create", "lego_fa_destroy", "lego_fa_process",
     "lego_mo_create", "lego_mo_destroy", "lego_mo_process",
-    "lego_pipeline_create", "lego_pipeline_destroy", "lego_pipeline_step", "lego_pipeline_get_poses",
+    "lego_pipeline_create", "lego_pipeline_destroy", "lego_pipeline_step", "lego_pipeline_get_poses", "lego_pipeline_poses_async", "lego_pipeline_poses_wait",
     "lego_pipeline_sync", "lego_pipeline_launch_count", "lego_pipeline_download", "lego_pipeline_upload",
     "lego_pipeline_timer_record", "lego_pipeline_timer_elapsed", "lego_pipeline_timer_elapsed_between", "lego_pipeline_profile", "lego_pipeline_profile_read",
     "lego_selftest_atan2f", "lego_selftest_std_sort", "lego_selftest_warp_sort", "lego_selftest_voxel_grid",
@@ -50,6 +50,8 @@ def load():
         lib.lego_pipeline_upload.argtypes = [ctypes.c_void_p, ctypes.c_int, ctypes.c_char_p, ctypes.c_void_p, ctypes.c_long]
         lib.lego_pipeline_upload.restype = ctypes.c_long
         lib.lego_pipeline_get_poses.argtypes = [ctypes.c_void_p, ctypes.c_void_p, ctypes.c_void_p]
+        lib.lego_pipeline_poses_async.argtypes = [ctypes.c_void_p, ctypes.c_int]
+        lib.lego_pipeline_poses_wait.argtypes = [ctypes.c_void_p, ctypes.c_int, ctypes.c_void_p, ctypes.c_void_p]
         lib.lego_pipeline_timer_record.argtypes = [ctypes.c_void_p, ctypes.c_int]
         lib.lego_pipeline_timer_elapsed.argtypes = [ctypes.c_void_p, ctypes.c_int, ctypes.c_int, ctypes.POINTER(ctypes.c_float)]
         lib.lego_pipeline_profile.argtypes = [ctypes.c_void_p, ctypes.c_int, ctypes.c_char_p]
@@ -183,6 +185,16 @@ class Pipeline:
         poses = np.zeros((self.lanes, 18), np.float32)
         flags = np.zeros(self.lanes, np.int32)
         _check(self.lib.lego_pipeline_get_poses(self.h, poses.ctypes.data, flags.ctypes.data), "lego_pipeline_get_poses")
+        return poses, flags
+
+    def poses_async(self, slot):
+        """Enqueue the read-back of the poses after the last step into pinned slot 0/1 (returns at once)."""
+        _check(self.lib.lego_pipeline_poses_async(self.h, int(slot)), "lego_pipeline_poses_async")
+
+    def poses_wait(self, slot):
+        poses = np.zeros((self.lanes, 18), np.float32)
+        flags = np.zeros(self.lanes, np.int32)
+        _check(self.lib.lego_pipeline_poses_wait(self.h, int(slot), poses.ctypes.data, flags.ctypes.data), "lego_pipeline_poses_wait")
         return poses, flags
 
     def download(self, name, lane=0):

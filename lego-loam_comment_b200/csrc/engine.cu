@@ -79,6 +79,7 @@ Engine::~Engine() {
     for (auto& pe : profLog) { if (pe.a) cudaEventDestroy(pe.a); if (pe.b) cudaEventDestroy(pe.b); }
     for (cudaEvent_t e : evPool) cudaEventDestroy(e);
     for (cudaEvent_t e : timerEv) if (e) cudaEventDestroy(e);
+    for (int b = 0; b < 2; ++b) { if (posePin[b]) cudaFreeHost(posePin[b]); if (poseEv[b]) cudaEventDestroy(poseEv[b]); }
     if (copyStream) cudaStreamDestroy(copyStream);
     if (stream) cudaStreamDestroy(stream);
 }
@@ -188,6 +189,35 @@ void Engine::getPoses(float* poses18, int* flags) {
         for (int k = 0; k < 6; ++k) poses18[l * 18 + k] = sum[l * 6 + k];
         for (int k = 0; k < 6; ++k) { poses18[l * 18 + 6 + k] = aft[l * 6 + k]; poses18[l * 18 + 12 + k] = bef[l * 6 + k]; }
         if (flags) flags[l] = (fl[l] & 7) | (moActiveLast.size() == (size_t)c.L && moActiveLast[l] ? 8 : 0);
+    }
+}
+
+// Streaming form of getPoses: the copies go into a pinned slot behind the step that was just enqueued, so the caller
+// can submit the next scan before it collects this one's result.
+void Engine::posesAsync(int slot) {
+    const size_t L = c.L;
+    if (!posePin[slot]) {
+        cuda_check(cudaMallocHost(reinterpret_cast<void**>(&posePin[slot]), sizeof(float) * 19 * L), "pinned poses");
+        cuda_check(cudaEventCreateWithFlags(&poseEv[slot], cudaEventDisableTiming), "event create");
+    }
+    float* p = posePin[slot];
+    cuda_check(cudaMemcpyAsync(p, fa.transformSum, sizeof(float) * 6 * L, cudaMemcpyDeviceToHost, stream), "poses");
+    cuda_check(cudaMemcpyAsync(p + 6 * L, mo.transformAftMapped, sizeof(float) * 6 * L, cudaMemcpyDeviceToHost, stream), "poses");
+    cuda_check(cudaMemcpyAsync(p + 12 * L, mo.transformBefMapped, sizeof(float) * 6 * L, cudaMemcpyDeviceToHost, stream), "poses");
+    cuda_check(cudaMemcpyAsync(p + 18 * L, fa.flags, sizeof(int) * L, cudaMemcpyDeviceToHost, stream), "flags");
+    cuda_check(cudaEventRecord(poseEv[slot], stream), "event record");
+    poseActive[slot] = moActiveLast;
+}
+
+void Engine::posesWait(int slot, float* poses18, int* flags) {
+    if (!posePin[slot]) { set_last_error("poses_wait without poses_async"); throw std::runtime_error("poses_wait"); }
+    cuda_check(cudaEventSynchronize(poseEv[slot]), "event sync");
+    const size_t L = c.L;
+    const float* p = posePin[slot];
+    const int* fl = reinterpret_cast<const int*>(p + 18 * L);
+    for (size_t l = 0; l < L; ++l) {
+        for (int k = 0; k < 6; ++k) { poses18[l * 18 + k] = p[l * 6 + k]; poses18[l * 18 + 6 + k] = p[6 * L + l * 6 + k]; poses18[l * 18 + 12 + k] = p[12 * L + l * 6 + k]; }
+        if (flags) flags[l] = (fl[l] & 7) | (poseActive[slot].size() == L && poseActive[slot][l] ? 8 : 0);
     }
 }
 

@@ -177,6 +177,9 @@ public:
     std::vector<ProfEntry> profLog;
     std::vector<cudaEvent_t> evPool;
     cudaEvent_t timerEv[8] = {};
+    float* posePin[2] = {nullptr, nullptr};      // pinned: [sum 6L | aft 6L | bef 6L | flags L]
+    cudaEvent_t poseEv[2] = {};
+    std::vector<int> poseActive[2];
     cudaEvent_t takeEvent();
     void profBegin(const char* name);
     void profEnd();
@@ -185,6 +188,8 @@ public:
     void timerRecord(int slot);
     float timerElapsed(int a, int b);
     void getPoses(float* poses18, int* flags);   // per lane: transformSum | transformAftMapped | transformBefMapped
+    void posesAsync(int slot);                   // enqueue the read-back of the current poses into pinned slot 0/1
+    void posesWait(int slot, float* poses18, int* flags);
     long download(int lane, const char* name, void* dst, long cap, int* elem_size);
     long upload(int lane, const char* name, const void* src, long count);
     bool lookup(int lane, const std::string& name, void** ptr, int* elem, long* count);

@@ -80,3 +80,42 @@ def test_image_projection_error_codes():
     b = ipn.process(holes, None, 0.1, is_dense=False)[1].numpy()
     assert np.array_equal(a.view(np.uint32), b.view(np.uint32))
     ipn.close()
+
+
+def test_streaming_pose_readback_equals_blocking():
+    """lego_pipeline_poses_async / _wait (scan k+1 submitted before the result of scan k is collected) returns what
+    lego_pipeline_get_poses returns for the same scans."""
+    sensor = "vlp16"
+    p = make_params(sensor)
+    seqs = [SynthSequence(sensor, seed=s, scene="street", speed=3.0) for s in (2, 9)]
+    cap = max(s.cap for s in seqs)
+    a = capi.Pipeline(p, lanes=2, max_points=cap)
+    b = capi.Pipeline(p, lanes=2, max_points=cap)
+    n = 12
+
+    def scan(k):
+        x = np.zeros((2, cap, 4), np.float32); r = np.zeros((2, cap), np.uint16); npts = []
+        for l, s in enumerate(seqs):
+            xyzi, ring = s.scan(k)
+            x[l, :len(xyzi)] = xyzi; r[l, :len(ring)] = ring; npts.append(len(xyzi))
+        return x, r, npts, [s.stamp(k) for s in seqs]
+
+    want = []
+    for k in range(n):
+        x, r, npts, st = scan(k)
+        a.step(x, r, npts, st, stage_mask=7)
+        want.append(a.poses())
+    got = []
+    held = []   # host arrays stay alive until their upload has been consumed
+    for k in range(n):
+        x, r, npts, st = scan(k)
+        held.append((x, r))
+        b.step(x, r, npts, st, stage_mask=7)
+        b.poses_async(k & 1)
+        if k > 0:
+            got.append(b.poses_wait((k - 1) & 1))
+    got.append(b.poses_wait((n - 1) & 1))
+    for k in range(n):
+        assert np.array_equal(got[k][0], want[k][0]), "poses differ at scan %d" % k
+        assert np.array_equal(got[k][1], want[k][1]), "flags differ at scan %d" % k
+    a.close(); b.close()
