@@ -327,7 +327,7 @@ void Engine::mapOptimizationBody(const std::vector<int>& active) {
     {
         ProfScope ps(this, "mo_scan2map(lm loop)");
         mo_lm_begin_kernel<<<(c.L + 63) / 64, 64, 0, stream>>>(mo, c.L);
-        dim3 g(mo.resBlocks, c.L);
+        dim3 g(std::min(mo.resBlocks, 16), c.L);   // 16 x 256 queries per lane in flight; larger scans loop
         for (int iter = 0; iter < 10; ++iter) {
             mo_residual_kernel<<<g, 256, 0, stream>>>(mo);
             mo_solve_kernel<<<c.L, 32, 0, stream>>>(mo, iter);

@@ -169,31 +169,35 @@ __global__ void __launch_bounds__(MO_RES_THREADS) mo_residual_kernel(MoDev m) {
     const int lane = blockIdx.y, tid = threadIdx.x, lid = tid & 31, warp = tid >> 5;
     if (!m.state[lane * 16 + 6]) return;
     const int nCorner = m.scanCounts[lane * 8 + 0], nSurf = m.scanCounts[lane * 8 + 4];
-    const int q = blockIdx.x * MO_RES_THREADS + tid;
-    if (blockIdx.x * MO_RES_THREADS >= nCorner + nSurf) return;
     __shared__ double red[MO_RES_THREADS / 32][MO_ACC];
     const MapSinCos sc = map_sincos(m.transformTobeMapped + lane * 6);
-    double acc[MO_ACC];
+    // a CTA takes the 256-query blocks blk = blockIdx.x, blockIdx.x + gridDim.x, ...; the partial sums stay per block
+    // (not per CTA) so the solve kernel adds them in the same order whatever the grid size
+    for (int blk = blockIdx.x; blk * MO_RES_THREADS < nCorner + nSurf; blk += gridDim.x) {
+        const int q = blk * MO_RES_THREADS + tid;
+        double acc[MO_ACC];
 #pragma unroll
-    for (int k = 0; k < MO_ACC; ++k) acc[k] = 0.0;
-    if (q < nCorner + nSurf) {
-        float cx, cy, cz, cd; bool ok; float4 o;
-        if (q < nCorner) {
-            o = m.cornerLastDS[(size_t)lane * m.scanCornerCap + q];
-            ok = mo_corner_residual(vh_lane(m.hashCornerMap, lane), m.cornerFromMapDS + (size_t)lane * m.cornerDSCap, sc, o, &cx, &cy, &cz, &cd);
-        } else {
-            o = m.surfTotalLastDS[(size_t)lane * (m.scanSurfCap + m.scanOutlierCap) + (q - nCorner)];
-            ok = mo_surf_residual(vh_lane(m.hashSurfMap, lane), m.surfFromMapDS + (size_t)lane * m.surfDSCap, sc, o, &cx, &cy, &cz, &cd);
+        for (int k = 0; k < MO_ACC; ++k) acc[k] = 0.0;
+        if (q < nCorner + nSurf) {
+            float cx, cy, cz, cd; bool ok; float4 o;
+            if (q < nCorner) {
+                o = m.cornerLastDS[(size_t)lane * m.scanCornerCap + q];
+                ok = mo_corner_residual(vh_lane(m.hashCornerMap, lane), m.cornerFromMapDS + (size_t)lane * m.cornerDSCap, sc, o, &cx, &cy, &cz, &cd);
+            } else {
+                o = m.surfTotalLastDS[(size_t)lane * (m.scanSurfCap + m.scanOutlierCap) + (q - nCorner)];
+                ok = mo_surf_residual(vh_lane(m.hashSurfMap, lane), m.surfFromMapDS + (size_t)lane * m.surfDSCap, sc, o, &cx, &cy, &cz, &cd);
+            }
+            if (ok) mo_accumulate(acc, sc, o, cx, cy, cz, cd);
         }
-        if (ok) mo_accumulate(acc, sc, o, cx, cy, cz, cd);
-    }
 #pragma unroll
-    for (int k = 0; k < MO_ACC; ++k) { const double v = warp_sum_d(acc[k]); if (lid == 0) red[warp][k] = v; }
-    __syncthreads();
-    if (tid < MO_ACC) {
-        double s = 0.0;
-        for (int w = 0; w < MO_RES_THREADS / 32; ++w) s += red[w][tid];
-        m.partials[((size_t)lane * m.resBlocks + blockIdx.x) * MO_ACC + tid] = s;
+        for (int k = 0; k < MO_ACC; ++k) { const double v = warp_sum_d(acc[k]); if (lid == 0) red[warp][k] = v; }
+        __syncthreads();
+        if (tid < MO_ACC) {
+            double s = 0.0;
+            for (int w = 0; w < MO_RES_THREADS / 32; ++w) s += red[w][tid];
+            m.partials[((size_t)lane * m.resBlocks + blk) * MO_ACC + tid] = s;
+        }
+        __syncthreads();
     }
 }
 
@@ -225,7 +229,10 @@ __global__ void __launch_bounds__(32) mo_solve_kernel(MoDev m, int iter) {
         for (int i = 0; i < 6; ++i) AtB[i] = (float)s[21 + i];
         sm::solve_qr<6, 6>(AtA, AtB, X);
         int degenerate = m.state[lane * 16 + 0];
-        if (iter == 0) { degenerate = sm::degeneracy_projector<6>(AtA, 100.f, matP) ? 1 : 0; m.state[lane * 16 + 0] = degenerate; }
+        if (iter == 0) {   // eigen decomposition only when the cheap bound cannot rule degeneracy out
+            degenerate = sm::min_eigen_certainly_above<6>(AtA, 100.f) ? 0 : (sm::degeneracy_projector<6>(AtA, 100.f, matP) ? 1 : 0);
+            m.state[lane * 16 + 0] = degenerate;
+        }
         if (degenerate) {
             float X2[6];
             for (int i = 0; i < 6; ++i) { double t = 0.0; for (int j = 0; j < 6; ++j) t += (double)matP[i * 6 + j] * (double)X[j]; X2[i] = (float)t; }

@@ -204,7 +204,7 @@ __device__ int odo_phase(OdoShared& sh, float4* sel, const float4* __restrict__ 
                 const float AtB[3] = {(float)s[6], (float)s[7], (float)s[8]};
                 float x[3];
                 sm::solve_qr<3, 3>(AtA, AtB, x);
-                if (iter == 0) sh.isDegenerate = sm::degeneracy_projector<3>(AtA, 10.f, sh.matP) ? 1 : 0;
+                if (iter == 0) sh.isDegenerate = sm::min_eigen_certainly_above<3>(AtA, 10.f) ? 0 : (sm::degeneracy_projector<3>(AtA, 10.f, sh.matP) ? 1 : 0);
                 if (sh.isDegenerate) {
                     float x2[3];
                     for (int i = 0; i < 3; ++i) x2[i] = (float)((double)sh.matP[i * 3] * x[0] + (double)sh.matP[i * 3 + 1] * x[1] + (double)sh.matP[i * 3 + 2] * x[2]);

@@ -136,4 +136,31 @@ __host__ __device__ inline bool degeneracy_projector(const float* AtA, float thr
     return degenerate;
 }
 
+// True when the smallest eigenvalue of the symmetric matrix A is certainly above `thresh` by a margin no float
+// eigen solver error can bridge (margin = 1e-5 * trace + 1 % of thresh; the error of a float Jacobi sweep on an N x N
+// matrix is a few N * 6e-8 * ||A||).  Test: Cholesky of A - (thresh + margin) I in double succeeds with positive
+// pivots.  Callers use it to skip degeneracy_projector when its answer is known to be "not degenerate" -- the
+// projector itself is only ever applied when isDegenerate is set (featureAssociation.cpp:1361-1367,
+// mapOptmization.cpp:1303-1308).
+template <int N>
+__host__ __device__ inline bool min_eigen_certainly_above(const float* A, float thresh) {
+    double tr = 0.0;
+    for (int i = 0; i < N; ++i) tr += (double)A[i * N + i];
+    const double shift = (double)thresh + 1e-5 * tr + 0.01 * (double)thresh;
+    double Lm[N * N];
+    for (int i = 0; i < N; ++i) {
+        for (int j = 0; j <= i; ++j) {
+            double sum = (double)A[i * N + j] - (i == j ? shift : 0.0);
+            for (int k = 0; k < j; ++k) sum -= Lm[i * N + k] * Lm[j * N + k];
+            if (i == j) {
+                if (!(sum > 1e-9 * (tr + 1.0))) return false;
+                Lm[i * N + i] = sqrt(sum);
+            } else {
+                Lm[i * N + j] = sum / Lm[j * N + j];
+            }
+        }
+    }
+    return true;
+}
+
 }  // namespace sm
