@@ -120,7 +120,7 @@ struct MoDev {
     int* scanCounts;           // [L][8]  cornerLastDS, surfLastDS, outlierLastDS, surfTotalLast, surfTotalLastDS sizes
     VoxelHash hashCornerMap, hashSurfMap;
     MoRecord* records;         // [L]
-    double* partials;          // [L][resBlocks][28] per-CTA partial sums of AtA / AtB / row count
+    double* partials;          // [L][resBlocks][8][28] per-warp partial sums of AtA / AtB / row count
     int resBlocks;             // CTAs per lane in mo_residual_kernel
     int poolCap, maxSel, cornerRawCap, surfRawCap, cornerDSCap, surfDSCap, scanCornerCap, scanSurfCap, scanOutlierCap, maxKeyFrames;
 };

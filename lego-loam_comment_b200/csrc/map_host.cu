@@ -50,7 +50,7 @@ void Engine::allocMapOptimization() {
     mo.hashCornerMap = allocHash(mo.cornerDSCap, 1.0f, mo.mapCounts + 2, 4); mo.hashSurfMap = allocHash(mo.surfDSCap, 1.0f, mo.mapCounts + 3, 4);
     mo.records = alloc<MoRecord>(L);
     mo.resBlocks = (mo.scanCornerCap + mo.scanSurfCap + mo.scanOutlierCap + 255) / 256;
-    mo.partials = alloc<double>(L * mo.resBlocks * 28);
+    mo.partials = alloc<double>(L * mo.resBlocks * 8 * 28);   // per 32-query warp slice
     moHost.assign(c.L, MoLaneHost());
 
     // ---- VoxelGrid segment tables ----

@@ -165,14 +165,13 @@ __global__ void mo_lm_begin_kernel(MoDev m, int L) {
     m.state[lane * 16 + 6] = go;
 }
 
-__global__ void __launch_bounds__(MO_RES_THREADS) mo_residual_kernel(MoDev m) {
+__global__ void __launch_bounds__(MO_RES_THREADS, 4) mo_residual_kernel(MoDev m) {
     const int lane = blockIdx.y, tid = threadIdx.x, lid = tid & 31, warp = tid >> 5;
     if (!m.state[lane * 16 + 6]) return;
     const int nCorner = m.scanCounts[lane * 8 + 0], nSurf = m.scanCounts[lane * 8 + 4];
-    __shared__ double red[MO_RES_THREADS / 32][MO_ACC];
     const MapSinCos sc = map_sincos(m.transformTobeMapped + lane * 6);
     // a CTA takes the 256-query blocks blk = blockIdx.x, blockIdx.x + gridDim.x, ...; the partial sums stay per block
-    // (not per CTA) so the solve kernel adds them in the same order whatever the grid size
+    // and warp (not per CTA) so the solve kernel adds them in the same order whatever the grid size
     for (int blk = blockIdx.x; blk * MO_RES_THREADS < nCorner + nSurf; blk += gridDim.x) {
         const int q = blk * MO_RES_THREADS + tid;
         double acc[MO_ACC];
@@ -189,15 +188,16 @@ __global__ void __launch_bounds__(MO_RES_THREADS) mo_residual_kernel(MoDev m) {
             }
             if (ok) mo_accumulate(acc, sc, o, cx, cy, cz, cd);
         }
+        // every warp writes its own 28 sums (no CTA barrier: the queries of a block differ a lot in length)
+        double mine = 0.0;
 #pragma unroll
-        for (int k = 0; k < MO_ACC; ++k) { const double v = warp_sum_d(acc[k]); if (lid == 0) red[warp][k] = v; }
-        __syncthreads();
-        if (tid < MO_ACC) {
-            double s = 0.0;
-            for (int w = 0; w < MO_RES_THREADS / 32; ++w) s += red[w][tid];
-            m.partials[((size_t)lane * m.resBlocks + blk) * MO_ACC + tid] = s;
+        for (int k = 0; k < MO_ACC; ++k) {
+            double v = acc[k];
+#pragma unroll
+            for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);
+            if (lid == k) mine = v;
         }
-        __syncthreads();
+        if (lid < MO_ACC) m.partials[(((size_t)lane * m.resBlocks + blk) * (MO_RES_THREADS / 32) + warp) * MO_ACC + lid] = mine;
     }
 }
 
@@ -210,8 +210,8 @@ __global__ void __launch_bounds__(32) mo_solve_kernel(MoDev m, int iter) {
     const int nb = (nQ + MO_RES_THREADS - 1) / MO_RES_THREADS;
     if (lid < MO_ACC) {
         double t = 0.0;
-        const double* p = m.partials + (size_t)lane * m.resBlocks * MO_ACC + lid;
-        for (int b = 0; b < nb; ++b) t += p[(size_t)b * MO_ACC];
+        const double* p = m.partials + (size_t)lane * m.resBlocks * (MO_RES_THREADS / 32) * MO_ACC + lid;
+        for (int b = 0; b < nb * (MO_RES_THREADS / 32); ++b) t += p[(size_t)b * MO_ACC];
         s[lid] = t;
     }
     __syncwarp();
