@@ -35,7 +35,7 @@ def parse_args():
     ap.add_argument("--gpus", type=int, default=1)
     ap.add_argument("--steps", type=int, default=20)
     ap.add_argument("--warmup", type=int, default=4)
-    ap.add_argument("--lanes", type=int, default=0, help="independent sequences per GPU stepped in lock step (0 = 296 for 16/32 rings, 64 above)")
+    ap.add_argument("--lanes", type=int, default=0, help="independent sequences per GPU stepped in lock step (0 = 592 for 16 rings, 296 for 32, 148 above)")
     ap.add_argument("--handles", type=int, default=4, help="pipeline handles (CUDA streams) the lanes of one GPU are split over")
     ap.add_argument("--sensor", default="vlp16")
     ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
@@ -48,8 +48,10 @@ def parse_args():
 
 
 def default_lanes(sensor):
-    """2 x 148 SMs for the small sensors; the dense sensors carry ~5x the points per lane."""
-    return 296 if sensor in ("vlp16", "vlp16_noring", "hdl32") else 64
+    """Multiples of the 148 SMs: 4 sequences per SM for 16 rings, 2 for 32, 1 for the dense sensors (~5x the points per lane)."""
+    if sensor in ("vlp16", "vlp16_noring"):
+        return 592
+    return 296 if sensor == "hdl32" else 148
 
 
 def dist_env():
