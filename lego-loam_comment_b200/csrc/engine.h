@@ -37,6 +37,7 @@ struct IpDev {
     int* labelMat;             // [L][N]   -1, 0 (transient), 1..K, 999999
     int* parent;               // [L][N]   union-find forest, root = smallest cell index of the component
     int* compSize;             // [L][N]   at roots: number of non-root members; later: the root's final label
+    int* runLen;               // [L][N]   at the last cell of a horizontal run: its length (0 elsewhere)
     uint32_t* compRows;        // [L][N][rowWords] at roots: bitmask of rows that hold a non-root member
     int* rowCounts;            // [L][R][4] per row: valid roots, kept cells, outlier cells, unused
     float4* segCloud;          // [L][N]

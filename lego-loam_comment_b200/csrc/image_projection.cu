@@ -143,29 +143,84 @@ __device__ __forceinline__ bool seg_edge(float r1, float r2, float sinA, float c
     return angle > theta;
 }
 
-__global__ void __launch_bounds__(256) ip_ccl_union_kernel(IpDev d, Consts c) {
-    const int lane = blockIdx.y;
-    const int cell = blockIdx.x * blockDim.x + threadIdx.x;
-    if (cell >= c.N) return;
+// Connected components in three passes.  (1) ip_ccl_runs_kernel: horizontal runs.  Every cell tests the edge to its
+// left neighbour once; a run of connected cells inside a 256-cell block gets its leftmost cell as parent by a ballot
+// scan, without atomics, and its last cell remembers the run length.  (2) ip_ccl_union_kernel: the remaining edges --
+// vertical ones, the column wrap, and the horizontal edges a block boundary cut -- are merged with the lock-free
+// min-index union.  (3) ip_ccl_stats_kernel: every cell is pointed at its root, and every RUN (not every cell) adds
+// its length and row bit to the root's statistics, which takes the atomic traffic on large components down by the
+// run length.
+constexpr int RUN_LEFT_BIT = 1 << 30;
+
+__global__ void __launch_bounds__(256) ip_ccl_runs_kernel(IpDev d, Consts c) {
+    const int lane = blockIdx.y, tid = threadIdx.x, lid = tid & 31, warp = tid >> 5;
+    const int cell = blockIdx.x * blockDim.x + tid;
     const size_t base = (size_t)lane * c.N;
-    if (!seg_cell(d, base + cell)) return;
-    const int row = cell / c.C, col = cell - row * c.C;
-    const float r = d.rangeMat[base + cell];
+    const bool valid = cell < c.N;
+    const bool seg = valid && seg_cell(d, base + cell);
+    const int col = valid ? cell % c.C : 0;
+    bool leftConn = false;
+    if (seg && tid > 0 && col > 0 && seg_cell(d, base + cell - 1))
+        leftConn = seg_edge(d.rangeMat[base + cell], d.rangeMat[base + cell - 1], c.sinAlphaX, c.cosAlphaX, c.segmentTheta);
+    const bool brk = !leftConn;
+    __shared__ int s_lastBrk[8];
+    __shared__ unsigned char s_brk[257];
+    const unsigned mask = __ballot_sync(0xffffffffu, brk);
+    if (lid == 0) s_lastBrk[warp] = mask ? (warp << 5) + 31 - __clz(mask) : -1;
+    s_brk[tid] = brk ? 1 : 0;
+    if (tid == 0) s_brk[256] = 1;
+    __syncthreads();
+    if (!valid) return;
+    const unsigned lower = mask & (lid == 31 ? 0xffffffffu : ((2u << lid) - 1u));
+    int leaderT;
+    if (lower) leaderT = (warp << 5) + 31 - __clz(lower);
+    else { leaderT = 0; for (int w = warp - 1; w >= 0; --w) if (s_lastBrk[w] >= 0) { leaderT = s_lastBrk[w]; break; } }
+    const int leader = cell - tid + leaderT;
+    const bool isLast = seg && (s_brk[tid + 1] != 0);
+    if (seg) d.parent[base + cell] = leader;
+    // run length at the last cell; bit 30 tells the union pass that this cell hangs on its left neighbour
+    d.runLen[base + cell] = (isLast ? cell - leader + 1 : 0) | (leftConn ? RUN_LEFT_BIT : 0);
+}
+
+__global__ void __launch_bounds__(256) ip_ccl_union_kernel(IpDev d, Consts c) {
+    const int lane = blockIdx.y, tid = threadIdx.x;
+    const int cell = blockIdx.x * blockDim.x + tid;
+    const size_t base = (size_t)lane * c.N;
+    const bool seg = cell < c.N && seg_cell(d, base + cell);
+    const int row = cell < c.N ? cell / c.C : 0, col = cell - row * c.C;
+    const float r = seg ? d.rangeMat[base + cell] : 0.f;
     int* parent = d.parent + base;
-    // horizontal neighbour, columns wrap (imageProjection.cpp:403-406)
-    const int rc = row * c.C + (col + 1 == c.C ? 0 : col + 1);
-    if (rc != cell && seg_cell(d, base + rc) && seg_edge(r, d.rangeMat[base + rc], c.sinAlphaX, c.cosAlphaX, c.segmentTheta))
-        uf_union(parent, cell, rc);
     // vertical neighbour, rows do not wrap (imageProjection.cpp:400-401)
-    if (row + 1 < c.R) {
+    bool vert = false, hang = false;
+    if (seg && row + 1 < c.R) {
         const int dc = cell + c.C;
-        if (seg_cell(d, base + dc) && seg_edge(r, d.rangeMat[base + dc], c.sinAlphaY, c.cosAlphaY, c.segmentTheta))
-            uf_union(parent, cell, dc);
+        if (seg_cell(d, base + dc)) {
+            vert = seg_edge(r, d.rangeMat[base + dc], c.sinAlphaY, c.cosAlphaY, c.segmentTheta);
+            // both this cell and the one below hang on their left neighbours: if the left pair is joined
+            // vertically too, this edge joins the same two runs again
+            hang = (d.runLen[base + cell] & RUN_LEFT_BIT) && (d.runLen[base + dc] & RUN_LEFT_BIT);
+        }
+    }
+    __shared__ unsigned char s_vert[256];
+    s_vert[tid] = vert ? 1 : 0;
+    __syncthreads();
+    if (!seg) return;
+    if (vert && !(hang && tid > 0 && s_vert[tid - 1])) uf_union(parent, cell, cell + c.C);
+    // horizontal edge a block boundary cut out of the run pass
+    if (tid == 0 && col > 0 && seg_cell(d, base + cell - 1) &&
+        seg_edge(r, d.rangeMat[base + cell - 1], c.sinAlphaX, c.cosAlphaX, c.segmentTheta))
+        uf_union(parent, cell, cell - 1);
+    // columns wrap (imageProjection.cpp:403-406)
+    if (col == c.C - 1 && c.C > 1) {
+        const int rc = row * c.C;
+        if (seg_cell(d, base + rc) && seg_edge(r, d.rangeMat[base + rc], c.sinAlphaX, c.cosAlphaX, c.segmentTheta))
+            uf_union(parent, cell, rc);
     }
 }
 
 // Component statistics: size and the set of rows among NON-seed members.  The reference sets lineCountFlag only
-// for cells it pushes, never for the seed itself (imageProjection.cpp:376-384 vs 431, quirk Q5).
+// for cells it pushes, never for the seed itself (imageProjection.cpp:376-384 vs 431, quirk Q5).  The seed is the
+// smallest index of the component, i.e. the leader of its own run.
 __global__ void __launch_bounds__(256) ip_ccl_stats_kernel(IpDev d, Consts c) {
     const int lane = blockIdx.y;
     const int cell = blockIdx.x * blockDim.x + threadIdx.x;
@@ -174,11 +229,17 @@ __global__ void __launch_bounds__(256) ip_ccl_stats_kernel(IpDev d, Consts c) {
     if (!seg_cell(d, base + cell)) return;
     int* parent = d.parent + base;
     const int root = uf_find(parent, cell);
-    if (root == cell) return;
-    parent[cell] = root;
-    atomicAdd(d.compSize + base + root, 1);
-    const int row = cell / c.C;
-    atomicOr(d.compRows + (base + root) * c.rowWords + (row >> 5), 1u << (row & 31));
+    if (root != cell) parent[cell] = root;
+    const int len = d.runLen[base + cell] & ~RUN_LEFT_BIT;
+    if (len > 0) {
+        const int leader = cell - len + 1;
+        const int n = len - (leader == root ? 1 : 0);
+        if (n > 0) {
+            atomicAdd(d.compSize + base + root, n);
+            const int row = cell / c.C;
+            atomicOr(d.compRows + (base + root) * c.rowWords + (row >> 5), 1u << (row & 31));
+        }
+    }
 }
 
 // feasibleSegment of imageProjection.cpp:441-451 for the component rooted at `root`.
@@ -319,12 +380,13 @@ void Engine::groundRemoval() {
 
 void Engine::cloudSegmentation() {
     dim3 g((c.N + 255) / 256, c.L);
+    { ProfScope ps(this, "ip_ccl_runs_kernel"); ip_ccl_runs_kernel<<<g, 256, 0, stream>>>(ip, c); }
     { ProfScope ps(this, "ip_ccl_union_kernel"); ip_ccl_union_kernel<<<g, 256, 0, stream>>>(ip, c); }
     { ProfScope ps(this, "ip_ccl_stats_kernel"); ip_ccl_stats_kernel<<<g, 256, 0, stream>>>(ip, c); }
     dim3 gr(c.R, c.L);
     { ProfScope ps(this, "ip_row_count_kernel"); ip_row_count_kernel<<<gr, 256, 0, stream>>>(ip, c); }
     { ProfScope ps(this, "ip_compact_kernel"); ip_compact_kernel<<<gr, 256, 0, stream>>>(ip, c); }
-    launches += 4;
+    launches += 5;
 }
 
 void Engine::finalizeLabelMat() {
