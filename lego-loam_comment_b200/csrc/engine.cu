@@ -53,7 +53,7 @@ Engine::Engine(const lego_params& p, int lanes, int max_points) : params(p) {
     ip.in_xyzi = d_ptr_xyzi[0]; ip.in_ring = d_ptr_ring[0]; ip.npts = d_npts[0];
     ip.owner = alloc<int>(L * N); ip.rangeMat = alloc<float>(L * N); ip.fullCloud = alloc<float4>(L * N);
     ip.groundMat = alloc<int8_t>(L * N); ip.labelMat = alloc<int>(L * N); ip.parent = alloc<int>(L * N);
-    ip.compSize = alloc<int>(L * N); ip.runLen = alloc<int>(L * N); ip.compRows = alloc<uint32_t>(L * N * c.rowWords); ip.rowCounts = alloc<int>(L * R * 4);
+    ip.compSize = alloc<int>(L * N); ip.runLen = alloc<int>(L * N); ip.cellClass = alloc<unsigned char>(L * N); ip.compRows = alloc<uint32_t>(L * N * c.rowWords); ip.rowCounts = alloc<int>(L * R * 4);
     ip.segCloud = alloc<float4>(L * N); ip.segGround = alloc<uint8_t>(L * N); ip.segCol = alloc<int>(L * N);
     ip.segRange = alloc<float>(L * N); ip.startRing = alloc<int>(L * R); ip.endRing = alloc<int>(L * R);
     ip.orient = alloc<float>(L * 4); ip.outlier = alloc<float4>(L * c.Ocap); ip.counts = alloc<int>(L * 8);

@@ -38,6 +38,7 @@ struct IpDev {
     int* parent;               // [L][N]   union-find forest, root = smallest cell index of the component
     int* compSize;             // [L][N]   at roots: number of non-root members; later: the root's final label
     int* runLen;               // [L][N]   at the last cell of a horizontal run: its length (0 elsewhere)
+    unsigned char* cellClass;  // [L][N]   classify_cell bits (valid-segment head | to segmentedCloud | to outlierCloud)
     uint32_t* compRows;        // [L][N][rowWords] at roots: bitmask of rows that hold a non-root member
     int* rowCounts;            // [L][R][4] per row: valid roots, kept cells, outlier cells, unused
     float4* segCloud;          // [L][N]

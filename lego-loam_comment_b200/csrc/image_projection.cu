@@ -276,6 +276,7 @@ __global__ void __launch_bounds__(256) ip_row_count_kernel(IpDev d, Consts c) {
     int n0 = 0, n1 = 0, n2 = 0;
     for (int col = threadIdx.x; col < c.C; col += blockDim.x) {
         const int f = classify_cell(d, c, base, row, col);
+        d.cellClass[base + row * c.C + col] = (unsigned char)f;   // read back by ip_compact_kernel
         n0 += f & 1; n1 += (f >> 1) & 1; n2 += (f >> 2) & 1;
     }
     __shared__ int sh[3][8];
@@ -291,60 +292,76 @@ __global__ void __launch_bounds__(256) ip_row_count_kernel(IpDev d, Consts c) {
 }
 
 // Ordered compaction (imageProjection.cpp:319-355): row-major order is kept by giving every row block the
-// prefix of the counts of the rows before it and scanning inside the row.  Also numbers the valid segments
-// 1..K in seed order (imageProjection.cpp:453-454) and marks the rest 999999 at their root cells.
+// prefix of the counts of the rows before it and ranking inside the row: a first sweep counts the three classes per
+// (256-column sweep, warp) with ballots, one warp per class scans those counts, a second sweep writes.  Also numbers
+// the valid segments 1..K in seed order (imageProjection.cpp:453-454) and marks the rest 999999 at their root cells.
+constexpr int COMPACT_MAX_SWEEPS = 16;   // Horizon_SCAN <= 4096
 __global__ void __launch_bounds__(256) ip_compact_kernel(IpDev d, Consts c) {
-    const int lane = blockIdx.y, row = blockIdx.x;
+    const int lane = blockIdx.y, row = blockIdx.x, tid = threadIdx.x;
     const size_t base = (size_t)lane * c.N;
     __shared__ int pre[3];
-    __shared__ int wsum[3][8];
-    __shared__ int carry[3];
-    if (threadIdx.x < 3) {
+    __shared__ int cnt[3][COMPACT_MAX_SWEEPS * 8 + 1];
+    const int w = tid >> 5, l = tid & 31;
+    const int nSweep = (c.C + 255) >> 8;
+    if (tid < 3) {
         int s = 0;
-        for (int r = 0; r < row; ++r) s += d.rowCounts[((size_t)lane * c.R + r) * 4 + threadIdx.x];
-        pre[threadIdx.x] = s; carry[threadIdx.x] = 0;
+        for (int r = 0; r < row; ++r) s += d.rowCounts[((size_t)lane * c.R + r) * 4 + tid];
+        pre[tid] = s;
+    }
+    const unsigned char* cls = d.cellClass + base + row * c.C;
+    for (int it = 0; it < nSweep; ++it) {
+        const int col = it * 256 + tid;
+        const int f = col < c.C ? cls[col] : 0;
+#pragma unroll
+        for (int k = 0; k < 3; ++k) {
+            const unsigned bal = __ballot_sync(0xffffffffu, (f >> k) & 1);
+            if (l == 0) cnt[k][it * 8 + w] = __popc(bal);
+        }
     }
     __syncthreads();
-    const int w = threadIdx.x >> 5, l = threadIdx.x & 31, nw = blockDim.x >> 5;
-    if (threadIdx.x == 0) d.startRing[lane * c.R + row] = pre[1] - 1 + 5;
-    for (int col0 = 0; col0 < c.C; col0 += blockDim.x) {
-        const int col = col0 + threadIdx.x;
-        const int f = col < c.C ? classify_cell(d, c, base, row, col) : 0;
-        int v[3] = {f & 1, (f >> 1) & 1, (f >> 2) & 1};
-        int inc[3];
+    if (w < 3) {   // exclusive scan of class w's counts, total in the last slot
+        const int nSlots = nSweep * 8;
+        int v[COMPACT_MAX_SWEEPS * 8 / 32], s = 0;
 #pragma unroll
-        for (int k = 0; k < 3; ++k) { inc[k] = warp_inclusive_scan(v[k]); if (l == 31) wsum[k][w] = inc[k]; }
-        __syncthreads();
+        for (int i = 0; i < COMPACT_MAX_SWEEPS * 8 / 32; ++i) { const int q = l * (COMPACT_MAX_SWEEPS * 8 / 32) + i; v[i] = q < nSlots ? cnt[w][q] : 0; s += v[i]; }
+        int run = warp_inclusive_scan(s) - s;
+#pragma unroll
+        for (int i = 0; i < COMPACT_MAX_SWEEPS * 8 / 32; ++i) { const int q = l * (COMPACT_MAX_SWEEPS * 8 / 32) + i; if (q < nSlots) cnt[w][q] = run; run += v[i]; }
+        if (l == 31) cnt[w][nSlots] = run;
+    }
+    __syncthreads();
+    if (tid == 0) d.startRing[lane * c.R + row] = pre[1] - 1 + 5;
+    const unsigned lt = (1u << l) - 1u;
+    for (int it = 0; it < nSweep; ++it) {
+        const int col = it * 256 + tid;
+        const int f = col < c.C ? cls[col] : 0;
         int off[3];
 #pragma unroll
         for (int k = 0; k < 3; ++k) {
-            int s = 0;
-            for (int q = 0; q < w; ++q) s += wsum[k][q];
-            off[k] = pre[k] + carry[k] + s + inc[k] - v[k];
+            const unsigned bal = __ballot_sync(0xffffffffu, (f >> k) & 1);
+            off[k] = pre[k] + cnt[k][it * 8 + w] + __popc(bal & lt);
         }
         if (col < c.C) {
             const size_t g = base + row * c.C + col;
-            if (v[0]) d.labelMat[g] = off[0] + 1;
+            if (f & 1) d.labelMat[g] = off[0] + 1;
             else if (d.owner[g] >= 0 && d.groundMat[g] != 1 && d.parent[g] == row * c.C + col) d.labelMat[g] = 999999;
-            if (v[1]) {
+            if (f & 2) {
                 const size_t o = base + off[1];
                 d.segCloud[o] = d.fullCloud[g];
                 d.segGround[o] = d.groundMat[g] == 1 ? 1 : 0;
                 d.segCol[o] = col;
                 d.segRange[o] = d.rangeMat[g];
             }
-            if (v[2] && off[2] < c.Ocap) d.outlier[(size_t)lane * c.Ocap + off[2]] = d.fullCloud[g];
+            if ((f & 4) && off[2] < c.Ocap) d.outlier[(size_t)lane * c.Ocap + off[2]] = d.fullCloud[g];
         }
-        __syncthreads();
-        if (threadIdx.x < 3) { int s = 0; for (int q = 0; q < nw; ++q) s += wsum[threadIdx.x][q]; carry[threadIdx.x] += s; }
-        __syncthreads();
     }
-    if (threadIdx.x == 0) {
-        d.endRing[lane * c.R + row] = pre[1] + carry[1] - 1 - 5;
+    if (tid == 0) {
+        const int nSlots = nSweep * 8;
+        d.endRing[lane * c.R + row] = pre[1] + cnt[1][nSlots] - 1 - 5;
         if (row == c.R - 1) {
-            d.counts[lane * 8 + 0] = pre[1] + carry[1];
-            d.counts[lane * 8 + 1] = min(pre[2] + carry[2], c.Ocap);
-            d.counts[lane * 8 + 2] = pre[0] + carry[0];
+            d.counts[lane * 8 + 0] = pre[1] + cnt[1][nSlots];
+            d.counts[lane * 8 + 1] = min(pre[2] + cnt[2][nSlots], c.Ocap);
+            d.counts[lane * 8 + 2] = pre[0] + cnt[0][nSlots];
         }
     }
 }
