@@ -136,23 +136,50 @@ __device__ inline int vh_nearest(const VhLane& v, float x, float y, float z, flo
 // Same result as vh_nearest: minimum of (distance, original index) in lexicographic order.
 __device__ inline int vh_nearest_warp(const VhLane& v, float x, float y, float z, float maxD2, float cellEdge, float* d2out) {
     const int lid = threadIdx.x & 31;
-    const int cx = vh_cell(x, v.invCell), cy = vh_cell(y, v.invCell), cz = vh_cell(z, v.invCell);
+    const float ux = x * v.invCell, uy = y * v.invCell, uz = z * v.invCell;
+    const float flx = floorf(ux), fly = floorf(uy), flz = floorf(uz);
+    const int cx = (int)flx, cy = (int)fly, cz = (int)flz;
+    // distance from the query to the lower / upper face of its own cell, per axis
+    const float lo0 = (ux - flx) * cellEdge, lo1 = (uy - fly) * cellEdge, lo2 = (uz - flz) * cellEdge;
+    const float hi0 = cellEdge - lo0, hi1 = cellEdge - lo1, hi2 = cellEdge - lo2;
     float best = maxD2; int bestI = 0x7fffffff;
+    auto offer = [&](const float4& a) {
+        const float d = vh_dist2(a, x, y, z);
+        const int ai = __float_as_int(a.w);
+        if (d < best || (d == best && bestI != 0x7fffffff && ai < bestI)) { best = d; bestI = ai; }
+    };
+    auto warp_min = [&]() {   // warp minimum of (best, bestI); lanes that found nothing carry (maxD2, INT_MAX)
+#pragma unroll
+        for (int o = 16; o > 0; o >>= 1) {
+            const float od = __shfl_xor_sync(0xffffffffu, best, o);
+            const int oi = __shfl_xor_sync(0xffffffffu, bestI, o);
+            if (od < best || (od == best && oi < bestI)) { best = od; bestI = oi; }
+        }
+    };
+    // the query's own cell first, its points dealt out to the lanes: the hit it yields prunes most of the shell
+    {
+        const int s = vh_find(v.keys, v.H, vh_pack(cx, cy, cz));
+        if (s >= 0) {
+            const int b = v.start[s], e = b + v.count[s];
+            for (int t = b + lid; t < e; t += 32) offer(v.sorted[t]);
+        }
+        warp_min();
+    }
     const int maxShell = (int)ceilf(sqrtf(maxD2) * v.invCell);
     for (int k = 1; k <= max(maxShell, 1); ++k) {
         const int side = 2 * k + 1, ncell = side * side * side;
         for (int c = lid; c < ncell; c += 32) {
             const int dz = c / (side * side) - k, r = c % (side * side), dy = r / side - k, dx = r % side - k;
-            // shell k adds the cells at Chebyshev distance exactly k; the first round (k = 1) also covers the centre cell
-            if (k > 1 && max(abs(dx), max(abs(dy), abs(dz))) < k) continue;
+            // shell k adds the cells at Chebyshev distance exactly k
+            if (max(abs(dx), max(abs(dy), abs(dz))) < k) continue;
+            // lower bound on the distance to anything inside that cell (with a margin for rounding)
+            const float gx = dx < 0 ? lo0 + (float)(-dx - 1) * cellEdge : (dx > 0 ? hi0 + (float)(dx - 1) * cellEdge : 0.f);
+            const float gy = dy < 0 ? lo1 + (float)(-dy - 1) * cellEdge : (dy > 0 ? hi1 + (float)(dy - 1) * cellEdge : 0.f);
+            const float gz = dz < 0 ? lo2 + (float)(-dz - 1) * cellEdge : (dz > 0 ? hi2 + (float)(dz - 1) * cellEdge : 0.f);
+            if (gx * gx + gy * gy + gz * gz > best * 1.0001f + 1e-5f) continue;
             const int s = vh_find(v.keys, v.H, vh_pack(cx + dx, cy + dy, cz + dz));
             if (s < 0) continue;
             const int b = v.start[s], e = b + v.count[s];
-            auto offer = [&](const float4& a) {
-                const float d = vh_dist2(a, x, y, z);
-                const int ai = __float_as_int(a.w);
-                if (d < best || (d == best && bestI != 0x7fffffff && ai < bestI)) { best = d; bestI = ai; }
-            };
             int t = b;
             for (; t + 3 < e; t += 4) {   // four loads in flight
                 const float4 a0 = v.sorted[t], a1 = v.sorted[t + 1], a2 = v.sorted[t + 2], a3 = v.sorted[t + 3];
@@ -160,13 +187,7 @@ __device__ inline int vh_nearest_warp(const VhLane& v, float x, float y, float z
             }
             for (; t < e; ++t) offer(v.sorted[t]);
         }
-        // warp minimum of (best, bestI); lanes that found nothing carry (maxD2, INT_MAX)
-#pragma unroll
-        for (int o = 16; o > 0; o >>= 1) {
-            const float od = __shfl_xor_sync(0xffffffffu, best, o);
-            const int oi = __shfl_xor_sync(0xffffffffu, bestI, o);
-            if (od < best || (od == best && oi < bestI)) { best = od; bestI = oi; }
-        }
+        warp_min();
         const float reach = (float)k * cellEdge;
         if (bestI != 0x7fffffff && best <= reach * reach) break;   // every unvisited point is farther than k cells
     }
