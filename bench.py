@@ -166,13 +166,16 @@ def algorithmic_bytes(name, c):
         "ip_project_kernel": 18 * P + 4 * P,
         "ip_gather_kernel": 4 * N + 16 * P + 20 * N,
         "ip_ground_kernel": 16 * (c["G"] + 1) * c["C"] * L + N,
-        "ip_ccl_union_kernel": 8 * N,
-        "ip_ccl_stats_kernel": 4 * N,
-        "ip_row_count_kernel": 9 * N,
-        "ip_compact_kernel": 9 * N + 41 * S + 16 * O + 8 * c["R"] * L,
+        "ip_ccl_runs_kernel": 17 * N,       # rangeMat, owner, groundMat in; parent, runLen out
+        "ip_ccl_union_kernel": 13 * N,      # rangeMat, owner, groundMat, runLen in; parent updated in place at the roots
+        "ip_ccl_stats_kernel": 17 * N,      # parent in/out, runLen, owner, groundMat in
+        "ip_row_count_kernel": 10 * N,      # owner, groundMat, parent in; cellClass out
+        "ip_compact_kernel": 10 * N + 41 * S + 16 * O + 8 * c["R"] * L,
         "fa_prepare_kernel": 20 * S,
         "fa_distort_kernel": 32 * S,
-        "fa_extract_kernel": 33 * S + 16 * F3 + 32 * S + 16 * c["Flf"],
+        "fa_sort_sectors_kernel": 13 * S + 4 * S,          # curvature, column, ground flag in; candidate lists out
+        "fa_select_kernel": 4 * S + 8 * S + 32 * F3,       # candidate lists, cloudNeighborPicked in/out; picked points in/out
+        "fa_voxel_ring_kernel": 4 * S + 16 * S + 16 * c["Flf"],   # cloudLabel, points in; less-flat cloud out
         "fa_gather_features_kernel": 32 * (F3 + c["Flf"]),
         "fa_odometry_kernel": c.get("odo_bytes", 0),
         "fa_clouds_last_kernel": 32 * (c["Fl"] + c["Flf"]) + 32 * O,
@@ -216,7 +219,9 @@ def gather_counts(pl, params, lanes):
         "vg_filter(surfTotal)": 16 * int(sc[3] + sc[4]),
         "vh_build(cornerMap)": 36 * int(mc[2]),
         "vh_build(surfMap)": 36 * int(mc[3]),
-        "mo_scan2map(lm loop)": s2m,
+        "mo_lm_begin_kernel": 40 * lanes,
+        "mo_residual_kernel": s2m / 10.0,   # average over the 10 launches of a mapping call (converged lanes do nothing)
+        "mo_solve_kernel": 0.0,
         "mo_save_keyframe_kernel": 32 * int(sc[0] + sc[1] + sc[2]),
     }
     c["map"] = {"cornerFromMap": int(mc[0]), "surfFromMap": int(mc[1]), "cornerFromMapDS": int(mc[2]), "surfFromMapDS": int(mc[3]),

@@ -165,7 +165,7 @@ int lego_selftest_atan2f(const float* y, const float* x, float* out, long n);
 /* Sorts nseg independent segments (offsets has nseg+1 entries) on the device with the replayed libstdc++
  * std::sort (csrc/std_sort_replay.cuh); inds_out receives, per segment, the original positions in sorted order. */
 int lego_selftest_std_sort(const float* values, const int* offsets, int nseg, int* inds_out);
-/* Same contract, sorted by the warp-parallel statement of std::sort that fa_extract_kernel uses (csrc/warp_sort.cuh:
+/* Same contract, sorted by the warp-parallel statement of std::sort that fa_sort_sectors_kernel uses (csrc/warp_sort.cuh:
  * radix sort when all values are distinct, introsort partition replay + stable radix sort otherwise); every segment
  * must hold at most 416 values (LEGO_ERR_ARG otherwise). */
 int lego_selftest_warp_sort(const float* values, const int* offsets, int nseg, int* inds_out);

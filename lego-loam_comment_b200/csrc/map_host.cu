@@ -324,13 +324,12 @@ void Engine::mapOptimizationBody(const std::vector<int>& active) {
     { ProfScope ps(this, "vg_filter(surfTotal)"); launches += vg_filter(vgSurfTotal, stream); }
     { ProfScope ps(this, "vh_build(cornerMap)"); launches += vh_build(mo.hashCornerMap, c.L, mo.cornerFromMapDS, (size_t)mo.cornerDSCap, stream); }
     { ProfScope ps(this, "vh_build(surfMap)"); launches += vh_build(mo.hashSurfMap, c.L, mo.surfFromMapDS, (size_t)mo.surfDSCap, stream); }
-    {
-        ProfScope ps(this, "mo_scan2map(lm loop)");
-        mo_lm_begin_kernel<<<(c.L + 63) / 64, 64, 0, stream>>>(mo, c.L);
+    {   // scan2MapOptimization: <= 10 x {residuals, solve}; a converged lane makes its share of later launches a no-op
+        { ProfScope ps(this, "mo_lm_begin_kernel"); mo_lm_begin_kernel<<<(c.L + 63) / 64, 64, 0, stream>>>(mo, c.L); }
         dim3 g(std::min(mo.resBlocks, 16), c.L);   // 16 x 256 queries per lane in flight; larger scans loop
         for (int iter = 0; iter < 10; ++iter) {
-            mo_residual_kernel<<<g, 256, 0, stream>>>(mo);
-            mo_solve_kernel<<<c.L, 32, 0, stream>>>(mo, iter);
+            { ProfScope ps(this, "mo_residual_kernel"); mo_residual_kernel<<<g, 256, 0, stream>>>(mo); }
+            { ProfScope ps(this, "mo_solve_kernel"); mo_solve_kernel<<<c.L, 32, 0, stream>>>(mo, iter); }
         }
         launches += 21;
     }

@@ -63,7 +63,7 @@ def test_device_std_sort_replay_equals_libstdcxx(tmp_path):
     want = np.frombuffer(subprocess.run([exe], input=blob, stdout=subprocess.PIPE, check=True).stdout, np.int32)
     got = capi.selftest_std_sort(values, offsets)
     assert np.array_equal(got, want)
-    # the warp-parallel statement fa_extract_kernel uses (segments of at most 416 values)
+    # the warp-parallel statement fa_sort_sectors_kernel uses (segments of at most 416 values)
     keep = [i for i, s in enumerate(segs) if len(s) <= 416]
     sub_off = np.concatenate([[0], np.cumsum([len(segs[i]) for i in keep])]).astype(np.int32)
     sub_val = np.concatenate([segs[i] for i in keep])
