@@ -121,6 +121,21 @@ int lego_mo_process(lego_mo* h, const lego_cloud_view* corner_last, const lego_c
                     const lego_cloud_view* outlier_last, const float transformSum[6], double stamp,
                     float transformAftMapped_out[6], float transformBefMapped_out[6], int* processed);
 
+/* ---------------------------------------------------------------- TransformFusion node (transformFusion.cpp)
+ * The fourth node: re-bases every odometry pose on the latest mapping correction (/integrated_to_init).
+ * lego_tf_laser_odometry replaces the body of TransformFusion::laserOdometryHandler (transformFusion.cpp:181-216):
+ * transformSum is the pose FeatureAssociation integrated (lego_fa_process's transformSum_out; the quaternion round
+ * trip of the message is applied inside), transformMapped_out the fused pose [rx ry rz tx ty tz],
+ * integrated_out the published pose: orientation x y z w, position x y z (transformFusion.cpp:201-208).
+ * lego_tf_aft_mapped replaces TransformFusion::odomAftMappedHandler (transformFusion.cpp:218-241): the two poses
+ * mapOptimization publishes in /aft_mapped_to_init (lego_mo_process's outputs when *processed = 1).
+ * Pointers may be host or device memory. */
+typedef struct lego_tf lego_tf;
+int lego_tf_create(const lego_params* p, lego_tf** out);
+int lego_tf_destroy(lego_tf* h);
+int lego_tf_laser_odometry(lego_tf* h, const float transformSum[6], float transformMapped_out[6], float integrated_out[7]);
+int lego_tf_aft_mapped(lego_tf* h, const float transformAftMapped[6], const float transformBefMapped[6]);
+
 /* ---------------------------------------------------------------- chained, batched pipeline */
 typedef struct lego_pipeline lego_pipeline;
 /* lanes independent sequences processed in lock step; max_points = capacity per scan (0 = N_SCAN*Horizon_SCAN+slack) */
@@ -128,7 +143,8 @@ int lego_pipeline_create(const lego_params* p, int lanes, int max_points, lego_p
 int lego_pipeline_destroy(lego_pipeline* h);
 /* One scan for every lane.  xyzi: lanes * stride_points * 4 floats, ring: lanes * stride_points, npts: lanes
  * ints, stamps: lanes doubles.  src_on_device = 1 when xyzi/ring are device pointers (npts/stamps stay host).
- * stage_mask: bit0 ImageProjection, bit1 FeatureAssociation, bit2 mapOptimization. */
+ * stage_mask: bit0 ImageProjection, bit1 FeatureAssociation, bit2 mapOptimization, bit3 TransformFusion (its poses are
+ * read with lego_pipeline_download: "transformMapped" 6 floats, "integratedToInit" 7 floats, per lane). */
 int lego_pipeline_step(lego_pipeline* h, const float* xyzi, const uint16_t* ring, const int* npts,
                        int stride_points, const double* stamps, int src_on_device, int stage_mask);
 /* poses_out: lanes * 18 floats = transformSum | transformAftMapped | transformBefMapped; flags_out: lanes ints,

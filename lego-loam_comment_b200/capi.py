@@ -19,6 +19,7 @@ EXPORTED = [
     "lego_pipeline_create", "lego_pipeline_destroy", "lego_pipeline_step", "lego_pipeline_get_poses", "lego_pipeline_poses_async", "lego_pipeline_poses_wait",
     "lego_pipeline_sync", "lego_pipeline_launch_count", "lego_pipeline_download", "lego_pipeline_upload",
     "lego_pipeline_timer_record", "lego_pipeline_timer_elapsed", "lego_pipeline_timer_elapsed_between", "lego_pipeline_profile", "lego_pipeline_profile_read",
+    "lego_tf_create", "lego_tf_destroy", "lego_tf_laser_odometry", "lego_tf_aft_mapped",
     "lego_selftest_atan2f", "lego_selftest_std_sort", "lego_selftest_warp_sort", "lego_selftest_voxel_grid",
 ]
 
@@ -222,7 +223,8 @@ class Pipeline:
 
 
 _FLOAT_NAMES = {"rangeMat", "segRange", "orientation", "cloudCurvature", "transformCur", "transformSum", "slot4val",
-                "matP", "moTransformSum", "transformTobeMapped", "transformAftMapped", "transformBefMapped"}
+                "matP", "moTransformSum", "transformTobeMapped", "transformAftMapped", "transformBefMapped",
+                "transformMapped", "integratedToInit", "tfTransformAftMapped", "tfTransformBefMapped"}
 
 
 # ---------------------------------------------------------------------------------------------- per-stage handles
@@ -315,3 +317,22 @@ class MapOptimization(_Stage):
         _check(f(self.h, ctypes.byref(corner_last), ctypes.byref(surf_last), ctypes.byref(outlier_last), ts.ctypes.data, stamp, aft, bef,
                  ctypes.byref(done)), "lego_mo_process")
         return np.array(aft[:], np.float32), np.array(bef[:], np.float32), bool(done.value)
+
+
+class TransformFusion(_Stage):
+    """lego_tf_* : drop-in for the two handlers of the TransformFusion node (transformFusion.cpp:181-241)."""
+    _prefix = "lego_tf"
+
+    def laser_odometry(self, transform_sum):
+        ts = np.ascontiguousarray(transform_sum, np.float32)
+        mapped, integrated = np.zeros(6, np.float32), np.zeros(7, np.float32)
+        f = self.lib.lego_tf_laser_odometry
+        f.argtypes = [ctypes.c_void_p, ctypes.c_void_p, ctypes.c_void_p, ctypes.c_void_p]
+        _check(f(self.h, ts.ctypes.data, mapped.ctypes.data, integrated.ctypes.data), "lego_tf_laser_odometry")
+        return mapped, integrated
+
+    def aft_mapped(self, transform_aft_mapped, transform_bef_mapped):
+        a = np.ascontiguousarray(transform_aft_mapped, np.float32); b = np.ascontiguousarray(transform_bef_mapped, np.float32)
+        f = self.lib.lego_tf_aft_mapped
+        f.argtypes = [ctypes.c_void_p, ctypes.c_void_p, ctypes.c_void_p]
+        _check(f(self.h, a.ctypes.data, b.ctypes.data), "lego_tf_aft_mapped")

@@ -62,8 +62,12 @@ int lego_pipeline_step(lego_pipeline* h, const float* xyzi, const uint16_t* ring
         e.updateTransformation();
         e.integrateTransformationPublishCloudsLast();
     }
-    if ((stage_mask & 6) == 6) e.mapOptimizationRun(h->stamps.data());
-    else e.moActiveLast.assign(e.c.L, 0);
+    // TransformFusion sees the odometry message of this scan before mapOptimization has answered it
+    if ((stage_mask & 10) == 10) e.transformFusionLaserOdometry();
+    if ((stage_mask & 6) == 6) {
+        e.mapOptimizationRun(h->stamps.data());
+        if ((stage_mask & 8) && e.moLastAny) e.transformFusionAftMapped();
+    } else e.moActiveLast.assign(e.c.L, 0);
     lego::cuda_check(cudaGetLastError(), "kernel launch");
     return LEGO_OK;
     LEGO_CATCH

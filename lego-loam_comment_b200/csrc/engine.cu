@@ -60,6 +60,7 @@ Engine::Engine(const lego_params& p, int lanes, int max_points) : params(p) {
 
     allocFeatureAssociation();
     allocMapOptimization();
+    allocTransformFusion();
     cuda_check(cudaStreamSynchronize(stream), "init sync");
 }
 

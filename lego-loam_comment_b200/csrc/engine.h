@@ -83,6 +83,14 @@ struct FaDev {
     VoxelHash hashCorner, hashSurf;   // 1 m voxel hash over the current "last" clouds (replaces the two kd-trees)
 };
 
+// ---- TransformFusion (transformFusion.cpp) ----
+struct TfDev {
+    float* aft; float* bef;    // [L][6]  the node's own transformAftMapped / transformBefMapped (last /aft_mapped_to_init message)
+    float* mapped;             // [L][6]  transformMapped
+    float* integrated;         // [L][7]  /integrated_to_init pose: orientation x y z w, position x y z
+    int* published;            // [L]     1 when the last step published a fused pose
+};
+
 // ---- mapOptimization ----
 // One surrounding key frame of this mapping call, prepared by the host bookkeeping (extractSurroundingKeyFrames,
 // mapOptmization.cpp:1001-1056): where its three down-sampled clouds live in the key-frame pool, where they go in
@@ -171,6 +179,12 @@ public:
     void consumeMapRecords();                        // host bookkeeping of saveKeyFramesAndFactor from the device records
     void selectSurroundingKeyFrames(int lane, std::vector<MoKfEntry>& out, int* nCorner, int* nSurf);
 
+    // ---- TransformFusion (names follow transformFusion.cpp) ----
+    void allocTransformFusion();
+    void transformFusionLaserOdometry();             // laserOdometryHandler for every lane that published odometry this scan
+    void transformFusionAftMapped();                 // odomAftMappedHandler for every lane whose mapping body ran this scan
+    bool lookupTransformFusion(int lane, const std::string& name, void** ptr, int* elem, long* count);
+
     void sync();
     // ---- timing: CUDA events on the engine's own stream (bench.py cannot see this stream through torch) ----
     int profMode = 0;                 // 0 off, 1 every kernel, 2 only kernels whose name contains profFilter
@@ -209,6 +223,7 @@ public:
     IpDev ip;
     FaDev fa;
     MoDev mo;
+    TfDev tf;
     std::vector<MoLaneHost> moHost;
     VgBatch vgMap;             // 2 segments per lane: local corner / surf map
     VgBatch vgScan[2];         // per value of faBuf, 3 segments per lane: corner / surf / outlier cloud of the current scan

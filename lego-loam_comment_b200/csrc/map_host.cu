@@ -133,7 +133,7 @@ bool Engine::lookupMapOptimization(int lane, const std::string& n, void** ptr, i
     if (n == "laserCloudOutlierLastDS") return set(mo.outlierLastDS + l * mo.scanOutlierCap, 16, cnt_of(mo.scanCounts, 8, 2));
     if (n == "laserCloudSurfTotalLastDS")
         return set(mo.surfTotalLastDS + l * ((size_t)mo.scanSurfCap + mo.scanOutlierCap), 16, cnt_of(mo.scanCounts, 8, 4));
-    return false;
+    return lookupTransformFusion(lane, n, ptr, elem, count);
 }
 
 // ------------------------------------------------------------------------------------------------------------

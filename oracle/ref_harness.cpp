@@ -2,7 +2,7 @@
 // read where they lie under /root/reference, into a ROS-free shared library.  Only tests/, smoke() and
 // bench.py's cpu_baseline / --impl reference arm may load the result; the product never does.
 //
-// The three sources are pulled in with #include (paths come from -DREF_IP_CPP=... etc, see oracle/Makefile)
+// The four sources (the three hot nodes + transformFusion.cpp) are pulled in with #include (paths come from -DREF_IP_CPP=... etc, see oracle/Makefile)
 // against the stand-in headers in oracle/shim/.  `private` is made public so the harness can drive the stage
 // methods in the order the reference's own cloudHandler (imageProjection.cpp:181-197), runFeatureAssociation
 // (featureAssociation.cpp:1817-1860) and run (mapOptmization.cpp:1487-1522) do, and snapshot intermediates
@@ -60,6 +60,9 @@ void operator delete[](void* p, std::size_t) noexcept { std::free(p); }
 #define main ref_mo_main
 #include REF_MO_CPP
 #undef main
+#define main ref_tf_main
+#include REF_TF_CPP
+#undef main
 #undef private
 
 namespace {
@@ -92,6 +95,7 @@ struct Ref {
     ImageProjection ip;
     FeatureAssociation fa;
     mapOptimization mo;
+    TransformFusion tf;
     Snap snap;
     bool verbatim = false;
     bool want_snap = true;
@@ -296,8 +300,8 @@ static int run_mo(Ref& R, int fa_flags, long odo_before, long outl_before) {
 
 extern "C" {
 
-// One lidar scan through IP -> FA -> MO.  stages: bit0 IP, bit1 FA, bit2 MO (which stages to run).
-// Returns bit0 = FA ran, bit1 = odometry LM ran, bit2 = clouds forwarded to mapping, bit3 = mapping body ran,
+// One lidar scan through IP -> FA -> MO (-> TransformFusion).  stages: bit0 IP, bit1 FA, bit2 MO, bit3 TransformFusion.
+// Returns bit0 = FA ran, bit1 = odometry LM ran, bit2 = clouds forwarded to mapping, bit3 = mapping body ran, bit4 = fused pose published,
 // or -1 on the reference's hard failure (non-dense cloud with ring channel, imageProjection.cpp:172-177).
 int ref_feed_scan(void* h, const float* xyzi, const uint16_t* ring, int P, int is_dense, double stamp, int stages) {
     Ref& R = *static_cast<Ref*>(h);
@@ -316,7 +320,22 @@ int ref_feed_scan(void* h, const float* xyzi, const uint16_t* ring, int P, int i
         const long odo_before = ros::shim_count("/laser_odom_to_init"), outl_before = ros::shim_count("/outlier_cloud_last");
         int f = run_fa(R);
         out |= f & 7;
-        if ((stages & 4) && run_mo(R, f, odo_before, outl_before)) out |= 8;
+        // TransformFusion (transformFusion.cpp:181-216): every /laser_odom_to_init message is fused with the last
+        // /aft_mapped_to_init it has seen, i.e. the mapping result of an EARLIER scan
+        const bool fuse = (stages & 8) && ros::shim_count("/laser_odom_to_init") != odo_before;
+        if (fuse) R.tf.laserOdometryHandler(ros::shim_last<nav_msgs::Odometry>("/laser_odom_to_init"));
+        if ((stages & 4) && run_mo(R, f, odo_before, outl_before)) {
+            out |= 8;
+            if (stages & 8) R.tf.odomAftMappedHandler(ros::shim_last<nav_msgs::Odometry>("/aft_mapped_to_init"));   // transformFusion.cpp:218-241
+        }
+        if (fuse) {
+            out |= 16;
+            R.snap.f["transformMapped"].assign(R.tf.transformMapped, R.tf.transformMapped + 6);
+            auto m = ros::shim_last<nav_msgs::Odometry>("/integrated_to_init");
+            if (m) R.snap.f["integratedToInit"] = {(float)m->pose.pose.orientation.x, (float)m->pose.pose.orientation.y, (float)m->pose.pose.orientation.z,
+                                                   (float)m->pose.pose.orientation.w, (float)m->pose.pose.position.x, (float)m->pose.pose.position.y,
+                                                   (float)m->pose.pose.position.z};
+        }
     }
     return out;
 }

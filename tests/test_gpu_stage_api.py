@@ -119,3 +119,40 @@ def test_streaming_pose_readback_equals_blocking():
         assert np.array_equal(got[k][0], want[k][0]), "poses differ at scan %d" % k
         assert np.array_equal(got[k][1], want[k][1]), "flags differ at scan %d" % k
     a.close(); b.close()
+
+
+def test_transform_fusion_matches_reference():
+    """Stage bit 3 of the pipeline and the lego_tf_* handle against the reference's transformFusion.cpp (compiled verbatim
+    into the oracle): fused pose transformMapped and the published /integrated_to_init pose within 1e-4 m / rad of the
+    reference, and pipeline == stage handle exactly (same kernels, poses passed through host memory)."""
+    import refpy
+    sensor = "vlp16"
+    require_ref(sensor)
+    seq = SynthSequence(sensor, seed=12, scene="street", speed=5.0)
+    p = make_params(sensor)
+    pl = capi.Pipeline(p, lanes=1, max_points=seq.cap)
+    tf = capi.TransformFusion(p)
+    ref = refpy.RefPipeline(sensor)
+    fused = mapped_updates = 0
+    for k in range(30):
+        xyzi, ring = seq.scan(k)
+        t = seq.stamp(k)
+        rf = ref.feed(xyzi, ring, t, stages=15)
+        x = np.zeros((1, seq.cap, 4), np.float32); x[0, :len(xyzi)] = xyzi
+        r = np.zeros((1, seq.cap), np.uint16); r[0, :len(ring)] = ring
+        pl.step(x, r, [len(xyzi)], [t], stage_mask=15)
+        poses, flags = pl.poses()
+        assert bool(pl.download("tfPublished")[0]) == bool(rf & 16), "publish flag differs at scan %d" % k
+        if rf & 16:
+            fused += 1
+            want_m, want_i = ref.get("transformMapped"), ref.get("integratedToInit")
+            got_m, got_i = pl.download("transformMapped"), pl.download("integratedToInit")
+            assert np.max(np.abs(got_m - want_m)) < 1e-4, "transformMapped scan %d: %s vs %s" % (k, got_m, want_m)
+            assert np.max(np.abs(got_i - want_i)) < 1e-4, "integratedToInit scan %d: %s vs %s" % (k, got_i, want_i)
+            m2, i2 = tf.laser_odometry(poses[0, :6])
+            assert np.array_equal(m2, got_m) and np.array_equal(i2, got_i), "stage handle differs from the pipeline at scan %d" % k
+        if flags[0] & 8:   # the mapping body ran: /aft_mapped_to_init was published
+            mapped_updates += 1
+            tf.aft_mapped(poses[0, 6:12], poses[0, 12:18])
+    assert fused >= 25 and mapped_updates >= 5
+    pl.close(); tf.close()

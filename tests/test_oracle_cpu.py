@@ -82,3 +82,31 @@ def test_oracle_small_solvers_match_numpy_and_cv2():
     x = np.zeros(3, np.float32)
     lib.oracle_solve_qr(A.ctypes.data, b.ctypes.data, x.ctypes.data, 5, 3)
     assert np.allclose(x, xc[:, 0], rtol=1e-4, atol=1e-6)
+
+
+def test_oracle_transform_fusion_is_identity_before_the_first_mapping_message():
+    """transformFusion.cpp compiled into the oracle: until TransformFusion has seen an /aft_mapped_to_init message its
+    transformBefMapped / transformAftMapped are zero, so the fused pose must equal the odometry pose (through the
+    quaternion round trip of the message); afterwards it must differ from it by the mapping correction only."""
+    import lego_loam_b200  # noqa: F401
+    from lego_loam_b200.synth import SynthSequence
+    sensor = "vlp16"
+    if not refpy.available(sensor):
+        pytest.skip("oracle/_ref not built")
+    seq = SynthSequence(sensor, seed=3, scene="street", speed=4.0)
+    ref = refpy.RefPipeline(sensor)
+    seen_mapping = False
+    checked = 0
+    for k in range(8):
+        xyzi, ring = seq.scan(k)
+        f = ref.feed(xyzi, ring, seq.stamp(k), stages=15)
+        if f & 16 and not seen_mapping:
+            # transformFusion.cpp:98-179 with zero Bef/Aft reduces to transformMapped = transformSum up to float rounding
+            assert np.max(np.abs(ref.get("transformMapped") - ref.get("transformSum"))) < 2e-6
+            checked += 1
+        if f & 8:
+            seen_mapping = True
+        if f & 16:
+            q = ref.get("integratedToInit")[:4]
+            assert abs(float(np.dot(q, q)) - 1.0) < 1e-5   # a unit quaternion is published
+    assert checked >= 1 and seen_mapping
