@@ -538,5 +538,18 @@ def main():
     print(json.dumps(line))
 
 
+def _shutdown_process_group():
+    try:
+        import torch.distributed as dist
+        if dist.is_available() and dist.is_initialized():
+            dist.destroy_process_group()
+    except Exception:   # noqa: BLE001  (best effort at exit)
+        pass
+
+
 if __name__ == "__main__":
-    main()
+    try:
+        main()
+    finally:
+        sys.stdout.flush()
+        _shutdown_process_group()
