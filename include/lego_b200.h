@@ -151,7 +151,7 @@ int lego_pipeline_step(lego_pipeline* h, const float* xyzi, const uint16_t* ring
  * bit1 odometry ran, bit2 clouds forwarded to mapping, bit3 mapping body ran.  Synchronises the handle's stream. */
 int lego_pipeline_get_poses(lego_pipeline* h, float* poses_out, int* flags_out);
 /* Streaming form: poses_async enqueues the read-back of the poses as they stand after the last lego_pipeline_step
- * into pinned slot 0 or 1 and returns at once; poses_wait blocks until that read-back has landed and unpacks it like
+ * into pinned slot 0..7 and returns at once; poses_wait blocks until that read-back has landed and unpacks it like
  * lego_pipeline_get_poses.  Lets a caller submit scan k+1 (its host-to-device copy runs on the copy stream) before it
  * collects the result of scan k -- the role the ROS message queues between the reference's nodes play. */
 int lego_pipeline_poses_async(lego_pipeline* h, int slot);

@@ -189,7 +189,7 @@ class Pipeline:
         return poses, flags
 
     def poses_async(self, slot):
-        """Enqueue the read-back of the poses after the last step into pinned slot 0/1 (returns at once)."""
+        """Enqueue the read-back of the poses after the last step into pinned slot 0..7 (returns at once)."""
         _check(self.lib.lego_pipeline_poses_async(self.h, int(slot)), "lego_pipeline_poses_async")
 
     def poses_wait(self, slot):

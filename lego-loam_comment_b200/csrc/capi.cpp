@@ -81,11 +81,11 @@ int lego_pipeline_get_poses(lego_pipeline* h, float* poses_out, int* flags_out) 
     LEGO_TRY h->e->getPoses(poses_out, flags_out); return LEGO_OK; LEGO_CATCH
 }
 int lego_pipeline_poses_async(lego_pipeline* h, int slot) {
-    if (!h || slot < 0 || slot > 1) return LEGO_ERR_ARG;
+    if (!h || slot < 0 || slot >= Engine::POSE_SLOTS) return LEGO_ERR_ARG;
     LEGO_TRY h->e->posesAsync(slot); return LEGO_OK; LEGO_CATCH
 }
 int lego_pipeline_poses_wait(lego_pipeline* h, int slot, float* poses_out, int* flags_out) {
-    if (!h || !poses_out || slot < 0 || slot > 1) return LEGO_ERR_ARG;
+    if (!h || !poses_out || slot < 0 || slot >= Engine::POSE_SLOTS) return LEGO_ERR_ARG;
     LEGO_TRY h->e->posesWait(slot, poses_out, flags_out); return LEGO_OK; LEGO_CATCH
 }
 long lego_pipeline_launch_count(lego_pipeline* h) { return h ? h->e->launches : 0; }

@@ -43,7 +43,7 @@ Engine::Engine(const lego_params& p, int lanes, int max_points) : params(p) {
     const size_t L = lanes, N = c.N, R = c.R;
     cuda_check(cudaStreamCreateWithFlags(&copyStream, cudaStreamNonBlocking), "cudaStreamCreate");
     const size_t tbl = sizeof(void*) * L;
-    for (int b = 0; b < 2; ++b) {
+    for (int b = 0; b < IN_SLOTS; ++b) {
         d_in_xyzi[b] = alloc<float4>(L * c.Pcap); d_in_ring[b] = alloc<uint16_t>(L * c.Pcap); d_npts[b] = alloc<int>(L);
         d_ptr_xyzi[b] = alloc<const float4*>(L); d_ptr_ring[b] = alloc<const uint16_t*>(L);
         cuda_check(cudaEventCreateWithFlags(&evCopied[b], cudaEventDisableTiming), "event");
@@ -68,7 +68,7 @@ Engine::~Engine() {
     if (stream) cudaStreamSynchronize(stream);
     if (copyStream) cudaStreamSynchronize(copyStream);
     for (void* p : allocations) cudaFree(p);
-    for (int b = 0; b < 2; ++b) {
+    for (int b = 0; b < IN_SLOTS; ++b) {
         if (h_pin[b]) cudaFreeHost(h_pin[b]);
         if (evCopied[b]) cudaEventDestroy(evCopied[b]);
         if (evConsumed[b]) cudaEventDestroy(evConsumed[b]);
@@ -80,7 +80,7 @@ Engine::~Engine() {
     for (auto& pe : profLog) { if (pe.a) cudaEventDestroy(pe.a); if (pe.b) cudaEventDestroy(pe.b); }
     for (cudaEvent_t e : evPool) cudaEventDestroy(e);
     for (cudaEvent_t e : timerEv) if (e) cudaEventDestroy(e);
-    for (int b = 0; b < 2; ++b) { if (posePin[b]) cudaFreeHost(posePin[b]); if (poseEv[b]) cudaEventDestroy(poseEv[b]); }
+    for (int b = 0; b < POSE_SLOTS; ++b) { if (posePin[b]) cudaFreeHost(posePin[b]); if (poseEv[b]) cudaEventDestroy(poseEv[b]); }
     if (copyStream) cudaStreamDestroy(copyStream);
     if (stream) cudaStreamDestroy(stream);
 }
@@ -139,9 +139,9 @@ void Engine::sync() { cuda_check(cudaStreamSynchronize(stream), "stream sync"); 
 // device sources are used in place through the per-lane pointer table (no copy at all).
 void Engine::uploadScan(const float* xyzi, const uint16_t* ring, const int* npts, int stride_points, bool src_on_device) {
     for (int l = 0; l < c.L; ++l) if (npts[l] < 0 || (!src_on_device && npts[l] > c.Pcap)) { set_last_error("scan larger than max_points"); throw std::length_error("capacity"); }
-    const int b = inBuf; inBuf ^= 1;
+    const int b = inBuf; inBuf = (inBuf + 1) % IN_SLOTS;
     const size_t tbl = sizeof(void*) * (size_t)c.L;
-    // the staging buffers / pinned tables of slot b were last used two steps ago: wait until that step consumed them
+    // the staging buffers / pinned tables of slot b were last used IN_SLOTS steps ago: wait until that step consumed them
     cuda_check(cudaEventSynchronize(evConsumed[b]), "event sync");
     const float4** hx = reinterpret_cast<const float4**>(h_pin[b]);
     const uint16_t** hr = reinterpret_cast<const uint16_t**>(h_pin[b] + tbl);

@@ -193,9 +193,10 @@ public:
     std::vector<ProfEntry> profLog;
     std::vector<cudaEvent_t> evPool;
     cudaEvent_t timerEv[8] = {};
-    float* posePin[2] = {nullptr, nullptr};      // pinned: [sum 6L | aft 6L | bef 6L | flags L]
-    cudaEvent_t poseEv[2] = {};
-    std::vector<int> poseActive[2];
+    static constexpr int POSE_SLOTS = 8;
+    float* posePin[POSE_SLOTS] = {};             // pinned: [sum 6L | aft 6L | bef 6L | flags L]
+    cudaEvent_t poseEv[POSE_SLOTS] = {};
+    std::vector<int> poseActive[POSE_SLOTS];
     cudaEvent_t takeEvent();
     void profBegin(const char* name);
     void profEnd();
@@ -204,7 +205,7 @@ public:
     void timerRecord(int slot);
     float timerElapsed(int a, int b);
     void getPoses(float* poses18, int* flags);   // per lane: transformSum | transformAftMapped | transformBefMapped
-    void posesAsync(int slot);                   // enqueue the read-back of the current poses into pinned slot 0/1
+    void posesAsync(int slot);                   // enqueue the read-back of the current poses into pinned slot 0..7
     void posesWait(int slot, float* poses18, int* flags);
     long download(int lane, const char* name, void* dst, long cap, int* elem_size);
     long upload(int lane, const char* name, const void* src, long count);
@@ -251,12 +252,13 @@ public:
     }
 private:
     // double-buffered input staging: the H2D copy of scan k+1 runs on copyStream while scan k is still being processed
-    float4* d_in_xyzi[2] = {nullptr, nullptr}; uint16_t* d_in_ring[2] = {nullptr, nullptr}; int* d_npts[2] = {nullptr, nullptr};
-    const float4** d_ptr_xyzi[2] = {nullptr, nullptr}; const uint16_t** d_ptr_ring[2] = {nullptr, nullptr};
+    static constexpr int IN_SLOTS = 5;   // staging slots: the uploads of scans k+1 .. k+4 may run while scan k is processed (a mapping scan lasts ~3 uploads)
+    float4* d_in_xyzi[IN_SLOTS] = {}; uint16_t* d_in_ring[IN_SLOTS] = {}; int* d_npts[IN_SLOTS] = {};
+    const float4** d_ptr_xyzi[IN_SLOTS] = {}; const uint16_t** d_ptr_ring[IN_SLOTS] = {};
     cudaStream_t copyStream = nullptr;
-    cudaEvent_t evCopied[2] = {nullptr, nullptr}, evConsumed[2] = {nullptr, nullptr};
+    cudaEvent_t evCopied[IN_SLOTS] = {}, evConsumed[IN_SLOTS] = {};
     int inBuf = 0, curIn = 0;
-    char* h_pin[2] = {nullptr, nullptr};   // pinned: per-lane pointer tables + npts of the step in flight
+    char* h_pin[IN_SLOTS] = {};   // pinned: per-lane pointer tables + npts of the step in flight
 };
 
 const std::string& last_error();
