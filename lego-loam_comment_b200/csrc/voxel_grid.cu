@@ -1,4 +1,5 @@
-// Kernels of the batched VoxelGrid (see voxel_grid.cuh).  blockIdx.y = segment, blockIdx.x = tile.
+// Kernels of the batched VoxelGrid (see voxel_grid.cuh).  blockIdx.y = segment; a CTA takes the tiles blockIdx.x,
+// blockIdx.x + gridDim.x, ... of its segment.
 #include <cfloat>
 #include <climits>
 #include "kernel_utils.cuh"
@@ -28,8 +29,8 @@ __global__ void vg_init_kernel(VgBatch b) {
 __global__ void __launch_bounds__(VG_THREADS) vg_bbox_kernel(VgBatch b) {
     const VgSeg& s = b.segs[blockIdx.y];
     const int n = s.state[9];
-    const int t0 = blockIdx.x * VG_TILE;
-    if (t0 >= n) return;
+    for (int tile = blockIdx.x; tile * VG_TILE < n; tile += gridDim.x) {   // the grid covers a typical cloud, larger ones loop
+    const int t0 = tile * VG_TILE;
     const int t1 = min(t0 + VG_TILE, n);
     float mn[3] = {FLT_MAX, FLT_MAX, FLT_MAX}, mx[3] = {-FLT_MAX, -FLT_MAX, -FLT_MAX};
     for (int i = t0 + threadIdx.x; i < t1; i += VG_THREADS) {
@@ -43,15 +44,14 @@ __global__ void __launch_bounds__(VG_THREADS) vg_bbox_kernel(VgBatch b) {
 #pragma unroll
         for (int a = 0; a < 3; ++a) { atomicMin(s.state + a, f2ord(mn[a])); atomicMax(s.state + 3 + a, f2ord(mx[a])); }
     }
+    }
 }
 
 // voxel index of every point: ijk = int(floor(p * inv) - float(min_b)), idx = i + j*dx + k*dx*dy  (PCL voxel_grid.hpp)
 __global__ void __launch_bounds__(VG_THREADS) vg_keys_kernel(VgBatch b) {
     const VgSeg& s = b.segs[blockIdx.y];
     const int n = s.state[9];
-    const int t0 = blockIdx.x * VG_TILE;
-    if (t0 >= n) return;
-    const int t1 = min(t0 + VG_TILE, n);
+    if (blockIdx.x * VG_TILE >= n) return;
     const float inv = PM_DIV(1.0f, s.leaf);
     int minb[3], divb[3]; long long dd[3];
 #pragma unroll
@@ -63,6 +63,8 @@ __global__ void __launch_bounds__(VG_THREADS) vg_keys_kernel(VgBatch b) {
     }
     // PCL refuses grids with more than INT_MAX voxels and returns the input unchanged: identity keys do the same
     const bool overflow = dd[0] * dd[1] * dd[2] > (long long)INT_MAX;
+    for (int tile = blockIdx.x; tile * VG_TILE < n; tile += gridDim.x) {
+    const int t0 = tile * VG_TILE, t1 = min(t0 + VG_TILE, n);
     for (int i = t0 + threadIdx.x; i < t1; i += VG_THREADS) {
         const float4 p = s.in[i];
         unsigned key;
@@ -76,22 +78,24 @@ __global__ void __launch_bounds__(VG_THREADS) vg_keys_kernel(VgBatch b) {
         s.keys[0][i] = key;
         s.vals[0][i] = (unsigned)i;
     }
+    }
 }
 
 // ---- LSD radix sort, one 8-bit digit per pass -----------------------------------------------------------------
 __global__ void __launch_bounds__(VG_THREADS) rs_hist_kernel(VgBatch b, int shift) {
     const VgSeg& s = b.segs[blockIdx.y];
     const int n = s.state[9];
-    const int t0 = blockIdx.x * VG_TILE;
-    if (t0 >= n) return;
-    const int t1 = min(t0 + VG_TILE, n);
     __shared__ int hist[256];
+    const unsigned* src = s.keys[s.state[6] ^ s.state[7]];
+    for (int tile = blockIdx.x; tile * VG_TILE < n; tile += gridDim.x) {
+    const int t0 = tile * VG_TILE, t1 = min(t0 + VG_TILE, n);
     hist[threadIdx.x] = 0;
     __syncthreads();
-    const unsigned* src = s.keys[s.state[6] ^ s.state[7]];
     for (int i = t0 + threadIdx.x; i < t1; i += VG_THREADS) atomicAdd(&hist[(src[i] >> shift) & 255u], 1);
     __syncthreads();
-    s.blockHist[threadIdx.x * b.maxBlocks + blockIdx.x] = hist[threadIdx.x];
+    s.blockHist[threadIdx.x * b.maxBlocks + tile] = hist[threadIdx.x];
+    __syncthreads();
+    }
 }
 
 // One CTA per segment: applies the buffer flip left pending by the previous pass, turns the block histograms into
@@ -127,16 +131,16 @@ __global__ void __launch_bounds__(256) rs_scan_kernel(VgBatch b) {
 __global__ void __launch_bounds__(VG_THREADS) rs_scatter_kernel(VgBatch b, int shift) {
     const VgSeg& s = b.segs[blockIdx.y];
     const int n = s.state[9];
-    const int t0 = blockIdx.x * VG_TILE;
-    if (t0 >= n || s.state[8]) return;
-    const int t1 = min(t0 + VG_TILE, n);
+    if (s.state[8]) return;
     const int cur = s.state[6];
     const unsigned* __restrict__ srcK = s.keys[cur]; const unsigned* __restrict__ srcV = s.vals[cur];
     unsigned* __restrict__ dstK = s.keys[cur ^ 1]; unsigned* __restrict__ dstV = s.vals[cur ^ 1];
     __shared__ int base[256];
     __shared__ int warpCnt[8][257];
     const int tid = threadIdx.x, lid = tid & 31, w = tid >> 5;
-    base[tid] = s.blockHist[tid * b.maxBlocks + blockIdx.x];
+    for (int tile = blockIdx.x; tile * VG_TILE < n; tile += gridDim.x) {
+    const int t0 = tile * VG_TILE, t1 = min(t0 + VG_TILE, n);
+    base[tid] = s.blockHist[tid * b.maxBlocks + tile];
 #pragma unroll
     for (int q = 0; q < 8; ++q) warpCnt[q][tid] = 0;
     __syncthreads();
@@ -174,40 +178,41 @@ __global__ void __launch_bounds__(VG_THREADS) rs_scatter_kernel(VgBatch b, int s
         for (int q = 0; q < 8; ++q) warpCnt[q][tid] = 0;
         __syncthreads();
     }
+    }
 }
 
 // ---- reduction of equal-key runs --------------------------------------------------------------------------------
 __global__ void __launch_bounds__(VG_THREADS) vg_heads_kernel(VgBatch b) {
     const VgSeg& s = b.segs[blockIdx.y];
     const int n = s.state[9];
-    const int t0 = blockIdx.x * VG_TILE;
-    if (t0 >= n) return;
-    const int t1 = min(t0 + VG_TILE, n);
+    __shared__ int ws[8];
+    for (int tile = blockIdx.x; tile * VG_TILE < n; tile += gridDim.x) {
+    const int t0 = tile * VG_TILE, t1 = min(t0 + VG_TILE, n);
     const unsigned* keys = s.keys[s.state[6] ^ s.state[7]];
     int c = 0;
     for (int i = t0 + threadIdx.x; i < t1; i += VG_THREADS) c += (i == 0 || keys[i - 1] != keys[i]) ? 1 : 0;
     c = warp_sum(c);
-    __shared__ int ws[8];
     if ((threadIdx.x & 31) == 0) ws[threadIdx.x >> 5] = c;
     __syncthreads();
-    if (threadIdx.x == 0) { int t = 0; for (int q = 0; q < 8; ++q) t += ws[q]; s.blockHeads[blockIdx.x] = t; }
+    if (threadIdx.x == 0) { int t = 0; for (int q = 0; q < 8; ++q) t += ws[q]; s.blockHeads[tile] = t; }
+    __syncthreads();
+    }
 }
 
 __global__ void __launch_bounds__(VG_THREADS) vg_reduce_kernel(VgBatch b) {
     const VgSeg& s = b.segs[blockIdx.y];
     const int n = s.state[9];
     if (n == 0) { if (blockIdx.x == 0 && threadIdx.x == 0 && vg_live(s)) *s.nOut = 0; return; }
-    const int t0 = blockIdx.x * VG_TILE;
-    if (t0 >= n) return;
-    const int t1 = min(t0 + VG_TILE, n);
     const int bufi = s.state[6] ^ s.state[7];
     const unsigned* __restrict__ keys = s.keys[bufi]; const unsigned* __restrict__ vals = s.vals[bufi];
     const int tid = threadIdx.x, lid = tid & 31, w = tid >> 5;
     __shared__ int ws[8];
     __shared__ int carry;
+    for (int tile = blockIdx.x; tile * VG_TILE < n; tile += gridDim.x) {
+    const int t0 = tile * VG_TILE, t1 = min(t0 + VG_TILE, n);
     // heads in the tiles before this one
     int pre = 0;
-    for (int k = tid; k < (int)blockIdx.x; k += VG_THREADS) pre += s.blockHeads[k];
+    for (int k = tid; k < tile; k += VG_THREADS) pre += s.blockHeads[k];
     pre = warp_sum(pre);
     if (lid == 0) ws[w] = pre;
     __syncthreads();
@@ -240,11 +245,15 @@ __global__ void __launch_bounds__(VG_THREADS) vg_reduce_kernel(VgBatch b) {
         if (total > s.outCap) { total = s.outCap; s.state[10] = 1; }
         *s.nOut = total;
     }
+    __syncthreads();
+    }
 }
 
 int vg_filter(const VgBatch& b, cudaStream_t stream) {
     if (b.nSeg <= 0) return 0;
-    dim3 g(b.maxBlocks, b.nSeg);
+    // tiles per segment in flight: 8 x 4096 points cover every cloud of the 16/32-ring sensors in one trip; the kernels
+    // stride over the live tiles, so a grid sized by the allocation (hundreds of empty CTAs per segment) is avoided
+    dim3 g(b.maxBlocks < 8 ? b.maxBlocks : 8, b.nSeg);
     vg_init_kernel<<<(b.nSeg + 127) / 128, 128, 0, stream>>>(b);
     vg_bbox_kernel<<<g, VG_THREADS, 0, stream>>>(b);
     vg_keys_kernel<<<g, VG_THREADS, 0, stream>>>(b);

@@ -1,4 +1,5 @@
 // Build kernels of the voxel hash (see voxel_hash.cuh).
+#include <algorithm>
 #include "voxel_hash.cuh"
 
 namespace lego {
@@ -6,10 +7,12 @@ namespace lego {
 // ---- build kernels; n[lane * nStride] = number of points of the lane's cloud ----
 __global__ void __launch_bounds__(256) vh_clear_kernel(VoxelHash h) {
     const int lane = blockIdx.y;
-    const int i = blockIdx.x * blockDim.x + threadIdx.x;
-    if (i >= vh_table_size(min(h.n[lane * h.nStride], h.cap), h.H, h.minH)) return;
-    h.keys[(size_t)lane * h.H + i] = VH_EMPTY;
-    h.count[(size_t)lane * h.H + i] = 0;
+    const int Hd = vh_table_size(min(h.n[lane * h.nStride], h.cap), h.H, h.minH);
+    // grid-stride over the LIVE table: the grid is sized for a typical table, not for the allocation
+    for (int i = blockIdx.x * blockDim.x + threadIdx.x; i < Hd; i += gridDim.x * blockDim.x) {
+        h.keys[(size_t)lane * h.H + i] = VH_EMPTY;
+        h.count[(size_t)lane * h.H + i] = 0;
+    }
 }
 
 __global__ void __launch_bounds__(256) vh_insert_kernel(VoxelHash h, const float4* __restrict__ pts, size_t ptsStride) {
@@ -68,31 +71,21 @@ __global__ void __launch_bounds__(256) vh_scatter_kernel(VoxelHash h, const floa
     for (int i = blockIdx.x * blockDim.x + threadIdx.x; i < M; i += gridDim.x * blockDim.x) {
         const float4 p = pts[(size_t)lane * ptsStride + i];
         const int s = h.slotOf[(size_t)lane * h.cap + i];
-        const int k = atomicSub(h.count + (size_t)lane * h.H + s, 1) - 1;   // count doubles as a cursor; restored below
-        h.sorted[(size_t)lane * h.cap + h.start[(size_t)lane * h.H + s] + k] = make_float4(p.x, p.y, p.z, __int_as_float(i));
+        // start[] doubles as the cursor: it ends up at the END of the run, which is what the look-ups read
+        const int pos = atomicAdd(h.start + (size_t)lane * h.H + s, 1);
+        h.sorted[(size_t)lane * h.cap + pos] = make_float4(p.x, p.y, p.z, __int_as_float(i));
     }
-}
-// the scatter consumed count[]; the run length of slot s is start[next] - start[s], recovered here once
-__global__ void __launch_bounds__(256) vh_recount_kernel(VoxelHash h) {
-    const int lane = blockIdx.y;
-    const int i = blockIdx.x * blockDim.x + threadIdx.x;
-    const int M = min(h.n[lane * h.nStride], h.cap);
-    const int Hd = vh_table_size(M, h.H, h.minH);
-    if (i >= Hd) return;
-    const int* st = h.start + (size_t)lane * h.H;
-    h.count[(size_t)lane * h.H + i] = (i + 1 < Hd ? st[i + 1] : M) - st[i];
 }
 
 int vh_build(const VoxelHash& h, int lanes, const float4* pts, size_t ptsStride, cudaStream_t stream) {
-    dim3 gH((h.H + 255) / 256, lanes);
-    const int pb = (h.cap + 255) / 256;
+    dim3 gH(std::min((h.H + 255) / 256, 16), lanes);
+    const int pb = std::min((h.cap + 255) / 256, 16);   // the insert / scatter kernels stride over the points
     dim3 gP(pb < 1 ? 1 : pb, lanes);
     vh_clear_kernel<<<gH, 256, 0, stream>>>(h);
     vh_insert_kernel<<<gP, 256, 0, stream>>>(h, pts, ptsStride);
     vh_scan_kernel<<<lanes, 1024, 0, stream>>>(h);
     vh_scatter_kernel<<<gP, 256, 0, stream>>>(h, pts, ptsStride);
-    vh_recount_kernel<<<gH, 256, 0, stream>>>(h);
-    return 5;
+    return 4;
 }
 
 }  // namespace lego

@@ -21,8 +21,8 @@ namespace lego {
 
 struct VoxelHash {
     unsigned long long* keys;   // [L][H]  packed cell coordinate, VH_EMPTY = free
-    int* count;                 // [L][H]  points in the cell (also used as the scatter cursor, counting down)
-    int* start;                 // [L][H]  first position of the cell's run in `sorted`
+    int* count;                 // [L][H]  points in the cell
+    int* start;                 // [L][H]  END of the cell's run in `sorted` (the scatter pass advances it from the run's first position)
     int* slotOf;                // [L][cap] table slot of every input point
     float4* sorted;             // [L][cap] cell-sorted copy, w = original index (int bits)
     int H;                      // slots ALLOCATED per lane, power of two; a build uses only vh_table_size(n, H) of them
@@ -54,13 +54,14 @@ __host__ __device__ __forceinline__ unsigned vh_hash(unsigned long long k) {
     k ^= k >> 33; k *= 0xff51afd7ed558ccdull; k ^= k >> 33; k *= 0xc4ceb9fe1a85ec53ull; k ^= k >> 33;
     return (unsigned)k;
 }
-// Table size actually used for a cloud of n points: the smallest power of two >= 4n (at least 1024, at most the
-// allocation).  Sizing by the live count instead of the capacity keeps the clear / scan / recount passes proportional
-// to the data; 4n keeps the load factor below 1/4 so that look-ups of EMPTY neighbour cells -- the common case of the
-// shell searches -- end after ~1.2 probes.
+// Table size actually used for a cloud of n points: the smallest power of two >= 2n (at least 1024, at most the
+// allocation).  Sizing by the live count instead of the capacity keeps the clear / scan passes proportional to the
+// data.  The table holds CELLS, and a 1 m cell of these clouds holds several points, so the load factor stays
+// far below its worst case of 1/2 and look-ups of EMPTY neighbour cells -- the common case of the shell searches --
+// end after ~1.1 probes.
 __host__ __device__ __forceinline__ int vh_table_size(int n, int Hmax, int Hmin = 1024) {
     int H = Hmin;
-    while (H < 4 * n && H < Hmax) H <<= 1;
+    while (H < 2 * n && H < Hmax) H <<= 1;
     return H;
 }
 __device__ __forceinline__ int vh_cell(float v, float invCell) { return (int)floorf(v * invCell); }
@@ -114,7 +115,7 @@ __device__ inline int vh_nearest(const VhLane& v, float x, float y, float z, flo
                 for (int dx = -k; dx <= k; dx += step) {
                     const int s = vh_find(v.keys, v.H, vh_pack(cx + dx, cy + dy, cz + dz));
                     if (s < 0) continue;
-                    const int b = v.start[s], e = b + v.count[s];
+                    const int e = v.start[s], b = e - v.count[s];
                     for (int t = b; t < e; ++t) {
                         const float4 a = v.sorted[t];
                         const float d = vh_dist2(a, x, y, z);
@@ -160,7 +161,7 @@ __device__ inline int vh_nearest_warp(const VhLane& v, float x, float y, float z
     {
         const int s = vh_find(v.keys, v.H, vh_pack(cx, cy, cz));
         if (s >= 0) {
-            const int b = v.start[s], e = b + v.count[s];
+            const int e = v.start[s], b = e - v.count[s];
             for (int t = b + lid; t < e; t += 32) offer(v.sorted[t]);
         }
         warp_min();
@@ -179,7 +180,7 @@ __device__ inline int vh_nearest_warp(const VhLane& v, float x, float y, float z
             if (gx * gx + gy * gy + gz * gz > best * 1.0001f + 1e-5f) continue;
             const int s = vh_find(v.keys, v.H, vh_pack(cx + dx, cy + dy, cz + dz));
             if (s < 0) continue;
-            const int b = v.start[s], e = b + v.count[s];
+            const int e = v.start[s], b = e - v.count[s];
             int t = b;
             for (; t + 3 < e; t += 4) {   // four loads in flight
                 const float4 a0 = v.sorted[t], a1 = v.sorted[t + 1], a2 = v.sorted[t + 2], a3 = v.sorted[t + 3];
@@ -223,7 +224,7 @@ __device__ inline int vh_knn5(const VhLane& v, float x, float y, float z, float 
             if (boxD2 > d2[4] * 1.0001f + 1e-5f) continue;
             const int s = vh_find(v.keys, v.H, vh_pack(cx + dx, cy + dy, cz + dz));
             if (s < 0) continue;
-            const int b = v.start[s], e = b + v.count[s];
+            const int e = v.start[s], b = e - v.count[s];
             for (int t = b; t < e; ++t) {
                 const float4 a = v.sorted[t];
                 float d = vh_dist2(a, x, y, z);
