@@ -123,12 +123,12 @@ __global__ void __launch_bounds__(32 * FS_WARPS) fa_sort_sectors_kernel(IpDev d,
 // General suppression for a point anywhere in the cloud (only the stale slot-4 entry of quirk Q11 can be outside its
 // own ring): lanes 0-4 test the five forward steps, lanes 5-9 the five backward steps, a ballot finds where each
 // walk stops, and the lanes before the stop mark their slot.
-__device__ __forceinline__ void suppress_warp(const int* gcol, int* gpicked, int ind, int lid) {
+__device__ __forceinline__ void suppress_warp(const int* gcol, int* gpicked, int ind, int lid, int N) {
     bool bad = false; int slot = ind;
     if (lid < 5) {
         const int l = lid + 1;
         slot = ind + l;
-        bad = abs(gcol[ind + l] - gcol[ind + l - 1]) > 10;
+        bad = (ind + l >= N) || abs(gcol[ind + l] - gcol[ind + l - 1]) > 10;   // the end of the array ends the walk too
     } else if (lid < 10) {
         const int l = -(lid - 4);
         slot = ind + l;
@@ -193,7 +193,7 @@ __global__ void __launch_bounds__(32 * SEL_WARPS) fa_select_kernel(IpDev d, FaDe
                         if (lid <= 10 && o >= -nB && o <= nF) gpicked[pind + o] = 1;
                         if (ind >= pind - nB && ind <= pind + nF) pk = true;
                     } else {
-                        suppress_warp(gcol, gpicked, pind, lid);
+                        suppress_warp(gcol, gpicked, pind, lid, c.N);
                         __syncwarp();
                         pk = valid ? gpicked[ind] != 0 : true;
                     }
