@@ -20,7 +20,8 @@ class SynthCfg(ctypes.Structure):
                 ("speed", ctypes.c_double), ("yaw_amp", ctypes.c_double), ("yaw_period", ctypes.c_double), ("sway_amp", ctypes.c_double),
                 ("noise_sigma", ctypes.c_double), ("max_range", ctypes.c_double), ("min_range", ctypes.c_double),
                 ("dropout_prob", ctypes.c_double), ("dup_col_prob", ctypes.c_double), ("jitter_frac", ctypes.c_double),
-                ("scan_period", ctypes.c_double)]
+                ("scan_period", ctypes.c_double),
+                ("traj", ctypes.c_int), ("circle_radius", ctypes.c_double)]
 
 
 def build_synth(force=False):
@@ -52,7 +53,7 @@ class SynthSequence:
     """One seeded synthetic trajectory for a sensor config. scan(k) -> (xyzi float32[P,4], ring uint16[P])."""
 
     def __init__(self, sensor="vlp16", seed=0, scene="street", speed=2.0, n_scans=1000, noise_sigma=0.01,
-                 dropout=0.0, dup_cols=0.0, yaw_amp=0.15, yaw_period=20.0, sway_amp=1.0):
+                 dropout=0.0, dup_cols=0.0, yaw_amp=0.15, yaw_period=20.0, sway_amp=1.0, circle_radius=0.0):
         p = make_params(sensor)
         eb, es, hgt = SENSOR_GEOMETRY[sensor]
         c = SynthCfg()
@@ -65,6 +66,7 @@ class SynthSequence:
         c.noise_sigma, c.max_range, c.min_range = noise_sigma, 100.0, 0.5
         c.dropout_prob, c.dup_col_prob, c.jitter_frac = dropout, dup_cols, 0.3
         c.scan_period = 0.1
+        c.traj, c.circle_radius = (1, circle_radius) if circle_radius > 0 else (0, 0.0)   # closed circle (room scene) for loop closure
         self.cfg, self.sensor, self.seed, self.n_scans = c, sensor, seed, n_scans
         self.cap = p.N_SCAN * p.Horizon_SCAN + (p.N_SCAN * 64 if dup_cols > 0 else 0)
         self._h = _load().lego_synth_create(ctypes.byref(c), seed, n_scans * 0.1 + 1.0)

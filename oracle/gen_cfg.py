@@ -13,7 +13,7 @@ import sys
 REF = os.environ.get("LEGO_REF_ROOT", "/root/reference")
 HERE = os.path.dirname(os.path.abspath(__file__))
 
-# name -> (N_SCAN, Horizon_SCAN, ang_res_x, ang_res_y, ang_bottom, groundScanInd, useCloudRing)
+# name -> (N_SCAN, Horizon_SCAN, ang_res_x, ang_res_y, ang_bottom, groundScanInd, useCloudRing[, loopClosureEnableFlag])
 CONFIGS = {
     # utility.h:63-68 as shipped
     "vlp16": ("16", "1800", "0.2", "2.0", "15.0+0.1", "7", "true"),
@@ -25,11 +25,14 @@ CONFIGS = {
     "hdl64": ("64", "2083", "360.0/float(Horizon_SCAN)", "26.9/float(N_SCAN-1)", "24.9", "50", "true"),
     # utility.h:79-84
     "vls128": ("128", "1800", "0.2", "0.3", "25.0", "10", "true"),
+    # VLP-16 with loop closure switched on (utility.h:104 = true), SURVEY.md section 8f n2 / BASELINE config 5
+    "vlp16_loop": ("16", "1800", "0.2", "2.0", "15.0+0.1", "7", "true", "true"),
 }
 
 
 def generate(name, out_root):
-    n_scan, hz, rx, ry, bottom, gsi, ring = CONFIGS[name]
+    n_scan, hz, rx, ry, bottom, gsi, ring = CONFIGS[name][:7]
+    loop = CONFIGS[name][7] if len(CONFIGS[name]) > 7 else "false"
     src = open(os.path.join(REF, "LeGO-LOAM/include/utility.h")).read().split("\n")
     # lines are 1-based in citations: 60 = useCloudRing, 63..68 = VLP-16 block
     assert "useCloudRing" in src[59] and "N_SCAN = 16" in src[62] and "groundScanInd" in src[67], "utility.h layout changed"
@@ -40,6 +43,8 @@ def generate(name, out_root):
     src[65] = "extern const float ang_res_y = %s;" % ry
     src[66] = "extern const float ang_bottom = %s;" % bottom
     src[67] = "extern const int groundScanInd = %s;" % gsi
+    assert "loopClosureEnableFlag" in src[103], "utility.h layout changed"
+    src[103] = "extern const bool loopClosureEnableFlag = %s;" % loop
     d = os.path.join(out_root, "cfg", name)
     os.makedirs(d, exist_ok=True)
     with open(os.path.join(d, "utility.h"), "w") as f:

@@ -101,6 +101,10 @@ struct Ref {
     bool want_snap = true;
     double t[T_COUNT];
     long scans = 0, mo_calls = 0;
+    // loop closure (mapOptmization.cpp:802-812 runs performLoopClosure in a 1 Hz side thread; the harness calls it
+    // synchronously after a mapping call once >= 1.0 s of scan time passed since its last call)
+    double timeLastLoop = -1e9;
+    long loopCalls = 0, loopsClosed = 0;
     Ref() { std::memset(t, 0, sizeof(t)); }
 };
 
@@ -286,6 +290,30 @@ static int run_mo(Ref& R, int fa_flags, long odo_before, long outl_before) {
         }
     }
     int ran = ros::shim_count("/aft_mapped_to_init") != aft_before;
+    if (ran && loopClosureEnableFlag && mo.timeLaserOdometry - R.timeLastLoop >= 1.0) {
+        R.timeLastLoop = mo.timeLaserOdometry;
+        const long icpBefore = pcl::shim_icp_log().runs;
+        const bool closedBefore = mo.aLoopIsClosed;
+        mo.aLoopIsClosed = false;
+        mo.performLoopClosure();
+        R.loopCalls += 1;
+        const bool closedNow = mo.aLoopIsClosed;
+        if (closedNow) R.loopsClosed += 1;
+        mo.aLoopIsClosed = closedBefore || closedNow;
+        if (R.want_snap) {
+            Snap& s = R.snap;
+            const pcl::ShimIcpLog& l = pcl::shim_icp_log();
+            const int icpRan = l.runs != icpBefore;
+            s.i["loopClosure"] = {1, icpRan, closedNow ? 1 : 0, icpRan ? mo.closestHistoryFrameID : -1, icpRan ? mo.latestFrameIDLoopCloure : -1,
+                                  icpRan ? (l.converged ? 1 : 0) : 0, icpRan ? l.iterations : 0, icpRan ? (int32_t)l.ns : 0, icpRan ? (int32_t)l.nt : 0};
+            if (icpRan) {
+                s.f["icpFitness"] = {(float)l.fitness};
+                s.f["icpTransform"].assign(l.T, l.T + 16);
+                s.f["latestSurfKeyFrameCloud"] = flat(*mo.latestSurfKeyFrameCloud);
+                s.f["nearHistorySurfKeyFrameCloudDS"] = flat(*mo.nearHistorySurfKeyFrameCloudDS);
+            }
+        }
+    }
     if (R.want_snap) {
         Snap& s = R.snap;
         s.f["transformAftMapped"].assign(mo.transformAftMapped, mo.transformAftMapped + 6);
@@ -293,6 +321,10 @@ static int run_mo(Ref& R, int fa_flags, long odo_before, long outl_before) {
         s.f["transformTobeMapped"].assign(mo.transformTobeMapped, mo.transformTobeMapped + 6);
         s.i["numKeyFrames"] = {static_cast<int32_t>(mo.cloudKeyPoses3D->points.size())};
         s.i["moDegenerate"] = {mo.isDegenerate ? 1 : 0};
+        s.i["loopStats"] = {(int32_t)R.loopCalls, (int32_t)R.loopsClosed};
+        std::vector<float>& kp = s.f["cloudKeyPoses6D"];
+        kp.clear();
+        for (const auto& p : mo.cloudKeyPoses6D->points) { kp.push_back(p.x); kp.push_back(p.y); kp.push_back(p.z); kp.push_back(p.roll); kp.push_back(p.pitch); kp.push_back(p.yaw); }
     }
     if (ran) R.mo_calls += 1;
     return ran;

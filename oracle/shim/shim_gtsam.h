@@ -2,14 +2,17 @@
 // loopClosureEnableFlag == false (utility.h:104) the factor graph built in mapOptmization.cpp:1375-1409 is a
 // prior plus a chain of BetweenFactors whose measurements are computed from the very values inserted, so the
 // iSAM2 estimate of the newest pose equals its inserted initial value (to ~1e-7, far inside the 1e-4 pose
-// tolerance).  This shim therefore keeps the inserted Pose3 values and hands them back: a chain-only
-// pass-through.  Rot3 keeps a double rotation matrix; roll/pitch/yaw follow GTSAM's documented RQ-style
-// extraction (x about X first, then y, then z for R = Rz*Ry*Rx).
+// tolerance).  While the graph is such a chain this shim keeps the inserted Pose3 values and hands them back
+// (pass-through); from the first loop BetweenFactor (mapOptmization.cpp:939) on, every ISAM2::update() is one
+// Gauss-Newton step over the whole graph (oracle/thirdparty/tp_pose_graph.h, PARITY UNPINNED).  Rot3 keeps a
+// double rotation matrix; roll/pitch/yaw follow GTSAM's documented RQ-style extraction (x about X first, then y,
+// then z for R = Rz*Ry*Rx).
 #pragma once
 #include <cmath>
 #include <map>
 #include <memory>
 #include <vector>
+#include "../thirdparty/tp_pose_graph.h"
 
 namespace gtsam {
 
@@ -69,16 +72,39 @@ struct Vector {
 namespace noiseModel {
 struct Diagonal {
     typedef std::shared_ptr<Diagonal> shared_ptr;
-    static shared_ptr Variances(const Vector&) { return std::make_shared<Diagonal>(); }
+    double sigma[6];
+    static shared_ptr Variances(const Vector& v) {
+        shared_ptr d = std::make_shared<Diagonal>();
+        for (int i = 0; i < 6; ++i) d->sigma[i] = std::sqrt(i < (int)v.d.size() ? v.d[i] : 1.0);
+        return d;
+    }
 };
 }
 
-template <class T> struct PriorFactor { template <class N> PriorFactor(size_t, const T&, const N&) {} };
-template <class T> struct BetweenFactor { template <class N> BetweenFactor(size_t, size_t, const T&, const N&) {} };
+inline tp::PgPose shim_pg(const Pose3& p) {
+    tp::PgPose o;
+    for (int i = 0; i < 3; ++i) { for (int j = 0; j < 3; ++j) o.R[3 * i + j] = p.r.R[i][j]; o.t[i] = p.t.v[i]; }
+    return o;
+}
+inline Pose3 shim_pose(const tp::PgPose& p) {
+    Pose3 o;
+    for (int i = 0; i < 3; ++i) { for (int j = 0; j < 3; ++j) o.r.R[i][j] = p.R[3 * i + j]; o.t.v[i] = p.t[i]; }
+    return o;
+}
+
+template <class T> struct PriorFactor {
+    tp::PgFactor f;
+    template <class N> PriorFactor(size_t k, const T& z, const N& noise) { f.i = -1; f.j = (int)k; f.z = shim_pg(z); for (int a = 0; a < 6; ++a) f.sigma[a] = noise->sigma[a]; }
+};
+template <class T> struct BetweenFactor {
+    tp::PgFactor f;
+    template <class N> BetweenFactor(size_t k1, size_t k2, const T& z, const N& noise) { f.i = (int)k1; f.j = (int)k2; f.z = shim_pg(z); for (int a = 0; a < 6; ++a) f.sigma[a] = noise->sigma[a]; }
+};
 
 struct NonlinearFactorGraph {
-    template <class F> void add(const F&) {}
-    void resize(size_t) {}
+    std::vector<tp::PgFactor> f;
+    template <class F> void add(const F& x) { f.push_back(x.f); }
+    void resize(size_t n) { f.resize(n); }
 };
 
 struct Values {
@@ -92,12 +118,18 @@ struct Values {
 struct ISAM2Params { double relinearizeThreshold = 0.1; int relinearizeSkip = 10; };
 
 struct ISAM2 {
-    Values est;
+    tp::PoseGraph g;
+    long gnSteps = 0;
     explicit ISAM2(const ISAM2Params& = ISAM2Params()) {}
-    void update() {}
-    void update(const NonlinearFactorGraph&) {}
-    void update(const NonlinearFactorGraph&, const Values& init) { for (auto& kv : init.m) est.m[kv.first] = kv.second; }
-    Values calculateEstimate() const { return est; }
+    void step() { if (g.hasLoop) { g.gaussNewtonStep(); ++gnSteps; } }
+    void update() { step(); }
+    void update(const NonlinearFactorGraph& graph) { update(graph, Values()); }
+    void update(const NonlinearFactorGraph& graph, const Values& init) {
+        for (auto& kv : init.m) { if (g.x.size() <= kv.first) g.x.resize(kv.first + 1); g.x[kv.first] = shim_pg(kv.second); }
+        for (const tp::PgFactor& F : graph.f) { g.f.push_back(F); if (F.i >= 0 && std::abs(F.i - F.j) != 1) g.hasLoop = true; }
+        step();
+    }
+    Values calculateEstimate() const { Values v; for (size_t k = 0; k < g.x.size(); ++k) v.m[k] = shim_pose(g.x[k]); return v; }
 };
 
 }  // namespace gtsam

@@ -1,7 +1,8 @@
 // TEST INFRASTRUCTURE ONLY (oracle).  Minimal stand-in for the PCL / Eigen names the reference sources use.
 // Containers are plain std::vector wrappers; VoxelGrid and KdTreeFLANN delegate to the restatements in
-// oracle/thirdparty/.  ICP / Eigen::Affine3f / PCD output exist only so the (disabled, utility.h:104) loop
-// closure code compiles; they are never executed with loopClosureEnableFlag == false.
+// oracle/thirdparty/.  IterativeClosestPoint delegates to oracle/thirdparty/tp_icp.h; Eigen::Affine3f,
+// pcl::getTransformation and pcl::getTranslationAndEulerAngles restate PCL's common/eigen.hpp (float); they only
+// run in the configs generated with loopClosureEnableFlag = true (utility.h:104).  PCD output is a no-op.
 #pragma once
 #include <cmath>
 #include <cstdint>
@@ -12,6 +13,7 @@
 #include "shim_ros.h"
 #include "../thirdparty/tp_voxel_grid.h"
 #include "../thirdparty/tp_kdtree.h"
+#include "../thirdparty/tp_icp.h"
 
 #define PCL_ADD_POINT4D union { float data[4]; struct { float x; float y; float z; }; };
 #define PCL_ADD_INTENSITY union { struct { float intensity; }; float data_c[4]; }
@@ -148,24 +150,62 @@ private:
     tp::KdTree3 tree_;
 };
 
-// ---- loop-closure-only API stubs (never executed: utility.h:104 loopClosureEnableFlag = false) ----
+// ---- loop closure (mapOptmization.cpp:875-945) ----
+struct ShimIcpLog { long runs = 0; bool converged = false; int iterations = 0; double fitness = 0; float T[16]; long ns = 0, nt = 0; };
+inline ShimIcpLog& shim_icp_log() { static ShimIcpLog l; return l; }
+
 template <class S, class D> class IterativeClosestPoint {
 public:
-    void setMaxCorrespondenceDistance(double) {}
-    void setMaximumIterations(int) {}
-    void setTransformationEpsilon(double) {}
-    void setEuclideanFitnessEpsilon(double) {}
+    void setMaxCorrespondenceDistance(double d) { maxDist_ = d; }
+    void setMaximumIterations(int n) { maxIter_ = n; }
+    void setTransformationEpsilon(double e) { epsT_ = e; }
+    void setEuclideanFitnessEpsilon(double e) { epsF_ = e; }
     void setRANSACIterations(int) {}
-    void setInputSource(const typename PointCloud<S>::Ptr&) {}
-    void setInputTarget(const typename PointCloud<D>::Ptr&) {}
-    void align(PointCloud<S>&) {}
-    bool hasConverged() const { return false; }
-    double getFitnessScore() const { return 1e30; }
-    Eigen::Matrix4f getFinalTransformation() const { return Eigen::Matrix4f(); }
+    void setInputSource(const typename PointCloud<S>::Ptr& c) { src_ = c; }
+    void setInputTarget(const typename PointCloud<D>::Ptr& c) { tgt_ = c; }
+    void align(PointCloud<S>& out) {
+        std::vector<float> a, b;
+        flatten(*src_, a); flatten(*tgt_, b);
+        res_ = tp::icp_align(a.data(), src_->points.size(), b.data(), tgt_->points.size(), maxDist_, maxIter_, epsT_, epsF_);
+        out = *src_;
+        for (auto& p : out.points) { float q[3] = {p.x, p.y, p.z}, o[3]; tp::icp_apply(res_.T, q, o); p.x = o[0]; p.y = o[1]; p.z = o[2]; }
+        ShimIcpLog& l = shim_icp_log();
+        l.runs += 1; l.converged = res_.converged; l.iterations = res_.iterations; l.fitness = res_.fitness;
+        std::memcpy(l.T, res_.T, sizeof(l.T)); l.ns = (long)src_->points.size(); l.nt = (long)tgt_->points.size();
+    }
+    bool hasConverged() const { return res_.converged; }
+    double getFitnessScore() const { return res_.fitness; }
+    Eigen::Matrix4f getFinalTransformation() const { Eigen::Matrix4f m; for (int r = 0; r < 4; ++r) for (int c = 0; c < 4; ++c) m.m[r][c] = res_.T[4 * r + c]; return m; }
+private:
+    template <class C> static void flatten(const C& c, std::vector<float>& o) {
+        o.resize(4 * c.points.size());
+        for (size_t i = 0; i < c.points.size(); ++i) { o[4 * i] = c.points[i].x; o[4 * i + 1] = c.points[i].y; o[4 * i + 2] = c.points[i].z; o[4 * i + 3] = c.points[i].intensity; }
+    }
+    double maxDist_ = 1e30, epsT_ = 0, epsF_ = 0; int maxIter_ = 10;
+    typename PointCloud<S>::Ptr src_; typename PointCloud<D>::Ptr tgt_;
+    tp::IcpResult res_;
 };
-template <class T> void transformPointCloud(const PointCloud<T>& in, PointCloud<T>& out, const Eigen::Matrix4f&) { out = in; }
-inline Eigen::Affine3f getTransformation(float, float, float, float, float, float) { return Eigen::Affine3f(); }
-inline void getTranslationAndEulerAngles(const Eigen::Affine3f&, float& x, float& y, float& z, float& r, float& p, float& w) { x = y = z = r = p = w = 0.f; }
+template <class T> void transformPointCloud(const PointCloud<T>& in, PointCloud<T>& out, const Eigen::Matrix4f& m) {
+    out = in;
+    for (auto& p : out.points) { float q[3] = {p.x, p.y, p.z}, o[3]; tp::icp_apply(&m.m[0][0], q, o); p.x = o[0]; p.y = o[1]; p.z = o[2]; }
+}
+// pcl::getTransformation (common/impl/eigen.hpp): R = Rz(yaw) Ry(pitch) Rx(roll), float
+inline Eigen::Affine3f getTransformation(float x, float y, float z, float roll, float pitch, float yaw) {
+    const float A = std::cos(yaw), B = std::sin(yaw), C = std::cos(pitch), D = std::sin(pitch), E = std::cos(roll), F = std::sin(roll);
+    const float DE = D * E, DF = D * F;
+    Eigen::Affine3f t;
+    t.mat.m[0][0] = A * C; t.mat.m[0][1] = A * DF - B * E; t.mat.m[0][2] = B * F + A * DE; t.mat.m[0][3] = x;
+    t.mat.m[1][0] = B * C; t.mat.m[1][1] = A * E + B * DF; t.mat.m[1][2] = B * DE - A * F; t.mat.m[1][3] = y;
+    t.mat.m[2][0] = -D;    t.mat.m[2][1] = C * F;          t.mat.m[2][2] = C * E;          t.mat.m[2][3] = z;
+    t.mat.m[3][0] = 0.f; t.mat.m[3][1] = 0.f; t.mat.m[3][2] = 0.f; t.mat.m[3][3] = 1.f;
+    return t;
+}
+inline void getTranslationAndEulerAngles(const Eigen::Affine3f& t, float& x, float& y, float& z, float& roll, float& pitch, float& yaw) {
+    x = t.mat.m[0][3]; y = t.mat.m[1][3]; z = t.mat.m[2][3];
+    roll = std::atan2(t.mat.m[2][1], t.mat.m[2][2]);
+    pitch = std::asin(-t.mat.m[2][0]);
+    yaw = std::atan2(t.mat.m[1][0], t.mat.m[0][0]);
+}
 namespace io { template <class T> int savePCDFileASCII(const std::string&, const PointCloud<T>&) { return 0; } }
 
 }  // namespace pcl

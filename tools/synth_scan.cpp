@@ -115,10 +115,18 @@ typedef struct {
     double noise_sigma, max_range, min_range;
     double dropout_prob, dup_col_prob, jitter_frac;
     double scan_period;
+    int traj;                                // 0 = forward drive with sway (above), 1 = closed circle around the origin (loop closure tests)
+    double circle_radius;
 } lego_synth_cfg;
 
 // Ground-truth sensor pose at time t: out = x,y,z,roll,pitch,yaw (lidar/world frame, z up).
 void lego_synth_pose(const lego_synth_cfg* c, double t, double* out6) {
+    if (c->traj == 1) {   // counter-clockwise circle, heading along the tangent; one lap takes 2 pi r / speed seconds
+        const double r = c->circle_radius, om = c->speed / r, a = om * t;
+        out6[0] = r * std::sin(a); out6[1] = -r * std::cos(a); out6[2] = c->sensor_height + 0.02 * std::sin(0.9 * t);
+        out6[3] = 0.01 * std::sin(0.7 * t); out6[4] = 0.01 * std::sin(0.5 * t + 1.0); out6[5] = a;
+        return;
+    }
     double w = 2 * M_PI / c->yaw_period;
     double x = c->speed * t, y = c->sway_amp * std::sin(w * t);
     double yaw = std::atan2(c->sway_amp * w * std::cos(w * t), c->speed > 1e-9 ? c->speed : 1e-9) + c->yaw_amp * std::sin(0.5 * w * t);
