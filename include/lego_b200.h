@@ -54,8 +54,13 @@ typedef struct lego_params {
     float nearestFeatureSearchSqDist;        /* utility.h:125                                            */
     float surroundingKeyframeSearchRadius;   /* utility.h:129                                            */
     double mappingProcessInterval;           /* utility.h:105                                            */
-    int loopClosureEnableFlag;               /* utility.h:104 (must be 0 in this release)                */
+    int loopClosureEnableFlag;               /* utility.h:104                                            */
     int device;                              /* CUDA device ordinal                                      */
+    /* loop closure (only read when loopClosureEnableFlag != 0) */
+    int surroundingKeyframeSearchNum;        /* utility.h:130 (50)                                       */
+    float historyKeyframeSearchRadius;       /* utility.h:132 (7.0)                                      */
+    int historyKeyframeSearchNum;            /* utility.h:133 (25)                                       */
+    float historyKeyframeFitnessScore;       /* utility.h:134 (0.3)                                      */
 } lego_params;
 
 /* A cloud living on the device (dev) with an optional host mirror (host, may be NULL). Valid until the next
@@ -174,6 +179,32 @@ long lego_pipeline_profile_read(lego_pipeline* h, char* names, long names_cap, d
  * element count (and copies min(count, cap) elements) or a negative error code.  elem_size_out gets 1/2/4/16. */
 long lego_pipeline_download(lego_pipeline* h, int lane, const char* name, void* dst, long cap, int* elem_size_out);
 long lego_pipeline_upload(lego_pipeline* h, int lane, const char* name, const void* src, long count);
+
+/* ---------------------------------------------------------------- loop closure building blocks
+ * With loopClosureEnableFlag set, lego_mo_process / lego_pipeline_step run the reference's loop-closure branch:
+ * the local map is the surroundingKeyframeSearchNum most recent key frames (mapOptmization.cpp:960-1000) and
+ * performLoopClosure (mapOptmization.cpp:875-945; a 1 Hz side thread in the reference) is called after a mapping call
+ * once >= 1.0 s of scan time passed since its last call.  Its two third-party pieces are exported on their own:
+ *
+ * lego_icp_align replaces pcl::IterativeClosestPoint<PointXYZI,PointXYZI>::align + hasConverged + getFitnessScore
+ * + getFinalTransformation as configured at mapOptmization.cpp:892-905.  source / target: n*4 floats, host memory.
+ * T_out: row-major 4x4.  Runs on the device (voxel-hash exact nearest neighbour, one CTA). */
+int lego_icp_align(int device, const float* source, int n_source, const float* target, int n_target,
+                   double max_correspondence_distance, int max_iterations, double transformation_epsilon,
+                   double euclidean_fitness_epsilon, float T_out[16], double* fitness_out, int* converged_out, int* iterations_out);
+/* lego_pg_* replaces the gtsam calls of mapOptmization.cpp:1375-1409 and 929-942 (ISAM2 on a Pose3 graph with diagonal
+ * noise): poses are (rx, ry, rz, tx, ty, tz) doubles with R = gtsam::Rot3::RzRyRx(rx, ry, rz); add_between takes the two
+ * poses whose relative transform from.between(to) is the measurement.  update = ISAM2::update() (host code, like GTSAM). */
+typedef struct lego_pg lego_pg;
+int lego_pg_create(lego_pg** out);
+int lego_pg_destroy(lego_pg* h);
+int lego_pg_add_prior(lego_pg* h, int key, const double pose[6], const double variances[6]);
+int lego_pg_add_between(lego_pg* h, int key1, int key2, const double from[6], const double to[6], const double variances[6]);
+int lego_pg_insert(lego_pg* h, int key, const double pose[6]);
+int lego_pg_update(lego_pg* h);
+int lego_pg_size(lego_pg* h);
+/* estimate of one key: translation x y z and Rot3::roll() pitch() yaw() */
+int lego_pg_estimate(lego_pg* h, int key, double xyz_rpy_out[6]);
 
 /* ---------------------------------------------------------------- device self-tests (parity suite) */
 /* out[i] = the device implementation of glibc's atan2f(y[i], x[i]) (csrc/parity_math.cuh); host pointers. */

@@ -21,6 +21,8 @@ EXPORTED = [
     "lego_pipeline_timer_record", "lego_pipeline_timer_elapsed", "lego_pipeline_timer_elapsed_between", "lego_pipeline_profile", "lego_pipeline_profile_read",
     "lego_tf_create", "lego_tf_destroy", "lego_tf_laser_odometry", "lego_tf_aft_mapped",
     "lego_selftest_atan2f", "lego_selftest_std_sort", "lego_selftest_warp_sort", "lego_selftest_voxel_grid",
+    "lego_icp_align",
+    "lego_pg_create", "lego_pg_destroy", "lego_pg_add_prior", "lego_pg_add_between", "lego_pg_insert", "lego_pg_update", "lego_pg_size", "lego_pg_estimate",
 ]
 
 _lib = None
@@ -224,7 +226,76 @@ class Pipeline:
 
 _FLOAT_NAMES = {"rangeMat", "segRange", "orientation", "cloudCurvature", "transformCur", "transformSum", "slot4val",
                 "matP", "moTransformSum", "transformTobeMapped", "transformAftMapped", "transformBefMapped",
-                "transformMapped", "integratedToInit", "tfTransformAftMapped", "tfTransformBefMapped"}
+                "transformMapped", "integratedToInit", "tfTransformAftMapped", "tfTransformBefMapped",
+                "cloudKeyPoses6D", "icpTransform", "icpFitness"}
+
+
+def icp_align(source, target, max_correspondence_distance=100.0, max_iterations=100, transformation_epsilon=1e-6,
+              euclidean_fitness_epsilon=1e-6, device=0):
+    """lego_icp_align: pcl::IterativeClosestPoint as configured at mapOptmization.cpp:892-905, on the device.
+    -> (T float32[4,4], fitness, converged, iterations)"""
+    source = np.ascontiguousarray(source, np.float32).reshape(-1, 4)
+    target = np.ascontiguousarray(target, np.float32).reshape(-1, 4)
+    T = np.zeros(16, np.float32)
+    fit, conv, it = ctypes.c_double(0), ctypes.c_int(0), ctypes.c_int(0)
+    lib = load()
+    lib.lego_icp_align.argtypes = [ctypes.c_int, ctypes.c_void_p, ctypes.c_int, ctypes.c_void_p, ctypes.c_int, ctypes.c_double, ctypes.c_int,
+                                   ctypes.c_double, ctypes.c_double, ctypes.c_void_p, ctypes.POINTER(ctypes.c_double),
+                                   ctypes.POINTER(ctypes.c_int), ctypes.POINTER(ctypes.c_int)]
+    _check(lib.lego_icp_align(device, source.ctypes.data, len(source), target.ctypes.data, len(target), max_correspondence_distance,
+                              max_iterations, transformation_epsilon, euclidean_fitness_epsilon, T.ctypes.data, ctypes.byref(fit),
+                              ctypes.byref(conv), ctypes.byref(it)), "lego_icp_align")
+    return T.reshape(4, 4), fit.value, conv.value, it.value
+
+
+class PoseGraph:
+    """lego_pg_*: the Pose3 graph mapOptimization keeps in iSAM2 (mapOptmization.cpp:1375-1409, 929-942). Host code."""
+
+    def __init__(self):
+        self.lib = lib = load()
+        P = ctypes.POINTER(ctypes.c_double)
+        lib.lego_pg_create.argtypes = [ctypes.POINTER(ctypes.c_void_p)]
+        lib.lego_pg_destroy.argtypes = [ctypes.c_void_p]
+        lib.lego_pg_add_prior.argtypes = [ctypes.c_void_p, ctypes.c_int, P, P]
+        lib.lego_pg_add_between.argtypes = [ctypes.c_void_p, ctypes.c_int, ctypes.c_int, P, P, P]
+        lib.lego_pg_insert.argtypes = [ctypes.c_void_p, ctypes.c_int, P]
+        lib.lego_pg_update.argtypes = [ctypes.c_void_p]
+        lib.lego_pg_size.argtypes = [ctypes.c_void_p]
+        lib.lego_pg_estimate.argtypes = [ctypes.c_void_p, ctypes.c_int, P]
+        self.h = ctypes.c_void_p()
+        _check(lib.lego_pg_create(ctypes.byref(self.h)), "lego_pg_create")
+
+    @staticmethod
+    def _v(x):
+        return (ctypes.c_double * 6)(*[float(v) for v in x])
+
+    def add_prior(self, key, pose, variances):
+        _check(self.lib.lego_pg_add_prior(self.h, key, self._v(pose), self._v(variances)), "lego_pg_add_prior")
+
+    def add_between(self, k1, k2, pose_from, pose_to, variances):
+        _check(self.lib.lego_pg_add_between(self.h, k1, k2, self._v(pose_from), self._v(pose_to), self._v(variances)), "lego_pg_add_between")
+
+    def insert(self, key, pose):
+        _check(self.lib.lego_pg_insert(self.h, key, self._v(pose)), "lego_pg_insert")
+
+    def update(self):
+        _check(self.lib.lego_pg_update(self.h), "lego_pg_update")
+
+    def estimate(self):
+        n = self.lib.lego_pg_size(self.h)
+        out = np.zeros((n, 6))
+        buf = (ctypes.c_double * 6)()
+        for k in range(n):
+            _check(self.lib.lego_pg_estimate(self.h, k, buf), "lego_pg_estimate")
+            out[k] = list(buf)
+        return out
+
+    def close(self):
+        if getattr(self, "h", None):
+            self.lib.lego_pg_destroy(self.h)
+            self.h = None
+
+    __del__ = close
 
 
 # ---------------------------------------------------------------------------------------------- per-stage handles

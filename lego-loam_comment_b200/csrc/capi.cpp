@@ -30,7 +30,6 @@ int lego_device_count(void) {
 // ------------------------------------------------------------------ pipeline
 int lego_pipeline_create(const lego_params* p, int lanes, int max_points, lego_pipeline** out) {
     if (!p || !out || lanes < 1 || p->N_SCAN < 2 || p->N_SCAN > 128 || p->Horizon_SCAN < 16) return LEGO_ERR_ARG;
-    if (p->loopClosureEnableFlag) { lego::set_last_error("loop closure is not part of this release"); return LEGO_ERR_ARG; }
     LEGO_TRY
     lego_pipeline* h = new lego_pipeline();
     h->e = new Engine(*p, lanes, max_points);
@@ -129,6 +128,22 @@ long lego_pipeline_download(lego_pipeline* h, int lane, const char* name, void* 
         if (elem_size_out) *elem_size_out = 4;
         const long n = (long)v.size();
         if (dst && n > 0) std::memcpy(dst, v.data(), sizeof(int) * (size_t)(n < cap ? n : cap));
+        return n;
+    }
+    if (!std::strcmp(name, "cloudKeyPoses6D") || !std::strcmp(name, "loopClosure") || !std::strcmp(name, "icpTransform") ||
+        !std::strcmp(name, "icpFitness") || !std::strcmp(name, "loopStats")) {   // host-side state of the loop-closure bookkeeping
+        if (lane < 0 || lane >= h->e->c.L) return LEGO_ERR_NAME;
+        const lego::MoLaneHost& H = h->e->moHost[lane];
+        std::vector<float> f; std::vector<int> iv;
+        if (name[0] == 'c') for (const lego::MoKeyFrame& k : H.keyFrames) { f.push_back(k.x); f.push_back(k.y); f.push_back(k.z); f.push_back(k.roll); f.push_back(k.pitch); f.push_back(k.yaw); }
+        else if (!std::strcmp(name, "icpTransform")) f.assign(H.lastIcpT, H.lastIcpT + 16);
+        else if (!std::strcmp(name, "icpFitness")) f.push_back((float)H.lastIcpFitness);
+        else if (!std::strcmp(name, "loopStats")) { iv.push_back(H.loopCalls); iv.push_back(H.loopsClosed); }
+        else iv.assign(H.lastLoop, H.lastLoop + 9);
+        if (elem_size_out) *elem_size_out = 4;
+        const long n = (long)(f.empty() ? iv.size() : f.size());
+        const void* srcp = f.empty() ? (const void*)iv.data() : (const void*)f.data();
+        if (dst && n > 0) std::memcpy(dst, srcp, 4 * (size_t)(n < cap ? n : cap));
         return n;
     }
     if (!std::strcmp(name, "labelMat")) h->e->finalizeLabelMat();

@@ -75,6 +75,10 @@ Engine::~Engine() {
     }
     if (moPinned) cudaFreeHost(moPinned);
     if (moRecordsHost) cudaFreeHost(moRecordsHost);
+    if (lcPinned) cudaFreeHost(lcPinned);
+    if (moOverridesHost) cudaFreeHost(moOverridesHost);
+    if (moAftHost) cudaFreeHost(moAftHost);
+    if (moScanCountsHost) cudaFreeHost(moScanCountsHost);
     for (int b = 0; b < 2; ++b) if (moStaged[b]) cudaEventDestroy(moStaged[b]);
     if (moRecordsReady) cudaEventDestroy(moRecordsReady);
     for (auto& pe : profLog) { if (pe.a) cudaEventDestroy(pe.a); if (pe.b) cudaEventDestroy(pe.b); }

@@ -5,9 +5,11 @@
 #pragma once
 #include <cuda_runtime.h>
 #include <stdint.h>
+#include <deque>
 #include <string>
 #include <vector>
 #include "../../include/lego_b200.h"
+#include "pose_graph.h"
 #include "voxel_grid.cuh"
 #include "voxel_hash.cuh"
 
@@ -111,6 +113,33 @@ struct MoRecord {
     int iters;                // LM iterations of scan2MapOptimization
     float robotPos[3];        // currentRobotPosPoint
     float pose6D[6];          // x, y, z, roll, pitch, yaw of cloudKeyPoses6D
+    float aftRaw[6];          // the pose the factor was built from: transformAftMapped before the estimate overwrote it
+                              // (transformTobeMapped for the first key frame, mapOptmization.cpp:1375-1392)
+};
+// saveKeyFramesAndFactor decided on the HOST: once a lane's pose graph holds a loop factor the newest estimate is no
+// longer the inserted value, so the host runs the graph update between scan2MapOptimization and the key-frame save
+// and hands the kernel its decision (mapOptmization.cpp:1395-1440).
+struct MoOverride { int use, save; float pose6D[6]; float aft[6]; };
+
+// ---- loop closure (mapOptmization.cpp:814-945): history submap + ICP, a few "slots" shared by all lanes ----
+struct LcEntry {              // one key-frame cloud to transform into the ICP source (which = 0) or target (which = 1)
+    int src, n, dst, which;
+    float ctRoll, stRoll, ctPitch, stPitch, ctYaw, stYaw, tInX, tInY, tInZ;
+};
+struct LcResult { int converged, iterations, pairs, nSrc; double fitness; float T[16]; };
+struct LcIcpParams { float maxDist2; int maxIter; double epsTransform, epsFitness; };
+struct LcDev {
+    int slots, srcCap, tgtRawCap, tgtDSCap, maxEntries;
+    int* slotLane;             // [slots] lane whose key-frame pool the slot reads, -1 = idle
+    int* slotActive;           // [slots]
+    int* counts;               // [slots][4] nSrc, nTgtRaw, nTgtDS, nEntries
+    LcEntry* entries;          // [slots][maxEntries]
+    float4* src; float4* work; // [slots][srcCap] latestSurfKeyFrameCloud and the copy ICP transforms in place
+    float4* tgtRaw; float4* tgtDS;   // [slots][tgtRawCap], [slots][tgtDSCap] nearHistorySurfKeyFrameCloud(DS)
+    int* miss;                 // [slots][srcCap] points whose nearest neighbour lies outside the shell search
+    int* nnIdx; float* nnD2;   // [slots][srcCap]
+    LcResult* results;         // [slots]
+    VoxelHash hash;            // over tgtDS
 };
 
 struct MoDev {
@@ -130,13 +159,14 @@ struct MoDev {
     int* scanCounts;           // [L][8]  cornerLastDS, surfLastDS, outlierLastDS, surfTotalLast, surfTotalLastDS sizes
     VoxelHash hashCornerMap, hashSurfMap;
     MoRecord* records;         // [L]
+    MoOverride* overrides;     // [L]
     double* partials;          // [L][resBlocks][8][28] per-warp partial sums of AtA / AtB / row count
     int resBlocks;             // CTAs per lane in mo_residual_kernel
     int poolCap, maxSel, cornerRawCap, surfRawCap, cornerDSCap, surfDSCap, scanCornerCap, scanSurfCap, scanOutlierCap, maxKeyFrames;
 };
 
 // host side of one lane's mapOptimization: the key-frame list and the message gates
-struct MoKeyFrame { float x, y, z, roll, pitch, yaw; int poolOff, nC, nS, nO; };
+struct MoKeyFrame { float x, y, z, roll, pitch, yaw; int poolOff, nC, nS, nO; double time; };
 struct MoLaneHost {
     std::vector<MoKeyFrame> keyFrames;                // cloudKeyPoses3D / 6D + where the clouds live
     std::vector<int> surroundingExistingKeyPosesID;   // mapOptmization.cpp:90
@@ -147,6 +177,19 @@ struct MoLaneHost {
     // FeatureAssociation's publish cadence mirrored on the host (featureAssociation.cpp:284, 314, 1790-1794)
     bool faInited = false; int faFrameCount = 1;
     int lastError = 0;
+    // ---- loop closure state (only used when loopClosureEnableFlag is set) ----
+    std::deque<int> recent;                           // recentCorner/Surf/OutlierCloudKeyFrames as key-frame ids (mapOptmization.cpp:960-1000)
+    int latestFrameID = 0;                            // mapOptmization.cpp:373
+    pg::Graph graph;                                  // gtSAMgraph + isam
+    std::vector<pg::Pose> estimate;                   // isamCurrentEstimate: only refreshed when a key frame is saved (mapOptmization.cpp:1408)
+    float transformLast[6] = {0, 0, 0, 0, 0, 0};
+    float prevRobotPos[3] = {0, 0, 0};
+    bool aLoopIsClosed = false;
+    double timeLastLoop = -1e9;                       // performLoopClosure cadence (1 Hz thread of mapOptmization.cpp:802-812)
+    int loopCalls = 0, loopsClosed = 0;
+    int lastLoop[9] = {0, 0, 0, -1, -1, 0, 0, 0, 0};  // called, icp ran, closed, closestHistoryFrameID, latestFrameIDLoopCloure, converged, iterations, nSrc, nTgtDS
+    float lastIcpT[16] = {1, 0, 0, 0, 0, 1, 0, 0, 0, 0, 1, 0, 0, 0, 0, 1};
+    double lastIcpFitness = 0;
 };
 
 void cuda_check(cudaError_t e, const char* what);
@@ -172,12 +215,24 @@ public:
 
     // ---- mapOptimization (names follow mapOptmization.cpp) ----
     void allocMapOptimization();
+    VgBatch makeVgBatch(std::vector<VgSeg>& segs, int maxCap);
+    VgSeg makeVgSeg(const float4* in, const int* nIn, float4* out, int* nOut, const int* active, float leaf, int cap, int outCap);
     void mapOptimizationRun(const double* stamps);   // gates + the body of mapOptimization::run for every lane that passes them
     bool mapOptimizationGates(const double* stamps, std::vector<int>& active);
     void mapOptimizationBody(const std::vector<int>& active);
     bool lookupMapOptimization(int lane, const std::string& name, void** ptr, int* elem, long* count);
     void consumeMapRecords();                        // host bookkeeping of saveKeyFramesAndFactor from the device records
     void selectSurroundingKeyFrames(int lane, std::vector<MoKfEntry>& out, int* nCorner, int* nSurf);
+    // ---- loop closure (names follow mapOptmization.cpp) ----
+    bool loopMode() const { return params.loopClosureEnableFlag != 0; }
+    void allocLoopClosure();
+    void selectRecentKeyFrames(int lane, std::vector<MoKfEntry>& out, int* nCorner, int* nSurf);   // extractSurroundingKeyFrames, loop-closure branch
+    void saveKeyFramesHostGraph(const std::vector<int>& active);   // saveKeyFramesAndFactor for lanes whose graph holds a loop factor
+    void correctPoses(int lane);
+    void performLoopClosure(const std::vector<int>& active);
+    bool detectLoopClosure(int lane, int* closest, int* latest);
+    void runIcpBatch(const std::vector<int>& lanes, const std::vector<int>& closest, const std::vector<int>& latest);
+    void addLoopConstraint(int lane, int closest, int latest, const LcResult& r);
 
     // ---- TransformFusion (names follow transformFusion.cpp) ----
     void allocTransformFusion();
@@ -213,7 +268,7 @@ public:
     bool lookupFeatureAssociation(int lane, const std::string& name, void** ptr, int* elem, long* count);
     void allocFeatureAssociation();
     void allocOdometry();
-    VoxelHash allocHash(int cap, float cell, const int* n, int nStride);
+    VoxelHash allocHash(int cap, float cell, const int* n, int nStride, int lanes = -1);
     bool lookupOdometry(int lane, const std::string& name, void** ptr, int* elem, long* count);
 
     Consts c;
@@ -229,6 +284,11 @@ public:
     VgBatch vgMap;             // 2 segments per lane: local corner / surf map
     VgBatch vgScan[2];         // per value of faBuf, 3 segments per lane: corner / surf / outlier cloud of the current scan
     VgBatch vgSurfTotal;       // 1 segment per lane
+    LcDev lc = {};             // loop-closure slots (allocated only when loopClosureEnableFlag is set)
+    VgBatch vgLoop;            // 1 segment per slot: downSizeFilterHistoryKeyFrames (leaf 0.4)
+    char* lcPinned = nullptr;  // pinned staging: entries | counts | slotActive | slotLane | results
+    MoOverride* moOverridesHost = nullptr;   // pinned [L]
+    float* moAftHost = nullptr; int* moScanCountsHost = nullptr;   // pinned [L][6], [L][8]
     char* moPinned = nullptr;  // pinned staging: entries | nEntries | mapCounts | active, double buffered
     size_t moPinnedStride = 0;
     int moPinnedSlot = 0;

@@ -25,6 +25,24 @@ static int env_int(const char* name, int dflt) {
     return v && *v ? std::atoi(v) : dflt;
 }
 
+VgBatch Engine::makeVgBatch(std::vector<VgSeg>& segs, int maxCap) {
+    VgBatch b; b.nSeg = (int)segs.size(); b.maxBlocks = (maxCap + VG_TILE - 1) / VG_TILE;
+    for (auto& g : segs) {
+        g.keys[0] = alloc<unsigned>(g.cap, false); g.keys[1] = alloc<unsigned>(g.cap, false);
+        g.vals[0] = alloc<unsigned>(g.cap, false); g.vals[1] = alloc<unsigned>(g.cap, false);
+        g.blockHist = alloc<int>((size_t)256 * b.maxBlocks); g.blockHeads = alloc<int>(b.maxBlocks); g.state = alloc<int>(16);
+    }
+    b.segs = alloc<VgSeg>(segs.size());
+    cuda_check(cudaMemcpyAsync(b.segs, segs.data(), sizeof(VgSeg) * segs.size(), cudaMemcpyHostToDevice, stream), "vg table");
+    cuda_check(cudaStreamSynchronize(stream), "vg table sync");
+    return b;
+}
+VgSeg Engine::makeVgSeg(const float4* in, const int* nIn, float4* out, int* nOut, const int* active, float leaf, int cap, int outCap) {
+    VgSeg g; std::memset(&g, 0, sizeof(g));
+    g.in = in; g.nIn = nIn; g.out = out; g.nOut = nOut; g.active = active; g.leaf = leaf; g.cap = cap; g.outCap = outCap;
+    return g;
+}
+
 void Engine::allocMapOptimization() {
     const size_t L = c.L, N = c.N, R = c.R;
     mo.maxKeyFrames = env_int("LEGO_MAX_KEYFRAMES", 640);
@@ -49,27 +67,15 @@ void Engine::allocMapOptimization() {
     mo.scanCounts = alloc<int>(L * 8);
     mo.hashCornerMap = allocHash(mo.cornerDSCap, 1.0f, mo.mapCounts + 2, 4); mo.hashSurfMap = allocHash(mo.surfDSCap, 1.0f, mo.mapCounts + 3, 4);
     mo.records = alloc<MoRecord>(L);
+    mo.overrides = alloc<MoOverride>(L);
     mo.resBlocks = (mo.scanCornerCap + mo.scanSurfCap + mo.scanOutlierCap + 255) / 256;
     mo.partials = alloc<double>(L * mo.resBlocks * 8 * 28);   // per 32-query warp slice
     moHost.assign(c.L, MoLaneHost());
 
     // ---- VoxelGrid segment tables ----
-    auto make_batch = [&](std::vector<VgSeg>& segs, int maxCap) {
-        VgBatch b; b.nSeg = (int)segs.size(); b.maxBlocks = (maxCap + VG_TILE - 1) / VG_TILE;
-        for (auto& g : segs) {
-            g.keys[0] = alloc<unsigned>(g.cap, false); g.keys[1] = alloc<unsigned>(g.cap, false);
-            g.vals[0] = alloc<unsigned>(g.cap, false); g.vals[1] = alloc<unsigned>(g.cap, false);
-            g.blockHist = alloc<int>((size_t)256 * b.maxBlocks); g.blockHeads = alloc<int>(b.maxBlocks); g.state = alloc<int>(16);
-        }
-        b.segs = alloc<VgSeg>(segs.size());
-        cuda_check(cudaMemcpyAsync(b.segs, segs.data(), sizeof(VgSeg) * segs.size(), cudaMemcpyHostToDevice, stream), "vg table");
-        cuda_check(cudaStreamSynchronize(stream), "vg table sync");
-        return b;
-    };
+    auto make_batch = [&](std::vector<VgSeg>& segs, int maxCap) { return makeVgBatch(segs, maxCap); };
     auto seg = [&](const float4* in, const int* nIn, float4* out, int* nOut, const int* active, float leaf, int cap, int outCap) {
-        VgSeg g; std::memset(&g, 0, sizeof(g));
-        g.in = in; g.nIn = nIn; g.out = out; g.nOut = nOut; g.active = active; g.leaf = leaf; g.cap = cap; g.outCap = outCap;
-        return g;
+        return makeVgSeg(in, nIn, out, nOut, active, leaf, cap, outCap);
     };
     // local map: leaf 0.2 for corners, 0.4 for surfaces (mapOptmization.cpp:249-250); the scratch of these segments is
     // shared between the two faBuf variants because only one of them is ever in flight
@@ -106,6 +112,7 @@ void Engine::allocMapOptimization() {
     cuda_check(cudaMallocHost(reinterpret_cast<void**>(&moRecordsHost), sizeof(MoRecord) * L), "cudaMallocHost");
     for (int b = 0; b < 2; ++b) cuda_check(cudaEventCreateWithFlags(&moStaged[b], cudaEventDisableTiming), "event");
     cuda_check(cudaEventCreateWithFlags(&moRecordsReady, cudaEventDisableTiming), "event");
+    allocLoopClosure();
 }
 
 bool Engine::lookupMapOptimization(int lane, const std::string& n, void** ptr, int* elem, long* count) {
@@ -222,11 +229,13 @@ void Engine::selectSurroundingKeyFrames(int lane, std::vector<MoKfEntry>& out, i
     *nCorner = offC; *nSurf = offS;
 }
 
-// The device wrote one MoRecord per lane at the end of the previous mapping call; fold it into the host key-frame lists.
+// The device wrote one MoRecord per lane at the end of a mapping call; fold it into the host key-frame lists (and, with
+// loop closure on, into the lane's pose graph: the prior / chain factors of mapOptmization.cpp:1375-1392).
 void Engine::consumeMapRecords() {
     if (!moRecordsPending) return;
     cuda_check(cudaEventSynchronize(moRecordsReady), "records sync");
     moRecordsPending = false;
+    static const double kVar[6] = {1e-6, 1e-6, 1e-6, 1e-8, 1e-8, 1e-6};   // priorNoise = odometryNoise (mapOptmization.cpp:346-350)
     for (int l = 0; l < c.L; ++l) {
         const MoRecord& r = moRecordsHost[l];
         if (!r.ran) continue;
@@ -236,9 +245,28 @@ void Engine::consumeMapRecords() {
         if (r.saved) {
             MoKeyFrame k;
             k.x = r.pose6D[0]; k.y = r.pose6D[1]; k.z = r.pose6D[2]; k.roll = r.pose6D[3]; k.pitch = r.pose6D[4]; k.yaw = r.pose6D[5];
-            k.poolOff = r.poolOff; k.nC = r.nC; k.nS = r.nS; k.nO = r.nO;
+            k.poolOff = r.poolOff; k.nC = r.nC; k.nS = r.nS; k.nO = r.nO; k.time = H.timeOdometry;
+            if (loopMode() && !H.graph.hasLoop) {   // (lanes with a loop factor were handled by saveKeyFramesHostGraph)
+                const int n = (int)H.keyFrames.size();
+                const float* a = r.aftRaw;
+                const pg::Pose to = pg::make_pose((double)a[2], (double)a[0], (double)a[1], (double)a[5], (double)a[3], (double)a[4]);
+                if (n == 0) {
+                    H.graph.addPrior(0, to, kVar);
+                    for (int i = 0; i < 6; ++i) H.transformLast[i] = a[i];
+                } else {
+                    const float* t = H.transformLast;
+                    const pg::Pose from = pg::make_pose((double)t[2], (double)t[0], (double)t[1], (double)t[5], (double)t[3], (double)t[4]);
+                    H.graph.addBetween(n - 1, n, pg::between(from, to), kVar);
+                    H.transformLast[0] = k.roll; H.transformLast[1] = k.pitch; H.transformLast[2] = k.yaw;
+                    H.transformLast[3] = k.x; H.transformLast[4] = k.y; H.transformLast[5] = k.z;
+                }
+                H.graph.insert(n, to);
+                H.estimate = H.graph.x;
+                for (int i = 0; i < 3; ++i) H.prevRobotPos[i] = r.robotPos[i];
+            }
             H.keyFrames.push_back(k);
         }
+        if (loopMode()) correctPoses(l);
     }
 }
 
@@ -294,7 +322,9 @@ void Engine::mapOptimizationBody(const std::vector<int>& active) {
     std::vector<MoKfEntry> sel;
     for (int l = 0; l < c.L; ++l) {
         int nC = 0, nS = 0;
-        if (active[l]) selectSurroundingKeyFrames(l, sel, &nC, &nS); else sel.clear();
+        if (!active[l]) sel.clear();
+        else if (loopMode()) selectRecentKeyFrames(l, sel, &nC, &nS);
+        else selectSurroundingKeyFrames(l, sel, &nC, &nS);
         std::memcpy(hEntries + (size_t)l * mo.maxSel, sel.data(), sizeof(MoKfEntry) * sel.size());
         hInts[l] = (int)sel.size(); hInts[c.L + l] = active[l];
         hInts[2 * c.L + l * 4 + 0] = nC; hInts[2 * c.L + l * 4 + 1] = nS; hInts[2 * c.L + l * 4 + 2] = 0; hInts[2 * c.L + l * 4 + 3] = 0;
@@ -333,11 +363,17 @@ void Engine::mapOptimizationBody(const std::vector<int>& active) {
         }
         launches += 21;
     }
+    if (loopMode()) saveKeyFramesHostGraph(active);   // lanes whose graph holds a loop factor: gate + iSAM update on the host
     { ProfScope ps(this, "mo_save_keyframe_kernel"); mo_save_keyframe_kernel<<<c.L, 256, 0, stream>>>(mo); }
     launches += 3;
     cuda_check(cudaMemcpyAsync(moRecordsHost, mo.records, sizeof(MoRecord) * c.L, cudaMemcpyDeviceToHost, stream), "records");
     cuda_check(cudaEventRecord(moRecordsReady, stream), "event record");
     moRecordsPending = true;
+    if (loopMode()) {
+        // the loop-closure search needs this call's key frame: take the records now instead of one call later
+        consumeMapRecords();            // + correctPoses
+        performLoopClosure(active);     // detect -> submap + ICP on the device -> constraint on the host graph
+    }
 }
 
 }  // namespace lego

@@ -277,30 +277,44 @@ __global__ void __launch_bounds__(256) mo_save_keyframe_kernel(MoDev m) {
         const float cx = Aft[3], cy = Aft[4], cz = Aft[5];
         rec.robotPos[0] = cx; rec.robotPos[1] = cy; rec.robotPos[2] = cz;
         const int nKF = m.state[lane * 16 + 1];
-        const float dist = sqrtf((prev[0] - cx) * (prev[0] - cx) + (prev[1] - cy) * (prev[1] - cy) + (prev[2] - cz) * (prev[2] - cz));
-        bool save = !((double)dist < 0.3);
+        const int used = m.state[lane * 16 + 2];
+        const MoOverride ov = m.overrides[lane];
         int err = 0;
-        if (!save && nKF > 0) { s_save = 0; }
-        else {
-            const int used = m.state[lane * 16 + 2];
-            if (nKF >= m.maxKeyFrames || used + nC + nS + nO > m.poolCap) { err = 1; s_save = 0; }
-            else {
+        s_save = 0;
+        if (ov.use) {
+            // the host ran the gate and the pose-graph update (a loop factor is in the graph): apply its decision
+            if (ov.save) {
                 prev[0] = cx; prev[1] = cy; prev[2] = cz;
-                const float* P = nKF == 0 ? T : Aft;   // first key frame is built from transformTobeMapped (1375-1382)
-                if (nKF == 0) for (int i = 0; i < 6; ++i) Last[i] = T[i];
-                double roll, pitch, yaw;
-                rzryrx_round_trip((double)P[2], (double)P[0], (double)P[1], &roll, &pitch, &yaw);
-                const float kx = P[3], ky = P[4], kz = P[5];   // translation (z, x, y) -> thisPose3D (y, z, x) of it
-                const float kroll = (float)pitch, kpitch = (float)yaw, kyaw = (float)roll;
-                rec.pose6D[0] = kx; rec.pose6D[1] = ky; rec.pose6D[2] = kz; rec.pose6D[3] = kroll; rec.pose6D[4] = kpitch; rec.pose6D[5] = kyaw;
-                if (nKF + 1 > 1) {
-                    Aft[0] = kroll; Aft[1] = kpitch; Aft[2] = kyaw; Aft[3] = kx; Aft[4] = ky; Aft[5] = kz;
-                    for (int i = 0; i < 6; ++i) { Last[i] = Aft[i]; T[i] = Aft[i]; }
-                }
+                for (int i = 0; i < 6; ++i) { rec.aftRaw[i] = Aft[i]; rec.pose6D[i] = ov.pose6D[i]; Aft[i] = ov.aft[i]; Last[i] = ov.aft[i]; T[i] = ov.aft[i]; }
                 m.state[lane * 16 + 1] = nKF + 1;
                 m.state[lane * 16 + 2] = used + nC + nS + nO;
                 s_save = 1; s_off = used;
                 rec.saved = 1; rec.poolOff = used; rec.nC = nC; rec.nS = nS; rec.nO = nO;
+            }
+        } else {
+            const float dist = sqrtf((prev[0] - cx) * (prev[0] - cx) + (prev[1] - cy) * (prev[1] - cy) + (prev[2] - cz) * (prev[2] - cz));
+            const bool save = !((double)dist < 0.3);
+            if (save || nKF == 0) {
+                if (nKF >= m.maxKeyFrames || used + nC + nS + nO > m.poolCap) err = 1;
+                else {
+                    prev[0] = cx; prev[1] = cy; prev[2] = cz;
+                    const float* P = nKF == 0 ? T : Aft;   // first key frame is built from transformTobeMapped (1375-1382)
+                    if (nKF == 0) for (int i = 0; i < 6; ++i) Last[i] = T[i];
+                    for (int i = 0; i < 6; ++i) rec.aftRaw[i] = P[i];
+                    double roll, pitch, yaw;
+                    rzryrx_round_trip((double)P[2], (double)P[0], (double)P[1], &roll, &pitch, &yaw);
+                    const float kx = P[3], ky = P[4], kz = P[5];   // translation (z, x, y) -> thisPose3D (y, z, x) of it
+                    const float kroll = (float)pitch, kpitch = (float)yaw, kyaw = (float)roll;
+                    rec.pose6D[0] = kx; rec.pose6D[1] = ky; rec.pose6D[2] = kz; rec.pose6D[3] = kroll; rec.pose6D[4] = kpitch; rec.pose6D[5] = kyaw;
+                    if (nKF + 1 > 1) {
+                        Aft[0] = kroll; Aft[1] = kpitch; Aft[2] = kyaw; Aft[3] = kx; Aft[4] = ky; Aft[5] = kz;
+                        for (int i = 0; i < 6; ++i) { Last[i] = Aft[i]; T[i] = Aft[i]; }
+                    }
+                    m.state[lane * 16 + 1] = nKF + 1;
+                    m.state[lane * 16 + 2] = used + nC + nS + nO;
+                    s_save = 1; s_off = used;
+                    rec.saved = 1; rec.poolOff = used; rec.nC = nC; rec.nS = nS; rec.nO = nO;
+                }
             }
         }
         s_err = err;

@@ -13,14 +13,15 @@ namespace lego {
 
 __global__ void fa_init_state_kernel(FaDev f, int L);
 
-VoxelHash Engine::allocHash(int cap, float cell, const int* n, int nStride) {
+VoxelHash Engine::allocHash(int cap, float cell, const int* n, int nStride, int lanes) {
     VoxelHash h;
+    const size_t nl = lanes > 0 ? lanes : c.L;
     int H = 1024;
     while (H < 2 * cap) H <<= 1;
     h.H = H; h.cap = cap; h.invCell = 1.0f / cell; h.n = n; h.nStride = nStride;
     { const char* e = std::getenv("LEGO_VH_MIN"); h.minH = e && *e ? std::min(H, std::max(1024, std::atoi(e))) : 1024; }
-    h.keys = alloc<unsigned long long>((size_t)c.L * H); h.count = alloc<int>((size_t)c.L * H); h.start = alloc<int>((size_t)c.L * H);
-    h.slotOf = alloc<int>((size_t)c.L * cap); h.sorted = alloc<float4>((size_t)c.L * cap);
+    h.keys = alloc<unsigned long long>(nl * H); h.count = alloc<int>(nl * H); h.start = alloc<int>(nl * H);
+    h.slotOf = alloc<int>(nl * cap); h.sorted = alloc<float4>(nl * cap);
     return h;
 }
 

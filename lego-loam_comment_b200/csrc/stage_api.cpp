@@ -34,7 +34,7 @@ int read_int(Engine& e, const int* dev) {
     return v;
 }
 bool params_ok(const lego_params* p) {
-    return p && p->N_SCAN >= 2 && p->N_SCAN <= 128 && p->Horizon_SCAN >= 16 && !p->loopClosureEnableFlag;
+    return p && p->N_SCAN >= 2 && p->N_SCAN <= 128 && p->Horizon_SCAN >= 16;
 }
 
 }  // namespace
@@ -239,6 +239,7 @@ int lego_mo_process(lego_mo* h, const lego_cloud_view* corner_last, const lego_c
         put(e, e.ip.counts + 1, &nO, sizeof(int));
         put(e, e.fa.transformSum, transformSum, sizeof(float) * 6);
         e.sync();
+        e.moHost[0].timeOdometry = stamp;   // timeLaserOdometry
         e.mapOptimizationBody(std::vector<int>(1, 1));
         *processed = 1;
     }

@@ -24,6 +24,8 @@ class LegoParams(ctypes.Structure):
         ("mappingProcessInterval", ctypes.c_double),
         ("loopClosureEnableFlag", ctypes.c_int),
         ("device", ctypes.c_int),
+        ("surroundingKeyframeSearchNum", ctypes.c_int), ("historyKeyframeSearchRadius", ctypes.c_float),
+        ("historyKeyframeSearchNum", ctypes.c_int), ("historyKeyframeFitnessScore", ctypes.c_float),
     ]
 
 
@@ -48,7 +50,9 @@ SENSOR_GEOMETRY = {
 }
 
 
-def make_params(sensor="vlp16", device=0):
+def make_params(sensor="vlp16", device=0, loop_closure=False):
+    if sensor.endswith("_loop"):
+        sensor, loop_closure = sensor[:-5], True
     n, h, rx, ry, bottom, gsi, ring = _SENSORS[sensor]
     p = LegoParams()
     p.N_SCAN, p.Horizon_SCAN = n, h
@@ -67,8 +71,12 @@ def make_params(sensor="vlp16", device=0):
     p.nearestFeatureSearchSqDist = 25.0             # utility.h:125
     p.surroundingKeyframeSearchRadius = 50.0        # utility.h:129
     p.mappingProcessInterval = 0.3                  # utility.h:105
-    p.loopClosureEnableFlag = 0                     # utility.h:104
+    p.loopClosureEnableFlag = 1 if loop_closure else 0   # utility.h:104 (false as shipped)
     p.device = device
+    p.surroundingKeyframeSearchNum = 50             # utility.h:130
+    p.historyKeyframeSearchRadius = 7.0             # utility.h:132
+    p.historyKeyframeSearchNum = 25                 # utility.h:133
+    p.historyKeyframeFitnessScore = 0.3             # utility.h:134
     return p
 
 

@@ -131,3 +131,28 @@ def knn(pts, queries, k):
     idx = np.empty((len(queries), k), np.int32); d2 = np.empty((len(queries), k), np.float32)
     port().oracle_knn(pts.ctypes.data, len(pts), queries.ctypes.data, len(queries), k, idx.ctypes.data, d2.ctypes.data)
     return idx, d2
+
+
+def icp(source, target, max_dist=100.0, max_iter=100, eps_t=1e-6, eps_f=1e-6):
+    """oracle restatement of pcl::IterativeClosestPoint -> (T float32[4,4], fitness, converged, iterations)"""
+    source = np.ascontiguousarray(source, np.float32).reshape(-1, 4)
+    target = np.ascontiguousarray(target, np.float32).reshape(-1, 4)
+    lib = port()
+    lib.oracle_icp.argtypes = [ctypes.c_void_p, ctypes.c_long, ctypes.c_void_p, ctypes.c_long, ctypes.c_double, ctypes.c_int, ctypes.c_double,
+                               ctypes.c_double, ctypes.c_void_p, ctypes.POINTER(ctypes.c_double), ctypes.POINTER(ctypes.c_int), ctypes.POINTER(ctypes.c_int)]
+    T = np.zeros(16, np.float32)
+    fit, conv, it = ctypes.c_double(0), ctypes.c_int(0), ctypes.c_int(0)
+    lib.oracle_icp(source.ctypes.data, len(source), target.ctypes.data, len(target), max_dist, max_iter, eps_t, eps_f, T.ctypes.data,
+                   ctypes.byref(fit), ctypes.byref(conv), ctypes.byref(it))
+    return T.reshape(4, 4), fit.value, conv.value, it.value
+
+
+def pose_graph(poses, factors, meas, variances, steps):
+    """oracle Gauss-Newton on a Pose3 graph; see oracle/port.cpp::oracle_pose_graph for the layouts."""
+    poses = np.ascontiguousarray(poses, np.float64); factors = np.ascontiguousarray(factors, np.int32)
+    meas = np.ascontiguousarray(meas, np.float64); variances = np.ascontiguousarray(variances, np.float64)
+    out = np.zeros_like(poses)
+    lib = port()
+    lib.oracle_pose_graph.argtypes = [ctypes.c_void_p, ctypes.c_int, ctypes.c_void_p, ctypes.c_void_p, ctypes.c_void_p, ctypes.c_int, ctypes.c_int, ctypes.c_void_p]
+    lib.oracle_pose_graph(poses.ctypes.data, len(poses), factors.ctypes.data, meas.ctypes.data, variances.ctypes.data, len(factors), steps, out.ctypes.data)
+    return out

@@ -70,7 +70,7 @@ def test_argument_errors():
     p = make_params("vlp16")
     assert lib.lego_pipeline_create(None, 1, 0, ctypes.byref(h)) == -1
     assert lib.lego_pipeline_create(ctypes.byref(p), 0, 0, ctypes.byref(h)) == -1
-    p.loopClosureEnableFlag = 1
+    p.N_SCAN = 1
     assert lib.lego_pipeline_create(ctypes.byref(p), 1, 0, ctypes.byref(h)) == -1
     assert lib.lego_pipeline_destroy(None) == -1
 
