@@ -115,6 +115,12 @@ int lego_fa_destroy(lego_fa* h);
 int lego_fa_process(lego_fa* h, const lego_cloud_info_view* info, const lego_cloud_view* segmented,
                     const lego_cloud_view* outlier, double stamp, float transformSum_out[6], lego_fa_outputs* out);
 
+/* FeatureAssociation::imuHandler (featureAssociation.cpp:431-459): one sensor_msgs/Imu message (orientation quaternion
+ * x y z w, angular velocity, linear acceleration incl. gravity, all in the IMU's own axes as the reference expects them).
+ * Optional: without any call the stage runs the reference's no-IMU path (imuPointerLast == -1). */
+int lego_fa_imu(lego_fa* h, double stamp, const double orientation_xyzw[4], const double angular_velocity[3],
+                const double linear_acceleration[3]);
+
 /* ---------------------------------------------------------------- mapOptimization (scan-to-map) */
 typedef struct lego_mo lego_mo;
 int lego_mo_create(const lego_params* p, lego_mo** out);
@@ -125,6 +131,10 @@ int lego_mo_destroy(lego_mo* h);
 int lego_mo_process(lego_mo* h, const lego_cloud_view* corner_last, const lego_cloud_view* surf_last,
                     const lego_cloud_view* outlier_last, const float transformSum[6], double stamp,
                     float transformAftMapped_out[6], float transformBefMapped_out[6], int* processed);
+
+/* mapOptimization::imuHandler (mapOptmization.cpp:643-652): roll / pitch for the 0.998 / 0.002 blend of transformUpdate */
+int lego_mo_imu(lego_mo* h, double stamp, const double orientation_xyzw[4], const double angular_velocity[3],
+                const double linear_acceleration[3]);
 
 /* ---------------------------------------------------------------- TransformFusion node (transformFusion.cpp)
  * The fourth node: re-bases every odometry pose on the latest mapping correction (/integrated_to_init).
@@ -152,6 +162,11 @@ int lego_pipeline_destroy(lego_pipeline* h);
  * read with lego_pipeline_download: "transformMapped" 6 floats, "integratedToInit" 7 floats, per lane). */
 int lego_pipeline_step(lego_pipeline* h, const float* xyzi, const uint16_t* ring, const int* npts,
                        int stride_points, const double* stamps, int src_on_device, int stage_mask);
+/* One /imu/data message for one lane: delivered to that lane's FeatureAssociation and mapOptimization imuHandler
+ * (featureAssociation.cpp:431-459, mapOptmization.cpp:643-652).  Call it before the lego_pipeline_step of the scan during
+ * which the message would have arrived (the reference's subscribers fill the ring buffer between two scans). */
+int lego_pipeline_imu(lego_pipeline* h, int lane, double stamp, const double orientation_xyzw[4], const double angular_velocity[3],
+                      const double linear_acceleration[3]);
 /* poses_out: lanes * 18 floats = transformSum | transformAftMapped | transformBefMapped; flags_out: lanes ints,
  * bit1 odometry ran, bit2 clouds forwarded to mapping, bit3 mapping body ran.  Synchronises the handle's stream. */
 int lego_pipeline_get_poses(lego_pipeline* h, float* poses_out, int* flags_out);
@@ -209,6 +224,8 @@ int lego_pg_estimate(lego_pg* h, int key, double xyz_rpy_out[6]);
 /* ---------------------------------------------------------------- device self-tests (parity suite) */
 /* out[i] = the device implementation of glibc's atan2f(y[i], x[i]) (csrc/parity_math.cuh); host pointers. */
 int lego_selftest_atan2f(const float* y, const float* x, float* out, long n);
+/* sin_out[i], cos_out[i] = the device statement of glibc's sinf / cosf (csrc/parity_math.cuh); host pointers. */
+int lego_selftest_sincosf(const float* x, float* sin_out, float* cos_out, long n);
 /* Sorts nseg independent segments (offsets has nseg+1 entries) on the device with the replayed libstdc++
  * std::sort (csrc/std_sort_replay.cuh); inds_out receives, per segment, the original positions in sorted order. */
 int lego_selftest_std_sort(const float* values, const int* offsets, int nseg, int* inds_out);

@@ -21,7 +21,7 @@ EXPORTED = [
     "lego_pipeline_timer_record", "lego_pipeline_timer_elapsed", "lego_pipeline_timer_elapsed_between", "lego_pipeline_profile", "lego_pipeline_profile_read",
     "lego_tf_create", "lego_tf_destroy", "lego_tf_laser_odometry", "lego_tf_aft_mapped",
     "lego_selftest_atan2f", "lego_selftest_std_sort", "lego_selftest_warp_sort", "lego_selftest_voxel_grid",
-    "lego_icp_align",
+    "lego_selftest_sincosf", "lego_icp_align", "lego_pipeline_imu", "lego_fa_imu", "lego_mo_imu",
     "lego_pg_create", "lego_pg_destroy", "lego_pg_add_prior", "lego_pg_add_between", "lego_pg_insert", "lego_pg_update", "lego_pg_size", "lego_pg_estimate",
 ]
 
@@ -81,6 +81,15 @@ def selftest_atan2f(y, x):
     lib.lego_selftest_atan2f.argtypes = [ctypes.c_void_p, ctypes.c_void_p, ctypes.c_void_p, ctypes.c_long]
     _check(lib.lego_selftest_atan2f(y.ctypes.data, x.ctypes.data, out.ctypes.data, y.size), "lego_selftest_atan2f")
     return out
+
+
+def selftest_sincosf(x):
+    x = np.ascontiguousarray(x, np.float32)
+    s = np.empty_like(x); c = np.empty_like(x)
+    lib = load()
+    lib.lego_selftest_sincosf.argtypes = [ctypes.c_void_p, ctypes.c_void_p, ctypes.c_void_p, ctypes.c_long]
+    _check(lib.lego_selftest_sincosf(x.ctypes.data, s.ctypes.data, c.ctypes.data, x.size), "lego_selftest_sincosf")
+    return s, c
 
 
 def selftest_std_sort(values, offsets):
@@ -150,6 +159,14 @@ class Pipeline:
             xp, rp = xyzi.ctypes.data, (None if ring is None else ring.ctypes.data)
         _check(self.lib.lego_pipeline_step(self.h, xp, rp, npts.ctypes.data, int(stride_points), stamps.ctypes.data,
                                            1 if on_device else 0, stage_mask), "lego_pipeline_step")
+
+    def imu(self, lane, stamp, orientation_xyzw, angular_velocity, linear_acceleration):
+        """one sensor_msgs/Imu message for one lane (lego_pipeline_imu)"""
+        f = self.lib.lego_pipeline_imu
+        f.argtypes = [ctypes.c_void_p, ctypes.c_int, ctypes.c_double, ctypes.c_void_p, ctypes.c_void_p, ctypes.c_void_p]
+        q = np.ascontiguousarray(orientation_xyzw, np.float64); w = np.ascontiguousarray(angular_velocity, np.float64)
+        a = np.ascontiguousarray(linear_acceleration, np.float64)
+        _check(f(self.h, lane, float(stamp), q.ctypes.data, w.ctypes.data, a.ctypes.data), "lego_pipeline_imu")
 
     def sync(self):
         _check(self.lib.lego_pipeline_sync(self.h), "lego_pipeline_sync")
@@ -227,7 +244,7 @@ class Pipeline:
 _FLOAT_NAMES = {"rangeMat", "segRange", "orientation", "cloudCurvature", "transformCur", "transformSum", "slot4val",
                 "matP", "moTransformSum", "transformTobeMapped", "transformAftMapped", "transformBefMapped",
                 "transformMapped", "integratedToInit", "tfTransformAftMapped", "tfTransformBefMapped",
-                "cloudKeyPoses6D", "icpTransform", "icpFitness"}
+                "cloudKeyPoses6D", "icpTransform", "icpFitness", "imuState"}
 
 
 def icp_align(source, target, max_correspondence_distance=100.0, max_iterations=100, transformation_epsilon=1e-6,

@@ -56,7 +56,7 @@ int lego_pipeline_step(lego_pipeline* h, const float* xyzi, const uint16_t* ring
         e.cloudSegmentation();
     }
     if (stage_mask & 2) {
-        e.adjustDistortionCalculateSmoothnessMarkOccluded();
+        e.adjustDistortionCalculateSmoothnessMarkOccluded(h->stamps.data());
         e.extractFeatures();
         e.updateTransformation();
         e.integrateTransformationPublishCloudsLast();
@@ -70,6 +70,11 @@ int lego_pipeline_step(lego_pipeline* h, const float* xyzi, const uint16_t* ring
     lego::cuda_check(cudaGetLastError(), "kernel launch");
     return LEGO_OK;
     LEGO_CATCH
+}
+int lego_pipeline_imu(lego_pipeline* h, int lane, double stamp, const double orientation_xyzw[4], const double angular_velocity[3],
+                      const double linear_acceleration[3]) {
+    if (!h || lane < 0 || lane >= h->e->c.L || !orientation_xyzw || !angular_velocity || !linear_acceleration) return LEGO_ERR_ARG;
+    LEGO_TRY h->e->imuHandler(lane, stamp, orientation_xyzw, angular_velocity, linear_acceleration); return LEGO_OK; LEGO_CATCH
 }
 int lego_pipeline_sync(lego_pipeline* h) {
     if (!h) return LEGO_ERR_ARG;

@@ -53,6 +53,36 @@ struct IpDev {
     int* counts;               // [L][8]   0: S (segmented size) 1: O (outliers) 2: number of valid segments
 };
 
+// ---- IMU (featureAssociation.cpp:317-459, 525-614, 1639-1664; optional: active once a lane received a message) ----
+constexpr int IMU_QUE = 200;          // imuQueLength (utility.h:109)
+constexpr int IMU_CH = 12;            // roll pitch yaw | velo xyz | shift xyz | angular rotation xyz
+enum ImuState {                       // FaImuDev::state[lane][IMU_STATE]
+    IS_ROLL_START = 0, IS_PITCH_START, IS_YAW_START, IS_VELO_START, IS_SHIFT_START = 6,
+    IS_COS_ROLL = 9, IS_COS_PITCH, IS_COS_YAW, IS_SIN_ROLL, IS_SIN_PITCH, IS_SIN_YAW,
+    IS_ANG_LAST = 15, IS_ANG_FROM_START = 18, IS_RPY_CUR = 21, IS_VELO_FROM_START_CUR = 24, IS_RPY_LAST = 27, IS_VELO_FROM_START = 30,
+    IMU_STATE = 36
+};
+struct FaImuDev {
+    double* time;              // [L][IMU_QUE] imuTime
+    float* ring;               // [L][IMU_QUE][IMU_CH]
+    int* ptr;                  // [L][2] imuPointerLast (-1 = no IMU), imuPointerLastIteration
+    double* scanTime;          // [L] timeScanCur
+    float* state;              // [L][IMU_STATE]
+};
+// host side of one lane's imuHandler (featureAssociation.cpp:431-459, mapOptmization.cpp:643-652)
+struct ImuLaneHost {
+    // FeatureAssociation's ring buffers
+    int pointerLast = -1, pointerLastIteration = 0;
+    double time[IMU_QUE] = {};
+    float roll[IMU_QUE] = {}, pitch[IMU_QUE] = {}, yaw[IMU_QUE] = {};
+    float acc[3][IMU_QUE] = {}, velo[3][IMU_QUE] = {}, shift[3][IMU_QUE] = {}, angVelo[3][IMU_QUE] = {}, angRot[3][IMU_QUE] = {};
+    bool dirty = false;
+    // mapOptimization's own buffers
+    int moPointerLast = -1, moPointerFront = 0;
+    double moTime[IMU_QUE] = {};
+    float moRoll[IMU_QUE] = {}, moPitch[IMU_QUE] = {};
+};
+
 // ---- FeatureAssociation device arrays ----
 struct FaDev {
     float4* segAdj;            // [L][N]   segmented cloud after adjustDistortion (camera axes)
@@ -83,6 +113,7 @@ struct FaDev {
     float4* outlierLast;       // [L][Ocap]
     int* flags;                // [L]      bit1 odometry ran, bit2 clouds forwarded
     VoxelHash hashCorner, hashSurf;   // 1 m voxel hash over the current "last" clouds (replaces the two kd-trees)
+    FaImuDev imu;
 };
 
 // ---- TransformFusion (transformFusion.cpp) ----
@@ -160,6 +191,7 @@ struct MoDev {
     VoxelHash hashCornerMap, hashSurfMap;
     MoRecord* records;         // [L]
     MoOverride* overrides;     // [L]
+    float* imuBlend;           // [L][4] transformUpdate's IMU blend (mapOptmization.cpp:465-490): active, imuRollLast, imuPitchLast
     double* partials;          // [L][resBlocks][8][28] per-warp partial sums of AtA / AtB / row count
     int resBlocks;             // CTAs per lane in mo_residual_kernel
     int poolCap, maxSel, cornerRawCap, surfRawCap, cornerDSCap, surfDSCap, scanCornerCap, scanSurfCap, scanOutlierCap, maxKeyFrames;
@@ -208,7 +240,7 @@ public:
     void cloudSegmentation();
     void finalizeLabelMat();      // numeric labels for every cell (only needed for parity / visualisation)
     // ---- FeatureAssociation (names follow featureAssociation.cpp) ----
-    void adjustDistortionCalculateSmoothnessMarkOccluded();
+    void adjustDistortionCalculateSmoothnessMarkOccluded(const double* stamps = nullptr);   // stamps: timeScanCur per lane (IMU path)
     void extractFeatures();
     void updateTransformation();
     void integrateTransformationPublishCloudsLast();
@@ -223,6 +255,12 @@ public:
     bool lookupMapOptimization(int lane, const std::string& name, void** ptr, int* elem, long* count);
     void consumeMapRecords();                        // host bookkeeping of saveKeyFramesAndFactor from the device records
     void selectSurroundingKeyFrames(int lane, std::vector<MoKfEntry>& out, int* nCorner, int* nSurf);
+    // ---- IMU ----
+    void imuHandler(int lane, double stamp, const double q_xyzw[4], const double angular_velocity[3], const double linear_acceleration[3]);
+    void uploadImu(const double* stamps);            // ring buffers of the lanes that received messages since the last scan
+    void mapOptimizationImuBlend(const std::vector<int>& active);
+    std::vector<ImuLaneHost> imuHost;
+    bool anyImu = false;
     // ---- loop closure (names follow mapOptmization.cpp) ----
     bool loopMode() const { return params.loopClosureEnableFlag != 0; }
     void allocLoopClosure();

@@ -416,10 +416,16 @@ __global__ void __launch_bounds__(128) fa_gather_features_kernel(FaDev f, Consts
 // Kernels defined in feature_association.cu
 __global__ void fa_prepare_kernel(IpDev d, FaDev f, Consts c);
 __global__ void fa_distort_kernel(IpDev d, FaDev f, Consts c);
+__global__ void fa_imu_start_kernel(IpDev d, FaDev f, Consts c);
 
-void Engine::adjustDistortionCalculateSmoothnessMarkOccluded() {
+void Engine::adjustDistortionCalculateSmoothnessMarkOccluded(const double* stamps) {
     cuda_check(cudaMemsetAsync(fa.halfFirst, 0x7F, sizeof(int) * c.L, stream), "memset halfFirst");
     dim3 g((c.N + 255) / 256, c.L);
+    if (anyImu && stamps) {
+        uploadImu(stamps);
+        ProfScope ps(this, "fa_imu_start_kernel"); fa_imu_start_kernel<<<(c.L + 63) / 64, 64, 0, stream>>>(ip, fa, c);
+        launches += 1;
+    }
     { ProfScope ps(this, "fa_prepare_kernel"); fa_prepare_kernel<<<g, 256, 0, stream>>>(ip, fa, c); }
     { ProfScope ps(this, "fa_distort_kernel"); fa_distort_kernel<<<g, 256, 0, stream>>>(ip, fa, c); }
     launches += 3;

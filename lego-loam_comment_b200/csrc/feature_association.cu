@@ -4,6 +4,7 @@
 #include <cfloat>
 #include <climits>
 #include "engine.h"
+#include "imu_kernels.cuh"
 #include "kernel_utils.cuh"
 #include "parity_math.cuh"
 #include "std_sort_replay.cuh"
@@ -26,6 +27,16 @@ void Engine::allocFeatureAssociation() {
     fa.sharp = alloc<float4>(L * R * 12); fa.lessSharp = alloc<float4>(L * R * 120);
     fa.flat = alloc<float4>(L * R * 24); fa.lessFlat = alloc<float4>(L * N);
     fa.featCounts = alloc<int>(L * 4);
+    fa.imu.time = alloc<double>(L * IMU_QUE); fa.imu.ring = alloc<float>(L * IMU_QUE * IMU_CH);
+    fa.imu.ptr = alloc<int>(L * 2); fa.imu.scanTime = alloc<double>(L); fa.imu.state = alloc<float>(L * IMU_STATE);
+    {   // imuPointerLast = -1 (featureAssociation.cpp:251); cos(0) = 1 for the start angles (updateImuRollPitchYawStartSinCos
+        // has not run yet in the reference either, where these members are zero-initialised: sin = cos = 0 -- but they are
+        // only ever read after an IMU message arrived, so the value before that is immaterial)
+        std::vector<int> ptr(L * 2, 0);
+        for (size_t l = 0; l < L; ++l) ptr[2 * l] = -1;
+        cuda_check(cudaMemcpyAsync(fa.imu.ptr, ptr.data(), sizeof(int) * ptr.size(), cudaMemcpyHostToDevice, stream), "imu ptr init");
+        cuda_check(cudaStreamSynchronize(stream), "imu ptr init sync");
+    }
     allocOdometry();
 }
 
@@ -50,6 +61,7 @@ bool Engine::lookupFeatureAssociation(int lane, const std::string& n, void** ptr
     if (n == "surfPointsFlat") return set(fa.flat + l * R * 24, 16, cnt_of(fa.featCounts, 4, 2));
     if (n == "surfPointsLessFlat") return set(fa.lessFlat + l * N, 16, cnt_of(fa.featCounts, 4, 3));
     if (n == "featCounts") return set(fa.featCounts + l * 4, 4, 4);
+    if (n == "imuState") return set(fa.imu.state + l * IMU_STATE, 4, IMU_STATE);
     return lookupOdometry(lane, n, ptr, elem, count);
 }
 
@@ -120,7 +132,32 @@ __global__ void __launch_bounds__(256) fa_prepare_kernel(IpDev d, FaDev f, Const
     if (trig) atomicMin(f.halfFirst + lane, i);
 }
 
-// adjustDistortion without IMU (featureAssociation.cpp:491-523, 615): axis swap and intensity = ring + 0.1*relTime.
+// The i == 0 branch of adjustDistortion's IMU block (featureAssociation.cpp:570-610), one thread per lane: the IMU state at
+// the first point of the sweep becomes the "start" state, and the integrated angular rotation since the previous sweep's
+// start becomes imuAngularFromStart (the rotation prior of updateInitialGuess).
+__global__ void fa_imu_start_kernel(IpDev d, FaDev f, Consts c) {
+    const int lane = blockIdx.x * blockDim.x + threadIdx.x;
+    if (lane >= c.L || f.imu.ptr[lane * 2] < 0 || d.counts[lane * 8 + 0] < 1) return;
+    const size_t base = (size_t)lane * c.N;
+    const float so = d.orient[lane * 4 + 0], od = d.orient[lane * 4 + 2];
+    bool trig;
+    const float ori = ori_branch_a(d.segCloud[base], so, &trig);
+    const float relTime = PM_DIV(PM_SUB(ori, so), od);
+    const float pointTime = PM_MUL(relTime, c.scanPeriod);
+    const ImuSample s = imu_interpolate(f.imu, lane, f.imu.scanTime[lane], pointTime);
+    float* st = f.imu.state + lane * IMU_STATE;
+    for (int k = 0; k < 3; ++k) {
+        st[IS_ROLL_START + k] = s.rpy[k]; st[IS_VELO_START + k] = s.velo[k]; st[IS_SHIFT_START + k] = s.shift[k];
+        st[IS_RPY_CUR + k] = s.rpy[k];
+        st[IS_ANG_FROM_START + k] = s.ang[k] - st[IS_ANG_LAST + k];
+        st[IS_ANG_LAST + k] = s.ang[k];
+    }
+    st[IS_COS_ROLL] = pm::cosf_glibc(s.rpy[0]); st[IS_COS_PITCH] = pm::cosf_glibc(s.rpy[1]); st[IS_COS_YAW] = pm::cosf_glibc(s.rpy[2]);
+    st[IS_SIN_ROLL] = pm::sinf_glibc(s.rpy[0]); st[IS_SIN_PITCH] = pm::sinf_glibc(s.rpy[1]); st[IS_SIN_YAW] = pm::sinf_glibc(s.rpy[2]);
+}
+
+// adjustDistortion (featureAssociation.cpp:491-619): axis swap and intensity = ring + 0.1*relTime; with IMU data also the
+// per-point de-skew TransformToStartIMU (the last point leaves its interpolated IMU state behind, as the loop does).
 __global__ void __launch_bounds__(256) fa_distort_kernel(IpDev d, FaDev f, Consts c) {
     const int lane = blockIdx.y;
     const int i = blockIdx.x * blockDim.x + threadIdx.x;
@@ -133,7 +170,18 @@ __global__ void __launch_bounds__(256) fa_distort_kernel(IpDev d, FaDev f, Const
     float ori = (i <= f.halfFirst[lane]) ? ori_branch_a(p, so, &trig) : ori_branch_b(p, eo);
     const float relTime = PM_DIV(PM_SUB(ori, so), od);
     const float inten = PM_ADD((float)(int)p.w, PM_MUL(c.scanPeriod, relTime));
-    f.segAdj[base + i] = make_float4(p.y, p.z, p.x, inten);
+    float px = p.y, py = p.z, pz = p.x;
+    if (f.imu.ptr[lane * 2] >= 0 && i > 0) {
+        const float pointTime = PM_MUL(relTime, c.scanPeriod);
+        const ImuSample s = imu_interpolate(f.imu, lane, f.imu.scanTime[lane], pointTime);
+        float* st = f.imu.state + lane * IMU_STATE;
+        imu_transform_to_start(st, s.rpy, px, py, pz);
+        if (i == S - 1) {
+            float v[3]; imu_velo_to_start(st, s.velo, v);
+            for (int k = 0; k < 3; ++k) { st[IS_RPY_CUR + k] = s.rpy[k]; st[IS_VELO_FROM_START_CUR + k] = v[k]; }
+        }
+    }
+    f.segAdj[base + i] = make_float4(px, py, pz, inten);
 }
 
 }  // namespace lego

@@ -68,6 +68,7 @@ void Engine::allocMapOptimization() {
     mo.hashCornerMap = allocHash(mo.cornerDSCap, 1.0f, mo.mapCounts + 2, 4); mo.hashSurfMap = allocHash(mo.surfDSCap, 1.0f, mo.mapCounts + 3, 4);
     mo.records = alloc<MoRecord>(L);
     mo.overrides = alloc<MoOverride>(L);
+    mo.imuBlend = alloc<float>(L * 4);
     mo.resBlocks = (mo.scanCornerCap + mo.scanSurfCap + mo.scanOutlierCap + 255) / 256;
     mo.partials = alloc<double>(L * mo.resBlocks * 8 * 28);   // per 32-query warp slice
     moHost.assign(c.L, MoLaneHost());
@@ -336,6 +337,7 @@ void Engine::mapOptimizationBody(const std::vector<int>& active) {
     cuda_check(cudaMemcpyAsync(mo.mapCounts, hInts + 2 * c.L, sizeof(int) * 4 * c.L, cudaMemcpyHostToDevice, stream), "mapCounts");
     cuda_check(cudaEventRecord(moStaged[slot], stream), "event record");
 
+    mapOptimizationImuBlend(active);
     // ---- the mapping body ----
     { ProfScope ps(this, "mo_begin_kernel"); mo_begin_kernel<<<(c.L + 63) / 64, 64, 0, stream>>>(fa, mo, c.L); }
     if (maxEntries > 0) {

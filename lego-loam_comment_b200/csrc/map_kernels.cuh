@@ -45,22 +45,22 @@ __device__ inline void odometry_message_round_trip(const float* S, float* out) {
 
 // transformAssociateToMap (mapOptmization.cpp:376-461), term by term.
 __device__ inline void transform_associate_to_map(const float* Sum, const float* Bef, const float* Aft, float* Incre, float* T) {
-    float x1 = cosf(Sum[1]) * (Bef[3] - Sum[3]) - sinf(Sum[1]) * (Bef[5] - Sum[5]);
+    float x1 = pm::cosf_glibc(Sum[1]) * (Bef[3] - Sum[3]) - pm::sinf_glibc(Sum[1]) * (Bef[5] - Sum[5]);
     float y1 = Bef[4] - Sum[4];
-    float z1 = sinf(Sum[1]) * (Bef[3] - Sum[3]) + cosf(Sum[1]) * (Bef[5] - Sum[5]);
+    float z1 = pm::sinf_glibc(Sum[1]) * (Bef[3] - Sum[3]) + pm::cosf_glibc(Sum[1]) * (Bef[5] - Sum[5]);
     float x2 = x1;
-    float y2 = cosf(Sum[0]) * y1 + sinf(Sum[0]) * z1;
-    float z2 = -sinf(Sum[0]) * y1 + cosf(Sum[0]) * z1;
-    Incre[3] = cosf(Sum[2]) * x2 + sinf(Sum[2]) * y2;
-    Incre[4] = -sinf(Sum[2]) * x2 + cosf(Sum[2]) * y2;
+    float y2 = pm::cosf_glibc(Sum[0]) * y1 + pm::sinf_glibc(Sum[0]) * z1;
+    float z2 = -pm::sinf_glibc(Sum[0]) * y1 + pm::cosf_glibc(Sum[0]) * z1;
+    Incre[3] = pm::cosf_glibc(Sum[2]) * x2 + pm::sinf_glibc(Sum[2]) * y2;
+    Incre[4] = -pm::sinf_glibc(Sum[2]) * x2 + pm::cosf_glibc(Sum[2]) * y2;
     Incre[5] = z2;
-    const float sbcx = sinf(Sum[0]), cbcx = cosf(Sum[0]), sbcy = sinf(Sum[1]), cbcy = cosf(Sum[1]), sbcz = sinf(Sum[2]), cbcz = cosf(Sum[2]);
-    const float sblx = sinf(Bef[0]), cblx = cosf(Bef[0]), sbly = sinf(Bef[1]), cbly = cosf(Bef[1]), sblz = sinf(Bef[2]), cblz = cosf(Bef[2]);
-    const float salx = sinf(Aft[0]), calx = cosf(Aft[0]), saly = sinf(Aft[1]), caly = cosf(Aft[1]), salz = sinf(Aft[2]), calz = cosf(Aft[2]);
+    const float sbcx = pm::sinf_glibc(Sum[0]), cbcx = pm::cosf_glibc(Sum[0]), sbcy = pm::sinf_glibc(Sum[1]), cbcy = pm::cosf_glibc(Sum[1]), sbcz = pm::sinf_glibc(Sum[2]), cbcz = pm::cosf_glibc(Sum[2]);
+    const float sblx = pm::sinf_glibc(Bef[0]), cblx = pm::cosf_glibc(Bef[0]), sbly = pm::sinf_glibc(Bef[1]), cbly = pm::cosf_glibc(Bef[1]), sblz = pm::sinf_glibc(Bef[2]), cblz = pm::cosf_glibc(Bef[2]);
+    const float salx = pm::sinf_glibc(Aft[0]), calx = pm::cosf_glibc(Aft[0]), saly = pm::sinf_glibc(Aft[1]), caly = pm::cosf_glibc(Aft[1]), salz = pm::sinf_glibc(Aft[2]), calz = pm::cosf_glibc(Aft[2]);
     const float srx = -sbcx * (salx * sblx + calx * cblx * salz * sblz + calx * calz * cblx * cblz)
                       - cbcx * sbcy * (calx * calz * (cbly * sblz - cblz * sblx * sbly) - calx * salz * (cbly * cblz + sblx * sbly * sblz) + cblx * salx * sbly)
                       - cbcx * cbcy * (calx * salz * (cblz * sbly - cbly * sblx * sblz) - calx * calz * (sbly * sblz + cbly * cblz * sblx) + cblx * cbly * salx);
-    T[0] = -asinf(srx);
+    T[0] = -pm::asinf_glibc(srx);
     const float srycrx = sbcx * (cblx * cblz * (caly * salz - calz * salx * saly) - cblx * sblz * (caly * calz + salx * saly * salz) + calx * saly * sblx)
                          - cbcx * cbcy * ((caly * calz + salx * saly * salz) * (cblz * sbly - cbly * sblx * sblz)
                                           + (caly * salz - calz * salx * saly) * (sbly * sblz + cbly * cblz * sblx) - calx * cblx * cbly * saly)
@@ -71,30 +71,30 @@ __device__ inline void transform_associate_to_map(const float* Sum, const float*
                                           + (calz * saly - caly * salx * salz) * (cblz * sbly - cbly * sblx * sblz) + calx * caly * cblx * cbly)
                          - cbcx * sbcy * ((saly * salz + caly * calz * salx) * (cbly * sblz - cblz * sblx * sbly)
                                           + (calz * saly - caly * salx * salz) * (cbly * cblz + sblx * sbly * sblz) - calx * caly * cblx * sbly);
-    T[1] = pm::atan2f_glibc(srycrx / cosf(T[0]), crycrx / cosf(T[0]));
+    T[1] = pm::atan2f_glibc(srycrx / pm::cosf_glibc(T[0]), crycrx / pm::cosf_glibc(T[0]));
     const float srzcrx = (cbcz * sbcy - cbcy * sbcx * sbcz) * (calx * salz * (cblz * sbly - cbly * sblx * sblz) - calx * calz * (sbly * sblz + cbly * cblz * sblx) + cblx * cbly * salx)
                          - (cbcy * cbcz + sbcx * sbcy * sbcz) * (calx * calz * (cbly * sblz - cblz * sblx * sbly) - calx * salz * (cbly * cblz + sblx * sbly * sblz) + cblx * salx * sbly)
                          + cbcx * sbcz * (salx * sblx + calx * cblx * salz * sblz + calx * calz * cblx * cblz);
     const float crzcrx = (cbcy * sbcz - cbcz * sbcx * sbcy) * (calx * calz * (cbly * sblz - cblz * sblx * sbly) - calx * salz * (cbly * cblz + sblx * sbly * sblz) + cblx * salx * sbly)
                          - (sbcy * sbcz + cbcy * cbcz * sbcx) * (calx * salz * (cblz * sbly - cbly * sblx * sblz) - calx * calz * (sbly * sblz + cbly * cblz * sblx) + cblx * cbly * salx)
                          + cbcx * cbcz * (salx * sblx + calx * cblx * salz * sblz + calx * calz * cblx * cblz);
-    T[2] = pm::atan2f_glibc(srzcrx / cosf(T[0]), crzcrx / cosf(T[0]));
-    x1 = cosf(T[2]) * Incre[3] - sinf(T[2]) * Incre[4];
-    y1 = sinf(T[2]) * Incre[3] + cosf(T[2]) * Incre[4];
+    T[2] = pm::atan2f_glibc(srzcrx / pm::cosf_glibc(T[0]), crzcrx / pm::cosf_glibc(T[0]));
+    x1 = pm::cosf_glibc(T[2]) * Incre[3] - pm::sinf_glibc(T[2]) * Incre[4];
+    y1 = pm::sinf_glibc(T[2]) * Incre[3] + pm::cosf_glibc(T[2]) * Incre[4];
     z1 = Incre[5];
     x2 = x1;
-    y2 = cosf(T[0]) * y1 - sinf(T[0]) * z1;
-    z2 = sinf(T[0]) * y1 + cosf(T[0]) * z1;
-    T[3] = Aft[3] - (cosf(T[1]) * x2 + sinf(T[1]) * z2);
+    y2 = pm::cosf_glibc(T[0]) * y1 - pm::sinf_glibc(T[0]) * z1;
+    z2 = pm::sinf_glibc(T[0]) * y1 + pm::cosf_glibc(T[0]) * z1;
+    T[3] = Aft[3] - (pm::cosf_glibc(T[1]) * x2 + pm::sinf_glibc(T[1]) * z2);
     T[4] = Aft[4] - y2;
-    T[5] = Aft[5] - (-sinf(T[1]) * x2 + cosf(T[1]) * z2);
+    T[5] = Aft[5] - (-pm::sinf_glibc(T[1]) * x2 + pm::cosf_glibc(T[1]) * z2);
 }
 
 struct MapSinCos { float cRoll, sRoll, cPitch, sPitch, cYaw, sYaw, tX, tY, tZ; };
 // updatePointAssociateToMapSinCos (mapOptmization.cpp:498-511)
 __device__ __forceinline__ MapSinCos map_sincos(const float* T) {
     MapSinCos m;
-    m.cRoll = cosf(T[0]); m.sRoll = sinf(T[0]); m.cPitch = cosf(T[1]); m.sPitch = sinf(T[1]); m.cYaw = cosf(T[2]); m.sYaw = sinf(T[2]);
+    m.cRoll = pm::cosf_glibc(T[0]); m.sRoll = pm::sinf_glibc(T[0]); m.cPitch = pm::cosf_glibc(T[1]); m.sPitch = pm::sinf_glibc(T[1]); m.cYaw = pm::cosf_glibc(T[2]); m.sYaw = pm::sinf_glibc(T[2]);
     m.tX = T[3]; m.tY = T[4]; m.tZ = T[5];
     return m;
 }

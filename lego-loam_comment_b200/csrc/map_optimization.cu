@@ -249,7 +249,12 @@ __global__ void __launch_bounds__(32) mo_solve_kernel(MoDev m, int iter) {
     if (done || iter == 9) {
         m.state[lane * 16 + 6] = 0;
         m.records[lane].iters = iter + 1;
-        // transformUpdate without IMU (mapOptmization.cpp:463-496)
+        // transformUpdate (mapOptmization.cpp:463-496); the host interpolated the IMU roll / pitch at the end of the sweep
+        const float* bl = m.imuBlend + lane * 4;
+        if (bl[0] != 0.f) {
+            T[0] = (float)(0.998 * (double)T[0] + 0.002 * (double)bl[2]);
+            T[2] = (float)(0.998 * (double)T[2] + 0.002 * (double)bl[1]);
+        }
         for (int i = 0; i < 6; ++i) { m.transformBefMapped[lane * 6 + i] = m.transformSum[lane * 6 + i]; m.transformAftMapped[lane * 6 + i] = T[i]; }
     }
 }

@@ -6,6 +6,7 @@
 #include <cfloat>
 #include <cstdlib>
 #include "engine.h"
+#include "imu_kernels.cuh"
 #include "kernel_utils.cuh"
 #include "odometry_kernels.cuh"
 
@@ -101,10 +102,13 @@ __global__ void __launch_bounds__(256) fa_clouds_last_kernel(IpDev d, FaDev f, C
     for (int k = 0; k < 6; ++k) T[k] = f.transformCur[lane * 6 + k];
     const int nC = f.featCounts[lane * 4 + 1], nS = f.featCounts[lane * 4 + 3], nO = d.counts[lane * 8 + 1];
     const int t0 = blockIdx.x * blockDim.x + threadIdx.x, stride = gridDim.x * blockDim.x;
+    const bool imu = f.imu.ptr[lane * 2] >= 0;   // the IMU tail of TransformToEnd is the identity without IMU data
+    const float* st = f.imu.state + lane * IMU_STATE;
+    auto to_end = [&](float4 p) { const float4 q = pose::transform_to_end(p, T); return imu ? imu_transform_to_end_tail(st, q) : q; };
     const float4* ls = f.lessSharp + lane * R * 120; float4* cl = f.cornerLast[nb] + lane * R * 120;
-    for (int i = t0; i < nC; i += stride) { const float4 p = ls[i]; cl[i] = inited ? pose::transform_to_end(p, T) : p; }
+    for (int i = t0; i < nC; i += stride) { const float4 p = ls[i]; cl[i] = inited ? to_end(p) : p; }
     const float4* lf = f.lessFlat + lane * N; float4* sl = f.surfLast[nb] + lane * N;
-    for (int i = t0; i < nS; i += stride) { const float4 p = lf[i]; sl[i] = inited ? pose::transform_to_end(p, T) : p; }
+    for (int i = t0; i < nS; i += stride) { const float4 p = lf[i]; sl[i] = inited ? to_end(p) : p; }
     const float4* oc = d.outlier + (size_t)lane * c.Ocap; float4* ol = f.outlierLast + (size_t)lane * c.Ocap;
     for (int i = t0; i < nO; i += stride) { const float4 p = oc[i]; ol[i] = make_float4(p.y, p.z, p.x, p.w); }
 }
@@ -115,13 +119,19 @@ __global__ void fa_finish_scan_kernel(IpDev d, FaDev f, Consts c) {
     const int lane = blockIdx.x * blockDim.x + threadIdx.x;
     if (lane >= c.L) return;
     int flags = 1;
+    const float* st = f.imu.state + lane * IMU_STATE;
     if (!f.lmState[lane * 8 + 0]) {
         f.lmState[lane * 8 + 0] = 1;
         flags |= 16;   // corner/surf "last" clouds are published once at initialisation, without odometry
+        // checkSystemInitialization (featureAssociation.cpp:1632-1633); both are 0 without IMU data
+        f.transformSum[lane * 6 + 0] += st[IS_PITCH_START];
+        f.transformSum[lane * 6 + 2] += st[IS_ROLL_START];
     } else {
         float S[6], T[6];
         for (int k = 0; k < 6; ++k) { S[k] = f.transformSum[lane * 6 + k]; T[k] = f.transformCur[lane * 6 + k]; }
-        pose::integrate_transformation(S, T);
+        // PluginIMURotation(rx, ry, rz, imuPitchStart, imuYawStart, imuRollStart, imuPitchLast, imuYawLast, imuRollLast, ...)
+        const float imuRot[6] = {st[IS_PITCH_START], st[IS_YAW_START], st[IS_ROLL_START], st[IS_RPY_LAST + 1], st[IS_RPY_LAST + 2], st[IS_RPY_LAST + 0]};
+        pose::integrate_transformation(S, T, imuRot);
         for (int k = 0; k < 6; ++k) f.transformSum[lane * 6 + k] = S[k];
         flags |= 2;
         int fc = f.lastCounts[lane * 4 + 3] + 1;
@@ -138,7 +148,21 @@ __global__ void fa_init_state_kernel(FaDev f, int L) {
     if (lane < L) f.lastCounts[lane * 4 + 3] = 1;   // frameCount = skipFrameNum (featureAssociation.cpp:314)
 }
 
+// updateInitialGuess (featureAssociation.cpp:1639-1664), one thread per lane; a no-op without IMU data (everything is 0)
+__global__ void fa_imu_initial_guess_kernel(FaDev f, Consts c) {
+    const int lane = blockIdx.x * blockDim.x + threadIdx.x;
+    if (lane >= c.L || !f.lmState[lane * 8 + 0]) return;   // the first scan only runs checkSystemInitialization
+    float* st = f.imu.state + lane * IMU_STATE;
+    float* T = f.transformCur + lane * 6;
+    for (int k = 0; k < 3; ++k) { st[IS_RPY_LAST + k] = st[IS_RPY_CUR + k]; st[IS_VELO_FROM_START + k] = st[IS_VELO_FROM_START_CUR + k]; }
+    const float ax = st[IS_ANG_FROM_START], ay = st[IS_ANG_FROM_START + 1], az = st[IS_ANG_FROM_START + 2];
+    if (ax != 0 || ay != 0 || az != 0) { T[0] = -ay; T[1] = -az; T[2] = -ax; }
+    const float vx = st[IS_VELO_FROM_START], vy = st[IS_VELO_FROM_START + 1], vz = st[IS_VELO_FROM_START + 2];
+    if (vx != 0 || vy != 0 || vz != 0) { T[3] -= vx * c.scanPeriod; T[4] -= vy * c.scanPeriod; T[5] -= vz * c.scanPeriod; }
+}
+
 void Engine::updateTransformation() {
+    if (anyImu) { ProfScope ps(this, "fa_imu_initial_guess_kernel"); fa_imu_initial_guess_kernel<<<(c.L + 63) / 64, 64, 0, stream>>>(fa, c); launches += 1; }
     const size_t smem = sizeof(float4) * 24 * (size_t)c.R;
     static bool attr_set = false;
     if (!attr_set) { cuda_check(cudaFuncSetAttribute(fa_odometry_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 64 * 1024), "smem attr"); attr_set = true; }

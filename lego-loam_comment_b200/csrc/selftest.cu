@@ -38,7 +38,27 @@ __global__ void __launch_bounds__(32) selftest_warp_sort_kernel(ssr::Item* items
 
 }  // namespace lego
 
+namespace lego {
+__global__ void selftest_sincosf_kernel(const float* x, float* s, float* c, long n) {
+    const long i = (long)blockIdx.x * blockDim.x + threadIdx.x;
+    if (i < n) { s[i] = pm::sinf_glibc(x[i]); c[i] = pm::cosf_glibc(x[i]); }
+}
+}  // namespace lego
+
 extern "C" {
+
+int lego_selftest_sincosf(const float* x, float* sin_out, float* cos_out, long n) {
+    try {
+        float *dx, *ds, *dc;
+        lego::cuda_check(cudaMalloc(&dx, n * 4), "malloc"); lego::cuda_check(cudaMalloc(&ds, n * 4), "malloc"); lego::cuda_check(cudaMalloc(&dc, n * 4), "malloc");
+        cudaMemcpy(dx, x, n * 4, cudaMemcpyHostToDevice);
+        lego::selftest_sincosf_kernel<<<(unsigned)((n + 255) / 256), 256>>>(dx, ds, dc, n);
+        lego::cuda_check(cudaMemcpy(sin_out, ds, n * 4, cudaMemcpyDeviceToHost), "selftest copy");
+        lego::cuda_check(cudaMemcpy(cos_out, dc, n * 4, cudaMemcpyDeviceToHost), "selftest copy");
+        cudaFree(dx); cudaFree(ds); cudaFree(dc);
+        return LEGO_OK;
+    } catch (...) { return LEGO_ERR_CUDA; }
+}
 
 int lego_selftest_atan2f(const float* y, const float* x, float* out, long n) {
     try {

@@ -151,7 +151,8 @@ int lego_fa_destroy(lego_fa* h) {
 }
 int lego_fa_process(lego_fa* h, const lego_cloud_info_view* info, const lego_cloud_view* segmented, const lego_cloud_view* outlier,
                     double stamp, float transformSum_out[6], lego_fa_outputs* out) {
-    (void)stamp;   // the three inputs of one call belong to one scan by construction (gate of featureAssociation.cpp:1820-1829)
+    // the three inputs of one call belong to one scan by construction (gate of featureAssociation.cpp:1820-1829); the stamp
+    // is timeScanCur for the IMU interpolation of adjustDistortion
     if (!h || !info || !segmented || !outlier || !transformSum_out || !out) return LEGO_ERR_ARG;
     Engine& e = *h->e;
     const int S = segmented->count, O = outlier->count, R = e.c.R;
@@ -173,7 +174,7 @@ int lego_fa_process(lego_fa* h, const lego_cloud_info_view* info, const lego_clo
     put(e, e.ip.orient, orient, sizeof(orient));
     put(e, e.ip.counts, counts, sizeof(counts));
     e.sync();   // orient / counts live on this stack frame
-    e.adjustDistortionCalculateSmoothnessMarkOccluded();
+    e.adjustDistortionCalculateSmoothnessMarkOccluded(&stamp);
     e.extractFeatures();
     e.updateTransformation();
     e.integrateTransformationPublishCloudsLast();
@@ -215,6 +216,16 @@ int lego_mo_destroy(lego_mo* h) {
     delete h->e; delete h;
     return LEGO_OK;
 }
+// imuHandler of the two nodes (featureAssociation.cpp:431-459, mapOptmization.cpp:643-652)
+int lego_fa_imu(lego_fa* h, double stamp, const double orientation_xyzw[4], const double angular_velocity[3], const double linear_acceleration[3]) {
+    if (!h || !orientation_xyzw || !angular_velocity || !linear_acceleration) return LEGO_ERR_ARG;
+    LEGO_TRY h->e->imuHandler(0, stamp, orientation_xyzw, angular_velocity, linear_acceleration); return LEGO_OK; LEGO_CATCH
+}
+int lego_mo_imu(lego_mo* h, double stamp, const double orientation_xyzw[4], const double angular_velocity[3], const double linear_acceleration[3]) {
+    if (!h || !orientation_xyzw || !angular_velocity || !linear_acceleration) return LEGO_ERR_ARG;
+    LEGO_TRY h->e->imuHandler(0, stamp, orientation_xyzw, angular_velocity, linear_acceleration); return LEGO_OK; LEGO_CATCH
+}
+
 int lego_mo_process(lego_mo* h, const lego_cloud_view* corner_last, const lego_cloud_view* surf_last, const lego_cloud_view* outlier_last,
                     const float transformSum[6], double stamp, float transformAftMapped_out[6], float transformBefMapped_out[6], int* processed) {
     if (!h || !corner_last || !surf_last || !outlier_last || !transformSum || !transformAftMapped_out || !processed) return LEGO_ERR_ARG;

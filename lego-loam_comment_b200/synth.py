@@ -98,3 +98,41 @@ class SynthSequence:
 
     def stamp(self, k):
         return k * 0.1
+
+    # ---- synthetic /imu/data (optional IMU path, featureAssociation.cpp:431-459) ----
+    IMU_RATE = 100.0
+    IMU_OFFSET = 0.003   # keeps IMU stamps off the scan stamps
+
+    def _rot(self, t):
+        p = self.pose(t)
+        cr, sr, cp, sp, cy, sy = np.cos(p[3]), np.sin(p[3]), np.cos(p[4]), np.sin(p[4]), np.cos(p[5]), np.sin(p[5])
+        return np.array([[cy * cp, cy * sp * sr - sy * cr, cy * sp * cr + sy * sr],
+                         [sy * cp, sy * sp * sr + cy * cr, sy * sp * cr - cy * sr],
+                         [-sp, cp * sr, cp * cr]]), p
+
+    def imu_sample(self, j):
+        """j-th IMU message -> (stamp, orientation xyzw, angular velocity, linear acceleration): an ideal IMU rigidly
+        mounted on the lidar (x forward, y left, z up), orientation = world_from_body, acceleration = specific force."""
+        t = self.IMU_OFFSET + j / self.IMU_RATE
+        h = 1e-3
+        R, p = self._rot(t)
+        Rm, pm = self._rot(t - h)
+        Rp, pp = self._rot(t + h)
+        acc_w = (pp[:3] - 2 * p[:3] + pm[:3]) / (h * h)
+        f_b = R.T @ (acc_w + np.array([0.0, 0.0, 9.81]))
+        dR = Rm.T @ Rp
+        w_b = np.array([dR[2, 1] - dR[1, 2], dR[0, 2] - dR[2, 0], dR[1, 0] - dR[0, 1]]) / (4 * h)
+        hr, hp, hy = p[3] / 2, p[4] / 2, p[5] / 2
+        q = np.array([np.sin(hr) * np.cos(hp) * np.cos(hy) - np.cos(hr) * np.sin(hp) * np.sin(hy),
+                      np.cos(hr) * np.sin(hp) * np.cos(hy) + np.sin(hr) * np.cos(hp) * np.sin(hy),
+                      np.cos(hr) * np.cos(hp) * np.sin(hy) - np.sin(hr) * np.sin(hp) * np.cos(hy),
+                      np.cos(hr) * np.cos(hp) * np.cos(hy) + np.sin(hr) * np.sin(hp) * np.sin(hy)])
+        return t, q, w_b, f_b
+
+    def imu_until(self, j0, t_end):
+        """messages j0, j0+1, ... with stamp <= t_end -> (list of samples, next j)"""
+        out = []
+        j = j0
+        while self.IMU_OFFSET + j / self.IMU_RATE <= t_end:
+            out.append(self.imu_sample(j)); j += 1
+        return out, j

@@ -236,6 +236,9 @@ static int run_fa(Ref& R) {
         s.f["laserCloudCornerLast"] = flat(*fa.laserCloudCornerLast);
         s.f["laserCloudSurfLast"] = flat(*fa.laserCloudSurfLast);
         s.i["faDegenerate"] = {fa.isDegenerate ? 1 : 0};
+        s.f["imuStart"] = {fa.imuRollStart, fa.imuPitchStart, fa.imuYawStart, fa.imuVeloXStart, fa.imuVeloYStart, fa.imuVeloZStart};
+        s.f["imuLast"] = {fa.imuRollLast, fa.imuPitchLast, fa.imuYawLast, fa.imuVeloFromStartX, fa.imuVeloFromStartY, fa.imuVeloFromStartZ,
+                          fa.imuAngularFromStartX, fa.imuAngularFromStartY, fa.imuAngularFromStartZ};
     }
     if (ros::shim_count("/laser_cloud_corner_last") != before) flags |= 4;
     return flags;
@@ -280,7 +283,26 @@ static int run_mo(Ref& R, int fa_flags, long odo_before, long outl_before) {
                 s.i["surroundingExistingKeyPosesID"].assign(mo.surroundingExistingKeyPosesID.begin(), mo.surroundingExistingKeyPosesID.end());
             }
             t0 = Clock::now();
-            mo.scan2MapOptimization();          R.t[T_MO_SCAN2MAP] += ms_since(t0); t0 = Clock::now();
+            if (R.want_snap) {
+                // scan2MapOptimization (mapOptmization.cpp:1329-1350) spelled out with the reference's own methods so that the
+                // pose after every LM iteration and before transformUpdate's IMU blend can be recorded
+                std::vector<float>& tr = R.snap.f["moIterations"]; tr.clear();
+                if (mo.laserCloudCornerFromMapDSNum > 10 && mo.laserCloudSurfFromMapDSNum > 100) {
+                    mo.kdtreeCornerFromMap->setInputCloud(mo.laserCloudCornerFromMapDS);
+                    mo.kdtreeSurfFromMap->setInputCloud(mo.laserCloudSurfFromMapDS);
+                    for (int iterCount = 0; iterCount < 10; iterCount++) {
+                        mo.laserCloudOri->clear(); mo.coeffSel->clear();
+                        mo.cornerOptimization(iterCount);
+                        mo.surfOptimization(iterCount);
+                        const bool done = mo.LMOptimization(iterCount);
+                        tr.insert(tr.end(), mo.transformTobeMapped, mo.transformTobeMapped + 6);
+                        tr.push_back((float)mo.laserCloudOri->points.size());
+                        if (done) break;
+                    }
+                    mo.transformUpdate();
+                }
+            } else mo.scan2MapOptimization();
+            R.t[T_MO_SCAN2MAP] += ms_since(t0); t0 = Clock::now();
             if (R.want_snap) R.snap.f["moTransformOpt"].assign(mo.transformTobeMapped, mo.transformTobeMapped + 6);
             mo.saveKeyFramesAndFactor();        R.t[T_MO_SAVE] += ms_since(t0); t0 = Clock::now();
             mo.correctPoses();
@@ -370,6 +392,19 @@ int ref_feed_scan(void* h, const float* xyzi, const uint16_t* ring, int P, int i
         }
     }
     return out;
+}
+
+// One sensor_msgs/Imu message, delivered to the two subscribers the reference has for /imu/data
+// (featureAssociation.cpp:193, mapOptmization.cpp:242).
+void ref_feed_imu(void* h, double stamp, const double* q_xyzw, const double* w, const double* a) {
+    Ref& R = *static_cast<Ref*>(h);
+    std::shared_ptr<sensor_msgs::Imu> m = std::make_shared<sensor_msgs::Imu>();
+    m->header.stamp = ros::Time(stamp);
+    m->orientation.x = q_xyzw[0]; m->orientation.y = q_xyzw[1]; m->orientation.z = q_xyzw[2]; m->orientation.w = q_xyzw[3];
+    m->angular_velocity.x = w[0]; m->angular_velocity.y = w[1]; m->angular_velocity.z = w[2];
+    m->linear_acceleration.x = a[0]; m->linear_acceleration.y = a[1]; m->linear_acceleration.z = a[2];
+    R.fa.imuHandler(m);
+    R.mo.imuHandler(m);
 }
 
 // Copy a named snapshot (float or int32) of the last scan. Returns the element count, or -1 if unknown.

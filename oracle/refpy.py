@@ -66,6 +66,14 @@ class RefPipeline:
         return self.lib.ref_feed_scan(self.h, xyzi.ctypes.data, ring_p, int(xyzi.shape[0]), 1 if is_dense else 0,
                                       float(stamp), stages)
 
+    def imu(self, stamp, orientation_xyzw, angular_velocity, linear_acceleration):
+        """one sensor_msgs/Imu message to FeatureAssociation::imuHandler and mapOptimization::imuHandler"""
+        f = self.lib.ref_feed_imu
+        f.argtypes = [ctypes.c_void_p, ctypes.c_double, ctypes.c_void_p, ctypes.c_void_p, ctypes.c_void_p]
+        q = np.ascontiguousarray(orientation_xyzw, np.float64); w = np.ascontiguousarray(angular_velocity, np.float64)
+        a = np.ascontiguousarray(linear_acceleration, np.float64)
+        f(self.h, float(stamp), q.ctypes.data, w.ctypes.data, a.ctypes.data)
+
     def get(self, name):
         b = name.encode()
         n = self.lib.ref_get_f32(self.h, b, None, 0)

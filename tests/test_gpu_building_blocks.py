@@ -95,3 +95,23 @@ def test_device_voxel_grid_equals_oracle(leaf):
         want = refpy.voxel_grid(c, leaf)
         assert g.shape == want.shape, (len(c), g.shape, want.shape)
         assert np.array_equal(g.view(np.uint32), want.view(np.uint32)), "n=%d leaf=%g" % (len(c), leaf)
+
+
+def test_device_sincosf_is_glibc_sincosf():
+    """pm::sinf_glibc / cosf_glibc (csrc/parity_math.cuh) against the host C library, bit for bit: glibc evaluates both in
+    double (range reduction + polynomial, FMA build on x86-64), which the device repeats operation by operation."""
+    import ctypes
+    import ctypes.util
+    libm = ctypes.CDLL(ctypes.util.find_library("m"))
+    libm.sinf.restype = ctypes.c_float; libm.sinf.argtypes = [ctypes.c_float]
+    libm.cosf.restype = ctypes.c_float; libm.cosf.argtypes = [ctypes.c_float]
+    rng = np.random.default_rng(17)
+    x = np.concatenate([rng.uniform(-4, 4, 150000), rng.uniform(-119, 119, 100000), rng.uniform(-0.01, 0.01, 50000),
+                        rng.uniform(-0.8, 0.8, 100000), [0.0, -0.0, 1e-30, 0.78539816, 0.78539822, 1.5707964, 3.1415927, -3.1415927]]).astype(np.float32)
+    s, c = capi.selftest_sincosf(x)
+    ws = np.array([libm.sinf(float(v)) for v in x], np.float32)
+    wc = np.array([libm.cosf(float(v)) for v in x], np.float32)
+    bad_s = int(np.count_nonzero(s.view(np.uint32) != ws.view(np.uint32)))
+    bad_c = int(np.count_nonzero(c.view(np.uint32) != wc.view(np.uint32)))
+    # the host's libm may be the non-FMA build on a CPU without FMA: that build differs in ~2e-7 of the inputs
+    assert bad_s <= 1 and bad_c <= 1, "sinf mismatches %d, cosf mismatches %d of %d" % (bad_s, bad_c, x.size)
