@@ -84,13 +84,12 @@ def _feed(pl, ref, seq, k):
 
 
 def test_loop_closure_matches_reference():
-    """Free-running for 346 scans (both sides integrate their own state).  Over the first 120 scans the north_star bar
-    (1e-4) is asserted; beyond that the two mapping trajectories are two runs of an iteration that stops at a 5e-4 m
-    step threshold (mapOptmization.cpp:1320) and drift apart at the 1e-3 level, so the long part
-    asserts the DISCRETE behaviour exactly -- mapping cadence, key-frame count, performLoopClosure cadence, which key
-    frames are matched, ICP convergence, source cloud size, constraints accepted -- and the poses, key
-    poses after correctPoses and the ICP result within 5e-3.  The reference's own ICP inputs are additionally run
-    through lego_icp_align and must reproduce its transformation to 1e-5."""
+    """Free-running for 346 scans (both sides integrate their own state; nothing is teacher-forced).  Every pose, every key
+    pose (also after correctPoses rewrote them) and the ICP result stay within the north_star bar of 1e-4 -- on the B200
+    they are in fact bit-identical, because every sin / cos / asin / atan2 of the pose math repeats glibc's evaluation
+    (csrc/parity_math.cuh).  The discrete behaviour is asserted exactly: mapping cadence, key-frame count,
+    performLoopClosure cadence, which key frames are matched, ICP convergence, constraints accepted.  The reference's own
+    ICP inputs are additionally run through lego_icp_align and must reproduce its transformation to 1e-5."""
     import refpy
     require_ref("vlp16_loop")
     seq = SynthSequence("vlp16", seed=3, scene="room", speed=0.8, circle_radius=4.0)   # one lap = 31.4 s
@@ -102,7 +101,7 @@ def test_loop_closure_matches_reference():
     for k in range(346):
         rf, poses, flags = _feed(pl, ref, seq, k)
         tag = "scan %d: " % k
-        tol = POSE_TOL if k < 120 else 5e-3
+        tol = POSE_TOL
         assert bool(flags & 8) == bool(rf & 8), tag + "mapping gate"
         assert np.max(np.abs(poses[:6] - ref.get("transformSum"))) < POSE_TOL, tag + "transformSum"
         if not (rf & 8):
@@ -122,16 +121,14 @@ def test_loop_closure_matches_reference():
         except KeyError:
             continue
         gl = pl.download("loopClosure")
-        # called, icp ran, closed, closest, latest, converged exactly; the down-sampled history submap may gain or lose a
-        # few voxels when key poses differ in the 4th digit, and the iteration count may then move by one
-        assert list(gl[:6]) == list(wl[:6]) and gl[7] == wl[7] and abs(int(gl[6]) - int(wl[6])) <= 1 and abs(int(gl[8]) - int(wl[8])) <= 16, \
+        assert list(gl) == list(wl), \
             tag + "loop record (called, icp ran, closed, closest, latest, converged, iterations, nSrc, nTgtDS): %s vs %s" % (gl, wl)
         if wl[1]:
             icp_runs += 1
             gT, wT = pl.download("icpTransform"), ref.get("icpTransform")
-            assert np.max(np.abs(gT - wT)) < 5e-3, tag + "icp transform differs by %g" % np.max(np.abs(gT - wT))
+            assert np.max(np.abs(gT - wT)) < 1e-5, tag + "icp transform differs by %g" % np.max(np.abs(gT - wT))
             gf, wf = float(pl.download("icpFitness")[0]), float(ref.get("icpFitness")[0])
-            assert abs(gf - wf) <= 1e-2 * max(1.0, wf), tag + "fitness"
+            assert abs(gf - wf) <= 1e-5 * max(1.0, wf), tag + "fitness"
             closed += int(wl[2])
             # the reference's own ICP inputs through the device ICP: same answer to float rounding
             T2, f2, c2, i2 = capi.icp_align(ref.cloud("latestSurfKeyFrameCloud"), ref.cloud("nearHistorySurfKeyFrameCloudDS"))

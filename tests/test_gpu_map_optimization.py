@@ -90,3 +90,19 @@ def test_mapping_lanes_independent():
     pl3.close()
     for s in singles:
         s.close()
+
+
+def test_long_free_running_trajectory_stays_within_bar():
+    """300 scans, both sides integrating their own state (nothing teacher-forced): ImageProjection outputs and feature
+    clouds bit-exact throughout, odometry and mapping poses within the north_star bar.  (With last-ulp differences in the
+    pose trigonometry this comparison used to leave the bar after ~230 scans -- one point moving to the neighbouring voxel
+    is enough to send the two LM runs down different paths; since every sin / cos / asin / atan2 repeats glibc's
+    evaluation, csrc/parity_math.cuh, the two trajectories coincide.)"""
+    import os
+    import sys
+    require_ref("vlp16")
+    sys.path.insert(0, os.path.join(os.path.dirname(os.path.dirname(os.path.abspath(__file__))), "tools"))
+    import long_parity
+    worst, first_bit_diff = long_parity.run("vlp16", 300, 11, verbose=False)
+    assert first_bit_diff is None, "bit-exact output differs first at %s" % (first_bit_diff,)
+    assert worst["sum"] < POSE_TOL and worst["aft"] < POSE_TOL, worst
