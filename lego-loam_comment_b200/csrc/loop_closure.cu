@@ -132,7 +132,7 @@ __global__ void __launch_bounds__(LC_THREADS) lc_icp_kernel(LcDev lc, LcIcpParam
     __shared__ double red[32][LC_SUMS];
     __shared__ double sTot[LC_SUMS];
     __shared__ float sT[16], sF[16];
-    __shared__ int sMiss, sStop, sConverged, sIter;
+    __shared__ int sMiss, sNext, sStop, sConverged, sIter;
     __shared__ double sPrevMSE;
     if (tid == 0) {
         for (int i = 0; i < 16; ++i) { sF[i] = (i % 5 == 0) ? 1.f : 0.f; sT[i] = sF[i]; }
@@ -150,9 +150,10 @@ __global__ void __launch_bounds__(LC_THREADS) lc_icp_kernel(LcDev lc, LcIcpParam
     // exact nearest target point of every source point: voxel-hash shells out to 3 m per thread, then the few points
     // with nothing that close are scanned against the whole target, one warp per point (ties: lowest target index)
     auto nearest_all = [&](const float4* pts, bool withFinal) {
-        if (tid == 0) sMiss = 0;
+        if (tid == 0) { sMiss = 0; sNext = 0; }
         __syncthreads();
-        for (int i = tid; i < ns; i += LC_THREADS) {
+        // points are handed out one at a time: the shell search takes 1 to 125 cells depending on where the neighbour sits
+        for (int i = atomicAdd(&sNext, 1); i < ns; i = atomicAdd(&sNext, 1)) {
             float4 p = pts[i];
             if (withFinal) p = lc_apply(sF, p);
             float d2;

@@ -27,21 +27,37 @@ def test_golden_fixtures_exist():
 @pytest.mark.parametrize("path", GOLDEN, ids=[os.path.basename(p) for p in GOLDEN])
 def test_oracle_reproduces_golden(path):
     g = json.load(open(path))
-    if not refpy.available(g["sensor"]):
-        pytest.skip("oracle/_ref for %s not built" % g["sensor"])
-    seq = SynthSequence(g["sensor"], seed=g["seed"], scene=g["scene"], speed=g["speed"])
-    ref = refpy.RefPipeline(g["sensor"])
+    cfg = g["sensor"] + ("_loop" if g.get("loop") else "")
+    if not refpy.available(cfg):
+        pytest.skip("oracle/_ref for %s not built" % cfg)
+    seq = SynthSequence(g["sensor"], seed=g["seed"], scene=g["scene"], speed=g["speed"], circle_radius=g.get("circle_radius", 0.0))
+    ref = refpy.RefPipeline(cfg)
+    j = 0
     for k, e in enumerate(g["scans"]):
+        if g.get("imu"):
+            msgs, j = seq.imu_until(j, seq.stamp(k) + 0.1)
+            for (t, q, w, a) in msgs:
+                ref.imu(t, q, w, a)
+            assert crc(np.concatenate([np.concatenate([[t], q, w, a]) for (t, q, w, a) in msgs]) if msgs else np.zeros(0)) == e["imu_crc"], "IMU generator drifted at scan %d" % k
         xyzi, ring = seq.scan(k)
         assert crc(xyzi) == e["input_crc"], "synthetic generator drifted at scan %d" % k
         f = ref.feed(xyzi, ring, seq.stamp(k), stages=g["stages"])
         assert f == e["flags"]
-        assert crc(ref.get("labelMat")) == e["labelMat_crc"]
-        assert crc(ref.cloud("segmentedCloud").view(np.uint32)) == e["segmentedCloud_crc"]
-        assert crc(ref.cloud("cornerPointsSharp").view(np.uint32)) == e["cornerPointsSharp_crc"]
-        assert crc(ref.cloud("surfPointsFlat").view(np.uint32)) == e["surfPointsFlat_crc"]
+        if "labelMat_crc" in e:
+            assert crc(ref.get("labelMat")) == e["labelMat_crc"]
+            assert crc(ref.cloud("segmentedCloud").view(np.uint32)) == e["segmentedCloud_crc"]
+            assert crc(ref.cloud("cornerPointsSharp").view(np.uint32)) == e["cornerPointsSharp_crc"]
+            assert crc(ref.cloud("surfPointsFlat").view(np.uint32)) == e["surfPointsFlat_crc"]
+        if "segmentedCloudAdj_crc" in e:
+            assert crc(ref.cloud("segmentedCloudAdj").view(np.uint32)) == e["segmentedCloudAdj_crc"]
         assert np.array_equal(ref.get("transformSum"), np.array(e["transformSum"], np.float32))
         if "transformAftMapped" in e:
             assert np.array_equal(ref.get("transformAftMapped"), np.array(e["transformAftMapped"], np.float32))
         if "transformMapped" in e:
             assert np.array_equal(ref.get("transformMapped"), np.array(e["transformMapped"], np.float32))
+        if "loopStats" in e:
+            assert [int(v) for v in ref.get("loopStats")] == e["loopStats"]
+        if "loopClosure" in e:
+            assert [int(v) for v in ref.get("loopClosure")] == e["loopClosure"]
+            assert np.array_equal(ref.get("icpTransform"), np.array(e["icpTransform"], np.float32))
+            assert np.array_equal(ref.get("cloudKeyPoses6D")[-6:], np.array(e["lastKeyPose"], np.float32))

@@ -36,6 +36,7 @@ def _cloud_close(g, r, what):
     ("vlp16", "room", {"dropout": 0.02}, 26),
     ("hdl32", "street", {}, 18),
     ("hdl64", "street", {}, 14),
+    ("vls128", "street", {}, 10),
 ])
 def test_scan_to_map_matches_reference(sensor, scene, kw, nscans):
     import refpy
