@@ -221,6 +221,21 @@ int lego_pg_size(lego_pg* h);
 /* estimate of one key: translation x y z and Rot3::roll() pitch() yaw() */
 int lego_pg_estimate(lego_pg* h, int key, double xyz_rpy_out[6]);
 
+/* ---------------------------------------------------------------- global map and PCD output
+ * The clouds mapOptimization::visualizeGlobalMapThread publishes every 5 s and saves at shutdown
+ * (mapOptmization.cpp:724-800).  which:
+ *   LEGO_MAP_GLOBAL      publishGlobalMap's globalMapKeyFramesDS (757-800) = /laser_cloud_surround and finalCloud.pcd (731)
+ *   LEGO_MAP_CORNER      cornerMapCloudDS  -> cornerMap.pcd  (734-749, 753)
+ *   LEGO_MAP_SURFACE     surfaceMapCloudDS -> surfaceMap.pcd (734-751, 753)
+ *   LEGO_MAP_TRAJECTORY  cloudKeyPoses3D   -> trajectory.pcd (754)
+ * xyzi_out: cap * 4 floats of host memory (may be NULL with cap 0 to ask for the size); *n_out = points of the cloud,
+ * min(*n_out, cap) of them copied.  Key-frame clouds are assembled and filtered on the device.
+ * lego_write_pcd_ascii replaces pcl::io::savePCDFileASCII for a PointXYZI cloud (host file output). */
+enum { LEGO_MAP_GLOBAL = 0, LEGO_MAP_CORNER = 1, LEGO_MAP_SURFACE = 2, LEGO_MAP_TRAJECTORY = 3 };
+int lego_pipeline_global_map(lego_pipeline* h, int lane, int which, float* xyzi_out, long cap, long* n_out);
+int lego_mo_global_map(lego_mo* h, int which, float* xyzi_out, long cap, long* n_out);
+int lego_write_pcd_ascii(const char* path, const float* xyzi, long n);
+
 /* ---------------------------------------------------------------- device self-tests (parity suite) */
 /* out[i] = the device implementation of glibc's atan2f(y[i], x[i]) (csrc/parity_math.cuh); host pointers. */
 int lego_selftest_atan2f(const float* y, const float* x, float* out, long n);

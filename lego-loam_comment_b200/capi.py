@@ -22,6 +22,7 @@ EXPORTED = [
     "lego_tf_create", "lego_tf_destroy", "lego_tf_laser_odometry", "lego_tf_aft_mapped",
     "lego_selftest_atan2f", "lego_selftest_std_sort", "lego_selftest_warp_sort", "lego_selftest_voxel_grid",
     "lego_selftest_sincosf", "lego_icp_align", "lego_pipeline_imu", "lego_fa_imu", "lego_mo_imu",
+    "lego_pipeline_global_map", "lego_mo_global_map", "lego_write_pcd_ascii",
     "lego_pg_create", "lego_pg_destroy", "lego_pg_add_prior", "lego_pg_add_between", "lego_pg_insert", "lego_pg_update", "lego_pg_size", "lego_pg_estimate",
 ]
 
@@ -68,6 +69,27 @@ def _check(rc, what):
     if rc < 0:
         raise LegoError("%s failed (%d): %s" % (what, rc, load().lego_last_error().decode()))
     return rc
+
+
+MAP_GLOBAL, MAP_CORNER, MAP_SURFACE, MAP_TRAJECTORY = 0, 1, 2, 3
+
+
+def _global_map(fn, head, what):
+    fn.argtypes = [ctypes.c_void_p] + [ctypes.c_int] * (len(head) - 1) + [ctypes.c_void_p, ctypes.c_long, ctypes.POINTER(ctypes.c_long)]
+    n = ctypes.c_long(0)
+    _check(fn(*head, None, 0, ctypes.byref(n)), what)
+    out = np.zeros((n.value, 4), np.float32)
+    if n.value:
+        _check(fn(*head, out.ctypes.data, n.value, ctypes.byref(n)), what)
+    return out[:n.value]
+
+
+def write_pcd_ascii(path, xyzi):
+    """pcl::io::savePCDFileASCII for an (n, 4) x y z intensity cloud (lego_write_pcd_ascii)"""
+    c = np.ascontiguousarray(xyzi, np.float32).reshape(-1, 4)
+    f = load().lego_write_pcd_ascii
+    f.argtypes = [ctypes.c_char_p, ctypes.c_void_p, ctypes.c_long]
+    _check(f(os.fsencode(path), c.ctypes.data if len(c) else None, len(c)), "lego_write_pcd_ascii")
 
 
 _DTYPES = {("f", 4): np.float32, ("i", 4): np.int32, ("i", 1): np.int8, ("u", 1): np.uint8, ("f", 16): np.float32}
@@ -167,6 +189,11 @@ class Pipeline:
         q = np.ascontiguousarray(orientation_xyzw, np.float64); w = np.ascontiguousarray(angular_velocity, np.float64)
         a = np.ascontiguousarray(linear_acceleration, np.float64)
         _check(f(self.h, lane, float(stamp), q.ctypes.data, w.ctypes.data, a.ctypes.data), "lego_pipeline_imu")
+
+    def global_map(self, which=MAP_GLOBAL, lane=0):
+        """publishGlobalMap's cloud (MAP_GLOBAL) or one of the clouds the reference saves at shutdown (MAP_CORNER,
+        MAP_SURFACE, MAP_TRAJECTORY), mapOptmization.cpp:724-800; (n, 4) float32"""
+        return _global_map(self.lib.lego_pipeline_global_map, (self.h, int(lane), int(which)), "lego_pipeline_global_map")
 
     def sync(self):
         _check(self.lib.lego_pipeline_sync(self.h), "lego_pipeline_sync")
@@ -405,6 +432,10 @@ class MapOptimization(_Stage):
         _check(f(self.h, ctypes.byref(corner_last), ctypes.byref(surf_last), ctypes.byref(outlier_last), ts.ctypes.data, stamp, aft, bef,
                  ctypes.byref(done)), "lego_mo_process")
         return np.array(aft[:], np.float32), np.array(bef[:], np.float32), bool(done.value)
+
+
+    def global_map(self, which=MAP_GLOBAL):
+        return _global_map(self.lib.lego_mo_global_map, (self.h, int(which)), "lego_mo_global_map")
 
 
 class TransformFusion(_Stage):

@@ -124,6 +124,20 @@ int lego_pipeline_timer_elapsed_between(lego_pipeline* ha, int slot_a, lego_pipe
     return LEGO_OK;
     LEGO_CATCH
 }
+// publishGlobalMap and the clouds saved at shutdown (mapOptmization.cpp:724-800) for one lane
+int lego_pipeline_global_map(lego_pipeline* h, int lane, int which, float* xyzi_out, long cap, long* n_out) {
+    if (!h || !n_out || which < 0 || which > 3 || cap < 0 || (cap > 0 && !xyzi_out)) return LEGO_ERR_ARG;
+    if (lane < 0 || lane >= h->e->c.L) return LEGO_ERR_ARG;
+    LEGO_TRY
+    std::vector<float4> cloud;
+    h->e->globalMap(lane, which, cloud);
+    *n_out = (long)cloud.size();
+    const long n = (long)cloud.size() < cap ? (long)cloud.size() : cap;
+    if (xyzi_out && n > 0) std::memcpy(xyzi_out, cloud.data(), sizeof(float4) * (size_t)n);
+    return LEGO_OK;
+    LEGO_CATCH
+}
+
 long lego_pipeline_download(lego_pipeline* h, int lane, const char* name, void* dst, long cap, int* elem_size_out) {
     if (!h || !name) return LEGO_ERR_ARG;
     LEGO_TRY

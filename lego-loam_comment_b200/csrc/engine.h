@@ -271,6 +271,8 @@ public:
     bool detectLoopClosure(int lane, int* closest, int* latest);
     void runIcpBatch(const std::vector<int>& lanes, const std::vector<int>& closest, const std::vector<int>& latest);
     void addLoopConstraint(int lane, int closest, int latest, const LcResult& r);
+    // ---- global map (publishGlobalMap / the clouds visualizeGlobalMapThread saves, mapOptmization.cpp:724-800) ----
+    void globalMap(int lane, int which, std::vector<float4>& out);
 
     // ---- TransformFusion (names follow transformFusion.cpp) ----
     void allocTransformFusion();
@@ -360,6 +362,27 @@ private:
 };
 
 const std::string& last_error();
+
+// pcl::VoxelGrid over a handful of key poses on the host (map_host.cu)
+void host_voxel_grid(const std::vector<float4>& in, float leaf, std::vector<float4>& out);
+
+// pcl::io::savePCDFileASCII for a PointXYZI cloud (global_map.cu); 0 on success
+int write_pcd_ascii(const char* path, const float* xyzi, long n);
+
+// device memory that lives for one call (lego_icp_align, the global-map queries)
+struct DevArena {
+    std::vector<void*> ptrs;
+    cudaStream_t stream = nullptr;
+    template <class T> T* alloc(size_t n, bool zero = true) {
+        void* p = nullptr;
+        if (n == 0) n = 1;
+        cuda_check(cudaMalloc(&p, n * sizeof(T)), "cudaMalloc");
+        ptrs.push_back(p);
+        if (zero) cuda_check(cudaMemsetAsync(p, 0, n * sizeof(T), stream), "cudaMemset");
+        return static_cast<T*>(p);
+    }
+    ~DevArena() { for (void* p : ptrs) cudaFree(p); }
+};
 
 // times the launches enqueued during its lifetime when profiling is on
 struct ProfScope {

@@ -544,21 +544,7 @@ void Engine::performLoopClosure(const std::vector<int>& active) {
 }  // namespace lego
 
 // ------------------------------------------------------------------------------------------------ C ABI
-namespace {
-struct DevArena {
-    std::vector<void*> ptrs;
-    cudaStream_t stream = nullptr;
-    template <class T> T* alloc(size_t n, bool zero = true) {
-        void* p = nullptr;
-        if (n == 0) n = 1;
-        lego::cuda_check(cudaMalloc(&p, n * sizeof(T)), "cudaMalloc");
-        ptrs.push_back(p);
-        if (zero) lego::cuda_check(cudaMemsetAsync(p, 0, n * sizeof(T), stream), "cudaMemset");
-        return static_cast<T*>(p);
-    }
-    ~DevArena() { for (void* p : ptrs) cudaFree(p); }
-};
-}  // namespace
+using lego::DevArena;
 
 struct lego_pg { lego::pg::Graph g; };
 

@@ -148,7 +148,7 @@ bool Engine::lookupMapOptimization(int lane, const std::string& n, void** ptr, i
 // pcl::VoxelGrid(leaf) over a handful of key poses, on the host (downSizeFilterSurroundingKeyPoses,
 // mapOptmization.cpp:1009-1010).  Same arithmetic as the device filter (voxel_grid.cu): note that the intensity
 // channel -- the key-frame index -- is averaged with the coordinates (quirk Q16).
-static void host_voxel_grid(const std::vector<float4>& in, float leaf, std::vector<float4>& out) {
+void host_voxel_grid(const std::vector<float4>& in, float leaf, std::vector<float4>& out) {
     out.clear();
     if (in.empty()) return;
     const float inv = 1.0f / leaf;

@@ -5,6 +5,7 @@
 //   lego_mo_process  <- mapOptimization::run                       mapOptmization.cpp:1487-1522
 // Every handle is a one-lane lego::Engine; inputs may be host or device memory (cudaMemcpyDefault resolves which),
 // outputs stay on the device with host mirrors filled, as the views in the header describe.
+#include <algorithm>
 #include <cmath>
 #include <cstring>
 #include <new>
@@ -224,6 +225,27 @@ int lego_fa_imu(lego_fa* h, double stamp, const double orientation_xyzw[4], cons
 int lego_mo_imu(lego_mo* h, double stamp, const double orientation_xyzw[4], const double angular_velocity[3], const double linear_acceleration[3]) {
     if (!h || !orientation_xyzw || !angular_velocity || !linear_acceleration) return LEGO_ERR_ARG;
     LEGO_TRY h->e->imuHandler(0, stamp, orientation_xyzw, angular_velocity, linear_acceleration); return LEGO_OK; LEGO_CATCH
+}
+
+// publishGlobalMap and the clouds saved at shutdown (mapOptmization.cpp:724-800)
+static int global_map_out(Engine& e, int lane, int which, float* xyzi_out, long cap, long* n_out) {
+    std::vector<float4> cloud;
+    e.globalMap(lane, which, cloud);
+    *n_out = (long)cloud.size();
+    const long n = std::min<long>((long)cloud.size(), cap);
+    if (xyzi_out && n > 0) std::memcpy(xyzi_out, cloud.data(), sizeof(float4) * (size_t)n);
+    return LEGO_OK;
+}
+int lego_mo_global_map(lego_mo* h, int which, float* xyzi_out, long cap, long* n_out) {
+    if (!h || !n_out || which < 0 || which > 3 || cap < 0 || (cap > 0 && !xyzi_out)) return LEGO_ERR_ARG;
+    LEGO_TRY return global_map_out(*h->e, 0, which, xyzi_out, cap, n_out); LEGO_CATCH
+}
+int lego_write_pcd_ascii(const char* path, const float* xyzi, long n) {
+    if (!path || n < 0 || (n > 0 && !xyzi)) return LEGO_ERR_ARG;
+    LEGO_TRY
+    if (lego::write_pcd_ascii(path, xyzi, n) != 0) { lego::set_last_error(std::string("cannot write ") + path); return LEGO_ERR_ARG; }
+    return LEGO_OK;
+    LEGO_CATCH
 }
 
 int lego_mo_process(lego_mo* h, const lego_cloud_view* corner_last, const lego_cloud_view* surf_last, const lego_cloud_view* outlier_last,

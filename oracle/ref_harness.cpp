@@ -407,6 +407,45 @@ void ref_feed_imu(void* h, double stamp, const double* q_xyzw, const double* w, 
     R.mo.imuHandler(m);
 }
 
+// mapOptimization::publishGlobalMap (mapOptmization.cpp:757-800) with a subscriber on /laser_cloud_surround, then the
+// shutdown half of visualizeGlobalMapThread (729-755; ros::ok() is false in the shim, so its 0.2 Hz loop is skipped).
+// Snapshots: "globalMapKeyFramesDS", and per saved file "pcd:finalCloud", "pcd:cornerMap", "pcd:surfaceMap",
+// "pcd:trajectory" (flat xyzi); the PCD text of each is read with ref_get_pcd_text.
+int ref_global_map(void* h) {
+    Ref& R = *static_cast<Ref*>(h);
+    ros::ShimState::get().subscribed.insert("/laser_cloud_surround");
+    R.mo.publishGlobalMap();
+    R.snap.f["globalMapKeyFramesDS"] = flat(*R.mo.globalMapKeyFramesDS);
+    pcl::shim_pcd_store().clear();
+    R.mo.visualizeGlobalMapThread();
+    int n = 0;
+    for (auto& kv : pcl::shim_pcd_store()) {
+        std::string name = kv.first;
+        const size_t slash = name.find_last_of('/');
+        if (slash != std::string::npos) name = name.substr(slash + 1);
+        const size_t dot = name.find_last_of('.');
+        if (dot != std::string::npos) name = name.substr(0, dot);
+        R.snap.f["pcd:" + name] = kv.second.xyzi;
+        ++n;
+    }
+    return n;
+}
+long ref_get_pcd_text(void* h, const char* name, char* buf, long cap) {
+    (void)h;
+    for (auto& kv : pcl::shim_pcd_store()) {
+        std::string base = kv.first;
+        const size_t slash = base.find_last_of('/');
+        if (slash != std::string::npos) base = base.substr(slash + 1);
+        const size_t dot = base.find_last_of('.');
+        if (dot != std::string::npos) base = base.substr(0, dot);
+        if (base != name) continue;
+        const long n = static_cast<long>(kv.second.text.size());
+        if (buf) std::memcpy(buf, kv.second.text.data(), std::min(n, cap));
+        return n;
+    }
+    return -1;
+}
+
 // Copy a named snapshot (float or int32) of the last scan. Returns the element count, or -1 if unknown.
 long ref_get_f32(void* h, const char* name, float* buf, long cap) {
     Ref& R = *static_cast<Ref*>(h);

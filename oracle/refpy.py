@@ -91,6 +91,24 @@ class RefPipeline:
     def cloud(self, name):
         return self.get(name).reshape(-1, 4)
 
+    def global_map(self):
+        """publishGlobalMap + the shutdown half of visualizeGlobalMapThread (mapOptmization.cpp:724-800); afterwards
+        cloud("globalMapKeyFramesDS"), cloud("pcd:finalCloud" | "pcd:cornerMap" | "pcd:surfaceMap" | "pcd:trajectory")
+        and pcd_text(name) are available.  Returns the number of PCD files the reference wrote."""
+        self.lib.ref_global_map.argtypes = [ctypes.c_void_p]
+        return self.lib.ref_global_map(self.h)
+
+    def pcd_text(self, name):
+        f = self.lib.ref_get_pcd_text
+        f.argtypes = [ctypes.c_void_p, ctypes.c_char_p, ctypes.c_void_p, ctypes.c_long]
+        f.restype = ctypes.c_long
+        n = f(self.h, name.encode(), None, 0)
+        if n < 0:
+            raise KeyError(name)
+        buf = ctypes.create_string_buffer(n)
+        f(self.h, name.encode(), buf, n)
+        return buf.raw[:n]
+
     def poses(self):
         out = np.zeros(18, np.float32)
         self.lib.ref_get_poses(self.h, out.ctypes.data)

@@ -2,7 +2,8 @@
 // Containers are plain std::vector wrappers; VoxelGrid and KdTreeFLANN delegate to the restatements in
 // oracle/thirdparty/.  IterativeClosestPoint delegates to oracle/thirdparty/tp_icp.h; Eigen::Affine3f,
 // pcl::getTransformation and pcl::getTranslationAndEulerAngles restate PCL's common/eigen.hpp (float); they only
-// run in the configs generated with loopClosureEnableFlag = true (utility.h:104).  PCD output is a no-op.
+// run in the configs generated with loopClosureEnableFlag = true (utility.h:104).  pcl::io::savePCDFileASCII writes no
+// file: it keeps the cloud and its PCD text (oracle/thirdparty/tp_pcd.h) in memory under the path it was given.
 #pragma once
 #include <cmath>
 #include <cstdint>
@@ -14,6 +15,8 @@
 #include "../thirdparty/tp_voxel_grid.h"
 #include "../thirdparty/tp_kdtree.h"
 #include "../thirdparty/tp_icp.h"
+#include "../thirdparty/tp_pcd.h"
+#include <map>
 
 #define PCL_ADD_POINT4D union { float data[4]; struct { float x; float y; float z; }; };
 #define PCL_ADD_INTENSITY union { struct { float intensity; }; float data_c[4]; }
@@ -206,6 +209,21 @@ inline void getTranslationAndEulerAngles(const Eigen::Affine3f& t, float& x, flo
     pitch = std::asin(-t.mat.m[2][0]);
     yaw = std::atan2(t.mat.m[1][0], t.mat.m[0][0]);
 }
-namespace io { template <class T> int savePCDFileASCII(const std::string&, const PointCloud<T>&) { return 0; } }
+// what the reference "saved": path -> (flat xyzi, PCD text); nothing touches the file system
+struct ShimPcdFile { std::vector<float> xyzi; std::string text; };
+inline std::map<std::string, ShimPcdFile>& shim_pcd_store() { static std::map<std::string, ShimPcdFile> m; return m; }
+namespace io {
+template <class T> int savePCDFileASCII(const std::string& path, const PointCloud<T>& cloud) {
+    ShimPcdFile f;
+    f.xyzi.resize(4 * cloud.points.size());
+    for (size_t k = 0; k < cloud.points.size(); ++k) {
+        f.xyzi[4 * k] = cloud.points[k].x; f.xyzi[4 * k + 1] = cloud.points[k].y; f.xyzi[4 * k + 2] = cloud.points[k].z;
+        f.xyzi[4 * k + 3] = cloud.points[k].intensity;
+    }
+    f.text = tp::pcd_ascii_xyzi(f.xyzi);
+    shim_pcd_store()[path] = f;
+    return 0;
+}
+}  // namespace io
 
 }  // namespace pcl

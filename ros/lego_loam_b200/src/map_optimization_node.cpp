@@ -1,6 +1,9 @@
 // mapOptmization node shell (reference mapOptmization.cpp:226-266 topic wiring, 608-652 handlers, 1487-1522 run, 654-673
-// publishTF).  Loop closure, when utility.h:104 enables it, runs inside lego_mo_process (no separate thread); the global-map
-// visualisation thread (724-800) is not served.  Uncompiled here, see common.h.
+// publishTF, 724-800 global map).  Loop closure, when utility.h:104 enables it, runs inside lego_mo_process (no separate
+// thread).  The global map the reference serves from visualizeGlobalMapThread is served from the node's own loop (a
+// lego_mo handle belongs to one thread): /laser_cloud_surround every 5 s while someone listens, and the four PCD files
+// of mapOptmization.cpp:729-755 at shutdown, all through lego_mo_global_map / lego_write_pcd_ascii.
+// Uncompiled here, see common.h.
 #include "common.h"
 
 class MapOptimizationNode {
@@ -14,6 +17,7 @@ public:
         subOdometry_ = nh_.subscribe<nav_msgs::Odometry>("/laser_odom_to_init", 5, &MapOptimizationNode::odometryHandler, this);
         subImu_ = nh_.subscribe<sensor_msgs::Imu>(imuTopic, 50, &MapOptimizationNode::imuHandler, this);
         pubAftMapped_ = nh_.advertise<nav_msgs::Odometry>("/aft_mapped_to_init", 5);
+        pubSurround_ = nh_.advertise<sensor_msgs::PointCloud2>("/laser_cloud_surround", 2);
     }
     ~MapOptimizationNode() { if (mo_) lego_mo_destroy(mo_); }
 
@@ -59,13 +63,39 @@ public:
         broadcaster_.sendTransform(t);
     }
 
+    // publishGlobalMap (mapOptmization.cpp:757-800)
+    void publishGlobalMap() {
+        if (pubSurround_.getNumSubscribers() == 0) return;
+        std::vector<float> xyzi;
+        if (!fetch(LEGO_MAP_GLOBAL, xyzi) || xyzi.empty()) return;
+        pcl::PointCloud<pcl::PointXYZI> c; lego_ros::unpack(lego_ros::view_of(xyzi), c);
+        lego_ros::publish_cloud(pubSurround_, c, ros::Time().fromSec(tOdometry_), "/camera_init");
+    }
+    // the tail of visualizeGlobalMapThread (mapOptmization.cpp:729-755)
+    void saveMaps() {
+        static const struct { int which; const char* file; } kFiles[4] = {{LEGO_MAP_GLOBAL, "finalCloud.pcd"}, {LEGO_MAP_CORNER, "cornerMap.pcd"},
+                                                                          {LEGO_MAP_SURFACE, "surfaceMap.pcd"}, {LEGO_MAP_TRAJECTORY, "trajectory.pcd"}};
+        for (const auto& f : kFiles) {
+            std::vector<float> xyzi;
+            if (!fetch(f.which, xyzi)) continue;
+            const std::string path = fileDirectory + f.file;
+            if (lego_write_pcd_ascii(path.c_str(), xyzi.data(), (long)(xyzi.size() / 4)) != LEGO_OK) ROS_ERROR("%s", lego_last_error());
+        }
+    }
+
 private:
+    bool fetch(int which, std::vector<float>& xyzi) {
+        long n = 0;
+        if (lego_mo_global_map(mo_, which, nullptr, 0, &n) != LEGO_OK) { ROS_ERROR("lego_mo_global_map: %s", lego_last_error()); return false; }
+        xyzi.resize((size_t)n * 4);
+        return n == 0 || lego_mo_global_map(mo_, which, xyzi.data(), n, &n) == LEGO_OK;
+    }
     static void take(const sensor_msgs::PointCloud2ConstPtr& m, std::vector<float>& xyzi) {
         pcl::PointCloud<pcl::PointXYZI> c; pcl::fromROSMsg(*m, c); lego_ros::pack(c, xyzi);
     }
     ros::NodeHandle nh_;
     ros::Subscriber subCorner_, subSurf_, subOutlier_, subOdometry_, subImu_;
-    ros::Publisher pubAftMapped_;
+    ros::Publisher pubAftMapped_, pubSurround_;
     tf::TransformBroadcaster broadcaster_;
     lego_mo* mo_ = nullptr;
     std::vector<float> corner_, surf_, outlier_;
@@ -79,6 +109,12 @@ int main(int argc, char** argv) {
     MapOptimizationNode node;
     ROS_INFO("\033[1;32m---->\033[0m Map Optimization (B200) Started.");
     ros::Rate rate(200);   // mapOptmization.cpp:1537
-    while (ros::ok()) { ros::spinOnce(); node.run(); rate.sleep(); }
+    ros::Time lastMap = ros::Time::now();
+    while (ros::ok()) {
+        ros::spinOnce(); node.run();
+        if ((ros::Time::now() - lastMap).toSec() >= 5.0) { lastMap = ros::Time::now(); node.publishGlobalMap(); }   // ros::Rate(0.2), mapOptmization.cpp:725
+        rate.sleep();
+    }
+    node.saveMaps();
     return 0;
 }

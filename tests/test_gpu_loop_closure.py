@@ -137,6 +137,14 @@ def test_loop_closure_matches_reference():
             assert abs(f2 - wf) <= 1e-5 * max(1.0, wf)
     assert icp_runs >= 2 and closed >= 2, "loop closure fired %d / closed %d times: the check would be vacuous" % (icp_runs, closed)
     assert corrected > 1e-3, "correctPoses never moved a key pose (max %g): the check would be vacuous" % corrected
+    # the map products after the loops were closed (key poses rewritten by correctPoses): publishGlobalMap and the clouds
+    # saved at shutdown (mapOptmization.cpp:724-800)
+    assert ref.global_map() == 4
+    for which, name in ((capi.MAP_GLOBAL, "globalMapKeyFramesDS"), (capi.MAP_CORNER, "pcd:cornerMap"), (capi.MAP_SURFACE, "pcd:surfaceMap"),
+                        (capi.MAP_TRAJECTORY, "pcd:trajectory")):
+        g, w = pl.global_map(which), ref.cloud(name)
+        assert g.shape == w.shape and len(w) > 0, "%s: %s vs %s points" % (name, g.shape, w.shape)
+        assert np.allclose(g, w, rtol=1e-5, atol=2e-4), "%s: max abs diff %g" % (name, np.abs(g - w).max())
     pl.close(); ref.close()
 
 

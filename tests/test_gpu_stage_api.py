@@ -53,6 +53,14 @@ def test_stage_handles_match_reference_and_pipeline():
             assert np.max(np.abs(bef - ref.get("transformBefMapped"))) < 1e-4
             assert np.array_equal(aft, poses[0, 6:12]), "stage handle and pipeline disagree on transformAftMapped"
     assert mapped >= 3
+    # lego_mo_global_map: the node's map products (mapOptmization.cpp:724-800) from the stage handle
+    ref.global_map()
+    for which, name in ((capi.MAP_GLOBAL, "globalMapKeyFramesDS"), (capi.MAP_CORNER, "pcd:cornerMap"), (capi.MAP_SURFACE, "pcd:surfaceMap"),
+                        (capi.MAP_TRAJECTORY, "pcd:trajectory")):
+        g, w = mo.global_map(which), ref.cloud(name)
+        assert g.shape == w.shape and len(w) > 0, "%s: %s vs %s points" % (name, g.shape, w.shape)
+        assert np.allclose(g, w, rtol=1e-5, atol=2e-4), "%s: max abs diff %g" % (name, np.abs(g - w).max())
+        assert np.array_equal(g.view(np.uint32), pl.global_map(which).view(np.uint32)), "stage handle and pipeline disagree on " + name
     for h in (ip, fa, mo, pl):
         h.close()
 
