@@ -365,8 +365,12 @@ def run_b200(args):
     barrier()
     for pl in group:
         pl.timer_record(0)
+    submit_ms = []   # host time to enqueue each step (no sync inside); once the launch queues are full it tracks the device
     for t in range(W, T):
+        t_submit = time.perf_counter()
         device_step(group, t)
+        submit_ms.append((time.perf_counter() - t_submit) * 1e3)
+    host_submit_ms = (sum(submit_ms), min(submit_ms))
     for pl in group:
         pl.timer_record(1)
     sync_group(group)
@@ -442,7 +446,7 @@ def run_b200(args):
 
     ms = max_over_ranks(ms, world, "cuda")
     return dict(rank=rank, world=world, ms=ms, L=L, K=K, W=W, e2e=e2e, clocks=clocks, launches=launches, prof=prof, tot_ms=tot_ms,
-                dominant=dominant, dom=dom, counts=counts, cap=cap, params=params,
+                dominant=dominant, dom=dom, counts=counts, cap=cap, params=params, host_submit_ms=host_submit_ms,
                 step_bytes=int(xyzi[0].nbytes + ring[0].nbytes), inputs=(xyzi, ring, npts, stamps))
 
 
@@ -556,6 +560,7 @@ def main():
                    "points_per_scan": r["cap"],
                    "l2": "per-step inputs %.0f MB + per-lane state exceed the 126 MB L2 (no flush needed)" % (r["step_bytes"] / 1e6)},
         "roofline": roofline, "clocks": r["clocks"], "gpu_launches": int(r["launches"]),
+        "host_submit_ms_per_step": {"mean": round(r["host_submit_ms"][0] / K, 3), "min": round(r["host_submit_ms"][1], 3)},
     }
     if r["e2e"]:
         line["e2e"] = r["e2e"]

@@ -15,6 +15,16 @@
 
 namespace lego {
 
+constexpr int MO_RES_THREADS = 256;   // one query per thread in mo_residual_kernel
+#ifndef LEGO_MO_RES_CTA
+#define LEGO_MO_RES_CTA 256
+#endif
+#ifndef LEGO_MO_RES_INFLIGHT
+#define LEGO_MO_RES_INFLIGHT 16
+#endif
+constexpr int MO_RES_INFLIGHT = LEGO_MO_RES_INFLIGHT;   // 256-query blocks of one lane in flight per launch; more queries loop
+constexpr int MO_RES_CTA = LEGO_MO_RES_CTA;   // threads per CTA of mo_residual_kernel (a slice of a 256-query block)
+
 // ---- constants derived once from lego_params (host side, with the reference's float/double semantics) ----
 struct Consts {
     int R, C, N, G, L, Pcap, Ocap;

@@ -358,9 +358,9 @@ void Engine::mapOptimizationBody(const std::vector<int>& active) {
     { ProfScope ps(this, "vh_build(surfMap)"); launches += vh_build(mo.hashSurfMap, c.L, mo.surfFromMapDS, (size_t)mo.surfDSCap, stream); }
     {   // scan2MapOptimization: <= 10 x {residuals, solve}; a converged lane makes its share of later launches a no-op
         { ProfScope ps(this, "mo_lm_begin_kernel"); mo_lm_begin_kernel<<<(c.L + 63) / 64, 64, 0, stream>>>(mo, c.L); }
-        dim3 g(std::min(mo.resBlocks, 16), c.L);   // 16 x 256 queries per lane in flight; larger scans loop
+        dim3 g(std::min(mo.resBlocks, MO_RES_INFLIGHT) * (MO_RES_THREADS / MO_RES_CTA), c.L);   // 16 x 256 queries per lane in flight; larger scans loop
         for (int iter = 0; iter < 10; ++iter) {
-            { ProfScope ps(this, "mo_residual_kernel"); mo_residual_kernel<<<g, 256, 0, stream>>>(mo); }
+            { ProfScope ps(this, "mo_residual_kernel"); mo_residual_kernel<<<g, MO_RES_CTA, 0, stream>>>(mo); }
             { ProfScope ps(this, "mo_solve_kernel"); mo_solve_kernel<<<c.L, 32, 0, stream>>>(mo, iter); }
         }
         launches += 21;

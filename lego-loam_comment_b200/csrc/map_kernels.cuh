@@ -12,7 +12,6 @@
 
 namespace lego {
 
-constexpr int MO_RES_THREADS = 256;   // one query per thread in mo_residual_kernel
 constexpr int MO_ACC = 28;   // 21 upper-triangle entries of AtA, 6 of AtB, 1 row count
 
 // The odometry pose reaches mapOptimization through a nav_msgs/Odometry message: publishOdometry builds a quaternion

@@ -165,14 +165,17 @@ __global__ void mo_lm_begin_kernel(MoDev m, int L) {
     m.state[lane * 16 + 6] = go;
 }
 
-__global__ void __launch_bounds__(MO_RES_THREADS, 4) mo_residual_kernel(MoDev m) {
-    const int lane = blockIdx.y, tid = threadIdx.x, lid = tid & 31, warp = tid >> 5;
+__global__ void __launch_bounds__(MO_RES_CTA, 1024 / MO_RES_CTA) mo_residual_kernel(MoDev m) {
+    // a CTA is one MO_RES_CTA-thread slice of a 256-query block: small CTAs give their registers back as soon as their
+    // own queries are done instead of waiting for the slowest of 256
+    constexpr int SUB = MO_RES_THREADS / MO_RES_CTA;
+    const int lane = blockIdx.y, sub = blockIdx.x % SUB, tid = sub * MO_RES_CTA + threadIdx.x, lid = tid & 31, warp = tid >> 5;
     if (!m.state[lane * 16 + 6]) return;
     const int nCorner = m.scanCounts[lane * 8 + 0], nSurf = m.scanCounts[lane * 8 + 4];
     const MapSinCos sc = map_sincos(m.transformTobeMapped + lane * 6);
     // a CTA takes the 256-query blocks blk = blockIdx.x, blockIdx.x + gridDim.x, ...; the partial sums stay per block
     // and warp (not per CTA) so the solve kernel adds them in the same order whatever the grid size
-    for (int blk = blockIdx.x; blk * MO_RES_THREADS < nCorner + nSurf; blk += gridDim.x) {
+    for (int blk = blockIdx.x / SUB; blk * MO_RES_THREADS < nCorner + nSurf; blk += gridDim.x / SUB) {
         const int q = blk * MO_RES_THREADS + tid;
         double acc[MO_ACC];
 #pragma unroll
