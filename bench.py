@@ -206,11 +206,16 @@ def gather_counts(pl, params, lanes):
         odo += ((it_c + 4) // 5) * (24 * int(fc[0]) + 16 * int(lc[0])) + it_c * 96 * int(fc[0])
     c["odo_bytes"] = odo
     # mapOptimization (counts of the last mapping call of every lane; K13..K18 of SURVEY.md 8d)
-    mc = np.zeros(4, np.int64); sc = np.zeros(8, np.int64); s2m = 0
+    mc = np.zeros(4, np.int64); sc = np.zeros(8, np.int64); s2m = 0; rerank = 0; search = 0
     for l in range(lanes):
         m_, s_, st = pl.download("mapCounts", l), pl.download("scanCounts", l), pl.download("moState", l)
         mc += m_; sc += s_
         s2m += int(st[3]) * (128 * (int(s_[0]) + int(s_[4])) + 32 * int(st[4]))
+        # the 5-NN of an LM iteration: iteration 0 searches every query (query 16 + neighbours 80 + candidate cache 48 + result 32),
+        # iterations >= 1 re-rank the cached candidates (query 16 + cache 48 + 8 candidates 128 + result 32); the searches of
+        # the queries whose cache could not prove the answer are not counted (lower bound)
+        search += 176 * (int(s_[0]) + int(s_[4]))
+        rerank += max(int(st[3]) - 1, 0) * 224 * (int(s_[0]) + int(s_[4]))
     c["mo_bytes"] = {
         "mo_begin_kernel": 200 * lanes,
         "mo_assemble_map_kernel": 32 * int(mc[0] + mc[1]),
@@ -221,7 +226,9 @@ def gather_counts(pl, params, lanes):
         "vh_build(cornerMap)": 36 * int(mc[2]),
         "vh_build(surfMap)": 36 * int(mc[3]),
         "mo_lm_begin_kernel": 40 * lanes,
-        "mo_residual_kernel": s2m / 10.0,   # average over the 10 launches of a mapping call (converged lanes do nothing)
+        "mo_rerank_kernel": rerank / 9.0,   # averages over the launches of a mapping call (converged lanes do nothing)
+        "mo_search_kernel": search / 10.0,
+        "mo_residual_kernel": s2m / 10.0,
         "mo_solve_kernel": 0.0,
         "mo_save_keyframe_kernel": 32 * int(sc[0] + sc[1] + sc[2]),
     }

@@ -16,14 +16,10 @@
 namespace lego {
 
 constexpr int MO_RES_THREADS = 256;   // one query per thread in mo_residual_kernel
-#ifndef LEGO_MO_RES_CTA
-#define LEGO_MO_RES_CTA 256
-#endif
 #ifndef LEGO_MO_RES_INFLIGHT
 #define LEGO_MO_RES_INFLIGHT 16
 #endif
 constexpr int MO_RES_INFLIGHT = LEGO_MO_RES_INFLIGHT;   // 256-query blocks of one lane in flight per launch; more queries loop
-constexpr int MO_RES_CTA = LEGO_MO_RES_CTA;   // threads per CTA of mo_residual_kernel (a slice of a 256-query block)
 
 // ---- constants derived once from lego_params (host side, with the reference's float/double semantics) ----
 struct Consts {
@@ -203,6 +199,11 @@ struct MoDev {
     MoOverride* overrides;     // [L]
     float* imuBlend;           // [L][4] transformUpdate's IMU blend (mapOptmization.cpp:465-490): active, imuRollLast, imuPitchLast
     double* partials;          // [L][resBlocks][8][28] per-warp partial sums of AtA / AtB / row count
+    int4* knnCand;             // [L][resBlocks*256][VH_CACHE_K/4] candidate cache of the scan-to-map 5-NN (map indices per query)
+    float4* knnMeta;           // [L][resBlocks*256] query position when the cache was filled, w = squared radius it covers
+    int4* knnRes;              // [L][resBlocks*256][2] idx0..3 | idx4, 5th squared distance, neighbours found
+    int* knnMissList;          // [L][resBlocks*256] queries to search again in this iteration
+    int* knnMissCount;         // [L]
     int resBlocks;             // CTAs per lane in mo_residual_kernel
     int poolCap, maxSel, cornerRawCap, surfRawCap, cornerDSCap, surfDSCap, scanCornerCap, scanSurfCap, scanOutlierCap, maxKeyFrames;
 };

@@ -16,6 +16,8 @@ __global__ void mo_begin_kernel(FaDev f, MoDev m, int L);
 __global__ void mo_assemble_map_kernel(MoDev m);
 __global__ void mo_concat_kernel(MoDev m, int surfCap, int outlierCap, int totalCap);
 __global__ void mo_lm_begin_kernel(MoDev m, int L);
+__global__ void mo_rerank_kernel(MoDev m);
+__global__ void mo_search_kernel(MoDev m, int iter);
 __global__ void mo_residual_kernel(MoDev m);
 __global__ void mo_solve_kernel(MoDev m, int iter);
 __global__ void mo_save_keyframe_kernel(MoDev m);
@@ -71,6 +73,12 @@ void Engine::allocMapOptimization() {
     mo.imuBlend = alloc<float>(L * 4);
     mo.resBlocks = (mo.scanCornerCap + mo.scanSurfCap + mo.scanOutlierCap + 255) / 256;
     mo.partials = alloc<double>(L * mo.resBlocks * 8 * 28);   // per 32-query warp slice
+    const size_t nSlots = L * mo.resBlocks * MO_RES_THREADS;           // one per query of every lane
+    mo.knnCand = alloc<int4>(nSlots * (VH_CACHE_K / 4), false);    // cached neighbour candidates per query (voxel_hash.cuh)
+    mo.knnMeta = alloc<float4>(nSlots, false);      // where the query was when its cache was filled, w = squared radius the candidates cover
+    mo.knnRes = alloc<int4>(nSlots * 2, false);     // this iteration's 5 neighbours, 5th distance, count
+    mo.knnMissList = alloc<int>(nSlots, false);     // queries whose cache could not prove the answer
+    mo.knnMissCount = alloc<int>(L);
     moHost.assign(c.L, MoLaneHost());
 
     // ---- VoxelGrid segment tables ----
@@ -358,12 +366,29 @@ void Engine::mapOptimizationBody(const std::vector<int>& active) {
     { ProfScope ps(this, "vh_build(surfMap)"); launches += vh_build(mo.hashSurfMap, c.L, mo.surfFromMapDS, (size_t)mo.surfDSCap, stream); }
     {   // scan2MapOptimization: <= 10 x {residuals, solve}; a converged lane makes its share of later launches a no-op
         { ProfScope ps(this, "mo_lm_begin_kernel"); mo_lm_begin_kernel<<<(c.L + 63) / 64, 64, 0, stream>>>(mo, c.L); }
-        dim3 g(std::min(mo.resBlocks, MO_RES_INFLIGHT) * (MO_RES_THREADS / MO_RES_CTA), c.L);   // 16 x 256 queries per lane in flight; larger scans loop
+        dim3 g(std::min(mo.resBlocks, MO_RES_INFLIGHT), c.L);   // 16 x 256 queries per lane in flight; larger scans loop
+#ifndef LEGO_MO_GRID_LATER
+#define LEGO_MO_GRID_LATER 8
+#endif
+        // later iterations mostly find lanes that are done or few misses: a smaller grid keeps the no-op launches cheap
+        dim3 gq(std::min(mo.resBlocks, 32), c.L), gLater(std::min(mo.resBlocks, LEGO_MO_GRID_LATER), c.L);
         for (int iter = 0; iter < 10; ++iter) {
-            { ProfScope ps(this, "mo_residual_kernel"); mo_residual_kernel<<<g, MO_RES_CTA, 0, stream>>>(mo); }
+            {   // cornerOptimization + surfOptimization: re-rank the cached neighbours, search the rest, fit (map_optimization.cu)
+#ifdef LEGO_KNN_ITER_NAMES
+                static const char* kR[10] = {"rerank#0", "rerank#1", "rerank#2", "rerank#3", "rerank#4", "rerank#5", "rerank#6", "rerank#7", "rerank#8", "rerank#9"};
+                static const char* kS[10] = {"search#0", "search#1", "search#2", "search#3", "search#4", "search#5", "search#6", "search#7", "search#8", "search#9"};
+                static const char* kF[10] = {"fit#0", "fit#1", "fit#2", "fit#3", "fit#4", "fit#5", "fit#6", "fit#7", "fit#8", "fit#9"};
+                const char *nR = kR[iter], *nS = kS[iter], *nF = kF[iter];
+#else
+                const char *nR = "mo_rerank_kernel", *nS = "mo_search_kernel", *nF = "mo_residual_kernel";
+#endif
+                if (iter > 0) { ProfScope ps(this, nR); mo_rerank_kernel<<<gLater, 256, 0, stream>>>(mo); }
+                { ProfScope ps(this, nS); mo_search_kernel<<<iter == 0 ? gq : gLater, 256, 0, stream>>>(mo, iter); }
+                { ProfScope ps(this, nF); mo_residual_kernel<<<g, MO_RES_THREADS, 0, stream>>>(mo); }
+            }
             { ProfScope ps(this, "mo_solve_kernel"); mo_solve_kernel<<<c.L, 32, 0, stream>>>(mo, iter); }
         }
-        launches += 21;
+        launches += 40;
     }
     if (loopMode()) saveKeyFramesHostGraph(active);   // lanes whose graph holds a loop factor: gate + iSAM update on the host
     { ProfScope ps(this, "mo_save_keyframe_kernel"); mo_save_keyframe_kernel<<<c.L, 256, 0, stream>>>(mo); }

@@ -84,11 +84,8 @@ __device__ __forceinline__ void mo_accumulate(double* acc, const MapSinCos& sc, 
 
 // cornerOptimization for one point (mapOptmization.cpp:1096-1172): returns true and the weighted coefficients when
 // the point yields a residual row.
-__device__ inline bool mo_corner_residual(const VhLane& vh, const float4* __restrict__ map, const MapSinCos& sc, float4 ori, float* cx_, float* cy_, float* cz_, float* cd_) {
-    const float4 ps = map_transform(sc, ori);
-    float d2[5]; int idx[5];
-    const int found = vh_knn5(vh, ps.x, ps.y, ps.z, 1.0f, d2, idx);
-    if (found < 5 || !((double)d2[4] < 1.0)) return false;
+__device__ inline bool mo_corner_residual(const float4* __restrict__ map, const float4 ps, int found, float d5, const int* idx, float* cx_, float* cy_, float* cz_, float* cd_) {
+    if (found < 5 || !((double)d5 < 1.0)) return false;
     float px[5], py[5], pz[5];
     float cx = 0.f, cy = 0.f, cz = 0.f;
 #pragma unroll
@@ -124,11 +121,8 @@ __device__ inline bool mo_corner_residual(const VhLane& vh, const float4* __rest
 }
 
 // surfOptimization for one point (mapOptmization.cpp:1179-1225)
-__device__ inline bool mo_surf_residual(const VhLane& vh, const float4* __restrict__ map, const MapSinCos& sc, float4 ori, float* cx_, float* cy_, float* cz_, float* cd_) {
-    const float4 ps = map_transform(sc, ori);
-    float d2[5]; int idx[5];
-    const int found = vh_knn5(vh, ps.x, ps.y, ps.z, 1.0f, d2, idx);
-    if (found < 5 || !((double)d2[4] < 1.0)) return false;
+__device__ inline bool mo_surf_residual(const float4* __restrict__ map, const float4 ps, int found, float d5, const int* idx, float* cx_, float* cy_, float* cz_, float* cd_) {
+    if (found < 5 || !((double)d5 < 1.0)) return false;
     float A0[15];
 #pragma unroll
     for (int j = 0; j < 5; ++j) { const float4 q = map[idx[j]]; A0[j * 3] = q.x; A0[j * 3 + 1] = q.y; A0[j * 3 + 2] = q.z; }
@@ -163,41 +157,119 @@ __global__ void mo_lm_begin_kernel(MoDev m, int L) {
         m.state[lane * 16 + 3] = 0; m.state[lane * 16 + 4] = 0;
     }
     m.state[lane * 16 + 6] = go;
+    m.knnMissCount[lane] = 0;
 }
 
-__global__ void __launch_bounds__(MO_RES_CTA, 1024 / MO_RES_CTA) mo_residual_kernel(MoDev m) {
-    // a CTA is one MO_RES_CTA-thread slice of a 256-query block: small CTAs give their registers back as soon as their
-    // own queries are done instead of waiting for the slowest of 256
-    constexpr int SUB = MO_RES_THREADS / MO_RES_CTA;
-    const int lane = blockIdx.y, sub = blockIdx.x % SUB, tid = sub * MO_RES_CTA + threadIdx.x, lid = tid & 31, warp = tid >> 5;
+// One LM iteration's residual rows in three launches, so that each phase runs dense:
+//   mo_rerank_kernel  (iterations >= 1) re-ranks every query's cached neighbour candidates at the new pose; a proven
+//                     answer (voxel_hash.cuh) goes to knnRes, an unproven query onto the lane's miss list
+//   mo_search_kernel  one thread per query (iteration 0) or per miss: voxel-hash search, refills the cache, writes knnRes
+//   mo_residual_kernel  line / plane fit of every query from knnRes, rows reduced into per-warp partial sums
+// A search is a chain of dependent loads (hash probe -> cell header -> points); mixed into one kernel with the re-rank,
+// the slowest query of a CTA set its lifetime and the cache saved nothing (profiles/README.md, session 20).
+// knnRes: [2 x int4] idx0..3 | idx4, d5 bits, found, -.  The miss list's order depends on atomics; the results do not.
+__device__ __forceinline__ void mo_store_result(MoDev& m, size_t slot, int found, float d5, const int* idx) {
+    m.knnRes[slot * 2] = make_int4(idx[0], idx[1], idx[2], idx[3]);
+    m.knnRes[slot * 2 + 1] = make_int4(idx[4], __float_as_int(d5), found, 0);
+}
+
+__global__ void __launch_bounds__(256) mo_rerank_kernel(MoDev m) {
+    const int lane = blockIdx.y, tid = threadIdx.x, lid = tid & 31;
+    if (!m.state[lane * 16 + 6]) return;
+    const int nCorner = m.scanCounts[lane * 8 + 0], nQ = nCorner + m.scanCounts[lane * 8 + 4];
+    const MapSinCos sc = map_sincos(m.transformTobeMapped + lane * 6);
+    const float4* mapC = m.cornerFromMapDS + (size_t)lane * m.cornerDSCap;
+    const float4* mapS = m.surfFromMapDS + (size_t)lane * m.surfDSCap;
+    const float4* qC = m.cornerLastDS + (size_t)lane * m.scanCornerCap;
+    const float4* qS = m.surfTotalLastDS + (size_t)lane * (m.scanSurfCap + m.scanOutlierCap);
+    const size_t slotBase = (size_t)lane * m.resBlocks * MO_RES_THREADS;
+    for (int base = blockIdx.x * 256; base < nQ; base += gridDim.x * 256) {
+        const int q = base + tid;
+        bool miss = false;
+        if (q < nQ) {
+            const bool corner = q < nCorner;
+            const float4 ps = map_transform(sc, corner ? qC[q] : qS[q - nCorner]);
+            const float4 meta = m.knnMeta[slotBase + q];
+            int cand[VH_CACHE_K];
+#pragma unroll
+            for (int j = 0; j < VH_CACHE_K / 4; ++j) {
+                const int4 c4 = m.knnCand[(slotBase + q) * (VH_CACHE_K / 4) + j];
+                cand[4 * j] = c4.x; cand[4 * j + 1] = c4.y; cand[4 * j + 2] = c4.z; cand[4 * j + 3] = c4.w;
+            }
+            float d2[5]; int idx[5]; int found;
+            if (vh_knn5_cached(corner ? mapC : mapS, cand, meta.x, meta.y, meta.z, meta.w, ps.x, ps.y, ps.z, 1.0f, d2, idx, &found))
+                mo_store_result(m, slotBase + q, found, d2[4], idx);
+            else miss = true;
+        }
+        // one atomic per warp
+        const unsigned bal = __ballot_sync(0xffffffffu, miss);
+        if (bal) {
+            int pos = 0;
+            if (lid == 0) pos = atomicAdd(&m.knnMissCount[lane], __popc(bal));
+            pos = __shfl_sync(0xffffffffu, pos, 0);
+            if (miss) m.knnMissList[slotBase + pos + __popc(bal & ((1u << lid) - 1))] = q;
+        }
+    }
+}
+
+__global__ void __launch_bounds__(256, 4) mo_search_kernel(MoDev m, int iter) {
+    const int lane = blockIdx.y, tid = threadIdx.x;
+    if (!m.state[lane * 16 + 6]) return;
+    const int nCorner = m.scanCounts[lane * 8 + 0], nQ = nCorner + m.scanCounts[lane * 8 + 4];
+    const int n = iter == 0 ? nQ : m.knnMissCount[lane];
+    const MapSinCos sc = map_sincos(m.transformTobeMapped + lane * 6);
+    const VhLane vhC = vh_lane(m.hashCornerMap, lane), vhS = vh_lane(m.hashSurfMap, lane);
+    const float4* qC = m.cornerLastDS + (size_t)lane * m.scanCornerCap;
+    const float4* qS = m.surfTotalLastDS + (size_t)lane * (m.scanSurfCap + m.scanOutlierCap);
+    const size_t slotBase = (size_t)lane * m.resBlocks * MO_RES_THREADS;
+    for (int i = blockIdx.x * 256 + tid; i < n; i += gridDim.x * 256) {
+        const int q = iter == 0 ? i : m.knnMissList[slotBase + i];
+        const bool corner = q < nCorner;
+        const float4 ps = map_transform(sc, corner ? qC[q] : qS[q - nCorner]);
+        float d2[5]; int idx[5]; int cand[VH_CACHE_K]; float rc2;
+        const int found = vh_knn5_fill(corner ? vhC : vhS, ps.x, ps.y, ps.z, 1.0f, d2, idx, cand, &rc2);
+#pragma unroll
+        for (int j = 0; j < VH_CACHE_K / 4; ++j)
+            m.knnCand[(slotBase + q) * (VH_CACHE_K / 4) + j] = make_int4(cand[4 * j], cand[4 * j + 1], cand[4 * j + 2], cand[4 * j + 3]);
+        m.knnMeta[slotBase + q] = make_float4(ps.x, ps.y, ps.z, rc2);
+        mo_store_result(m, slotBase + q, found, d2[4], idx);
+    }
+}
+
+__global__ void __launch_bounds__(MO_RES_THREADS, 4) mo_residual_kernel(MoDev m) {
+    const int lane = blockIdx.y, tid = threadIdx.x, lid = tid & 31, warp = tid >> 5;
     if (!m.state[lane * 16 + 6]) return;
     const int nCorner = m.scanCounts[lane * 8 + 0], nSurf = m.scanCounts[lane * 8 + 4];
     const MapSinCos sc = map_sincos(m.transformTobeMapped + lane * 6);
+    const float4* mapC = m.cornerFromMapDS + (size_t)lane * m.cornerDSCap;
+    const float4* mapS = m.surfFromMapDS + (size_t)lane * m.surfDSCap;
+    const size_t slotBase = (size_t)lane * m.resBlocks * MO_RES_THREADS;
     // a CTA takes the 256-query blocks blk = blockIdx.x, blockIdx.x + gridDim.x, ...; the partial sums stay per block
     // and warp (not per CTA) so the solve kernel adds them in the same order whatever the grid size
-    for (int blk = blockIdx.x / SUB; blk * MO_RES_THREADS < nCorner + nSurf; blk += gridDim.x / SUB) {
+    for (int blk = blockIdx.x; blk * MO_RES_THREADS < nCorner + nSurf; blk += gridDim.x) {
         const int q = blk * MO_RES_THREADS + tid;
         double acc[MO_ACC];
 #pragma unroll
         for (int k = 0; k < MO_ACC; ++k) acc[k] = 0.0;
         if (q < nCorner + nSurf) {
-            float cx, cy, cz, cd; bool ok; float4 o;
-            if (q < nCorner) {
-                o = m.cornerLastDS[(size_t)lane * m.scanCornerCap + q];
-                ok = mo_corner_residual(vh_lane(m.hashCornerMap, lane), m.cornerFromMapDS + (size_t)lane * m.cornerDSCap, sc, o, &cx, &cy, &cz, &cd);
-            } else {
-                o = m.surfTotalLastDS[(size_t)lane * (m.scanSurfCap + m.scanOutlierCap) + (q - nCorner)];
-                ok = mo_surf_residual(vh_lane(m.hashSurfMap, lane), m.surfFromMapDS + (size_t)lane * m.surfDSCap, sc, o, &cx, &cy, &cz, &cd);
-            }
+            const bool corner = q < nCorner;
+            const float4 o = corner ? m.cornerLastDS[(size_t)lane * m.scanCornerCap + q]
+                                    : m.surfTotalLastDS[(size_t)lane * (m.scanSurfCap + m.scanOutlierCap) + (q - nCorner)];
+            const float4 ps = map_transform(sc, o);
+            const int4 r0 = m.knnRes[(slotBase + q) * 2], r1 = m.knnRes[(slotBase + q) * 2 + 1];
+            const int idx[5] = {r0.x, r0.y, r0.z, r0.w, r1.x};
+            float cx, cy, cz, cd;
+            const bool ok = corner ? mo_corner_residual(mapC, ps, r1.z, __int_as_float(r1.y), idx, &cx, &cy, &cz, &cd)
+                                   : mo_surf_residual(mapS, ps, r1.z, __int_as_float(r1.y), idx, &cx, &cy, &cz, &cd);
             if (ok) mo_accumulate(acc, sc, o, cx, cy, cz, cd);
         }
-        // every warp writes its own 28 sums (no CTA barrier: the queries of a block differ a lot in length)
+        // every warp writes its own 28 sums
         double mine = 0.0;
 #pragma unroll
         for (int k = 0; k < MO_ACC; ++k) {
             double v = acc[k];
 #pragma unroll
-            for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);
+            for (int o2 = 16; o2 > 0; o2 >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o2);
             if (lid == k) mine = v;
         }
         if (lid < MO_ACC) m.partials[(((size_t)lane * m.resBlocks + blk) * (MO_RES_THREADS / 32) + warp) * MO_ACC + lid] = mine;
@@ -248,6 +320,7 @@ __global__ void __launch_bounds__(32) mo_solve_kernel(MoDev m, int iter) {
         const float deltaR = (float)sqrt(dr), deltaT = (float)sqrt(dt);
         if ((double)deltaR < 0.05 && (double)deltaT < 0.05) done = 1;
     }
+    m.knnMissCount[lane] = 0;
     m.state[lane * 16 + 3] = iter + 1; m.state[lane * 16 + 4] = rows;
     if (done || iter == 9) {
         m.state[lane * 16 + 6] = 0;

@@ -242,4 +242,106 @@ __device__ inline int vh_knn5(const VhLane& v, float x, float y, float z, float 
     return found < 5 ? found : 5;
 }
 
+// ---- 5-NN with a candidate cache for the later LM iterations of one mapping call ---------------------------------
+// scan2MapOptimization repeats the same queries up to 10 times while the pose moves by millimetres.  The first search
+// of a query (vh_knn5_fill) keeps its VH_CACHE_K nearest candidates, looking VH_CACHE_MARGIN beyond the acceptance
+// bound, together with the query position and the squared radius rc2 inside which that list is COMPLETE: the K-th
+// distance when K points were found, else the widened bound -- and never more than the distance to the nearest map
+// region outside the 27 visited cells.  A later iteration re-ranks the cached candidates at the new position
+// (vh_knn5_cached).  A point outside the list was at least sqrt(rc2) from the old position, hence at least
+// sqrt(rc2) - delta from the new one (delta = how far the query moved); when the new 5th distance -- or, with fewer
+// than five candidates inside the bound, the bound itself -- is smaller than that (with a millimetre of slack for
+// float rounding), the re-ranked list IS what vh_knn5 would return: same distances, same tie order, same count.
+// Otherwise the caller searches again, so the result never differs from vh_knn5.
+#ifndef LEGO_KNN_K
+#define LEGO_KNN_K 8
+#endif
+constexpr int VH_CACHE_K = LEGO_KNN_K;   // multiple of 4 (stored as int4s)
+constexpr float VH_CACHE_MARGIN = 0.1f;
+
+// Exact top VH_CACHE_K inside (sqrt(bound) + margin)^2, ties by original index.  d2 / idx: what vh_knn5(bound) returns.
+// cand[VH_CACHE_K]: original indices (-1 = none).
+__device__ inline int vh_knn5_fill(const VhLane& v, float x, float y, float z, float bound, float* d2, int* idx, int* cand, float* rc2) {
+    const float ux = x * v.invCell, uy = y * v.invCell, uz = z * v.invCell;
+    const float flx = floorf(ux), fly = floorf(uy), flz = floorf(uz);
+    const int cx = (int)flx, cy = (int)fly, cz = (int)flz;
+    const float cell = 1.0f / v.invCell;
+    const float lo[3] = {(ux - flx) * cell, (uy - fly) * cell, (uz - flz) * cell};
+    const float hi[3] = {cell - lo[0], cell - lo[1], cell - lo[2]};
+    const float wideR = sqrtf(bound) + VH_CACHE_MARGIN, wide = wideR * wideR;
+    float e2[VH_CACHE_K]; int ei[VH_CACHE_K];
+    int found = 0;
+#pragma unroll
+    for (int k = 0; k < VH_CACHE_K; ++k) { e2[k] = wide; ei[k] = 0x7fffffff; }
+    for (int o = 0; o < 27; ++o) {
+        const int code = VH_ORDER27[o];
+        const int dx = (code & 3) - 1, dy = ((code >> 2) & 3) - 1, dz = ((code >> 4) & 3) - 1;
+        const float gx = dx < 0 ? lo[0] : (dx > 0 ? hi[0] : 0.f);
+        const float gy = dy < 0 ? lo[1] : (dy > 0 ? hi[1] : 0.f);
+        const float gz = dz < 0 ? lo[2] : (dz > 0 ? hi[2] : 0.f);
+        const float boxD2 = gx * gx + gy * gy + gz * gz;
+        if (boxD2 > e2[VH_CACHE_K - 1] * 1.0001f + 1e-5f) continue;
+        const int s = vh_find(v.keys, v.H, vh_pack(cx + dx, cy + dy, cz + dz));
+        if (s < 0) continue;
+        const int e = v.start[s], b = e - v.count[s];
+        for (int t = b; t < e; ++t) {
+            const float4 a = v.sorted[t];
+            float d = vh_dist2(a, x, y, z);
+            int ai = __float_as_int(a.w);
+            if (d > e2[VH_CACHE_K - 1] || (d == e2[VH_CACHE_K - 1] && ai > ei[VH_CACHE_K - 1])) continue;
+            ++found;
+#pragma unroll
+            for (int k = 0; k < VH_CACHE_K; ++k) {
+                const bool lt = d < e2[k] || (d == e2[k] && ai < ei[k]);
+                if (lt) { const float td = e2[k]; const int ti = ei[k]; e2[k] = d; ei[k] = ai; d = td; ai = ti; }
+            }
+        }
+    }
+    int found5 = 0;
+#pragma unroll
+    for (int k = 0; k < 5; ++k) {
+        const bool in = ei[k] != 0x7fffffff && e2[k] <= bound;
+        d2[k] = in ? e2[k] : bound; idx[k] = in ? ei[k] : 0x7fffffff;
+        found5 += in ? 1 : 0;
+    }
+#pragma unroll
+    for (int k = 0; k < VH_CACHE_K; ++k) cand[k] = ei[k] == 0x7fffffff ? -1 : ei[k];
+    // everything nearer than `reach` lies inside the 27 visited cells
+    const float reach = cell + fminf(fminf(fminf(lo[0], hi[0]), fminf(lo[1], hi[1])), fminf(lo[2], hi[2]));
+    const float rc = fminf(found >= VH_CACHE_K ? sqrtf(e2[VH_CACHE_K - 1]) : wideR, reach);
+    *rc2 = rc * rc;
+    return found5;
+}
+
+// Re-ranks the cached candidates at the new query position.  Returns true when the outcome is proven to be what
+// vh_knn5(bound) returns there: d2 / idx hold it and *found5 = min(neighbours inside the bound, 5).
+__device__ inline bool vh_knn5_cached(const float4* __restrict__ cloud, const int* cand, float ox, float oy, float oz, float rc2,
+                                      float x, float y, float z, float bound, float* d2, int* idx, int* found5) {
+    int found = 0;
+#pragma unroll
+    for (int k = 0; k < 5; ++k) { d2[k] = bound; idx[k] = 0x7fffffff; }
+    float4 pts[VH_CACHE_K];
+#pragma unroll
+    for (int k = 0; k < VH_CACHE_K; ++k) pts[k] = cand[k] >= 0 ? cloud[cand[k]] : make_float4(0.f, 0.f, 0.f, 0.f);   // all gathers in flight
+#pragma unroll
+    for (int k = 0; k < VH_CACHE_K; ++k) {
+        const int ci = cand[k];
+        if (ci < 0) continue;
+        float d = vh_dist2(pts[k], x, y, z);
+        int ai = ci;
+        if (d > d2[4] || (d == d2[4] && ai > idx[4])) continue;
+        ++found;
+#pragma unroll
+        for (int j = 0; j < 5; ++j) {
+            const bool lt = d < d2[j] || (d == d2[j] && ai < idx[j]);
+            if (lt) { const float td = d2[j]; const int ti = idx[j]; d2[j] = d; idx[j] = ai; d = td; ai = ti; }
+        }
+    }
+    *found5 = found < 5 ? found : 5;
+    const float mx = x - ox, my = y - oy, mz = z - oz;
+    const float delta = sqrtf(mx * mx + my * my + mz * mz);
+    // d2[4] is the 5th distance, or still `bound` when fewer than five candidates lie inside the bound
+    return sqrtf(d2[4]) + delta + 1e-3f < sqrtf(rc2);
+}
+
 }  // namespace lego
