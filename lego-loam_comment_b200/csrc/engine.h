@@ -346,6 +346,7 @@ public:
     cudaEvent_t moStaged[2] = {nullptr, nullptr};
     MoRecord* moRecordsHost = nullptr;   // pinned [L]
     cudaEvent_t moRecordsReady = nullptr;
+    bool moKnnCache = true;          // LEGO_KNN_CACHE=0 searches the voxel hash in every LM iteration (parity check of the cache)
     bool moRecordsPending = false;
     bool moLastAny = false;
     std::vector<int> moActiveLast;   // per lane: the mapping body ran in the last step

@@ -48,6 +48,7 @@ VgSeg Engine::makeVgSeg(const float4* in, const int* nIn, float4* out, int* nOut
 void Engine::allocMapOptimization() {
     const size_t L = c.L, N = c.N, R = c.R;
     mo.maxKeyFrames = env_int("LEGO_MAX_KEYFRAMES", 640);
+    moKnnCache = env_int("LEGO_KNN_CACHE", 1) != 0;
     const size_t perKf = std::min<size_t>(N / 4, 16384);
     mo.poolCap = (int)std::min<size_t>((size_t)mo.maxKeyFrames * perKf, (size_t)INT_MAX / 2);
     mo.maxSel = 256;
@@ -382,8 +383,9 @@ void Engine::mapOptimizationBody(const std::vector<int>& active) {
 #else
                 const char *nR = "mo_rerank_kernel", *nS = "mo_search_kernel", *nF = "mo_residual_kernel";
 #endif
-                if (iter > 0) { ProfScope ps(this, nR); mo_rerank_kernel<<<gLater, 256, 0, stream>>>(mo); }
-                { ProfScope ps(this, nS); mo_search_kernel<<<iter == 0 ? gq : gLater, 256, 0, stream>>>(mo, iter); }
+                const bool all = iter == 0 || !moKnnCache;   // search every query / only those the cache could not answer
+                if (!all) { ProfScope ps(this, nR); mo_rerank_kernel<<<gLater, 256, 0, stream>>>(mo); }
+                { ProfScope ps(this, nS); mo_search_kernel<<<all ? gq : gLater, 256, 0, stream>>>(mo, all ? 0 : iter); }
                 { ProfScope ps(this, nF); mo_residual_kernel<<<g, MO_RES_THREADS, 0, stream>>>(mo); }
             }
             { ProfScope ps(this, "mo_solve_kernel"); mo_solve_kernel<<<c.L, 32, 0, stream>>>(mo, iter); }

@@ -107,3 +107,33 @@ def test_long_free_running_trajectory_stays_within_bar():
     worst, first_bit_diff = long_parity.run("vlp16", 300, 11, verbose=False)
     assert first_bit_diff is None, "bit-exact output differs first at %s" % (first_bit_diff,)
     assert worst["sum"] < POSE_TOL and worst["aft"] < POSE_TOL, worst
+
+
+def test_neighbour_cache_changes_nothing(monkeypatch):
+    """The scan-to-map 5-NN of LM iterations >= 1 is answered from a per-query candidate cache when that is provably exact
+    (csrc/voxel_hash.cuh).  With LEGO_KNN_CACHE=0 every iteration searches the voxel hash instead: poses, iteration
+    counts and row counts of the two runs must be bit-identical."""
+    sensor = "hdl32"
+    seq = SynthSequence(sensor, seed=17, scene="street", speed=6.0, dropout=0.01)
+    monkeypatch.setenv("LEGO_KNN_CACHE", "0")
+    plain = Pipeline(make_params(sensor), lanes=1, max_points=seq.cap)
+    monkeypatch.setenv("LEGO_KNN_CACHE", "1")
+    cached = Pipeline(make_params(sensor), lanes=1, max_points=seq.cap)
+    mapped = iters = 0
+    for k in range(34):
+        xyzi, ring = seq.scan(k)
+        x = np.zeros((1, seq.cap, 4), np.float32); x[0, :len(xyzi)] = xyzi
+        r = np.zeros((1, seq.cap), np.uint16); r[0, :len(ring)] = ring
+        out = []
+        for pl in (plain, cached):
+            pl.step(x, r, [len(xyzi)], [seq.stamp(k)], stage_mask=7)
+            poses, flags = pl.poses()
+            out.append((poses[0].copy(), int(flags[0]), pl.download("moState").copy(), pl.download("transformTobeMapped").copy()))
+        assert out[0][1] == out[1][1]
+        assert np.array_equal(out[0][0].view(np.uint32), out[1][0].view(np.uint32)), "scan %d: poses differ" % k
+        assert np.array_equal(out[0][2], out[1][2]), "scan %d: moState %s vs %s" % (k, out[0][2], out[1][2])
+        assert np.array_equal(out[0][3].view(np.uint32), out[1][3].view(np.uint32))
+        if out[0][1] & 8:
+            mapped += 1; iters += int(out[0][2][3])
+    assert mapped >= 6 and iters >= 2 * mapped, "too few LM iterations (%d in %d calls) for the cache to matter" % (iters, mapped)
+    plain.close(); cached.close()
