@@ -97,6 +97,17 @@ __device__ __forceinline__ MapSinCos map_sincos(const float* T) {
     m.tX = T[3]; m.tY = T[4]; m.tZ = T[5];
     return m;
 }
+// The same for a whole CTA: six threads evaluate one value each (the double-precision sin / cos restatements are costly
+// when every thread of every CTA repeats them), everybody reads the result.  Contains a __syncthreads().
+__device__ __forceinline__ MapSinCos map_sincos_cta(const float* T) {
+    __shared__ float sTrig[6];
+    if (threadIdx.x < 6) sTrig[threadIdx.x] = pm::sincosf_glibc(T[threadIdx.x >> 1], (threadIdx.x & 1) ^ 1);   // cos, sin, cos, sin, ...
+    __syncthreads();
+    MapSinCos m;
+    m.cRoll = sTrig[0]; m.sRoll = sTrig[1]; m.cPitch = sTrig[2]; m.sPitch = sTrig[3]; m.cYaw = sTrig[4]; m.sYaw = sTrig[5];
+    m.tX = T[3]; m.tY = T[4]; m.tZ = T[5];
+    return m;
+}
 // pointAssociateToMap (mapOptmization.cpp:513-527) and transformPointCloud (mapOptmization.cpp:545-575): same formula
 __device__ __forceinline__ float4 map_transform(const MapSinCos& m, float4 p) {
     const float x1 = m.cYaw * p.x - m.sYaw * p.y;

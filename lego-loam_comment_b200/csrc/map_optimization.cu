@@ -177,7 +177,7 @@ __global__ void __launch_bounds__(256) mo_rerank_kernel(MoDev m) {
     const int lane = blockIdx.y, tid = threadIdx.x, lid = tid & 31;
     if (!m.state[lane * 16 + 6]) return;
     const int nCorner = m.scanCounts[lane * 8 + 0], nQ = nCorner + m.scanCounts[lane * 8 + 4];
-    const MapSinCos sc = map_sincos(m.transformTobeMapped + lane * 6);
+    const MapSinCos sc = map_sincos_cta(m.transformTobeMapped + lane * 6);
     const float4* mapC = m.cornerFromMapDS + (size_t)lane * m.cornerDSCap;
     const float4* mapS = m.surfFromMapDS + (size_t)lane * m.surfDSCap;
     const float4* qC = m.cornerLastDS + (size_t)lane * m.scanCornerCap;
@@ -217,7 +217,7 @@ __global__ void __launch_bounds__(256, 4) mo_search_kernel(MoDev m, int iter) {
     if (!m.state[lane * 16 + 6]) return;
     const int nCorner = m.scanCounts[lane * 8 + 0], nQ = nCorner + m.scanCounts[lane * 8 + 4];
     const int n = iter == 0 ? nQ : m.knnMissCount[lane];
-    const MapSinCos sc = map_sincos(m.transformTobeMapped + lane * 6);
+    const MapSinCos sc = map_sincos_cta(m.transformTobeMapped + lane * 6);
     const VhLane vhC = vh_lane(m.hashCornerMap, lane), vhS = vh_lane(m.hashSurfMap, lane);
     const float4* qC = m.cornerLastDS + (size_t)lane * m.scanCornerCap;
     const float4* qS = m.surfTotalLastDS + (size_t)lane * (m.scanSurfCap + m.scanOutlierCap);
@@ -240,7 +240,7 @@ __global__ void __launch_bounds__(MO_RES_THREADS, 4) mo_residual_kernel(MoDev m)
     const int lane = blockIdx.y, tid = threadIdx.x, lid = tid & 31, warp = tid >> 5;
     if (!m.state[lane * 16 + 6]) return;
     const int nCorner = m.scanCounts[lane * 8 + 0], nSurf = m.scanCounts[lane * 8 + 4];
-    const MapSinCos sc = map_sincos(m.transformTobeMapped + lane * 6);
+    const MapSinCos sc = map_sincos_cta(m.transformTobeMapped + lane * 6);
     const float4* mapC = m.cornerFromMapDS + (size_t)lane * m.cornerDSCap;
     const float4* mapS = m.surfFromMapDS + (size_t)lane * m.surfDSCap;
     const size_t slotBase = (size_t)lane * m.resBlocks * MO_RES_THREADS;

@@ -23,6 +23,7 @@ struct OdoShared {
     int keepGoing;
     int ringOff[132];
     int nextQuery;             // dynamic distribution of the correspondence searches over the warps
+    float trig[6];             // sin / cos of transformCur's three angles for the current iteration (srx crx sry cry srz crz)
     double red[ODO_WARPS][10];
 };
 
@@ -69,6 +70,8 @@ __device__ int odo_phase(OdoShared& sh, float4* sel, const float4* __restrict__ 
         itersDone = iter + 1;
         for (int q = tid; q < Q; q += ODO_THREADS) sel[q] = pose::transform_to_start(feats[q], sh.T);
         if (tid == 0) sh.nextQuery = 0;
+        // six otherwise idle threads evaluate the iteration's sin / cos (double-precision restatements of glibc) once for the CTA
+        if (tid >= ODO_THREADS - 6) { const int k = tid - (ODO_THREADS - 6); sh.trig[k] = pm::sincosf_glibc(sh.T[k >> 1], k & 1); }
         __syncthreads();
         if (iter % 5 == 0) {
             // one query per warp at a time, handed out dynamically: the searches differ a lot in length
@@ -123,8 +126,7 @@ __device__ int odo_phase(OdoShared& sh, float4* sel, const float4* __restrict__ 
             __syncthreads();
         }
         // ---- residuals and normal equations ----
-        const float srx = pm::sinf_glibc(sh.T[0]), crx = pm::cosf_glibc(sh.T[0]), sry = pm::sinf_glibc(sh.T[1]), cry = pm::cosf_glibc(sh.T[1]);
-        const float srz = pm::sinf_glibc(sh.T[2]), crz = pm::cosf_glibc(sh.T[2]);
+        const float srx = sh.trig[0], crx = sh.trig[1], sry = sh.trig[2], cry = sh.trig[3], srz = sh.trig[4], crz = sh.trig[5];
         const float tx = sh.T[3], ty = sh.T[4], tz = sh.T[5];
         double acc[10];
 #pragma unroll
