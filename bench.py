@@ -49,10 +49,11 @@ def parse_args():
 
 
 def default_lanes(sensor):
-    """Multiples of the 148 SMs: 4 sequences per SM for 16 rings, 2 for 32, 1 for the dense sensors (~5x the points per lane)."""
+    """Multiples of the 148 SMs: 4 sequences per SM for 16 rings, 2 for 32 and 64 (64 x 2083: 33.9 k scans/s against 31.7 k with
+    1 per SM), 1 for 128 rings (2 per SM do not fit in 180 GB)."""
     if sensor in ("vlp16", "vlp16_noring"):
         return 592
-    return 296 if sensor == "hdl32" else 148
+    return 296 if sensor in ("hdl32", "hdl64") else 148
 
 
 def dist_env():
