@@ -183,3 +183,12 @@ void Engine::integrateTransformationPublishCloudsLast() {
 }
 
 }  // namespace lego
+
+#ifdef LEGO_ODO_PROF
+extern "C" int lego_debug_odo_prof(unsigned long long* out8) {
+    return cudaMemcpyFromSymbol(out8, lego::g_odo_prof, sizeof(unsigned long long) * 8) == cudaSuccess ? 0 : -1;
+}
+extern "C" int lego_debug_odo_prof2(unsigned long long* out8) {
+    return cudaMemcpyFromSymbol(out8, lego::g_odo_prof2, sizeof(unsigned long long) * 8) == cudaSuccess ? 0 : -1;
+}
+#endif

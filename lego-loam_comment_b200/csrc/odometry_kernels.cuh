@@ -44,6 +44,38 @@ __device__ __forceinline__ Cand cand_warp_min(Cand b) {
     return b;
 }
 
+// Exact nearest neighbour of a small cloud by one warp: every lane strides over the points (coalesced, four loads in
+// flight), then the warp takes the minimum of (distance, index) -- the rule of vh_nearest / vh_nearest_warp.  Measured
+// (clock64 per phase, -DLEGO_ODO_PROF): the 1-NN shell walk is ~4000 cycles per query and 52 % of this kernel; on the ~500-point
+// corner cloud of a 16-ring scan the scan takes ~2000.  That shortens a lone handle's step (94.2 k -> 96.3 k scans/s with 296
+// lanes) but costs more instructions, and with four handles saturating the GPU the headline drops (119.1 k -> 117.3 k, twice
+// each): off by default, -DLEGO_ODO_BRUTE_MAX=1024 (LEGO_NVCC_DEFS) turns it on for latency-bound use (few lanes).
+#ifndef LEGO_ODO_BRUTE_MAX
+#define LEGO_ODO_BRUTE_MAX 0
+#endif
+constexpr int ODO_BRUTE_MAX = LEGO_ODO_BRUTE_MAX;
+__device__ inline int nearest_brute_warp(const float4* __restrict__ cloud, int M, float x, float y, float z, float maxD2) {
+    const int lid = threadIdx.x & 31;
+    float best = maxD2; int bestI = 0x7fffffff;
+    auto offer = [&](const float4& a, int j) {
+        const float d = vh_dist2(a, x, y, z);
+        if (d < best || (d == best && bestI != 0x7fffffff && j < bestI)) { best = d; bestI = j; }
+    };
+    int j = lid;
+    for (; j + 96 < M; j += 128) {
+        const float4 a0 = cloud[j], a1 = cloud[j + 32], a2 = cloud[j + 64], a3 = cloud[j + 96];
+        offer(a0, j); offer(a1, j + 32); offer(a2, j + 64); offer(a3, j + 96);
+    }
+    for (; j < M; j += 32) offer(cloud[j], j);
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) {
+        const float od = __shfl_xor_sync(0xffffffffu, best, o);
+        const int oi = __shfl_xor_sync(0xffffffffu, bestI, o);
+        if (od < best || (od == best && oi < bestI)) { best = od; bestI = oi; }
+    }
+    return bestI == 0x7fffffff ? -1 : bestI;
+}
+
 // Start offset of every ring inside a ring-ordered cloud (intensity = ring after TransformToEnd).
 __device__ inline void build_ring_offsets(const float4* __restrict__ cloud, int M, int R, int* off) {
     for (int r = threadIdx.x; r <= R + 2; r += blockDim.x) off[r] = M;
@@ -58,13 +90,24 @@ __device__ inline void build_ring_offsets(const float4* __restrict__ cloud, int 
 
 // One LM phase.  SURF: features = surfPointsFlat, unknowns [rx, rz, ty] (featureAssociation.cpp:1155-1377);
 // otherwise features = cornerPointsSharp, unknowns [ry, tx, tz] (featureAssociation.cpp:1044-1153, 1379-1478).
+#ifdef LEGO_ODO_PROF
+static __device__ unsigned long long g_odo_prof2[8];   // per warp: nearest cycles, scan cycles, queries, misses, surf nearest, surf scan
+static __device__ unsigned long long g_odo_prof[8];   // ring offsets, transform, search, rows + reduce, solve, searches, iterations
+#define ODO_T(i) if (threadIdx.x == 0) { const long long t_ = clock64(); atomicAdd(&g_odo_prof[i], (unsigned long long)(t_ - t0_)); t0_ = t_; }
+#else
+#define ODO_T(i)
+#endif
 template <bool SURF>
 __device__ int odo_phase(OdoShared& sh, float4* sel, const float4* __restrict__ feats, int Q,
                           const float4* __restrict__ last, int M, const VhLane& vh, int* ind, const Consts& c) {
     constexpr int K = SURF ? 3 : 2;
     const int tid = threadIdx.x, lid = tid & 31, warp = tid >> 5;
     const float maxD2 = c.nearestFeatureSearchSqDist;
+#ifdef LEGO_ODO_PROF
+    long long t0_ = clock64();
+#endif
     build_ring_offsets(last, M, c.R, sh.ringOff);
+    ODO_T(0)
     int itersDone = 0;
     for (int iter = 0; iter < 25; ++iter) {
         itersDone = iter + 1;
@@ -73,6 +116,7 @@ __device__ int odo_phase(OdoShared& sh, float4* sel, const float4* __restrict__ 
         // six otherwise idle threads evaluate the iteration's sin / cos (double-precision restatements of glibc) once for the CTA
         if (tid >= ODO_THREADS - 6) { const int k = tid - (ODO_THREADS - 6); sh.trig[k] = pm::sincosf_glibc(sh.T[k >> 1], k & 1); }
         __syncthreads();
+        ODO_T(1)
         if (iter % 5 == 0) {
             // one query per warp at a time, handed out dynamically: the searches differ a lot in length
             while (true) {
@@ -82,7 +126,14 @@ __device__ int odo_phase(OdoShared& sh, float4* sel, const float4* __restrict__ 
                 if (q >= Q) break;
                 float d2near;
                 const float4 pq = sel[q];
-                const int closest = vh_nearest_warp(vh, pq.x, pq.y, pq.z, maxD2, 1.0f, &d2near);
+#ifdef LEGO_ODO_PROF
+                const long long w0_ = clock64();
+#endif
+                const int closest = M <= ODO_BRUTE_MAX ? nearest_brute_warp(last, M, pq.x, pq.y, pq.z, maxD2)
+                                                       : vh_nearest_warp(vh, pq.x, pq.y, pq.z, maxD2, 1.0f, &d2near);
+#ifdef LEGO_ODO_PROF
+                const long long w1_ = clock64();
+#endif
                 if (lid == 0) ind[q * K] = closest;
                 Cand b2 = {maxD2, 0x7fffffff, -1}, b3 = {maxD2, 0x7fffffff, -1};
                 if (closest >= 0) {
@@ -122,8 +173,15 @@ __device__ int odo_phase(OdoShared& sh, float4* sel, const float4* __restrict__ 
                 b2 = cand_warp_min(b2);
                 if (SURF) b3 = cand_warp_min(b3);
                 if (lid == 0) { ind[q * K + 1] = b2.j; if (SURF) ind[q * K + 2] = b3.j; }
+#ifdef LEGO_ODO_PROF
+                if (lid == 0) { const long long w2_ = clock64(); atomicAdd(&g_odo_prof2[SURF ? 4 : 0], (unsigned long long)(w1_ - w0_)); atomicAdd(&g_odo_prof2[SURF ? 5 : 1], (unsigned long long)(w2_ - w1_)); atomicAdd(&g_odo_prof2[SURF ? 6 : 2], 1ull); if (closest < 0) atomicAdd(&g_odo_prof2[3], 1ull); }
+#endif
             }
             __syncthreads();
+            ODO_T(2)
+#ifdef LEGO_ODO_PROF
+            if (threadIdx.x == 0) atomicAdd(&g_odo_prof[5], 1ull);
+#endif
         }
         // ---- residuals and normal equations ----
         const float srx = sh.trig[0], crx = sh.trig[1], sry = sh.trig[2], cry = sh.trig[3], srz = sh.trig[4], crz = sh.trig[5];
@@ -197,6 +255,7 @@ __device__ int odo_phase(OdoShared& sh, float4* sel, const float4* __restrict__ 
 #pragma unroll
         for (int k = 0; k < 10; ++k) { const double v = warp_sum_d(acc[k]); if (lid == 0) sh.red[warp][k] = v; }
         __syncthreads();
+        ODO_T(3)
         if (tid == 0) {
             double s[10];
             for (int k = 0; k < 10; ++k) { s[k] = 0.0; for (int w = 0; w < ODO_WARPS; ++w) s[k] += sh.red[w][k]; }
@@ -224,6 +283,10 @@ __device__ int odo_phase(OdoShared& sh, float4* sel, const float4* __restrict__ 
             sh.keepGoing = keep;
         }
         __syncthreads();
+        ODO_T(4)
+#ifdef LEGO_ODO_PROF
+        if (threadIdx.x == 0) atomicAdd(&g_odo_prof[6], 1ull);
+#endif
         if (!sh.keepGoing) break;
     }
     __syncthreads();
