@@ -35,7 +35,7 @@ void Engine::allocOdometry() {
     fa.cornerInd = alloc<int>(L * R * 12 * 2); fa.surfInd = alloc<int>(L * R * 24 * 3);
     fa.partials = alloc<double>(L * 16); fa.tickets = alloc<unsigned int>(L);
     fa.outlierLast = alloc<float4>(L * c.Ocap); fa.flags = alloc<int>(L);
-    fa.hashCorner = allocHash(c.R * 120, 1.0f, fa.lastCounts + 0, 4); fa.hashSurf = allocHash(c.N, 1.0f, fa.lastCounts + 1, 4);
+    fa.hashCorner = allocHash(c.R * 120, ODO_CORNER_CELL, fa.lastCounts + 0, 4); fa.hashSurf = allocHash(c.N, 1.0f, fa.lastCounts + 1, 4);
     fa_init_state_kernel<<<(c.L + 63) / 64, 64, 0, stream>>>(fa, c.L);
 }
 

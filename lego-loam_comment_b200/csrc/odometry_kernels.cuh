@@ -15,6 +15,10 @@ namespace lego {
 constexpr int ODO_THREADS = 512;
 constexpr int ODO_WARPS = ODO_THREADS / 32;
 constexpr int ODO_TE_BLOCKS = 24;
+#ifndef LEGO_ODO_CORNER_CELL
+#define LEGO_ODO_CORNER_CELL 4.0f
+#endif
+constexpr float ODO_CORNER_CELL = LEGO_ODO_CORNER_CELL;   // voxel-hash cell edge of the (sparse) corner cloud, metres
 
 struct OdoShared {
     float T[6];
@@ -130,7 +134,7 @@ __device__ int odo_phase(OdoShared& sh, float4* sel, const float4* __restrict__ 
                 const long long w0_ = clock64();
 #endif
                 const int closest = M <= ODO_BRUTE_MAX ? nearest_brute_warp(last, M, pq.x, pq.y, pq.z, maxD2)
-                                                       : vh_nearest_warp(vh, pq.x, pq.y, pq.z, maxD2, 1.0f, &d2near);
+                                                       : vh_nearest_warp(vh, pq.x, pq.y, pq.z, maxD2, SURF ? 1.0f : ODO_CORNER_CELL, &d2near);
 #ifdef LEGO_ODO_PROF
                 const long long w1_ = clock64();
 #endif
