@@ -61,6 +61,9 @@ typedef struct lego_params {
     float historyKeyframeSearchRadius;       /* utility.h:132 (7.0)                                      */
     int historyKeyframeSearchNum;            /* utility.h:133 (25)                                       */
     float historyKeyframeFitnessScore;       /* utility.h:134 (0.3)                                      */
+    /* capacity of the handle (the reference's std::vector / deque of key frames grows without bound,
+     * mapOptmization.cpp:1443-1453): key frames a sequence may save before LEGO_ERR_CAPACITY; 0 = 640 */
+    int maxKeyFrames;
 } lego_params;
 
 /* A cloud living on the device (dev) with an optional host mirror (host, may be NULL). Valid until the next
@@ -153,7 +156,13 @@ int lego_tf_aft_mapped(lego_tf* h, const float transformAftMapped[6], const floa
 
 /* ---------------------------------------------------------------- chained, batched pipeline */
 typedef struct lego_pipeline lego_pipeline;
-/* lanes independent sequences processed in lock step; max_points = capacity per scan (0 = N_SCAN*Horizon_SCAN+slack) */
+/* lanes independent sequences processed in lock step; max_points = capacity per scan (0 = N_SCAN*Horizon_SCAN+slack).
+ * Capacity errors: a scan with more than max_points points, or npts > stride_points, fails the step with
+ * LEGO_ERR_CAPACITY before anything is enqueued.  A lane that runs out of key-frame pool (lego_params.maxKeyFrames) or
+ * local-map capacity is reported by the first lego_pipeline_step / step_lanes that learns of it (the device reports
+ * one mapping call late): that call and every later one returns LEGO_ERR_CAPACITY with the lane in lego_last_error();
+ * the step was still enqueued, but from then on that lane maps against a truncated map and no longer follows the
+ * reference. */
 int lego_pipeline_create(const lego_params* p, int lanes, int max_points, lego_pipeline** out);
 int lego_pipeline_destroy(lego_pipeline* h);
 /* One scan for every lane.  xyzi: lanes * stride_points * 4 floats, ring: lanes * stride_points, npts: lanes
@@ -162,6 +171,21 @@ int lego_pipeline_destroy(lego_pipeline* h);
  * read with lego_pipeline_download: "transformMapped" 6 floats, "integratedToInit" 7 floats, per lane). */
 int lego_pipeline_step(lego_pipeline* h, const float* xyzi, const uint16_t* ring, const int* npts,
                        int stride_points, const double* stamps, int src_on_device, int stage_mask);
+/* Same step with ONE POINTER PER LANE and no padding on the wire: xyz[l] points at npts[l] points of lane l,
+ * floats_per_point = 4 (x y z intensity, like lego_pipeline_step) or 3 (x y z packed -- ImageProjection never reads the
+ * input intensity, imageProjection.cpp:248-255 overwrites it); ring[l] at npts[l] uint16 (ring may be NULL without
+ * useCloudRing).  The pointer TABLES are host memory; with src_on_device = 1 the pointers in them are device pointers.
+ * Host sources: exactly npts[l] * (4 * floats_per_point + 2) bytes per lane cross PCIe.
+ *
+ * Input lifetime (both step forms): host buffers are copied asynchronously on the handle's copy stream -- they must
+ * stay valid and unmodified until lego_pipeline_input_wait() returns (or any later synchronising call on the handle:
+ * lego_pipeline_sync, get_poses, the poses_wait of this step).  Device buffers are read in place by kernels on the
+ * handle's own stream, which is NOT ordered against the caller's streams: the data must be complete before the call
+ * (synchronise the producing stream first) and must not be rewritten before lego_pipeline_input_wait() returns. */
+int lego_pipeline_step_lanes(lego_pipeline* h, const float* const* xyz, const uint16_t* const* ring, const int* npts,
+                             int floats_per_point, const double* stamps, int src_on_device, int stage_mask);
+/* Blocks until the input buffers handed to the last step may be refilled (host: copied; device: consumed). */
+int lego_pipeline_input_wait(lego_pipeline* h);
 /* One /imu/data message for one lane: delivered to that lane's FeatureAssociation and mapOptimization imuHandler
  * (featureAssociation.cpp:431-459, mapOptmization.cpp:643-652).  Call it before the lego_pipeline_step of the scan during
  * which the message would have arrived (the reference's subscribers fill the ring buffer between two scans). */

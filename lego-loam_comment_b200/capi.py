@@ -16,7 +16,7 @@ EXPORTED = [
     "lego_ip_create", "lego_ip_destroy", "lego_ip_process",
     "lego_fa_create", "lego_fa_destroy", "lego_fa_process",
     "lego_mo_create", "lego_mo_destroy", "lego_mo_process",
-    "lego_pipeline_create", "lego_pipeline_destroy", "lego_pipeline_step", "lego_pipeline_get_poses", "lego_pipeline_poses_async", "lego_pipeline_poses_wait",
+    "lego_pipeline_create", "lego_pipeline_destroy", "lego_pipeline_step", "lego_pipeline_step_lanes", "lego_pipeline_input_wait", "lego_pipeline_get_poses", "lego_pipeline_poses_async", "lego_pipeline_poses_wait",
     "lego_pipeline_sync", "lego_pipeline_launch_count", "lego_pipeline_download", "lego_pipeline_upload",
     "lego_pipeline_timer_record", "lego_pipeline_timer_elapsed", "lego_pipeline_timer_elapsed_between", "lego_pipeline_profile", "lego_pipeline_profile_read",
     "lego_tf_create", "lego_tf_destroy", "lego_tf_laser_odometry", "lego_tf_aft_mapped",
@@ -45,6 +45,9 @@ def load():
         lib.lego_pipeline_destroy.argtypes = [ctypes.c_void_p]
         lib.lego_pipeline_step.argtypes = [ctypes.c_void_p, ctypes.c_void_p, ctypes.c_void_p, ctypes.c_void_p, ctypes.c_int,
                                            ctypes.c_void_p, ctypes.c_int, ctypes.c_int]
+        lib.lego_pipeline_step_lanes.argtypes = [ctypes.c_void_p, ctypes.c_void_p, ctypes.c_void_p, ctypes.c_void_p, ctypes.c_int,
+                                                 ctypes.c_void_p, ctypes.c_int, ctypes.c_int]
+        lib.lego_pipeline_input_wait.argtypes = [ctypes.c_void_p]
         lib.lego_pipeline_sync.argtypes = [ctypes.c_void_p]
         lib.lego_pipeline_launch_count.argtypes = [ctypes.c_void_p]
         lib.lego_pipeline_launch_count.restype = ctypes.c_long
@@ -181,6 +184,21 @@ class Pipeline:
             xp, rp = xyzi.ctypes.data, (None if ring is None else ring.ctypes.data)
         _check(self.lib.lego_pipeline_step(self.h, xp, rp, npts.ctypes.data, int(stride_points), stamps.ctypes.data,
                                            1 if on_device else 0, stage_mask), "lego_pipeline_step")
+
+    def step_lanes(self, xyz_ptrs, ring_ptrs, npts, stamps, floats_per_point=4, stage_mask=7, on_device=False):
+        """lego_pipeline_step_lanes: xyz_ptrs / ring_ptrs = uint64[lanes] tables of per-lane addresses (host memory, or device
+        memory when on_device); only npts[l] points of lane l are read."""
+        npts = np.ascontiguousarray(npts, np.int32)
+        stamps = np.ascontiguousarray(stamps, np.float64)
+        xp = np.ascontiguousarray(xyz_ptrs, np.uint64)
+        rp = None if ring_ptrs is None else np.ascontiguousarray(ring_ptrs, np.uint64)
+        assert xp.shape == (self.lanes,) and npts.shape == (self.lanes,) and stamps.shape == (self.lanes,)
+        _check(self.lib.lego_pipeline_step_lanes(self.h, xp.ctypes.data, None if rp is None else rp.ctypes.data, npts.ctypes.data,
+                                                 int(floats_per_point), stamps.ctypes.data, 1 if on_device else 0, stage_mask),
+               "lego_pipeline_step_lanes")
+
+    def input_wait(self):
+        _check(self.lib.lego_pipeline_input_wait(self.h), "lego_pipeline_input_wait")
 
     def imu(self, lane, stamp, orientation_xyzw, angular_velocity, linear_acceleration):
         """one sensor_msgs/Imu message for one lane (lego_pipeline_imu)"""

@@ -1,5 +1,6 @@
 // C ABI (include/lego_b200.h) over lego::Engine.  Exceptions never cross the boundary: every entry point
 // converts them into an error code and a message retrievable with lego_last_error().
+#include <cstdio>
 #include <cstring>
 #include <new>
 #include <stdexcept>
@@ -14,6 +15,7 @@ struct lego_ip { Engine* e; std::vector<float> h_seg, h_outlier, h_range; std::v
 #define LEGO_TRY try {
 #define LEGO_CATCH \
     } catch (const std::length_error& ex) { lego::set_last_error(ex.what()); return LEGO_ERR_CAPACITY; } \
+      catch (const std::invalid_argument& ex) { lego::set_last_error(ex.what()); return LEGO_ERR_ARG; } \
       catch (const std::bad_alloc&) { lego::set_last_error("out of host memory"); return LEGO_ERR_CUDA; } \
       catch (const std::exception& ex) { if (lego::last_error().empty()) lego::set_last_error(ex.what()); return LEGO_ERR_CUDA; }
 
@@ -42,15 +44,10 @@ int lego_pipeline_destroy(lego_pipeline* h) {
     delete h->e; delete h;
     return LEGO_OK;
 }
-int lego_pipeline_step(lego_pipeline* h, const float* xyzi, const uint16_t* ring, const int* npts, int stride_points,
-                       const double* stamps, int src_on_device, int stage_mask) {
-    if (!h || !xyzi || !npts || !stamps) return LEGO_ERR_ARG;
+// the stages of one scan for every lane, after the input was handed to the engine
+static int run_stages(lego_pipeline* h, int stage_mask) {
     Engine& e = *h->e;
-    if (e.c.useRing && !ring) return LEGO_ERR_ARG;
-    LEGO_TRY
-    h->stamps.assign(stamps, stamps + e.c.L);
     if (stage_mask & 1) {
-        e.uploadScan(xyzi, ring, npts, stride_points, src_on_device != 0);
         e.projectPointCloud();
         e.groundRemoval();
         e.cloudSegmentation();
@@ -68,8 +65,46 @@ int lego_pipeline_step(lego_pipeline* h, const float* xyzi, const uint16_t* ring
         if ((stage_mask & 8) && e.moLastAny) e.transformFusionAftMapped();
     } else e.moActiveLast.assign(e.c.L, 0);
     lego::cuda_check(cudaGetLastError(), "kernel launch");
+    // capacity overflows of mapOptimization (key-frame pool, selection table, local-map buffers): sticky per lane
+    const int bad = e.firstCapacityError();
+    if (bad >= 0) {
+        char msg[200];
+        snprintf(msg, sizeof msg, "lane %d: mapOptimization capacity exceeded (bits 0x%x: 1 key-frame pool / maxKeyFrames, 2 surrounding key frames, 4 local-map points)",
+                 bad, e.moHost[bad].lastError);
+        lego::set_last_error(msg);
+        return LEGO_ERR_CAPACITY;
+    }
     return LEGO_OK;
+}
+
+int lego_pipeline_step(lego_pipeline* h, const float* xyzi, const uint16_t* ring, const int* npts, int stride_points,
+                       const double* stamps, int src_on_device, int stage_mask) {
+    if (!h || !xyzi || !npts || !stamps) return LEGO_ERR_ARG;
+    Engine& e = *h->e;
+    if (e.c.useRing && !ring) return LEGO_ERR_ARG;
+    LEGO_TRY
+    h->stamps.assign(stamps, stamps + e.c.L);
+    if (stage_mask & 1) e.uploadScan(xyzi, ring, npts, stride_points, src_on_device != 0);
+    return run_stages(h, stage_mask);
     LEGO_CATCH
+}
+int lego_pipeline_step_lanes(lego_pipeline* h, const float* const* xyz, const uint16_t* const* ring, const int* npts,
+                             int floats_per_point, const double* stamps, int src_on_device, int stage_mask) {
+    if (!h || !xyz || !npts || !stamps || (floats_per_point != 3 && floats_per_point != 4)) {
+        lego::set_last_error("lego_pipeline_step_lanes: null argument or floats_per_point not 3 / 4");
+        return LEGO_ERR_ARG;
+    }
+    Engine& e = *h->e;
+    if (e.c.useRing && !ring) return LEGO_ERR_ARG;
+    LEGO_TRY
+    h->stamps.assign(stamps, stamps + e.c.L);
+    if (stage_mask & 1) e.uploadScanLanes(xyz, ring, npts, floats_per_point, src_on_device != 0);
+    return run_stages(h, stage_mask);
+    LEGO_CATCH
+}
+int lego_pipeline_input_wait(lego_pipeline* h) {
+    if (!h) return LEGO_ERR_ARG;
+    LEGO_TRY h->e->inputWait(); return LEGO_OK; LEGO_CATCH
 }
 int lego_pipeline_imu(lego_pipeline* h, int lane, double stamp, const double orientation_xyzw[4], const double angular_velocity[3],
                       const double linear_acceleration[3]) {

@@ -50,7 +50,7 @@ Engine::Engine(const lego_params& p, int lanes, int max_points) : params(p) {
         cuda_check(cudaEventCreateWithFlags(&evConsumed[b], cudaEventDisableTiming), "event");
         cuda_check(cudaMallocHost(reinterpret_cast<void**>(&h_pin[b]), 2 * tbl + sizeof(int) * L), "cudaMallocHost");
     }
-    ip.in_xyzi = d_ptr_xyzi[0]; ip.in_ring = d_ptr_ring[0]; ip.npts = d_npts[0];
+    ip.in_xyzi = d_ptr_xyzi[0]; ip.in_ring = d_ptr_ring[0]; ip.npts = d_npts[0]; ip.in_floats = 4;
     ip.owner = alloc<int>(L * N); ip.rangeMat = alloc<float>(L * N); ip.fullCloud = alloc<float4>(L * N);
     ip.groundMat = alloc<int8_t>(L * N); ip.labelMat = alloc<int>(L * N); ip.parent = alloc<int>(L * N);
     ip.compSize = alloc<int>(L * N); ip.runLen = alloc<int>(L * N); ip.cellClass = alloc<unsigned char>(L * N); ip.compRows = alloc<uint32_t>(L * N * c.rowWords); ip.rowCounts = alloc<int>(L * R * 4);
@@ -139,19 +139,41 @@ float Engine::timerElapsed(int a, int b) {
 void Engine::sync() { cuda_check(cudaStreamSynchronize(stream), "stream sync"); }
 
 // copyPointCloud (imageProjection.cpp:163-179): the host message becomes device arrays.  Host sources are copied into
-// one of two staging buffers on a separate copy stream, so the upload of scan k+1 overlaps the processing of scan k;
-// device sources are used in place through the per-lane pointer table (no copy at all).
-void Engine::uploadScan(const float* xyzi, const uint16_t* ring, const int* npts, int stride_points, bool src_on_device) {
-    for (int l = 0; l < c.L; ++l) if (npts[l] < 0 || (!src_on_device && npts[l] > c.Pcap)) { set_last_error("scan larger than max_points"); throw std::length_error("capacity"); }
+// one of IN_SLOTS staging buffers on a separate copy stream, so the uploads of the next scans overlap the processing of
+// this one; device sources are used in place through the per-lane pointer table (no copy at all).
+// Contract (include/lego_b200.h): host sources must stay valid and unmodified until lego_pipeline_input_wait() returns
+// (or the next synchronising call); device sources until the step has run.
+int Engine::beginUpload(const int* npts, bool src_on_device) {
+    // the projection grid covers Pcap points per lane, whatever memory the points live in
+    for (int l = 0; l < c.L; ++l) if (npts[l] < 0 || npts[l] > c.Pcap) throw std::length_error("scan larger than max_points (or negative point count)");
+    curInOnDevice = src_on_device;
     const int b = inBuf; inBuf = (inBuf + 1) % IN_SLOTS;
-    const size_t tbl = sizeof(void*) * (size_t)c.L;
     // the staging buffers / pinned tables of slot b were last used IN_SLOTS steps ago: wait until that step consumed them
     cuda_check(cudaEventSynchronize(evConsumed[b]), "event sync");
+    return b;
+}
+
+void Engine::finishUpload(int b, const int* npts, int floats_per_point) {
+    const size_t tbl = sizeof(void*) * (size_t)c.L;
+    int* hn = reinterpret_cast<int*>(h_pin[b] + 2 * tbl);
+    for (int l = 0; l < c.L; ++l) hn[l] = npts[l];
+    cuda_check(cudaMemcpyAsync(d_ptr_xyzi[b], h_pin[b], tbl, cudaMemcpyHostToDevice, copyStream), "upload table");
+    cuda_check(cudaMemcpyAsync(d_ptr_ring[b], h_pin[b] + tbl, tbl, cudaMemcpyHostToDevice, copyStream), "upload table");
+    cuda_check(cudaMemcpyAsync(d_npts[b], hn, sizeof(int) * c.L, cudaMemcpyHostToDevice, copyStream), "upload npts");
+    cuda_check(cudaEventRecord(evCopied[b], copyStream), "event record");
+    cuda_check(cudaStreamWaitEvent(stream, evCopied[b], 0), "stream wait");
+    ip.in_xyzi = d_ptr_xyzi[b]; ip.in_ring = d_ptr_ring[b]; ip.npts = d_npts[b]; ip.in_floats = floats_per_point;
+    curIn = b;
+}
+
+void Engine::uploadScan(const float* xyzi, const uint16_t* ring, const int* npts, int stride_points, bool src_on_device) {
+    if (stride_points < 0) throw std::invalid_argument("negative stride_points");
+    for (int l = 0; l < c.L; ++l) if (npts[l] > stride_points) throw std::length_error("npts larger than stride_points");
+    const int b = beginUpload(npts, src_on_device);
+    const size_t tbl = sizeof(void*) * (size_t)c.L;
     const float4** hx = reinterpret_cast<const float4**>(h_pin[b]);
     const uint16_t** hr = reinterpret_cast<const uint16_t**>(h_pin[b] + tbl);
-    int* hn = reinterpret_cast<int*>(h_pin[b] + 2 * tbl);
     for (int l = 0; l < c.L; ++l) {
-        hn[l] = npts[l];
         if (src_on_device) {
             hx[l] = reinterpret_cast<const float4*>(xyzi) + (size_t)l * stride_points;
             hr[l] = ring ? ring + (size_t)l * stride_points : nullptr;
@@ -171,14 +193,38 @@ void Engine::uploadScan(const float* xyzi, const uint16_t* ring, const int* npts
             }
         }
     }
-    cuda_check(cudaMemcpyAsync(d_ptr_xyzi[b], hx, tbl, cudaMemcpyHostToDevice, copyStream), "upload table");
-    cuda_check(cudaMemcpyAsync(d_ptr_ring[b], hr, tbl, cudaMemcpyHostToDevice, copyStream), "upload table");
-    cuda_check(cudaMemcpyAsync(d_npts[b], hn, sizeof(int) * c.L, cudaMemcpyHostToDevice, copyStream), "upload npts");
-    cuda_check(cudaEventRecord(evCopied[b], copyStream), "event record");
-    cuda_check(cudaStreamWaitEvent(stream, evCopied[b], 0), "stream wait");
-    ip.in_xyzi = d_ptr_xyzi[b]; ip.in_ring = d_ptr_ring[b]; ip.npts = d_npts[b];
-    curIn = b;
+    finishUpload(b, npts, 4);
 }
+
+// One pointer per lane, floats_per_point = 4 (x y z intensity) or 3 (x y z packed: the reference never reads the input
+// intensity, imageProjection.cpp:248-255 overwrites it).  Host sources: npts[l] points of lane l cross PCIe, nothing else.
+void Engine::uploadScanLanes(const float* const* xyz, const uint16_t* const* ring, const int* npts, int floats_per_point, bool src_on_device) {
+    if (floats_per_point != 3 && floats_per_point != 4) throw std::invalid_argument("floats_per_point must be 3 or 4");
+    for (int l = 0; l < c.L; ++l) if (!xyz[l] || (c.useRing && (!ring || !ring[l]))) throw std::invalid_argument("null lane pointer");
+    const int b = beginUpload(npts, src_on_device);
+    const size_t tbl = sizeof(void*) * (size_t)c.L;
+    const float4** hx = reinterpret_cast<const float4**>(h_pin[b]);
+    const uint16_t** hr = reinterpret_cast<const uint16_t**>(h_pin[b] + tbl);
+    const size_t psz = sizeof(float) * (size_t)floats_per_point;
+    for (int l = 0; l < c.L; ++l) {
+        if (src_on_device) {
+            hx[l] = reinterpret_cast<const float4*>(xyz[l]);
+            hr[l] = ring ? ring[l] : nullptr;
+        } else {
+            hx[l] = d_in_xyzi[b] + (size_t)l * c.Pcap;
+            hr[l] = d_in_ring[b] + (size_t)l * c.Pcap;
+            if (npts[l] > 0) {
+                cuda_check(cudaMemcpyAsync(d_in_xyzi[b] + (size_t)l * c.Pcap, xyz[l], psz * npts[l], cudaMemcpyHostToDevice, copyStream), "upload xyz");
+                if (ring) cuda_check(cudaMemcpyAsync(d_in_ring[b] + (size_t)l * c.Pcap, ring[l], sizeof(uint16_t) * npts[l], cudaMemcpyHostToDevice, copyStream), "upload ring");
+            }
+        }
+    }
+    finishUpload(b, npts, floats_per_point);
+}
+
+// blocks until the input buffers handed to the last step may be refilled: host sources once they were copied to the
+// device, device sources once the kernels that read them have run
+void Engine::inputWait() { cuda_check(cudaEventSynchronize(curInOnDevice ? evConsumed[curIn] : evCopied[curIn]), "event sync"); }
 
 void Engine::inputConsumed() { cuda_check(cudaEventRecord(evConsumed[curIn], stream), "event record"); }
 
@@ -277,6 +323,8 @@ long Engine::download(int lane, const char* name, void* dst, long cap, int* elem
 long Engine::upload(int lane, const char* name, const void* src, long count) {
     void* p; int e; long cnt;
     if (lane < 0 || lane >= c.L || !lookup(lane, name, &p, &e, &cnt)) return LEGO_ERR_NAME;
+    if (count < 0 || count > cnt) { set_last_error("upload: count out of range for this array"); return LEGO_ERR_ARG; }
+    if (count == 0) return 0;
     cuda_check(cudaMemcpyAsync(p, src, (size_t)count * e, cudaMemcpyHostToDevice, stream), "upload");
     cuda_check(cudaStreamSynchronize(stream), "upload sync");
     return count;

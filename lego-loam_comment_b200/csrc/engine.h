@@ -38,6 +38,7 @@ struct IpDev {
     const float4* const* in_xyzi;     // [L] per-lane pointer to the scan's points (staging buffer or caller's device memory)
     const uint16_t* const* in_ring;   // [L] per-lane pointer to the ring channel
     const int* npts;           // [L]
+    int in_floats;             // floats per input point: 4 = x y z intensity, 3 = x y z packed
     int* owner;                // [L][N]   index of the last input point that fell into the cell, -1 = empty
     float* rangeMat;           // [L][N]   FLT_MAX = empty           (imageProjection.cpp:152)
     float4* fullCloud;         // [L][N]   NaN / intensity -1 = empty (imageProjection.cpp:157)
@@ -245,6 +246,8 @@ public:
 
     // ---- ImageProjection (names follow imageProjection.cpp) ----
     void uploadScan(const float* xyzi, const uint16_t* ring, const int* npts, int stride_points, bool src_on_device);
+    void uploadScanLanes(const float* const* xyz, const uint16_t* const* ring, const int* npts, int floats_per_point, bool src_on_device);
+    void inputWait();             // input buffers of the last step may be refilled once this returns
     void inputConsumed();         // marks the point after which the current input buffers may be overwritten
     void projectPointCloud();     // + findStartEndAngle
     void groundRemoval();
@@ -264,6 +267,10 @@ public:
     bool mapOptimizationGates(const double* stamps, std::vector<int>& active);
     void mapOptimizationBody(const std::vector<int>& active);
     bool lookupMapOptimization(int lane, const std::string& name, void** ptr, int* elem, long* count);
+    int firstCapacityError() const {                 // first lane whose mapOptimization ran out of capacity, -1 = none
+        for (int l = 0; l < c.L; ++l) if (moHost[l].lastError) return l;
+        return -1;
+    }
     void consumeMapRecords();                        // host bookkeeping of saveKeyFramesAndFactor from the device records
     void selectSurroundingKeyFrames(int lane, std::vector<MoKfEntry>& out, int* nCorner, int* nSurf);
     // ---- IMU ----
@@ -370,6 +377,9 @@ private:
     cudaStream_t copyStream = nullptr;
     cudaEvent_t evCopied[IN_SLOTS] = {}, evConsumed[IN_SLOTS] = {};
     int inBuf = 0, curIn = 0;
+    bool curInOnDevice = false;
+    int beginUpload(const int* npts, bool src_on_device);
+    void finishUpload(int b, const int* npts, int floats_per_point);
     char* h_pin[IN_SLOTS] = {};   // pinned: per-lane pointer tables + npts of the step in flight
 };
 

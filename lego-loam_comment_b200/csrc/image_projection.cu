@@ -16,6 +16,13 @@ namespace lego {
 // (quirk Q3); here each point does atomicMax(owner[cell], pointIndex) and a gather pass reads the winner.
 // Arithmetic mirrors the C++ expression types: atan2f * 180 is a FLOAT product, the division by M_PI and the
 // column computation are double, the result is narrowed to float on assignment.
+// An input point: 16-byte x y z intensity, or 12-byte packed x y z (the intensity is never read, imageProjection.cpp:248-255).
+__device__ __forceinline__ float4 load_input_point(const float4* __restrict__ in, int i, int floats) {
+    if (floats == 4) return in[i];
+    const float* q = reinterpret_cast<const float*>(in) + 3 * (size_t)i;
+    return make_float4(q[0], q[1], q[2], 0.f);
+}
+
 __global__ void __launch_bounds__(256) ip_project_kernel(IpDev d, Consts c) {
     const int lane = blockIdx.y;
     const int i = blockIdx.x * blockDim.x + threadIdx.x;
@@ -24,7 +31,7 @@ __global__ void __launch_bounds__(256) ip_project_kernel(IpDev d, Consts c) {
     if (i == 0) {
         float* o = d.orient + lane * 4;
         if (P > 0) {
-            const float4 a = in[0], b = in[P - 1];
+            const float4 a = load_input_point(in, 0, d.in_floats), b = load_input_point(in, P - 1, d.in_floats);
             const float so = -pm::atan2f_glibc(a.y, a.x);
             float eo = (float)((double)(-pm::atan2f_glibc(b.y, b.x)) + 2.0 * M_PI);
             const float diff = PM_SUB(eo, so);
@@ -34,7 +41,7 @@ __global__ void __launch_bounds__(256) ip_project_kernel(IpDev d, Consts c) {
         }
     }
     if (i >= P) return;
-    const float4 p = in[i];
+    const float4 p = load_input_point(in, i, d.in_floats);
     long long row;
     if (c.useRing) {
         row = d.in_ring[lane][i];
@@ -70,7 +77,7 @@ __global__ void __launch_bounds__(256) ip_gather_kernel(IpDev d, Consts c) {
         out = make_float4(CUDART_NAN_F, CUDART_NAN_F, CUDART_NAN_F, -1.0f);
         range = FLT_MAX;
     } else {
-        const float4 p = d.in_xyzi[lane][o];
+        const float4 p = load_input_point(d.in_xyzi[lane], o, d.in_floats);
         range = PM_SQRT(PM_ADD(PM_ADD(PM_MUL(p.x, p.x), PM_MUL(p.y, p.y)), PM_MUL(p.z, p.z)));
         const int row = cell / c.C, col = cell - row * c.C;
         const float inten = (float)((double)(float)row + (double)(float)col / 10000.0);

@@ -47,7 +47,7 @@ VgSeg Engine::makeVgSeg(const float4* in, const int* nIn, float4* out, int* nOut
 
 void Engine::allocMapOptimization() {
     const size_t L = c.L, N = c.N, R = c.R;
-    mo.maxKeyFrames = env_int("LEGO_MAX_KEYFRAMES", 640);
+    mo.maxKeyFrames = params.maxKeyFrames > 0 ? params.maxKeyFrames : env_int("LEGO_MAX_KEYFRAMES", 640);
     moKnnCache = env_int("LEGO_KNN_CACHE", 1) != 0;
     const size_t perKf = std::min<size_t>(N / 4, 16384);
     mo.poolCap = (int)std::min<size_t>((size_t)mo.maxKeyFrames * perKf, (size_t)INT_MAX / 2);

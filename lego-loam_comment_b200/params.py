@@ -26,6 +26,7 @@ class LegoParams(ctypes.Structure):
         ("device", ctypes.c_int),
         ("surroundingKeyframeSearchNum", ctypes.c_int), ("historyKeyframeSearchRadius", ctypes.c_float),
         ("historyKeyframeSearchNum", ctypes.c_int), ("historyKeyframeFitnessScore", ctypes.c_float),
+        ("maxKeyFrames", ctypes.c_int),
     ]
 
 
@@ -50,7 +51,7 @@ SENSOR_GEOMETRY = {
 }
 
 
-def make_params(sensor="vlp16", device=0, loop_closure=False):
+def make_params(sensor="vlp16", device=0, loop_closure=False, max_keyframes=0):
     if sensor.endswith("_loop"):
         sensor, loop_closure = sensor[:-5], True
     n, h, rx, ry, bottom, gsi, ring = _SENSORS[sensor]
@@ -77,6 +78,7 @@ def make_params(sensor="vlp16", device=0, loop_closure=False):
     p.historyKeyframeSearchRadius = 7.0             # utility.h:132
     p.historyKeyframeSearchNum = 25                 # utility.h:133
     p.historyKeyframeFitnessScore = 0.3             # utility.h:134
+    p.maxKeyFrames = max_keyframes                  # handle capacity, 0 = default (640)
     return p
 
 

@@ -1,0 +1,128 @@
+"""GPU tests of the batched pipeline's C ABI beyond plain parity: the per-lane pointer form of the step
+(lego_pipeline_step_lanes, x y z packed or x y z intensity, host or device memory), the input-lifetime call
+(lego_pipeline_input_wait) and the capacity errors the header promises (include/lego_b200.h)."""
+import numpy as np
+import pytest
+
+import lego_loam_b200  # noqa: F401
+from lego_loam_b200.capi import LegoError, Pipeline, load
+from lego_loam_b200.params import make_params
+from lego_loam_b200.synth import SynthSequence
+
+pytestmark = pytest.mark.gpu
+
+NAMES = ("labelMat", "segmentedCloud", "cornerPointsSharp", "cornerPointsLessSharp", "surfPointsFlat", "surfPointsLessFlat")
+
+
+def _scans(sensor, seeds, n, speed=4.0):
+    seqs = [SynthSequence(sensor, seed=s, scene="street", speed=speed) for s in seeds]
+    return seqs, [[q.scan(k) for q in seqs] for k in range(n)]
+
+
+def _same(a, b):
+    return a.shape == b.shape and np.array_equal(a.view(np.uint8), b.view(np.uint8))
+
+
+def test_step_lanes_xyz_and_xyzi_equal_padded_step():
+    """Three forms of the same 10 scans (2 lanes) give bit-identical images, features and poses: the padded xyzi block of
+    lego_pipeline_step, one xyzi pointer per lane, one packed xyz pointer per lane (the input intensity is never read,
+    imageProjection.cpp:248-255)."""
+    sensor = "vlp16"
+    seqs, scans = _scans(sensor, (31, 32), 10)
+    cap = seqs[0].cap
+    pls = [Pipeline(make_params(sensor), lanes=2, max_points=cap) for _ in range(3)]
+    for k, pair in enumerate(scans):
+        x = np.zeros((2, cap, 4), np.float32); r = np.zeros((2, cap), np.uint16)
+        n = np.array([len(p[0]) for p in pair], np.int32)
+        for l, (xyzi, ring) in enumerate(pair):
+            x[l, :n[l]] = xyzi; r[l, :n[l]] = ring
+        st = [k * 0.1, k * 0.1]
+        pls[0].step(x, r, n, st)
+        xi = [np.ascontiguousarray(p[0]) for p in pair]
+        x3 = [np.ascontiguousarray(p[0][:, :3]) for p in pair]
+        rg = [np.ascontiguousarray(p[1]) for p in pair]
+        rp = np.array([a.ctypes.data for a in rg], np.uint64)
+        pls[1].step_lanes(np.array([a.ctypes.data for a in xi], np.uint64), rp, n, st, floats_per_point=4)
+        pls[2].step_lanes(np.array([a.ctypes.data for a in x3], np.uint64), rp, n, st, floats_per_point=3)
+        for pl in pls[1:]:
+            pl.input_wait()          # the numpy buffers go out of scope at the end of this iteration
+        p0 = pls[0].poses()[0]
+        for pl in pls[1:]:
+            assert np.array_equal(pl.poses()[0], p0), "poses differ at scan %d" % k
+            for lane in range(2):
+                for name in NAMES:
+                    assert _same(pl.download(name, lane), pls[0].download(name, lane)), "%s lane %d scan %d" % (name, lane, k)
+    assert np.abs(p0[:, 6:12]).max() > 0.05
+    for pl in pls:
+        pl.close()
+
+
+def test_step_lanes_from_device_memory():
+    import torch
+    sensor = "vlp16"
+    seqs, scans = _scans(sensor, (41,), 6)
+    cap = seqs[0].cap
+    a = Pipeline(make_params(sensor), lanes=1, max_points=cap)
+    b = Pipeline(make_params(sensor), lanes=1, max_points=cap)
+    for k, pair in enumerate(scans):
+        xyzi, ring = pair[0]
+        n = np.array([len(xyzi)], np.int32)
+        x3 = np.ascontiguousarray(xyzi[:, :3])
+        a.step_lanes(np.array([x3.ctypes.data], np.uint64), np.array([ring.ctypes.data], np.uint64), n, [k * 0.1], floats_per_point=3)
+        a.input_wait()
+        dx = torch.from_numpy(x3).cuda(); dr = torch.from_numpy(ring.view(np.int16)).cuda()
+        torch.cuda.synchronize()
+        b.step_lanes(np.array([dx.data_ptr()], np.uint64), np.array([dr.data_ptr()], np.uint64), n, [k * 0.1], floats_per_point=3, on_device=True)
+        b.input_wait()               # dx / dr may be freed once the kernels that read them have run
+        assert np.array_equal(a.poses()[0], b.poses()[0])
+        assert _same(a.download("labelMat"), b.download("labelMat"))
+    a.close(); b.close()
+
+
+def test_step_argument_and_capacity_errors():
+    sensor = "vlp16"
+    seq = SynthSequence(sensor, seed=3)
+    xyzi, ring = seq.scan(0)
+    pl = Pipeline(make_params(sensor), lanes=1, max_points=1000)         # far fewer points than a scan has
+    x = np.zeros((1, len(xyzi), 4), np.float32); x[0] = xyzi
+    r = ring.reshape(1, -1).copy()
+    with pytest.raises(LegoError, match=r"\(-4\).*max_points"):
+        pl.step(x, r, [len(xyzi)], [0.0])
+    with pytest.raises(LegoError, match=r"\(-4\)"):
+        pl.step(np.ascontiguousarray(x[:, :500]), np.ascontiguousarray(r[:, :500]), [600], [0.0])     # npts > stride_points
+    with pytest.raises(LegoError, match=r"\(-4\)"):
+        pl.step(np.ascontiguousarray(x[:, :500]), np.ascontiguousarray(r[:, :500]), [-1], [0.0])
+    with pytest.raises(LegoError, match=r"\(-1\)"):
+        pl.step_lanes(np.array([x.ctypes.data], np.uint64), np.array([r.ctypes.data], np.uint64), [500], [0.0], floats_per_point=5)
+    with pytest.raises(LegoError, match=r"\(-1\).*null lane pointer"):
+        pl.step_lanes(np.array([0], np.uint64), np.array([r.ctypes.data], np.uint64), [500], [0.0], floats_per_point=4)
+    # named-array upload: bounds are checked against the array's size
+    lib = load()
+    buf = np.zeros(64, np.float32)
+    assert lib.lego_pipeline_upload(pl.h, 0, b"transformCur", buf.ctypes.data, 7) == -1
+    assert lib.lego_pipeline_upload(pl.h, 0, b"transformCur", buf.ctypes.data, -1) == -1
+    assert lib.lego_pipeline_upload(pl.h, 0, b"transformCur", buf.ctypes.data, 6) == 6
+    pl.close()
+
+
+def test_keyframe_pool_overflow_is_reported():
+    """lego_params.maxKeyFrames = 3: the fourth key frame cannot be saved; the step that learns of it (one mapping call
+    later) and every later step return LEGO_ERR_CAPACITY naming the lane -- the pipeline does not silently map against a
+    frozen key-frame list."""
+    sensor = "vlp16"
+    seq = SynthSequence(sensor, seed=11, scene="street", speed=4.0)
+    pl = Pipeline(make_params(sensor, max_keyframes=3), lanes=2, max_points=seq.cap)
+    failed_at = None
+    for k in range(40):
+        xyzi, ring = seq.scan(k)
+        x = np.zeros((2, seq.cap, 4), np.float32); x[:, :len(xyzi)] = xyzi
+        r = np.zeros((2, seq.cap), np.uint16); r[:, :len(ring)] = ring
+        try:
+            pl.step(x, r, [len(xyzi)] * 2, [k * 0.1] * 2)
+        except LegoError as ex:
+            assert "(-4)" in str(ex) and "lane 0" in str(ex) and "capacity" in str(ex)
+            failed_at = failed_at if failed_at is not None else k
+    # a key frame every mapping call at 4 m/s (scans 2, 6, 10, 14): the 4th is refused at scan 14, reported by scan 18
+    assert failed_at is not None and failed_at <= 22, failed_at
+    assert int(pl.download("moState")[1]) == 3
+    pl.close()
