@@ -44,6 +44,8 @@ def _load():
         lib.lego_synth_scan.argtypes = [ctypes.c_void_p, ctypes.c_int, ctypes.c_void_p, ctypes.c_void_p, ctypes.c_int]
         lib.lego_synth_batch.argtypes = [ctypes.c_void_p, ctypes.c_int, ctypes.c_int, ctypes.c_void_p, ctypes.c_void_p,
                                          ctypes.c_void_p, ctypes.c_int, ctypes.c_int]
+        lib.lego_synth_batch_fmt.argtypes = [ctypes.c_void_p, ctypes.c_int, ctypes.c_int, ctypes.c_void_p, ctypes.c_void_p, ctypes.c_void_p,
+                                             ctypes.c_int, ctypes.c_int, ctypes.c_int, ctypes.c_long, ctypes.c_int]
         lib.lego_synth_pose.argtypes = [ctypes.POINTER(SynthCfg), ctypes.c_double, ctypes.c_void_p]
         _lib = lib
     return _lib
@@ -90,6 +92,13 @@ class SynthSequence:
         npts = np.zeros(count, np.int32)
         _load().lego_synth_batch(self._h, k0, count, xyzi.ctypes.data, ring.ctypes.data, npts.ctypes.data, self.cap, threads)
         return xyzi, ring, npts
+
+    def batch_into(self, k0, count, xyz, ring, npts, floats_per_point, scan_stride_points, npts_stride=1, threads=None):
+        """scans k0 .. k0+count-1 written straight into caller memory (e.g. one sequence's slots of a pinned
+        [scan][sequence][cap] buffer): xyz / ring / npts are numpy views whose first element is scan k0's slot."""
+        threads = threads or min(32, os.cpu_count() or 1)
+        _load().lego_synth_batch_fmt(self._h, k0, count, xyz.ctypes.data, ring.ctypes.data, npts.ctypes.data, self.cap, threads,
+                                     int(floats_per_point), int(scan_stride_points), int(npts_stride))
 
     def pose(self, t):
         out = np.zeros(6)

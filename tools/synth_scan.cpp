@@ -28,6 +28,12 @@ inline double u01(uint64_t h) { return (double)((h >> 11) + 1) / 900719925474099
 struct World {
     std::vector<Box> boxes;
     std::vector<Cyl> cyls;
+    // uniform XY grid over the primitives (acceleration only: a ray visits the cells under its ground track in order and
+    // stops once its nearest hit lies before the exit of the current cell; the nearest hit is the same minimum the
+    // exhaustive loop over all primitives finds)
+    double gx0 = 0, gy0 = 0, cell = 4.0;
+    int gnx = 0, gny = 0;
+    std::vector<int> cellStart, cellItems;   // CSR: items >= 0 box index, < 0 cylinder index -(k+1)
 };
 
 void build_room(World& w, uint64_t seed) {
@@ -76,6 +82,29 @@ void build_street(World& w, uint64_t seed, double x_begin, double x_end) {
     w.boxes.push_back(Box{{x_end + 1, -25, 0}, {x_end + 2, 25, 12}});
 }
 
+void build_grid(World& w) {
+    const double margin = 0.05;   // primitives are registered a little fat, so a ray grazing a cell corner still meets them
+    double x0 = 1e300, y0 = 1e300, x1 = -1e300, y1 = -1e300;
+    for (const Box& b : w.boxes) { x0 = std::min(x0, b.lo[0]); y0 = std::min(y0, b.lo[1]); x1 = std::max(x1, b.hi[0]); y1 = std::max(y1, b.hi[1]); }
+    for (const Cyl& c : w.cyls) { x0 = std::min(x0, c.cx - c.r); y0 = std::min(y0, c.cy - c.r); x1 = std::max(x1, c.cx + c.r); y1 = std::max(y1, c.cy + c.r); }
+    if (x0 > x1) { w.gnx = w.gny = 0; return; }
+    w.gx0 = x0 - 1.0; w.gy0 = y0 - 1.0;
+    w.gnx = (int)std::ceil((x1 + 1.0 - w.gx0) / w.cell) + 1; w.gny = (int)std::ceil((y1 + 1.0 - w.gy0) / w.cell) + 1;
+    std::vector<std::vector<int> > cells((size_t)w.gnx * w.gny);
+    auto reg = [&](double ax0, double ay0, double ax1, double ay1, int item) {
+        int i0 = (int)std::floor((ax0 - margin - w.gx0) / w.cell), i1 = (int)std::floor((ax1 + margin - w.gx0) / w.cell);
+        int j0 = (int)std::floor((ay0 - margin - w.gy0) / w.cell), j1 = (int)std::floor((ay1 + margin - w.gy0) / w.cell);
+        i0 = std::max(i0, 0); j0 = std::max(j0, 0); i1 = std::min(i1, w.gnx - 1); j1 = std::min(j1, w.gny - 1);
+        for (int j = j0; j <= j1; ++j) for (int i = i0; i <= i1; ++i) cells[(size_t)j * w.gnx + i].push_back(item);
+    };
+    for (size_t k = 0; k < w.boxes.size(); ++k) reg(w.boxes[k].lo[0], w.boxes[k].lo[1], w.boxes[k].hi[0], w.boxes[k].hi[1], (int)k);
+    for (size_t k = 0; k < w.cyls.size(); ++k) reg(w.cyls[k].cx - w.cyls[k].r, w.cyls[k].cy - w.cyls[k].r, w.cyls[k].cx + w.cyls[k].r, w.cyls[k].cy + w.cyls[k].r, -(int)k - 1);
+    w.cellStart.assign(cells.size() + 1, 0);
+    for (size_t c = 0; c < cells.size(); ++c) w.cellStart[c + 1] = w.cellStart[c] + (int)cells[c].size();
+    w.cellItems.resize(w.cellStart.back());
+    for (size_t c = 0; c < cells.size(); ++c) std::copy(cells[c].begin(), cells[c].end(), w.cellItems.begin() + w.cellStart[c]);
+}
+
 inline double hit_box(const Box& b, const double o[3], const double d[3], double tmax) {
     double t0 = 1e-9, t1 = tmax;
     for (int a = 0; a < 3; ++a) {
@@ -98,6 +127,44 @@ inline double hit_cyl(const Cyl& c, const double o[3], const double d[3], double
     if (t <= 1e-6 || t >= tmax) return -1;
     double z = o[2] + t * d[2];
     return (z >= c.z0 && z <= c.z1) ? t : -1;
+}
+
+// Nearest primitive hit along o + t d with t < best (returns the new best).  Walks the grid cells under the ray in order
+// of t (2-D DDA) and tests the primitives registered in each; ends when the nearest hit so far lies before the cell's exit.
+inline double nearest_hit(const World& w, const double o[3], const double d[3], double best) {
+    if (w.gnx == 0) return best;
+    const double cs = w.cell;
+    double t0 = 0.0, t1 = best;   // the ground track clipped against the grid rectangle
+    const double lo[2] = {w.gx0, w.gy0}, hi[2] = {w.gx0 + cs * w.gnx, w.gy0 + cs * w.gny};
+    for (int a = 0; a < 2; ++a) {
+        if (std::fabs(d[a]) < 1e-12) { if (o[a] < lo[a] || o[a] >= hi[a]) return best; continue; }
+        double inv = 1.0 / d[a], ta = (lo[a] - o[a]) * inv, tb = (hi[a] - o[a]) * inv;
+        if (ta > tb) std::swap(ta, tb);
+        if (ta > t0) t0 = ta;
+        if (tb < t1) t1 = tb;
+        if (t0 > t1) return best;
+    }
+    const double px = o[0] + (t0 + 1e-9) * d[0], py = o[1] + (t0 + 1e-9) * d[1];
+    int ix = (int)std::floor((px - w.gx0) / cs), iy = (int)std::floor((py - w.gy0) / cs);
+    ix = std::min(std::max(ix, 0), w.gnx - 1); iy = std::min(std::max(iy, 0), w.gny - 1);
+    const int sx = d[0] > 0 ? 1 : -1, sy = d[1] > 0 ? 1 : -1;
+    const double big = 1e300;
+    double tmx = std::fabs(d[0]) < 1e-12 ? big : ((w.gx0 + (ix + (sx > 0 ? 1 : 0)) * cs) - o[0]) / d[0];
+    double tmy = std::fabs(d[1]) < 1e-12 ? big : ((w.gy0 + (iy + (sy > 0 ? 1 : 0)) * cs) - o[1]) / d[1];
+    const double tdx = std::fabs(d[0]) < 1e-12 ? big : cs / std::fabs(d[0]), tdy = std::fabs(d[1]) < 1e-12 ? big : cs / std::fabs(d[1]);
+    for (;;) {
+        const size_t c = (size_t)iy * w.gnx + ix;
+        for (int k = w.cellStart[c]; k < w.cellStart[c + 1]; ++k) {
+            const int it = w.cellItems[k];
+            const double t = it >= 0 ? hit_box(w.boxes[it], o, d, best) : hit_cyl(w.cyls[-it - 1], o, d, best);
+            if (t > 0 && t < best) best = t;
+        }
+        const double texit = std::min(tmx, tmy);
+        if (best <= texit || texit >= t1) break;
+        if (tmx < tmy) { ix += sx; tmx += tdx; if (ix < 0 || ix >= w.gnx) break; }
+        else { iy += sy; tmy += tdy; if (iy < 0 || iy >= w.gny) break; }
+    }
+    return best;
 }
 
 }  // namespace
@@ -142,12 +209,14 @@ void* lego_synth_create(const lego_synth_cfg* c, uint64_t seed, double total_tim
     s->seed = seed; s->cfg = *c;
     if (c->scene == 0) build_room(s->w, seed);
     else build_street(s->w, seed, -60.0, c->speed * total_time + 120.0);
+    build_grid(s->w);
     return s;
 }
 void lego_synth_destroy(void* h) { delete static_cast<lego_synth_world*>(h); }
 
-// One scan. xyzi: cap*4 floats, ring: cap u16. Returns the number of points written (<= cap), firing order.
-int lego_synth_scan(void* h, int scan_idx, float* xyzi, uint16_t* ring, int cap) {
+// One scan. xyzi: cap*fpp floats (fpp = 4: x y z intensity, 3: x y z packed), ring: cap u16. Returns the number of points
+// written (<= cap), firing order.
+int lego_synth_scan_fmt(void* h, int scan_idx, float* xyzi, uint16_t* ring, int cap, int fpp) {
     const lego_synth_world& S = *static_cast<lego_synth_world*>(h);
     const lego_synth_cfg& c = S.cfg;
     const int R = c.n_scan, C = c.horizon_scan;
@@ -176,9 +245,7 @@ int lego_synth_scan(void* h, int scan_idx, float* xyzi, uint16_t* ring, int cap)
                 for (int a = 0; a < 3; ++a) d[a] = Rm[a][0] * ds[0] + Rm[a][1] * ds[1] + Rm[a][2] * ds[2];
                 double best = c.max_range;
                 if (d[2] < -1e-9) { double t = -o[2] / d[2]; if (t < best) best = t; }
-                const double xlo = o[0] - c.max_range, xhi = o[0] + c.max_range;
-                for (const Box& b : S.w.boxes) { if (b.hi[0] < xlo || b.lo[0] > xhi) continue; double t = hit_box(b, o, d, best); if (t > 0 && t < best) best = t; }
-                for (const Cyl& q : S.w.cyls) { if (q.cx + q.r < xlo || q.cx - q.r > xhi) continue; double t = hit_cyl(q, o, d, best); if (t > 0 && t < best) best = t; }
+                best = nearest_hit(S.w, o, d, best);
                 if (best >= c.max_range) continue;   // no return
                 uint64_t hr = hash3(S.seed ^ 0xABCDEF, ((uint64_t)scan_idx << 24) ^ (uint64_t)(k * 2 + rep), i);
                 if (c.dropout_prob > 0 && u01(mix64(hr + 5)) < c.dropout_prob) continue;
@@ -187,12 +254,30 @@ int lego_synth_scan(void* h, int scan_idx, float* xyzi, uint16_t* ring, int cap)
                 double rng = best + c.noise_sigma * g;
                 if (rng < c.min_range) continue;
                 if (n >= cap) return n;
-                xyzi[4 * n] = (float)(rng * ds[0]); xyzi[4 * n + 1] = (float)(rng * ds[1]); xyzi[4 * n + 2] = (float)(rng * ds[2]); xyzi[4 * n + 3] = 10.0f;
+                float* q = xyzi + (size_t)fpp * n;
+                q[0] = (float)(rng * ds[0]); q[1] = (float)(rng * ds[1]); q[2] = (float)(rng * ds[2]); if (fpp == 4) q[3] = 10.0f;
                 ring[n] = (uint16_t)i; ++n;
             }
         }
     }
     return n;
+}
+
+int lego_synth_scan(void* h, int scan_idx, float* xyzi, uint16_t* ring, int cap) { return lego_synth_scan_fmt(h, scan_idx, xyzi, ring, cap, 4); }
+
+// count scans starting at scan0, multi-threaded, written straight into a strided destination: scan s goes to
+// xyz + s*scan_stride_points*fpp floats / ring + s*scan_stride_points (lets a caller interleave several sequences in one
+// pinned [scan][sequence][cap] buffer without an intermediate copy).  npts advances by npts_stride per scan.
+void lego_synth_batch_fmt(void* h, int scan0, int count, float* xyz, uint16_t* ring, int* npts, int cap, int threads, int fpp,
+                          long scan_stride_points, int npts_stride) {
+    if (threads < 1) threads = 1;
+    std::vector<std::thread> pool;
+    for (int t = 0; t < threads; ++t)
+        pool.emplace_back([=]() {
+            for (int s = t; s < count; s += threads)
+                npts[(size_t)s * npts_stride] = lego_synth_scan_fmt(h, scan0 + s, xyz + (size_t)s * scan_stride_points * fpp, ring + (size_t)s * scan_stride_points, cap, fpp);
+        });
+    for (auto& th : pool) th.join();
 }
 
 // count scans starting at scan0, multi-threaded. xyzi: count*cap*4, ring: count*cap, npts: count.
