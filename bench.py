@@ -2,18 +2,29 @@
 """bench.py -- throughput of the LeGO-LOAM per-scan hot path (ImageProjection -> FeatureAssociation ->
 mapOptimization scan-to-map) on B200, in scans/s, on synthetic scans of the named sensor shape.
 
-A "step" = one lidar scan for each of `lanes` independent sequences stepped in lock step through the whole
-pipeline (the reference processes one scan per ROS callback; sequences are the only data-parallel axis,
-SURVEY.md 8e).  value = lanes * steps * n_gpus / device time, inputs resident in HBM; e2e = the same through
-the C ABI with HOST buffers (pinned), H2D of every scan and D2H of the poses inside the timed region.
+Workload = BASELINE.json configs[1]: full pipeline on long synthetic ground-vehicle trajectories.  Every lane
+(independent sequence) drives one trajectory from scan 0; a "step" is `scans_per_step` consecutive scans of every lane
+(25 for the 16-ring sensor), so the driver's `--steps 20 --warmup 5` is 125 untimed + 500 timed scans per lane.  The
+timed window never starts before scan `ceil(surroundingKeyframeSearchRadius / (speed * scanPeriod))` (= 125 at 4 m/s):
+from there on the local map of extractSurroundingKeyFrames (mapOptmization.cpp:956-1065) holds every key frame
+within 50 m and no longer grows.  BOTH arms (this one and --impl reference) process scans 0 .. T-1 and time exactly
+the same scan indices; config.timed_scan_range states them.
+
+value = lanes * timed scans * n_gpus / device time with the inputs resident in HBM; e2e = the same through the C ABI
+(lego_pipeline_step_lanes) from pinned HOST buffers, the H2D copy of every scan of every lane and the D2H of every
+scan's poses inside the timed region.  Lanes replay one of `distinct_sequences` generated trajectories (592 lanes x
+625 scans of private input would be 150 GB); every lane still owns its state, and in the e2e arm every lane's scan
+crosses PCIe separately.
 
     python bench.py [--gpus N] [--steps K] [--warmup W] [--lanes L] [--sensor vlp16] [--impl reference]
+                    [--workload drive|loop]
 
 --impl reference times the reference's own CPU code (oracle/_ref, the reference sources compiled verbatim) on the
-host cores, one independent sequence per core.
+host cores, one independent sequence per core, over the same scan range.
 """
 import argparse
 import json
+import math
 import os
 import subprocess
 import sys
@@ -28,39 +39,70 @@ sys.path.insert(0, os.path.join(ROOT, "oracle"))
 
 METRIC = "scans_per_sec"
 UNIT = "scans/s"
+SHAPES = {"vlp16": "VLP-16 16x1800", "vlp16_noring": "VLP-16 16x1800 (no ring channel)", "hdl32": "HDL-32E 32x1800",
+          "hdl64": "64-beam 64x2083", "vls128": "VLS-128 128x1800", "os1_16": "OS1-16 16x1024", "os1_64": "OS1-64 64x1024"}
 
 
 def parse_args():
     ap = argparse.ArgumentParser()
     ap.add_argument("--gpus", type=int, default=1)
     ap.add_argument("--steps", type=int, default=20)
-    ap.add_argument("--warmup", type=int, default=4)
-    ap.add_argument("--lanes", type=int, default=0, help="independent sequences per GPU stepped in lock step (0 = 592 for 16 rings, 296 for 32, 148 above)")
-    ap.add_argument("--stagger", type=int, default=0, help="1: handle h runs h scans ahead of handle 0 so the mapping calls of the handles do not coincide")
+    ap.add_argument("--warmup", type=int, default=5)
+    ap.add_argument("--lanes", type=int, default=0, help="independent sequences per GPU stepped in lock step (0 = 592 for 16 rings, 296 for 32/64, 148 above)")
     ap.add_argument("--handles", type=int, default=4, help="pipeline handles (CUDA streams) the lanes of one GPU are split over")
+    ap.add_argument("--stagger", type=int, default=0, help="1: handle h runs h scans ahead of handle 0 so the mapping calls of the handles do not coincide")
     ap.add_argument("--sensor", default="vlp16")
     ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
+    ap.add_argument("--workload", default="drive", choices=["drive", "loop"],
+                    help="drive: street trajectories, loop closure off (BASELINE config 2); loop: closed circles with loopClosureEnableFlag (config 5)")
     ap.add_argument("--stages", type=int, default=7, help="bit0 ImageProjection, bit1 FeatureAssociation, bit2 mapOptimization")
     ap.add_argument("--speed", type=float, default=4.0)
+    ap.add_argument("--scans-per-step", type=int, default=0, help="scans of every lane in one step (0 = 25 for 16 rings, 10 for 32/64, 5 above)")
+    ap.add_argument("--distinct", type=int, default=0, help="distinct generated sequences per GPU the lanes replay (0 = auto)")
+    ap.add_argument("--input", default="xyz", choices=["xyz", "xyzi"], help="point format on the wire: xyz = 12 B + ring, xyzi = 16 B + ring")
+    ap.add_argument("--secondary", default="auto", help="second sensor measured inside the same line at N=1 ('auto' = hdl64 when --sensor vlp16, 'none')")
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-e2e", action="store_true")
+    ap.add_argument("--no-latency", action="store_true")
     ap.add_argument("--profile-json", default="", help="write the per-kernel CUDA-event breakdown to this file")
     return ap.parse_args()
 
 
 def default_lanes(sensor):
-    """Multiples of the 148 SMs: 4 sequences per SM for 16 rings, 2 for 32 and 64 (64 x 2083: 33.9 k scans/s against 31.7 k with
-    1 per SM), 1 for 128 rings (2 per SM do not fit in 180 GB)."""
-    if sensor in ("vlp16", "vlp16_noring"):
+    """Multiples of the 148 SMs: 4 sequences per SM for 16 rings, 2 for 32 and 64, 1 for 128 rings."""
+    if sensor in ("vlp16", "vlp16_noring", "os1_16"):
         return 592
-    return 296 if sensor in ("hdl32", "hdl64") else 148
+    return 296 if sensor in ("hdl32", "hdl64", "os1_64") else 148
+
+
+def default_scans_per_step(sensor):
+    if sensor in ("vlp16", "vlp16_noring", "os1_16"):
+        return 25
+    return 10 if sensor in ("hdl32", "hdl64", "os1_64") else 5
 
 
 def dist_env():
-    rank = int(os.environ.get("RANK", "0"))
-    world = int(os.environ.get("WORLD_SIZE", "1"))
-    local = int(os.environ.get("LOCAL_RANK", "0"))
-    return rank, world, local
+    return int(os.environ.get("RANK", "0")), int(os.environ.get("WORLD_SIZE", "1")), int(os.environ.get("LOCAL_RANK", "0"))
+
+
+class Window:
+    """Which scans of a trajectory are primed / warmed up / timed.  Identical for both arms."""
+
+    def __init__(self, args, sensor, workload="drive"):
+        self.S = args.scans_per_step if args.scans_per_step > 0 and sensor == args.sensor else default_scans_per_step(sensor)
+        self.W, self.K = args.warmup, args.steps
+        if workload == "loop":
+            self.steady = 0
+        else:
+            # local map complete: every key frame within surroundingKeyframeSearchRadius (50 m, utility.h:129) lies behind the vehicle
+            self.steady = int(math.ceil(50.0 / (args.speed * 0.1)))
+        self.first_timed = max(self.W * self.S, self.steady)
+        self.prime = self.first_timed - self.W * self.S
+        self.T = self.first_timed + self.K * self.S
+
+    def describe(self):
+        return {"scans_per_step": self.S, "scans_per_lane": self.T, "timed_scan_range": [self.first_timed, self.T - 1],
+                "timed_scans_per_lane": self.K * self.S, "untimed_scans_per_lane": self.first_timed}
 
 
 # ------------------------------------------------------------------------------------------------ clocks
@@ -113,11 +155,20 @@ class ClockSampler:
 
 
 # ------------------------------------------------------------------------------------------------ sharding
-def lane_seeds(rank, lanes):
-    """Sequences are the only axis the path shards on: rank r owns sequences r*1000 .. r*1000+lanes-1,
-    no sequence is shared, nothing is exchanged on the data path."""
-    assert lanes <= 1000
-    return [1000 * rank + l for l in range(lanes)]
+def rank_seeds(rank, world, n_distinct):
+    """Sequences are the only axis the path shards on: rank r generates seeds r*1000 .. r*1000+D-1 and its
+    lanes replay them (lane l -> sequence l % D); no sequence is shared between ranks, nothing is exchanged on the data path."""
+    assert n_distinct <= 1000
+    return [1000 * rank + d for d in range(n_distinct)]
+
+
+def default_distinct(sensor, world, lanes, T, cap):
+    """Distinct sequences per rank: 32 per box for the 16-ring sensor (generation time and pinned memory are the limits:
+    T scans x cap points x 14 B each), never more than the lanes, at least 4 per rank."""
+    per_seq = T * cap * 14
+    budget = 10e9 / max(world, 1)
+    d = int(max(4, min(32 // max(world, 1), budget // max(per_seq, 1))))
+    return max(1, min(d, lanes))
 
 
 def max_over_ranks(x, world, device=None):
@@ -132,28 +183,48 @@ def max_over_ranks(x, world, device=None):
 
 
 # ------------------------------------------------------------------------------------------------ inputs
-def gen_inputs(sensor, seeds, n_scans, speed, pinned=False):
-    """Synthetic scans (tools/synth_scan.cpp): lane l = sequence with seed seeds[l], scans 0..n_scans-1.
-    -> xyzi float32[T, L, cap, 4], ring uint16[T, L, cap], npts int32[T, L], stamps float64[T]"""
+LOOP_RADIUS = 8.0
+
+
+def make_sequence(sensor, seed, workload, speed, n_scans):
     import lego_loam_b200  # noqa: F401
     from lego_loam_b200.synth import SynthSequence
-    seqs = [SynthSequence(sensor, seed=sd, scene="street", speed=speed, n_scans=max(n_scans, 64)) for sd in seeds]
-    lanes = len(seeds)
-    cap = seqs[0].cap
-    if pinned:
-        # one pinned host copy serves both arms: source of the one-off upload (value) and of the per-step H2D (e2e)
+    if workload == "loop":
+        # closed circle in the room scene: the vehicle re-visits its own key frames every lap (loop closure, config 5)
+        return SynthSequence(sensor, seed=seed, scene="room", speed=speed, n_scans=max(n_scans, 64), circle_radius=LOOP_RADIUS)
+    return SynthSequence(sensor, seed=seed, scene="street", speed=speed, n_scans=max(n_scans, 64))
+
+
+class Inputs:
+    """Pinned host copy of D sequences x T scans, layout [scan][sequence][cap] so that one scan of all sequences is
+    contiguous: xyz float32[T, D, cap, fpp] (fpp 3 or 4), ring uint16[T, D, cap], npts int32[T, D]."""
+
+    def __init__(self, sensor, seeds, T, workload, speed, fpp, pinned=True):
         import torch
-        xyzi = torch.zeros((n_scans, lanes, cap, 4), dtype=torch.float32).pin_memory().numpy()
-        ring = torch.zeros((n_scans, lanes, cap), dtype=torch.int16).pin_memory().numpy().view(np.uint16)
-    else:
-        xyzi = np.zeros((n_scans, lanes, cap, 4), np.float32)
-        ring = np.zeros((n_scans, lanes, cap), np.uint16)
-    npts = np.zeros((n_scans, lanes), np.int32)
-    for l, s in enumerate(seqs):
-        x, r, n = s.batch(0, n_scans)
-        xyzi[:, l] = x; ring[:, l] = r; npts[:, l] = n
-    stamps = np.arange(n_scans, dtype=np.float64) * 0.1
-    return xyzi, ring, npts, stamps, cap
+        seqs = [make_sequence(sensor, sd, workload, speed, T) for sd in seeds]
+        self.D, self.T, self.fpp = len(seeds), T, fpp
+        self.cap = cap = seqs[0].cap
+        D = self.D
+        t0 = time.perf_counter()
+        xs = torch.zeros((T, D, cap, fpp), dtype=torch.float32)
+        rs = torch.zeros((T, D, cap), dtype=torch.int16)
+        if pinned:
+            xs, rs = xs.pin_memory(), rs.pin_memory()
+        self._keep = (xs, rs)
+        self.xyz = xs.numpy()
+        self.ring = rs.numpy().view(np.uint16)
+        self.npts = np.zeros((T, D), np.int32)
+        for d, s in enumerate(seqs):
+            s.batch_into(0, T, self.xyz[0, d], self.ring[0, d], self.npts[0, d:], fpp, D * cap, D)
+        self.gen_s = time.perf_counter() - t0
+        self.stamps = np.arange(T, dtype=np.float64) * 0.1
+        self.scan_bytes_xyz = D * cap * fpp * 4
+        self.scan_bytes_ring = D * cap * 2
+
+    def tables(self, base_xyz, base_ring, lanes):
+        """per-lane address tables of scan 0 (uint64); scan t adds t * scan_bytes_*"""
+        seq = np.arange(lanes, dtype=np.uint64) % np.uint64(self.D)
+        return (np.uint64(base_xyz) + seq * np.uint64(self.cap * self.fpp * 4), np.uint64(base_ring) + seq * np.uint64(self.cap * 2), seq.astype(np.int64))
 
 
 # ------------------------------------------------------------------------------------------------ roofline
@@ -238,23 +309,20 @@ def gather_counts(pl, params, lanes):
     return c
 
 
-def merge_counts(a, b):
-    out = dict(a)
-    for k in ("N", "L", "S", "O", "Fs", "Fl", "Ff", "Flf", "odo_bytes"):
-        out[k] = a[k] + b[k]
-    out["mo_bytes"] = {k: a["mo_bytes"][k] + b["mo_bytes"][k] for k in a["mo_bytes"]}
-    out["map"] = {k: a["map"][k] + b["map"][k] for k in a["map"]}
-    return out
-
-
-def ncu_traffic(kernel, lanes):
+def ncu_traffic(kernel, lanes, sensor):
     """DRAM bytes per launch of `kernel` from the committed ncu --set full capture (profiles/ncu_traffic.json), scaled to
-    the lanes of one launch; None when the kernel was not captured."""
+    the lanes of one launch.  None when there is no capture of this kernel for this sensor at the steady-state local map
+    (entries carry "sensor" and, for the kernels whose traffic grows with the map, "steady": true)."""
     p = os.path.join(ROOT, "profiles", "ncu_traffic.json")
     try:
         with open(p) as f:
             e = json.load(f).get(kernel)
-        return float(e["bytes_per_lane"]) * lanes if e else None
+        if not e or e.get("sensor", "vlp16") != sensor:
+            return None
+        map_dependent = kernel.startswith("mo_") or "Map" in kernel
+        if map_dependent and not e.get("steady", False):
+            return None
+        return float(e["bytes_per_lane"]) * lanes
     except (OSError, ValueError, KeyError):
         return None
 
@@ -267,8 +335,37 @@ def load_peaks():
     return 6650.0, "fallback (B200_PROFILING.md)"
 
 
+def build_roofline(prof_h0, prof_all, counts_h0, counts_all, dom_timed, lanes_h0, sensor, step_ms, scans_profiled, scans_per_step):
+    """roofline of the dominant kernel from ONE handle's launches (bytes, traffic and launch time all describe the lanes_h0
+    lanes one launch covers) + the whole pipeline's algorithmic bytes per step against the step time."""
+    peak, peak_src = load_peaks()
+    tot_ms = sum(v[0] for v in prof_h0.values()) or 1.0
+    dominant = dom_timed["kernel"]
+    abytes = algorithmic_bytes(dominant, counts_h0)
+    avg_ms = dom_timed["ms"] / max(dom_timed["n"], 1)
+    achieved = abytes / (avg_ms * 1e-3) / 1e9 if avg_ms > 0 else 0.0
+    traffic = ncu_traffic(dominant, lanes_h0, sensor)
+    frac = achieved / peak
+    assert frac <= 1.0, "roofline.frac > 1: bytes and launch time do not describe the same lanes"
+    # pipeline aggregate: sum over kernels and handles of (launches in the profiled step) x (algorithmic bytes per launch)
+    pipe_bytes = 0.0
+    for prof, counts in zip(prof_all, counts_all):
+        for k, (_, n) in prof.items():
+            pipe_bytes += n * algorithmic_bytes(k, counts)
+    pipe_bytes *= scans_per_step / float(max(scans_profiled, 1))
+    pipe_gbs = pipe_bytes / (step_ms * 1e-3) / 1e9
+    return {"bound": "hbm", "kernel": dominant, "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": frac,
+            "traffic": traffic, "peak_source": peak_src, "lanes_per_launch": lanes_h0,
+            "algorithmic_bytes_per_launch": abytes, "avg_launch_ms": avg_ms,
+            "share_of_step": prof_h0[dominant][0] / tot_ms if dominant in prof_h0 else None,
+            "pipeline": {"algorithmic_bytes_per_step": pipe_bytes, "achieved": pipe_gbs, "frac": pipe_gbs / peak,
+                         "note": "sum over all kernels and handles of launches x algorithmic bytes per launch in one step, / ms_per_step; the profile is flat, "
+                                 "so this, not the dominant kernel, says how far the whole step is from the HBM roof"}}
+
+
 # ------------------------------------------------------------------------------------------------ B200 arm
-def run_b200(args):
+def run_b200(args, sensor, lanes, workload):
+    """One sensor through both arms (device-resident `value`, host-buffer `e2e`) on this rank's GPU."""
     import torch
     import torch.distributed as dist
     import lego_loam_b200  # noqa: F401
@@ -276,20 +373,20 @@ def run_b200(args):
     from lego_loam_b200.params import make_params
 
     rank, world, local = dist_env()
-    if not torch.cuda.is_available():
-        raise SystemExit("bench.py: no CUDA device (the product has no CPU fallback)")
-    torch.cuda.set_device(local)
-    if world > 1:
-        dist.init_process_group("nccl", device_id=torch.device("cuda", local))
-    L, K, W = args.lanes, args.steps, args.warmup
-    T = W + K
-    params = make_params(args.sensor, device=local)
+    win = Window(args, sensor, workload)
+    S, W, K = win.S, win.W, win.K
+    L = lanes
     H = max(1, min(args.handles, L))
-    # Handle h runs `phase[h]` scans ahead of handle 0 (primed before the warm-up): mapOptimization fires every 4th or
-    # 5th scan of a sequence, and staggering the handles spreads those heavy steps evenly instead of stacking the
-    # mapping calls of all handles in the same step.  Independent sequences have independent phases anyway.
+    fpp = 3 if args.input == "xyz" else 4
+    # 2000-scan sequences save ~500 key frames (one per mapping call at 4 m/s): size the pool for the run, with head room
+    params = make_params(sensor, device=local, loop_closure=(workload == "loop"), max_keyframes=max(640, win.T // 3 + 64))
     phase = [(h if args.stagger else 0) for h in range(H)]
-    xyzi, ring, npts, stamps, cap = gen_inputs(args.sensor, lane_seeds(rank, L), T + max(phase), speed=args.speed, pinned=True)
+    Ttot = win.T + max(phase)
+    cap0 = params.N_SCAN * params.Horizon_SCAN
+    D = args.distinct if args.distinct > 0 else default_distinct(sensor, world, L, Ttot, cap0)
+    inp = Inputs(sensor, rank_seeds(rank, world, D), Ttot, workload, args.speed, fpp)
+    cap = inp.cap
+    bounds = [(h * L) // H for h in range(H + 1)]
 
     def barrier():
         torch.cuda.synchronize()
@@ -297,75 +394,62 @@ def run_b200(args):
             dist.barrier()
         torch.cuda.synchronize()
 
-    def stamps_of(t):
-        return np.full(L, stamps[t])
-
-    # ---- device-resident inputs (value) -------------------------------------------------------------
-    # The lanes are split over `handles` pipeline handles = CUDA streams: while one handle sits in its latency-bound LM
-    # kernels (one CTA per lane) the others' streaming kernels fill the rest of the GPU.
-    bounds = [(h * L) // H for h in range(H + 1)]
-    d_xyzi = torch.from_numpy(xyzi).cuda()
-    d_ring = torch.from_numpy(ring.view(np.int16)).cuda()
-    torch.cuda.synchronize()
-    xs, rs = d_xyzi.stride(0) * 4, d_ring.stride(0) * 2
-
     def make_group():
         return [Pipeline(params, lanes=bounds[h + 1] - bounds[h], max_points=cap) for h in range(H)]
-
-    def device_scan(h, pl, s):
-        l0, l1 = bounds[h], bounds[h + 1]
-        pl.step(d_xyzi.data_ptr() + s * xs + l0 * cap * 16, d_ring.data_ptr() + s * rs + l0 * cap * 2, npts[s, l0:l1], stamps_of(s)[l0:l1],
-                stage_mask=args.stages, on_device=True, stride_points=cap)
-
-    def device_step(group, t):
-        for h, pl in enumerate(group):
-            device_scan(h, pl, t + phase[h])
-
-    def prime(group, scan_fn):
-        for h, pl in enumerate(group):
-            for s in range(phase[h]):
-                scan_fn(h, pl, s)
-
-    def sync_group(group):
-        for pl in group:
-            pl.sync()
 
     def close_group(group):
         for pl in group:
             pl.close()
 
-    # pass 1 (untimed): per-kernel CUDA-event breakdown, finds the dominant kernel
-    group = make_group()
-    prime(group, device_scan)
-    for t in range(W):
-        device_step(group, t)
-    sync_group(group)
-    for pl in group:
-        pl.profile(1)
-    for t in range(W, T):
-        device_step(group, t)
-    prof = {}
-    for pl in group:
-        for k, (ms_k, n_k) in pl.profile_read().items():
-            a_ms, a_n = prof.get(k, (0.0, 0))
-            prof[k] = (a_ms + ms_k, a_n + n_k)
-        pl.profile(0)
-    counts = None
-    for h, pl in enumerate(group):
-        ch = gather_counts(pl, params, bounds[h + 1] - bounds[h])
-        counts = ch if counts is None else merge_counts(counts, ch)
-    counts["P"] = int(npts[T - 1].sum())
-    close_group(group)
-    tot_ms = sum(v[0] for v in prof.values()) or 1.0
-    dominant = max(prof, key=lambda k: prof[k][0])
+    def make_scan_fn(base_xyz, base_ring, on_device):
+        xt, rt, seq = inp.tables(base_xyz, base_ring, L)
 
-    # pass 2 (timed): K steps, events on the pipelines' streams; only the dominant kernel stays bracketed
+        def scan(h, pl, s):
+            l0, l1 = bounds[h], bounds[h + 1]
+            pl.step_lanes(xt[l0:l1] + np.uint64(s * inp.scan_bytes_xyz), rt[l0:l1] + np.uint64(s * inp.scan_bytes_ring),
+                          inp.npts[s][seq[l0:l1]], np.full(l1 - l0, inp.stamps[s]), floats_per_point=fpp,
+                          stage_mask=args.stages, on_device=on_device)
+        return scan, seq
+
+    # ---- device-resident inputs (value) -------------------------------------------------------------
+    # The lanes are split over `handles` pipeline handles = CUDA streams: while one handle sits in its latency-bound LM
+    # kernels (one CTA per lane) the others' streaming kernels fill the rest of the GPU.
+    d_x = torch.from_numpy(inp.xyz).cuda()
+    d_r = torch.from_numpy(inp.ring.view(np.int16)).cuda()
+    torch.cuda.synchronize()
+    dev_scan, seq = make_scan_fn(d_x.data_ptr(), d_r.data_ptr(), True)
     group = make_group()
-    prime(group, device_scan)
-    for t in range(W):
-        device_step(group, t)
-    sync_group(group)
+
+    def run_scans(scan_fn, s0, s1):
+        for s in range(s0, s1):
+            for h, pl in enumerate(group):
+                scan_fn(h, pl, s + phase[h])
+
+    for h, pl in enumerate(group):           # handle h runs phase[h] scans ahead
+        for s in range(phase[h]):
+            dev_scan(h, pl, s)
+    run_scans(dev_scan, 0, win.prime + max(W - 1, 0) * S)
+    # last warm-up step: every kernel bracketed with events -> per-kernel shares, launches per step, the dominant kernel
+    prof_all = [{} for _ in group]
+    scans_profiled = 0
+    if W >= 1:
+        for pl in group:
+            pl.sync()
+        for pl in group:
+            pl.profile(1)
+        run_scans(dev_scan, win.first_timed - S, win.first_timed)
+        scans_profiled = S
+        prof_all = [pl.profile_read() for pl in group]
+        for pl in group:
+            pl.profile(0)
+    prof_sum = {}
+    for prof in prof_all:
+        for k, (ms_k, n_k) in prof.items():
+            a = prof_sum.get(k, (0.0, 0))
+            prof_sum[k] = (a[0] + ms_k, a[1] + n_k)
+    dominant = max(prof_sum, key=lambda k: prof_sum[k][0]) if prof_sum else "fa_odometry_kernel"
     for pl in group:
+        pl.sync()
         pl.profile(2, dominant)
     launches0 = sum(pl.launch_count() for pl in group)
     clk = ClockSampler(local)
@@ -373,134 +457,229 @@ def run_b200(args):
     barrier()
     for pl in group:
         pl.timer_record(0)
-    submit_ms = []   # host time to enqueue each step (no sync inside); once the launch queues are full it tracks the device
-    for t in range(W, T):
-        t_submit = time.perf_counter()
-        device_step(group, t)
-        submit_ms.append((time.perf_counter() - t_submit) * 1e3)
-    host_submit_ms = (sum(submit_ms), min(submit_ms))
+    t_host0 = time.perf_counter()
+    run_scans(dev_scan, win.first_timed, win.T)
+    host_submit_s = time.perf_counter() - t_host0
     for pl in group:
         pl.timer_record(1)
-    sync_group(group)
+    for pl in group:
+        pl.sync()
     barrier()
     ms = max(group[0].timer_elapsed_to(0, pl, 1) for pl in group)
     clocks = clk.stop()
     launches = sum(pl.launch_count() for pl in group) - launches0
-    dom_ms, dom_n = 0.0, 0
+    d_ms, d_n = group[0].profile_read().get(dominant, (0.0, 0))
     for pl in group:
-        d_ms, d_n = pl.profile_read().get(dominant, (0.0, 0))
-        dom_ms += d_ms; dom_n += d_n
         pl.profile(0)
-    dom = (dom_ms, dom_n)
+    dom_timed = {"kernel": dominant, "ms": d_ms, "n": d_n}
+    counts_all = []
+    for h, pl in enumerate(group):
+        ch = gather_counts(pl, params, bounds[h + 1] - bounds[h])
+        ch["P"] = int(inp.npts[win.T - 1][seq[bounds[h]:bounds[h + 1]]].sum())
+        counts_all.append(ch)
+    kf_total, kf_in_map = [], []
+    for pl in group:
+        for l in range(0, pl.lanes, max(1, pl.lanes // 16)):     # a sample of the lanes
+            kf_total.append(int(pl.download("moState", l)[1]))
+            kf_in_map.append(len(pl.download("surroundingExistingKeyPosesID", l)))
     poses_dev = np.concatenate([pl.poses()[0] for pl in group])
     close_group(group)
-
+    del d_x, d_r
+    torch.cuda.empty_cache()
+    ms = max_over_ranks(ms, world, "cuda")
     # ---- host buffers through the C ABI (e2e) --------------------------------------------------------
     e2e = None
     if not args.no_e2e:
-        hx, hr = xyzi, ring   # pinned (gen_inputs)
         group = make_group()
-
-        # Streaming use of the C ABI: scan t is submitted from pinned host memory (H2D on the handle's copy stream),
-        # its pose read-back is enqueued behind it, and the result of scan t-4 is collected while scans t-3 .. t are
-        # in flight (a mapping step lasts as long as three uploads, so less slack leaves the PCIe link idle behind it).
-        # Every step's inputs cross PCIe and every step's poses are read on the host inside the timed region.
-        def host_scan(h, pl, s):
-            l0, l1 = bounds[h], bounds[h + 1]
-            pl.step(hx[s, l0:l1], hr[s, l0:l1], npts[s, l0:l1], stamps_of(s)[l0:l1], stage_mask=args.stages)
-
+        host_scan, _ = make_scan_fn(inp.xyz.ctypes.data, inp.ring.ctypes.data, False)
+        # Streaming use of the C ABI: scan t is submitted from pinned host memory (one H2D copy per lane of exactly its
+        # points on the handle's copy stream), its pose read-back is enqueued behind it, and the result of scan t-4 is
+        # collected while scans t-3 .. t are in flight (a mapping scan lasts as long as several uploads, so less slack
+        # leaves the PCIe link idle behind it).  Every scan's inputs cross PCIe and every scan's poses are read on the host
+        # inside the timed region.
         DEPTH = 5   # scans in flight per handle: the poses of scan k are collected after scan k+4 was submitted
 
-        def submit(t):
+        def submit(s):
             for h, pl in enumerate(group):
-                host_scan(h, pl, t + phase[h])
-                pl.poses_async(t % 8)
+                host_scan(h, pl, s + phase[h])
+                pl.poses_async(s % 8)
 
-        def collect(t):
-            return np.concatenate([pl.poses_wait(t % 8)[0] for pl in group])
+        def collect(s):
+            return np.concatenate([pl.poses_wait(s % 8)[0] for pl in group])
 
-        prime(group, host_scan)
-        for t in range(W):
-            submit(t)
-            collect(t)
+        for h, pl in enumerate(group):
+            for s in range(phase[h]):
+                host_scan(h, pl, s)
+        for s in range(win.first_timed):
+            submit(s)
+            if s - (DEPTH - 1) >= 0:
+                collect(s - (DEPTH - 1))
+        for s in range(max(0, win.first_timed - (DEPTH - 1)), win.first_timed):
+            collect(s)
         barrier()
         t0 = time.perf_counter()
-        for t in range(W, T):
-            submit(t)
-            if t - (DEPTH - 1) >= W:
-                poses_host = collect(t - (DEPTH - 1))
-        for t in range(max(W, T - (DEPTH - 1) + 0), T):
-            poses_host = collect(t)
+        poses_host = None
+        for s in range(win.first_timed, win.T):
+            submit(s)
+            if s - (DEPTH - 1) >= win.first_timed:
+                poses_host = collect(s - (DEPTH - 1))
+        for s in range(max(win.first_timed, win.T - (DEPTH - 1)), win.T):
+            poses_host = collect(s)
         barrier()
         e2e_s = time.perf_counter() - t0
         close_group(group)
         e2e_s = max_over_ranks(e2e_s, world, "cuda")
-        assert np.allclose(poses_host, poses_dev, atol=1e-6), "host-buffer and device-buffer runs disagree"
-        # what the PCIe link of this box gives a plain pinned->device copy of one step's points (context for E: the
-        # streaming loop above cannot beat h2d_bytes_per_step / this rate)
-        probe = torch.empty(hx[0].shape, dtype=torch.float32, device="cuda")
-        src = torch.from_numpy(hx[0])
+        same = bool(np.allclose(poses_host, poses_dev, atol=1e-6))
+        assert same, "host-buffer and device-buffer runs disagree"
+        # what the PCIe link of this box gives a plain pinned->device copy (context for E: the streaming loop cannot beat
+        # h2d_bytes_per_step / this rate)
+        n_probe = max(1, min(inp.T, int(256e6 // max(inp.scan_bytes_xyz, 1))))
+        src = torch.from_numpy(inp.xyz[:n_probe])
+        probe = torch.empty(src.shape, dtype=torch.float32, device="cuda")
         ev0, ev1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
         probe.copy_(src, non_blocking=True); torch.cuda.synchronize()
         ev0.record()
         for _ in range(3):
             probe.copy_(src, non_blocking=True)
         ev1.record(); torch.cuda.synchronize()
-        h2d_gbs = 3 * hx[0].nbytes / (ev0.elapsed_time(ev1) * 1e-3) / 1e9
+        h2d_gbs = 3 * src.numel() * 4 / (ev0.elapsed_time(ev1) * 1e-3) / 1e9
         del probe
-        e2e = {"value": L * K * world / e2e_s, "unit": UNIT,
-               "h2d_bytes_per_step": int(hx[0].nbytes + hr[0].nbytes + npts[0].nbytes), "d2h_bytes_per_step": int(L * (18 * 4 + 4)),
-               "pcie_h2d_gbs_plain_copy": round(h2d_gbs, 1), "mode": "streaming: up to 5 scans in flight per handle, the poses of scan k are collected after scan k+4 was submitted"}
+        pts_timed = int(sum(int(inp.npts[s][seq].sum()) for s in range(win.first_timed, win.T)))
+        e2e = {"value": L * K * S * world / e2e_s, "unit": UNIT,
+               "h2d_bytes_per_step": int(pts_timed * (fpp * 4 + 2) / K + S * L * (16 + 4)),
+               "d2h_bytes_per_step": int(S * L * 19 * 4),
+               "h2d_bytes_per_scan": round(pts_timed * (fpp * 4 + 2) / float(K * S * L), 1),
+               "input_format": "x y z float32 + ring uint16 (14 B/point), only the npts points of each lane" if fpp == 3 else
+                               "x y z intensity float32 + ring uint16 (18 B/point), only the npts points of each lane",
+               "seconds": e2e_s, "pcie_h2d_gbs_plain_copy": round(h2d_gbs, 1), "poses_equal_device_arm": same,
+               "mode": "streaming: up to 5 scans in flight per handle, the poses of scan k are collected after scan k+4 was submitted"}
 
-    ms = max_over_ranks(ms, world, "cuda")
-    return dict(rank=rank, world=world, ms=ms, L=L, K=K, W=W, e2e=e2e, clocks=clocks, launches=launches, prof=prof, tot_ms=tot_ms,
-                dominant=dominant, dom=dom, counts=counts, cap=cap, params=params, host_submit_ms=host_submit_ms,
-                step_bytes=int(xyzi[0].nbytes + ring[0].nbytes), inputs=(xyzi, ring, npts, stamps))
+    prof_h0 = prof_all[0]
+    step_ms = ms / K
+    roofline = build_roofline(prof_h0, prof_all, counts_all[0], counts_all, dom_timed, bounds[1] - bounds[0], sensor, step_ms, scans_profiled, S) \
+        if prof_sum else None
+    cmap = {k: sum(c["map"][k] for c in counts_all) / float(L) for k in counts_all[0]["map"]}
+    local_map = {"keyframes_saved": float(np.mean(kf_total)), "keyframes_in_local_map": float(np.mean(kf_in_map)),
+                 "cornerFromMap": cmap["cornerFromMap"], "surfFromMap": cmap["surfFromMap"],
+                 "cornerFromMapDS": cmap["cornerFromMapDS"], "surfFromMapDS": cmap["surfFromMapDS"],
+                 "note": "mean per lane at the last mapping call of the run"}
+    return dict(rank=rank, world=world, ms=ms, L=L, K=K, W=W, S=S, win=win, e2e=e2e, clocks=clocks, launches=launches,
+                prof_all=prof_all, prof_sum=prof_sum, counts_all=counts_all, roofline=roofline, cap=cap, params=params, D=D,
+                host_submit_ms=host_submit_s * 1e3 / K, local_map=local_map, gen_s=inp.gen_s, fpp=fpp, H=H,
+                mean_points=float(inp.npts[win.first_timed:win.T].mean()), inputs=inp)
+
+
+def measure_latency(args, sensor, workload, inp, win, device):
+    """One lane alone through the full pipeline, host buffers in, poses out, one scan at a time (the reference's own
+    shape: one callback per scan at 10 Hz, imageProjection.cpp:181-197): wall ms from the call to the poses on the host."""
+    import lego_loam_b200  # noqa: F401
+    from lego_loam_b200.capi import Pipeline
+    from lego_loam_b200.params import make_params
+    params = make_params(sensor, device=device, loop_closure=(workload == "loop"), max_keyframes=max(640, win.T // 3 + 64))
+    pl = Pipeline(params, lanes=1, max_points=inp.cap)
+    xt, rt, _ = inp.tables(inp.xyz.ctypes.data, inp.ring.ctypes.data, 1)
+    n_timed = min(200, win.T - win.first_timed)
+    lat, mapped = [], []
+    for s in range(win.first_timed + n_timed):
+        t0 = time.perf_counter()
+        pl.step_lanes(xt + np.uint64(s * inp.scan_bytes_xyz), rt + np.uint64(s * inp.scan_bytes_ring), inp.npts[s][:1],
+                      inp.stamps[s:s + 1], floats_per_point=inp.fpp, stage_mask=args.stages)
+        _, flags = pl.poses()
+        dt = (time.perf_counter() - t0) * 1e3
+        if s >= win.first_timed:
+            lat.append(dt); mapped.append(bool(flags[0] & 8))
+    launches = pl.launch_count()
+    pl.close()
+    lat = np.array(lat); mapped = np.array(mapped)
+    out = {"lanes": 1, "scans": int(len(lat)), "scan_range": [win.first_timed, win.first_timed + n_timed - 1],
+           "ms_per_scan": {"mean": float(lat.mean()), "p50": float(np.percentile(lat, 50)), "p99": float(np.percentile(lat, 99)), "max": float(lat.max())},
+           "launches_per_scan": launches / float(win.first_timed + n_timed),
+           "what": "wall time of lego_pipeline_step_lanes (pinned host scan in) + lego_pipeline_get_poses (poses on the host), one scan at a time"}
+    if mapped.any() and (~mapped).any():
+        out["ms_per_scan"]["p50_mapping_scan"] = float(np.percentile(lat[mapped], 50))
+        out["ms_per_scan"]["p50_other_scan"] = float(np.percentile(lat[~mapped], 50))
+    return out
 
 
 # ------------------------------------------------------------------------------------------------ CPU reference
-def _ref_worker(q, sensor, seed, n_scans, speed, stages, pin_core):
-    """One process = one sequence through the reference's own code (oracle/_ref), timed without scan generation."""
+def ref_cfg(sensor, workload):
+    return sensor + "_loop" if workload == "loop" else sensor
+
+
+def _ref_worker(q, sensor, workload, seed, n_scans, first_timed, speed, stages, pin_core):
+    """One process = one sequence through the reference's own code (oracle/_ref): scans 0 .. n_scans-1 are fed, the scans
+    from first_timed on are timed (scan generation happens in chunks outside the clock)."""
     try:
         if pin_core is not None and hasattr(os, "sched_setaffinity"):
             os.sched_setaffinity(0, {pin_core})
-        import lego_loam_b200  # noqa: F401
-        from lego_loam_b200.synth import SynthSequence
         import refpy
-        seq = SynthSequence(sensor, seed=seed, scene="street", speed=speed, n_scans=max(n_scans, 64))
-        x, r, n = seq.batch(0, n_scans, threads=1)
-        ref = refpy.RefPipeline(sensor, snapshots=False)
-        t0 = time.perf_counter()
-        for k in range(n_scans):
-            ref.feed(x[k, :n[k]], r[k, :n[k]], k * 0.1, stages)
-        dt = time.perf_counter() - t0
+        seq = make_sequence(sensor, seed, workload, speed, n_scans)
+        ref = refpy.RefPipeline(ref_cfg(sensor, workload), snapshots=False)
+        dt, CH = 0.0, 25
+        t_stage0 = None
+        for k0 in range(0, n_scans, CH):
+            cnt = min(CH, n_scans - k0)
+            x, r, n = seq.batch(k0, cnt, threads=1)
+            for j in range(cnt):
+                k = k0 + j
+                if k == first_timed:
+                    t_stage0 = ref.timers()
+                t0 = time.perf_counter()
+                ref.feed(x[j, :n[j]], r[j, :n[j]], k * 0.1, stages)
+                if k >= first_timed:
+                    dt += time.perf_counter() - t0
         timers, scans, mo_calls = ref.timers()
+        if t_stage0 is not None:
+            timers = {k: v - t_stage0[0].get(k, 0.0) for k, v in timers.items()}
+            scans -= t_stage0[1]; mo_calls -= t_stage0[2]
         ref.close()
-        q.put((n_scans, dt, {k: v / max(scans, 1) for k, v in timers.items()}, mo_calls))
+        q.put((n_scans - first_timed, dt, {k: v / max(scans, 1) for k, v in timers.items()}, mo_calls))
     except Exception as ex:  # noqa: BLE001
         q.put((0, 0.0, {"error": repr(ex)}, 0))
 
 
-def run_reference_cpu(sensor, n_procs, scans_per_proc, speed, stages, seed0=0, pin=False):
-    """-> (scans/s over all processes, per-stage ms of process 0, mapping calls of process 0, wall seconds)"""
+def run_reference_cpu(sensor, workload, n_procs, n_scans, first_timed, speed, stages, seed0=0, pin=False):
+    """-> (timed scans/s over all processes, per-stage ms per scan of process 0 over the timed scans, its mapping calls,
+    the slowest process's timed seconds)"""
     import multiprocessing as mp
     ctx = mp.get_context("spawn")
     q = ctx.Queue()
-    procs = [ctx.Process(target=_ref_worker, args=(q, sensor, seed0 + i, scans_per_proc, speed, stages, i if pin else None))
+    procs = [ctx.Process(target=_ref_worker, args=(q, sensor, workload, seed0 + i, n_scans, first_timed, speed, stages, i if pin else None))
              for i in range(n_procs)]
     for p in procs:
         p.start()
     res = [q.get() for _ in procs]
     for p in procs:
         p.join()
+    errs = [r[2] for r in res if r[0] == 0]
+    if errs:
+        raise RuntimeError("reference worker failed: %s" % errs[0])
     total = sum(r[0] for r in res)
     slowest = max(r[1] for r in res) or 1e-9
     return total / slowest, res[0][2], res[0][3], slowest
 
 
-def reference_available(sensor):
+def reference_available(sensor, workload="drive"):
     import refpy
-    return refpy.available(sensor)
+    return refpy.available(ref_cfg(sensor, workload))
+
+
+def workload_name(args, sensor, workload, win):
+    st = "+".join(n for b, n in ((1, "imageProjection"), (2, "featureAssociation"), (4, "mapOptimization")) if args.stages & b)
+    if workload == "loop":
+        return "%s synthetic closed-circle trajectories (radius %.0f m, %.1f m/s) with loopClosureEnableFlag, %s incl. loop-closure ICP + pose graph, " \
+               "%d-scan sequences, scans %d..%d timed" % (SHAPES[sensor], LOOP_RADIUS, args.speed, st, win.T, win.first_timed, win.T - 1)
+    return "%s synthetic street trajectories (%.1f m/s), %s, %d-scan sequences, scans %d..%d timed (local map at its steady-state size: " \
+           "every key frame within 50 m)" % (SHAPES[sensor], args.speed, st, win.T, win.first_timed, win.T - 1)
+
+
+def cpu_baseline_block(args, sensor, workload, win):
+    rate, stages_ms, mo_calls, secs = run_reference_cpu(sensor, workload, 1, win.T, win.first_timed, args.speed, args.stages, pin=False)
+    return {"value": rate, "unit": UNIT, "cores": 1, "kind": "reference",
+            "sample": "one sequence (seed 0), scans 0..%d fed, scans %d..%d timed (%.1f s): the same scan range as the GPU arm; "
+                      "reference sources compiled verbatim (oracle/_ref)" % (win.T - 1, win.first_timed, win.T - 1, secs),
+            "ms_per_scan": 1000.0 / rate if rate > 0 else None, "mapping_calls": int(mo_calls),
+            "per_stage_ms": {k: round(v, 4) for k, v in stages_ms.items() if isinstance(v, float)}}
 
 
 def run_reference_arm(args):
@@ -508,82 +687,122 @@ def run_reference_arm(args):
     if rank != 0:
         return None
     cores = os.cpu_count() or 1
-    per_step = 25 if args.sensor.startswith("vlp16") else 8          # scans per process per "step": bounded sample
-    n_scans = per_step * (args.steps + args.warmup)
-    rate, stages_ms, mo_calls, wall = run_reference_cpu(args.sensor, cores, n_scans, args.speed, args.stages)
-    line = {
+    win = Window(args, args.sensor, args.workload)
+    rate, stages_ms, mo_calls, secs = run_reference_cpu(args.sensor, args.workload, cores, win.T, win.first_timed, args.speed, args.stages)
+    cfg = {"workload": workload_name(args, args.sensor, args.workload, win), "sensor": args.sensor, "stages": args.stages,
+           "note": "reference sources compiled verbatim (oracle/_ref), one independent sequence per host core, every process feeds scans 0..T-1 "
+                   "and times exactly the scans the GPU arm times"}
+    cfg.update(win.describe())
+    return {
         "impl": "reference", "metric": METRIC, "value": rate, "unit": UNIT, "n_gpus": args.gpus, "steps": args.steps, "warmup": args.warmup,
-        "ms_per_step": 1000.0 * wall / (args.steps + args.warmup), "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
-        "dtype": "f32", "data": "synthetic",
-        "config": {"workload": workload_name(args), "sensor": args.sensor, "stages": args.stages,
-                   "note": "reference sources compiled verbatim (oracle/_ref), one independent sequence per host core"},
+        "ms_per_step": 1000.0 * secs / max(args.steps, 1), "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
+        "dtype": "f32", "data": "synthetic", "config": cfg,
         "cpu_baseline": {"value": rate, "unit": UNIT, "cores": cores, "kind": "reference",
-                         "sample": "%d processes x %d scans of the street sequence, all stages" % (cores, n_scans)},
+                         "sample": "%d processes x %d timed scans (scans %d..%d of a %d-scan sequence each), all stages"
+                                   % (cores, win.T - win.first_timed, win.first_timed, win.T - 1, win.T),
+                         "per_stage_ms": {k: round(v, 4) for k, v in stages_ms.items() if isinstance(v, float)}},
         "e2e": {"value": rate, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
         "gpu_launches": 0,
     }
-    return line
-
-
-def workload_name(args):
-    shape = {"vlp16": "VLP-16 16x1800", "vlp16_noring": "VLP-16 16x1800 (no ring channel)", "hdl32": "HDL-32E 32x1800",
-             "hdl64": "64-beam 64x2083", "vls128": "VLS-128 128x1800"}[args.sensor]
-    st = "+".join(n for b, n in ((1, "imageProjection"), (2, "featureAssociation"), (4, "mapOptimization")) if args.stages & b)
-    return "%s synthetic street trajectories, %s" % (shape, st)
 
 
 # ------------------------------------------------------------------------------------------------ main
+def result_block(args, r, sensor, workload):
+    """the measured numbers of one sensor as they appear in the JSON line (top level for the primary, under
+    `secondary.<sensor>` for the second one)"""
+    L, K, S, world = r["L"], r["K"], r["S"], r["world"]
+    win = r["win"]
+    cfg = {"workload": workload_name(args, sensor, workload, win), "sensor": sensor, "lanes_per_gpu": L, "handles_per_gpu": r["H"],
+           "handle_stagger_scans": args.stagger, "stages": args.stages,
+           "distinct_sequences_per_gpu": r["D"],
+           "lane_inputs": "lane l replays generated sequence l %% %d of its GPU (own state per lane; own H2D copy per lane in the e2e arm)" % r["D"],
+           "points_per_scan": round(r["mean_points"], 1), "input_format": "xyz+ring (14 B/point)" if r["fpp"] == 3 else "xyzi+ring (18 B/point)",
+           "local_map": r["local_map"],
+           "l2": "one scan of all lanes reads %.0f MB of input and touches %.0f GB of per-lane state: far beyond the 126 MB L2 (no flush needed)"
+                 % (L * r["mean_points"] * (r["fpp"] * 4 + 2) / 1e6, L * 0.115 if sensor.startswith("vlp16") else L * 0.3)}
+    cfg.update(win.describe())
+    blk = {"value": L * K * S * world / (r["ms"] * 1e-3), "unit": UNIT, "ms_per_step": r["ms"] / K, "timed_region_s": r["ms"] * 1e-3,
+           "config": cfg, "roofline": r["roofline"], "clocks": r["clocks"], "gpu_launches": int(r["launches"]),
+           "gpu_launches_per_scan_step": round(r["launches"] / float(K * S), 1),
+           "host_submit_ms_per_step": round(r["host_submit_ms"], 3), "input_generation_s": round(r["gen_s"], 1)}
+    if r["e2e"]:
+        blk["e2e"] = r["e2e"]
+    return blk
+
+
 def main():
     args = parse_args()
-    if args.lanes <= 0:
-        args.lanes = default_lanes(args.sensor)
+    rank, world, local = dist_env()
     if args.impl == "reference":
-        if not reference_available(args.sensor):
+        if not reference_available(args.sensor, args.workload):
             # the oracle restatement always exists in the repo; only the verbatim-compiled .so can be missing
-            print(json.dumps({"impl": "reference", "unavailable": "oracle/_ref/liblego_ref_%s.so not built" % args.sensor}))
+            print(json.dumps({"impl": "reference", "unavailable": "oracle/_ref/liblego_ref_%s.so not built" % ref_cfg(args.sensor, args.workload)}))
             return
         line = run_reference_arm(args)
         if line is not None:
             print(json.dumps(line))
         return
 
-    r = run_b200(args)
-    if r["rank"] != 0:
+    import torch
+    import torch.distributed as dist
+    if not torch.cuda.is_available():
+        raise SystemExit("bench.py: no CUDA device (the product has no CPU fallback)")
+    torch.cuda.set_device(local)
+    if world > 1:
+        dist.init_process_group("nccl", device_id=torch.device("cuda", local))
+
+    lanes = args.lanes if args.lanes > 0 else default_lanes(args.sensor)
+    r = run_b200(args, args.sensor, lanes, args.workload)
+    blk = result_block(args, r, args.sensor, args.workload)
+    line = {"metric": METRIC, "value": blk["value"], "unit": UNIT, "n_gpus": world, "steps": r["K"], "warmup": r["W"],
+            "ms_per_step": blk["ms_per_step"], "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
+            "dtype": "f32", "data": "synthetic"}
+    for k in ("config", "roofline", "clocks", "gpu_launches", "gpu_launches_per_scan_step", "host_submit_ms_per_step", "timed_region_s",
+              "input_generation_s", "e2e"):
+        if k in blk:
+            line[k] = blk[k]
+    if rank == 0 and world == 1 and not args.no_latency:
+        line["latency"] = measure_latency(args, args.sensor, args.workload, r["inputs"], r["win"], local)
+    profile_dump = None
+    if args.profile_json and rank == 0:
+        profile_dump = {"per_kernel_ms_over_profiled_step_handle0": {k: {"ms": v[0], "launches": v[1], "algorithmic_bytes_per_launch": algorithmic_bytes(k, r["counts_all"][0])}
+                                                                      for k, v in r["prof_all"][0].items()},
+                        "per_kernel_ms_all_handles": {k: {"ms": v[0], "launches": v[1]} for k, v in r["prof_sum"].items()},
+                        "profiled_scans": r["S"], "lanes_handle0": r["L"] // r["H"],
+                        "counts_handle0": {k: v for k, v in r["counts_all"][0].items() if k != "mo_bytes"}}
+    r["inputs"] = None
+    win = r["win"]
+    if rank == 0 and not args.no_cpu_baseline and reference_available(args.sensor, args.workload):
+        line["cpu_baseline"] = cpu_baseline_block(args, args.sensor, args.workload, win)
+        if "latency" in line:
+            line["latency"]["reference_ms_per_scan_one_core"] = line["cpu_baseline"]["ms_per_scan"]
+
+    # second sensor inside the same line (north-star target shape 64 x 2083), N = 1 only
+    sec = args.secondary
+    if sec == "auto":
+        sec = "hdl64" if (args.sensor == "vlp16" and args.workload == "drive") else "none"
+    if sec != "none" and world == 1:
+        import gc
+        del r
+        gc.collect()
+        torch.cuda.empty_cache()
+        r2 = run_b200(args, sec, default_lanes(sec), "drive")
+        b2 = result_block(args, r2, sec, "drive")
+        win2 = r2["win"]
+        del r2
+        gc.collect()
+        if not args.no_cpu_baseline and reference_available(sec):
+            b2["cpu_baseline"] = cpu_baseline_block(args, sec, "drive", win2)
+            b2["vs_one_core"] = {"device": b2["value"] / b2["cpu_baseline"]["value"],
+                                 "e2e": (b2["e2e"]["value"] / b2["cpu_baseline"]["value"]) if "e2e" in b2 else None,
+                                 "north_star_target": ">= 100x the reference's single-core rate at 64 x 2083"}
+        line["secondary"] = {sec: b2}
+    if rank != 0:
         return
-    L, K, world = r["L"], r["K"], r["world"]
-    value = L * K * world / (r["ms"] * 1e-3)
-    peak, peak_src = load_peaks()
-    dom_ms, dom_n = r["dom"]
-    abytes = algorithmic_bytes(r["dominant"], r["counts"])
-    achieved = (abytes / (dom_ms * 1e-3 / max(dom_n, 1)) / 1e9) if dom_ms > 0 else 0.0
-    roofline = {"bound": "hbm", "kernel": r["dominant"], "achieved": achieved, "peak": peak, "unit": "GB/s",
-                "frac": achieved / peak, "traffic": ncu_traffic(r["dominant"], L / max(1, min(args.handles, L))), "peak_source": peak_src,
-                "algorithmic_bytes_per_launch": abytes, "avg_launch_ms": dom_ms / max(dom_n, 1),
-                "share_of_step": r["prof"][r["dominant"]][0] / r["tot_ms"]}
-    line = {
-        "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": K, "warmup": r["W"],
-        "ms_per_step": r["ms"] / K, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
-        "dtype": "f32", "data": "synthetic",
-        "config": {"workload": workload_name(args), "sensor": args.sensor, "lanes_per_gpu": L, "handles_per_gpu": args.handles, "handle_stagger_scans": args.stagger, "stages": args.stages,
-                   "points_per_scan": r["cap"],
-                   "l2": "per-step inputs %.0f MB + per-lane state exceed the 126 MB L2 (no flush needed)" % (r["step_bytes"] / 1e6)},
-        "roofline": roofline, "clocks": r["clocks"], "gpu_launches": int(r["launches"]),
-        "host_submit_ms_per_step": {"mean": round(r["host_submit_ms"][0] / K, 3), "min": round(r["host_submit_ms"][1], 3)},
-    }
-    if r["e2e"]:
-        line["e2e"] = r["e2e"]
-    if not args.no_cpu_baseline and reference_available(args.sensor):
-        n = 400 if args.sensor.startswith("vlp16") else 120
-        rate, stages_ms, mo_calls, wall = run_reference_cpu(args.sensor, 1, n, args.speed, args.stages, pin=False)
-        line["cpu_baseline"] = {"value": rate, "unit": UNIT, "cores": 1, "kind": "reference",
-                                "sample": "%d scans of one street sequence, reference sources compiled verbatim (oracle/_ref), %.1f s" % (n, wall),
-                                "per_stage_ms": {k: round(v, 4) for k, v in stages_ms.items() if isinstance(v, float)}}
-    if args.profile_json:
+    if profile_dump is not None:
+        profile_dump["line"] = line
         with open(args.profile_json, "w") as f:
-            json.dump({"per_kernel_ms_over_timed_steps": {k: {"ms": v[0], "launches": v[1],
-                                                             "algorithmic_bytes_per_launch": algorithmic_bytes(k, r["counts"])}
-                                                         for k, v in r["prof"].items()},
-                       "counts": {k: v for k, v in r["counts"].items() if k != "mo_bytes"}, "line": line}, f, indent=1)
+            json.dump(profile_dump, f, indent=1)
     print(json.dumps(line))
 
 

@@ -19,17 +19,21 @@ def _worker(rank, world, port, q):
     import bench
     dist.init_process_group("gloo", rank=rank, world_size=world)
     try:
-        seeds = bench.lane_seeds(rank, 4)
+        seeds = bench.rank_seeds(rank, world, 4)
         gathered = [None] * world
         dist.all_gather_object(gathered, seeds)
         slow = bench.max_over_ranks(10.0 + rank, world)         # rank 1 is the slow one
         r, w, l = bench.dist_env()
         # same synthetic generator, different seeds -> different scans on every rank
-        x, ring, npts, stamps, cap = bench.gen_inputs("vlp16", seeds[:1], 1, speed=3.0)
-        digest = float(x[0, 0, :npts[0, 0], :3].sum())
+        inp = bench.Inputs("vlp16", seeds[:2], 3, "drive", 3.0, 3, pinned=False)
+        assert inp.xyz.shape == (3, 2, inp.cap, 3) and inp.npts.shape == (3, 2)
+        digest = float(inp.xyz[0, 0, :inp.npts[0, 0]].sum())
+        # lane l replays sequence l % D: the per-lane address tables point into the [scan][sequence][cap] buffer
+        xt, rt, seq = inp.tables(inp.xyz.ctypes.data, inp.ring.ctypes.data, 5)
+        assert list(seq) == [0, 1, 0, 1, 0] and int(xt[1] - xt[0]) == inp.cap * 12 and int(rt[3] - rt[2]) == inp.cap * 2
         digests = [None] * world
         dist.all_gather_object(digests, digest)
-        class A: sensor = "vlp16"; steps = 1; warmup = 0; speed = 3.0; stages = 3; gpus = world
+        class A: sensor = "vlp16"; steps = 1; warmup = 0; speed = 3.0; stages = 3; gpus = world; workload = "drive"; scans_per_step = 0
         ref_line = None
         if rank != 0:
             ref_line = bench.run_reference_arm(A)                # must be None without doing work
@@ -56,3 +60,20 @@ def test_two_ranks_shard_sequences_and_reduce_max():
         assert len(set(flat)) == len(flat) == 8                  # disjoint sequences
         assert digests[0] != digests[1]
         assert ref_line is None
+
+
+def test_window_is_the_same_for_both_arms():
+    """the driver's --steps 20 --warmup 5: 125 untimed + 500 timed scans per lane, starting at the steady-state local map"""
+    sys.path.insert(0, ROOT)
+    import bench
+    class A: sensor = "vlp16"; steps = 20; warmup = 5; speed = 4.0; scans_per_step = 0
+    w = bench.Window(A, "vlp16")
+    assert (w.S, w.first_timed, w.T, w.prime) == (25, 125, 625, 0)
+    assert w.describe()["timed_scan_range"] == [125, 624]
+    w = bench.Window(A, "hdl64")                  # fewer scans per step: the window is primed up to the steady state
+    assert (w.S, w.first_timed, w.T, w.prime) == (10, 125, 325, 75)
+    A.steps, A.warmup = 2, 1
+    w = bench.Window(A, "vlp16")
+    assert w.first_timed == 125 and w.prime == 100 and w.T == 175
+    assert bench.default_distinct("vlp16", 1, 592, 625, 28800) == 32
+    assert bench.default_distinct("vlp16", 8, 592, 625, 28800) == 4
