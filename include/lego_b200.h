@@ -260,6 +260,24 @@ int lego_pipeline_global_map(lego_pipeline* h, int lane, int which, float* xyzi_
 int lego_mo_global_map(lego_mo* h, int which, float* xyzi_out, long cap, long* n_out);
 int lego_write_pcd_ascii(const char* path, const float* xyzi, long n);
 
+/* ---------------------------------------------------------------- allocation-free VoxelGrid
+ * No counterpart in the reference: added for callers that cannot call cudaMalloc
+ * (code under CUDA graph capture, tight serving loops, harnesses that forbid it).  pcl::VoxelGrid<PointXYZI>::filter with
+ * setLeafSize(leaf, leaf, leaf) on ONE cloud, the same kernels as every other VoxelGrid of this library, but with the
+ * sort scratch in a file-scope static __device__ array instead of allocated memory (csrc/voxel_grid_noalloc.cu):
+ *   - d_xyzi: n * 4 floats of DEVICE memory; d_out: out_cap * 4 floats of DEVICE memory (out_cap >= n is always enough);
+ *     d_n_out: one int of DEVICE memory that receives the size of the filtered cloud; cuda_stream: a cudaStream_t
+ *     (NULL = the default stream) of the current device.
+ *   - n <= LEGO_VG_NOALLOC_MAX_POINTS, otherwise LEGO_ERR_CAPACITY (lego_last_error() names the limit).  The scratch
+ *     (4.3 MB) is held by every GPU that loads the library until the process exits.
+ *   - the call only ENQUEUES kernels on cuda_stream and returns; it calls no cudaMalloc / cudaFree / allocating routine
+ *     and does not synchronise.  Results are complete when the stream has run.
+ *   - all calls on one GPU share the scratch array (it keeps the last call's contents; every call re-initialises what
+ *     it reads): calls that OVERLAP on the same GPU -- different streams or host threads -- race.  Serialise them. */
+#define LEGO_VG_NOALLOC_MAX_POINTS 262144
+int lego_voxel_grid_noalloc(const float* d_xyzi, int n, float leaf, float* d_out, int out_cap, int* d_n_out, void* cuda_stream);
+int lego_voxel_grid_noalloc_max_points(void);
+
 /* ---------------------------------------------------------------- device self-tests (parity suite) */
 /* out[i] = the device implementation of glibc's atan2f(y[i], x[i]) (csrc/parity_math.cuh); host pointers. */
 int lego_selftest_atan2f(const float* y, const float* x, float* out, long n);

@@ -23,6 +23,7 @@ EXPORTED = [
     "lego_selftest_atan2f", "lego_selftest_std_sort", "lego_selftest_warp_sort", "lego_selftest_voxel_grid",
     "lego_selftest_sincosf", "lego_icp_align", "lego_pipeline_imu", "lego_fa_imu", "lego_mo_imu",
     "lego_pipeline_global_map", "lego_mo_global_map", "lego_write_pcd_ascii",
+    "lego_voxel_grid_noalloc", "lego_voxel_grid_noalloc_max_points",
     "lego_pg_create", "lego_pg_destroy", "lego_pg_add_prior", "lego_pg_add_between", "lego_pg_insert", "lego_pg_update", "lego_pg_size", "lego_pg_estimate",
 ]
 
@@ -149,6 +150,14 @@ def selftest_voxel_grid(clouds, leaf):
     for c in counts:
         res.append(out[w:w + c].copy()); w += c
     return res
+
+
+def voxel_grid_noalloc(d_xyzi_ptr, n, leaf, d_out_ptr, out_cap, d_n_out_ptr, stream=0):
+    """lego_voxel_grid_noalloc: raw DEVICE addresses in, kernels enqueued on `stream` (a cudaStream_t as int, 0 = default
+    stream), nothing allocated, nothing synchronised.  Returns the C return code (LEGO_OK = 0, negative = error)."""
+    lib = load()
+    lib.lego_voxel_grid_noalloc.argtypes = [ctypes.c_void_p, ctypes.c_int, ctypes.c_float, ctypes.c_void_p, ctypes.c_int, ctypes.c_void_p, ctypes.c_void_p]
+    return lib.lego_voxel_grid_noalloc(d_xyzi_ptr, int(n), float(leaf), d_out_ptr, int(out_cap), d_n_out_ptr, stream or None)
 
 
 class Pipeline:
