@@ -206,10 +206,8 @@ class Inputs:
         self.cap = cap = seqs[0].cap
         D = self.D
         t0 = time.perf_counter()
-        xs = torch.zeros((T, D, cap, fpp), dtype=torch.float32)
-        rs = torch.zeros((T, D, cap), dtype=torch.int16)
-        if pinned:
-            xs, rs = xs.pin_memory(), rs.pin_memory()
+        xs = torch.zeros((T, D, cap, fpp), dtype=torch.float32, pin_memory=pinned)
+        rs = torch.zeros((T, D, cap), dtype=torch.int16, pin_memory=pinned)
         self._keep = (xs, rs)
         self.xyz = xs.numpy()
         self.ring = rs.numpy().view(np.uint16)
