@@ -140,7 +140,40 @@ struct MoKfEntry {
     int srcS, nS, dstS;       // surf cloud -> laserCloudSurfFromMap
     int srcO, nO, dstO;       // outlier cloud -> laserCloudSurfFromMap (right behind the surf cloud of the same key frame)
     float ctRoll, stRoll, ctPitch, stPitch, ctYaw, stYaw, tInX, tInY, tInZ;
+    int id;                   // key-frame index (cloudKeyPoses3D position); the incremental local map tags its points with it
 };
+
+// ---- incremental local map (incremental_map.cu) ----
+// extractSurroundingKeyFrames (mapOptmization.cpp:1013-1063) re-filters the whole local map in every call although its
+// key-frame list only loses the frames that left the 50 m neighbourhood and gains the new ones at the END (1013-1049 is a
+// cache diff).  The device keeps, per lane and per cloud (corner / surf+outlier), the transformed key-frame points SORTED
+// by (voxel of the map's VoxelGrid, position in the list, point index) -- the order pcl::VoxelGrid sums them in -- and per
+// call deletes, merges and re-reduces instead of sorting everything again.
+constexpr int IM_MAX_DEPARTED = 16;   // more frames leaving in one call -> the lane rebuilds from scratch
+constexpr int IM_TILE = 1024;
+struct ImCtl {                // per lane, written by the host bookkeeping for every mapping call
+    int changed;              // 0: same key-frame list as in the last call, the down-sampled map on the device is still valid
+    int rebuild;              // 1: forget the sorted state, every listed frame arrives as new
+    int nDeparted;
+    int departed[IM_MAX_DEPARTED];   // key-frame ids that left the list
+};
+struct ImSeg {                // one sorted cloud: segment 2*lane = corner map (leaf 0.2), 2*lane+1 = surf map (leaf 0.4)
+    float4* pts[2];           // [cap] ping-pong: the sorted points
+    int* frame[2];            // [cap] key-frame id of every point
+    int* rank;                // [cap] number of surviving points in front of point i (written by the merge)
+    float4* newPts; int* newFrame; unsigned long long* newKey;   // [newCap] the arriving points, sorted
+    const float4* raw;        // the arriving points as mo_assemble_map_kernel wrote them (list order)
+    const int* nRaw;          // their number
+    const VgSeg* sorter;      // radix-sort scratch of this segment: vg_sorted_vals() = order of `raw`
+    float4* out; int* nOut;   // down-sampled map + its size (laserCloud*FromMapDS)
+    int* nTotal;              // size of the sorted cloud, for the records (laserCloud*FromMap)
+    int* state;               // [8] 0: current buffer, 1: points in it, 2: survivors of this call, 3: arrivals of this call
+    int* tileKept; int* tileHeads;   // [cap / IM_TILE + 1]
+    int* errors;              // moState[lane][5]
+    float leaf;
+    int cap, newCap, outCap, type;
+};
+struct ImBatch { ImSeg* segs; int nSeg; int maxTiles; int maxNewTiles; };
 // What saveKeyFramesAndFactor (mapOptmization.cpp:1353-1454) decided on the device, read back asynchronously by the
 // host bookkeeping before the next mapping call.
 struct MoRecord {
@@ -205,6 +238,8 @@ struct MoDev {
     int4* knnRes;              // [L][resBlocks*256][2] idx0..3 | idx4, 5th squared distance, neighbours found
     int* knnMissList;          // [L][resBlocks*256] queries to search again in this iteration
     int* knnMissCount;         // [L]
+    ImCtl* imCtl;              // [L] incremental local map: this call's list diff
+    int* imNewCounts;          // [L][4] points of the arriving key frames (corner, surf+outlier)
     int resBlocks;             // CTAs per lane in mo_residual_kernel
     int poolCap, maxSel, cornerRawCap, surfRawCap, cornerDSCap, surfDSCap, scanCornerCap, scanSurfCap, scanOutlierCap, maxKeyFrames;
 };
@@ -221,6 +256,8 @@ struct MoLaneHost {
     // FeatureAssociation's publish cadence mirrored on the host (featureAssociation.cpp:284, 314, 1790-1794)
     bool faInited = false; int faFrameCount = 1;
     int lastError = 0;
+    std::vector<int> imList;                          // key frames in the device's sorted local map, in list order
+    bool imValid = false;
     // ---- loop closure state (only used when loopClosureEnableFlag is set) ----
     std::deque<int> recent;                           // recentCorner/Surf/OutlierCloudKeyFrames as key-frame ids (mapOptmization.cpp:960-1000)
     int latestFrameID = 0;                            // mapOptmization.cpp:373
@@ -340,6 +377,12 @@ public:
     TfDev tf;
     std::vector<MoLaneHost> moHost;
     VgBatch vgMap;             // 2 segments per lane: local corner / surf map
+    VgBatch vgMapNew;          // the same scratch, sorting only the arriving key frames (incremental local map)
+    ImBatch im = {};
+    bool imEnabled = false;    // LEGO_INCR_MAP=0 (or loop closure, which rewrites key poses) keeps the full filter
+    void allocIncrementalMap(const std::vector<VgSeg>& mapSegs);
+    void diffSurroundingKeyFrames(int lane, const std::vector<MoKfEntry>& all, std::vector<MoKfEntry>& arriving, ImCtl* ctl, int* nCorner, int* nSurf);
+    int incrementalLocalMap();   // enqueues the merge / reduce launches, returns their number
     VgBatch vgScan[2];         // per value of faBuf, 3 segments per lane: corner / surf / outlier cloud of the current scan
     VgBatch vgSurfTotal;       // 1 segment per lane
     LcDev lc = {};             // loop-closure slots (allocated only when loopClosureEnableFlag is set)

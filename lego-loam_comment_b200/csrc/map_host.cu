@@ -97,6 +97,7 @@ void Engine::allocMapOptimization() {
                               mo.mapCounts + l * 4 + 3, mo.active + l, 0.4f, mo.surfRawCap, mo.surfDSCap));
     }
     vgMap = make_batch(mapSegs, mo.surfRawCap);
+    allocIncrementalMap(mapSegs);   // (make_batch filled in the scratch pointers of mapSegs)
     // current scan (mapOptmization.cpp:1067-1081): the inputs are FeatureAssociation's "last" clouds, double buffered
     for (int b = 0; b < 2; ++b) {
         std::vector<VgSeg> s;
@@ -117,7 +118,7 @@ void Engine::allocMapOptimization() {
     vgSurfTotal = make_batch(tot, (int)totCap);
 
     // ---- pinned staging for the per-call selection and the records ----
-    moPinnedStride = sizeof(MoKfEntry) * L * mo.maxSel + sizeof(int) * L * 6;
+    moPinnedStride = sizeof(MoKfEntry) * L * mo.maxSel + sizeof(int) * L * 6 + sizeof(ImCtl) * L;
     cuda_check(cudaMallocHost(reinterpret_cast<void**>(&moPinned), 2 * moPinnedStride), "cudaMallocHost");
     cuda_check(cudaMallocHost(reinterpret_cast<void**>(&moRecordsHost), sizeof(MoRecord) * L), "cudaMallocHost");
     for (int b = 0; b < 2; ++b) cuda_check(cudaEventCreateWithFlags(&moStaged[b], cudaEventDisableTiming), "event");
@@ -227,6 +228,7 @@ void Engine::selectSurroundingKeyFrames(int lane, std::vector<MoKfEntry>& out, i
     for (int id : ex) {
         const MoKeyFrame& k = H.keyFrames[id];
         MoKfEntry e;
+        e.id = id;
         e.srcC = k.poolOff; e.nC = k.nC; e.dstC = offC; offC += k.nC;
         e.srcS = k.poolOff + k.nC; e.nS = k.nS; e.dstS = offS; offS += k.nS;
         e.srcO = k.poolOff + k.nC + k.nS; e.nO = k.nO; e.dstO = offS; offS += k.nO;
@@ -328,22 +330,34 @@ void Engine::mapOptimizationBody(const std::vector<int>& active) {
     char* base = moPinned + (size_t)slot * moPinnedStride;
     MoKfEntry* hEntries = reinterpret_cast<MoKfEntry*>(base);
     int* hInts = reinterpret_cast<int*>(base + sizeof(MoKfEntry) * (size_t)c.L * mo.maxSel);   // nEntries[L] | active[L] | mapCounts[L][4]
+    ImCtl* hCtl = reinterpret_cast<ImCtl*>(hInts + 6 * (size_t)c.L);
     int maxEntries = 0;
-    std::vector<MoKfEntry> sel;
+    std::vector<MoKfEntry> sel, arriving;
     for (int l = 0; l < c.L; ++l) {
         int nC = 0, nS = 0;
         if (!active[l]) sel.clear();
         else if (loopMode()) selectRecentKeyFrames(l, sel, &nC, &nS);
         else selectSurroundingKeyFrames(l, sel, &nC, &nS);
+        if (imEnabled) {
+            // only the key frames that entered the list are assembled; the device merges them into its sorted local map
+            if (active[l]) { diffSurroundingKeyFrames(l, sel, arriving, hCtl + l, &nC, &nS); sel.swap(arriving); }
+            else std::memset(hCtl + l, 0, sizeof(ImCtl));
+        }
         std::memcpy(hEntries + (size_t)l * mo.maxSel, sel.data(), sizeof(MoKfEntry) * sel.size());
         hInts[l] = (int)sel.size(); hInts[c.L + l] = active[l];
         hInts[2 * c.L + l * 4 + 0] = nC; hInts[2 * c.L + l * 4 + 1] = nS; hInts[2 * c.L + l * 4 + 2] = 0; hInts[2 * c.L + l * 4 + 3] = 0;
         maxEntries = std::max(maxEntries, (int)sel.size());
     }
+    // (only the live part of the entry table travels: maxEntries rows per lane would need a strided copy, the whole table is 2.7 MB)
     cuda_check(cudaMemcpyAsync(mo.entries, hEntries, sizeof(MoKfEntry) * (size_t)c.L * mo.maxSel, cudaMemcpyHostToDevice, stream), "entries");
     cuda_check(cudaMemcpyAsync(mo.nEntries, hInts, sizeof(int) * c.L, cudaMemcpyHostToDevice, stream), "nEntries");
     cuda_check(cudaMemcpyAsync(mo.active, hInts + c.L, sizeof(int) * c.L, cudaMemcpyHostToDevice, stream), "active");
-    cuda_check(cudaMemcpyAsync(mo.mapCounts, hInts + 2 * c.L, sizeof(int) * 4 * c.L, cudaMemcpyHostToDevice, stream), "mapCounts");
+    if (imEnabled) {
+        cuda_check(cudaMemcpyAsync(mo.imNewCounts, hInts + 2 * c.L, sizeof(int) * 4 * c.L, cudaMemcpyHostToDevice, stream), "imNewCounts");
+        cuda_check(cudaMemcpyAsync(mo.imCtl, hCtl, sizeof(ImCtl) * c.L, cudaMemcpyHostToDevice, stream), "imCtl");
+    } else {
+        cuda_check(cudaMemcpyAsync(mo.mapCounts, hInts + 2 * c.L, sizeof(int) * 4 * c.L, cudaMemcpyHostToDevice, stream), "mapCounts");
+    }
     cuda_check(cudaEventRecord(moStaged[slot], stream), "event record");
 
     mapOptimizationImuBlend(active);
@@ -355,7 +369,8 @@ void Engine::mapOptimizationBody(const std::vector<int>& active) {
         mo_assemble_map_kernel<<<g, 256, 0, stream>>>(mo);
         launches += 1;
     }
-    { ProfScope ps(this, "vg_filter(localMap)"); launches += vg_filter(vgMap, stream); }
+    if (imEnabled) launches += incrementalLocalMap();
+    else { ProfScope ps(this, "vg_filter(localMap)"); launches += vg_filter(vgMap, stream); }
     { ProfScope ps(this, "vg_filter(currentScan)"); launches += vg_filter(vgScan[faBuf], stream); }
     {
         dim3 g(8, c.L);

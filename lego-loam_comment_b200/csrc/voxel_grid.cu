@@ -20,7 +20,7 @@ __global__ void vg_init_kernel(VgBatch b) {
     const VgSeg& s = b.segs[si];
     if (!vg_live(s)) { s.state[9] = 0; return; }
     for (int a = 0; a < 3; ++a) { s.state[a] = INT_MAX; s.state[3 + a] = INT_MIN; }
-    s.state[6] = 0; s.state[7] = 0; s.state[8] = 0; s.state[10] = 0;
+    s.state[6] = 0; s.state[7] = 0; s.state[8] = 0; s.state[10] = 0; s.state[12] = 0;
     int n = *s.nIn;
     if (n > s.cap) { n = s.cap; s.state[10] = 1; }
     s.state[9] = n;
@@ -63,6 +63,7 @@ __global__ void __launch_bounds__(VG_THREADS) vg_keys_kernel(VgBatch b) {
     }
     // PCL refuses grids with more than INT_MAX voxels and returns the input unchanged: identity keys do the same
     const bool overflow = dd[0] * dd[1] * dd[2] > (long long)INT_MAX;
+    if (overflow && blockIdx.x == 0 && threadIdx.x == 0) s.state[12] = 1;
     for (int tile = blockIdx.x; tile * VG_TILE < n; tile += gridDim.x) {
     const int t0 = tile * VG_TILE, t1 = min(t0 + VG_TILE, n);
     for (int i = t0 + threadIdx.x; i < t1; i += VG_THREADS) {
@@ -247,6 +248,20 @@ __global__ void __launch_bounds__(VG_THREADS) vg_reduce_kernel(VgBatch b) {
     }
     __syncthreads();
     }
+}
+
+int vg_sort_keys(const VgBatch& b, cudaStream_t stream) {
+    if (b.nSeg <= 0) return 0;
+    dim3 g(b.maxBlocks < 8 ? b.maxBlocks : 8, b.nSeg);
+    vg_init_kernel<<<(b.nSeg + 127) / 128, 128, 0, stream>>>(b);
+    vg_bbox_kernel<<<g, VG_THREADS, 0, stream>>>(b);
+    vg_keys_kernel<<<g, VG_THREADS, 0, stream>>>(b);
+    for (int pass = 0; pass < 4; ++pass) {
+        rs_hist_kernel<<<g, VG_THREADS, 0, stream>>>(b, pass * 8);
+        rs_scan_kernel<<<b.nSeg, 256, 0, stream>>>(b);
+        rs_scatter_kernel<<<g, VG_THREADS, 0, stream>>>(b, pass * 8);
+    }
+    return 15;
 }
 
 int vg_filter(const VgBatch& b, cudaStream_t stream) {

@@ -28,7 +28,8 @@ struct VgSeg {
     int* blockHist;          // [256][maxBlocks] digit-major block histograms of the current pass, then block offsets
     int* blockHeads;         // [maxBlocks]
     int* state;              // [16]: 0..2 ordered-int min xyz, 3..5 ordered-int max xyz, 6 current buffer, 7 pending flip,
-                             //       8 skip this pass, 9 live size n, 10 error (output truncated)
+                             //       8 skip this pass, 9 live size n, 10 error (output truncated),
+                             //       12 the grid would exceed INT_MAX voxels (PCL returns the input unchanged: identity keys)
 };
 
 struct VgBatch {
@@ -39,5 +40,10 @@ struct VgBatch {
 
 // Enqueues the launches of one batched filter; returns the number of launches.
 int vg_filter(const VgBatch& b, cudaStream_t stream);
+// Only the first half: bounding box, voxel keys and the stable radix sort.  Afterwards vg_sorted_vals(seg)[j] is the input
+// index of the j-th point in (voxel index, input order) order; out / nOut are not touched.  Used by the incremental local
+// map (incremental_map.cu), which sorts just the key frames that entered the neighbourhood.
+int vg_sort_keys(const VgBatch& b, cudaStream_t stream);
+__device__ __forceinline__ const unsigned* vg_sorted_vals(const VgSeg& s) { return s.vals[s.state[6] ^ s.state[7]]; }
 
 }  // namespace lego

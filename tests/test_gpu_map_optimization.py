@@ -137,3 +137,44 @@ def test_neighbour_cache_changes_nothing(monkeypatch):
             mapped += 1; iters += int(out[0][2][3])
     assert mapped >= 6 and iters >= 2 * mapped, "too few LM iterations (%d in %d calls) for the cache to matter" % (iters, mapped)
     plain.close(); cached.close()
+
+
+def test_incremental_local_map_changes_nothing(monkeypatch):
+    """The local map of extractSurroundingKeyFrames is kept sorted on the device and updated per call (key frames that left
+    are deleted, the new ones merged in: csrc/incremental_map.cu).  With LEGO_INCR_MAP=0 every call assembles and filters
+    the whole map like the reference (mapOptmization.cpp:1041-1063).  Both paths must give the same down-sampled maps
+    and poses bit for bit, long enough for key frames to LEAVE the 50 m neighbourhood (10 m/s: from scan ~50 on)."""
+    sensor = "vlp16"
+    seqs = [SynthSequence(sensor, seed=61, scene="street", speed=10.0), SynthSequence(sensor, seed=62, scene="street", speed=7.0, dropout=0.01)]
+    cap = seqs[0].cap
+    monkeypatch.setenv("LEGO_INCR_MAP", "0")
+    full = Pipeline(make_params(sensor), lanes=2, max_points=cap)
+    monkeypatch.setenv("LEGO_INCR_MAP", "1")
+    incr = Pipeline(make_params(sensor), lanes=2, max_points=cap)
+    mapped = 0
+    max_kf, departed_seen = 0, False
+    for k in range(200):
+        x = np.zeros((2, cap, 4), np.float32); r = np.zeros((2, cap), np.uint16); n = np.zeros(2, np.int32)
+        for l, q in enumerate(seqs):
+            xyzi, ring = q.scan(k)
+            n[l] = len(xyzi); x[l, :n[l]] = xyzi; r[l, :n[l]] = ring
+        res = []
+        for pl in (full, incr):
+            pl.step(x, r, n, [k * 0.1, k * 0.1], stage_mask=7)
+            res.append(pl.poses())
+        assert np.array_equal(res[0][1], res[1][1])
+        assert np.array_equal(res[0][0].view(np.uint32), res[1][0].view(np.uint32)), "scan %d: poses differ" % k
+        if res[0][1][0] & 8:
+            mapped += 1
+            for lane in range(2):
+                for name in ("laserCloudCornerFromMapDS", "laserCloudSurfFromMapDS"):
+                    a, b = full.download(name, lane), incr.download(name, lane)
+                    assert a.shape == b.shape and np.array_equal(a.view(np.uint32), b.view(np.uint32)), "scan %d lane %d %s" % (k, lane, name)
+                assert np.array_equal(full.download("moState", lane), incr.download("moState", lane))
+            in_map = len(incr.download("surroundingExistingKeyPosesID", 0))
+            saved = int(incr.download("moState", 0)[1])
+            max_kf = max(max_kf, in_map)
+            departed_seen |= saved > in_map + 2
+    assert mapped >= 45 and departed_seen and max_kf >= 8, (mapped, departed_seen, max_kf)
+    assert int(incr.download("moState", 0)[5]) == 0
+    full.close(); incr.close()
