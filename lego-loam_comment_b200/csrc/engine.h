@@ -160,7 +160,7 @@ struct ImCtl {                // per lane, written by the host bookkeeping for e
 struct ImSeg {                // one sorted cloud: segment 2*lane = corner map (leaf 0.2), 2*lane+1 = surf map (leaf 0.4)
     float4* pts[2];           // [cap] ping-pong: the sorted points
     int* frame[2];            // [cap] key-frame id of every point
-    int* rank;                // [cap] number of surviving points in front of point i (written by the merge)
+    int* rank;                // [cap / 32] number of surviving points in front of point 32 k (written by the merge)
     float4* newPts; int* newFrame; unsigned long long* newKey;   // [newCap] the arriving points, sorted
     const float4* raw;        // the arriving points as mo_assemble_map_kernel wrote them (list order)
     const int* nRaw;          // their number

@@ -33,7 +33,10 @@ __device__ __forceinline__ unsigned long long im_key(float4 p, float inv) {
     return vh_pack(I, J, K);   // x in the low 21 bits, z in the high ones: ascending = (K, J, I) lexicographic
 }
 
-__device__ __forceinline__ int block_sum_1024(int v, int* ws) {
+constexpr int IM_THREADS = 256;   // every thread owns IM_TILE / IM_THREADS = 4 consecutive points of a tile
+constexpr int IM_PER = IM_TILE / IM_THREADS;
+
+__device__ __forceinline__ int block_sum(int v, int* ws) {
     const int lid = threadIdx.x & 31, w = threadIdx.x >> 5;
     v = warp_sum(v);
     __syncthreads();
@@ -44,14 +47,14 @@ __device__ __forceinline__ int block_sum_1024(int v, int* ws) {
     return t;
 }
 
-// exclusive prefix of `flag` over the block (1024 threads) + the block total
-__device__ __forceinline__ int block_excl_scan_1024(int flag, int* ws, int* total) {
+// exclusive prefix of `v` over the block + the block total
+__device__ __forceinline__ int block_excl_scan(int v, int* ws, int* total) {
     const int lid = threadIdx.x & 31, w = threadIdx.x >> 5;
-    const int inc = warp_inclusive_scan(flag);
+    const int inc = warp_inclusive_scan(v);
     __syncthreads();
     if (lid == 31) ws[w] = inc;
     __syncthreads();
-    int off = inc - flag, t = 0;
+    int off = inc - v, t = 0;
     for (int q = 0; q < (int)(blockDim.x >> 5); ++q) { const int x = ws[q]; if (q < w) off += x; t += x; }
     *total = t;
     return off;
@@ -69,7 +72,7 @@ __device__ __forceinline__ int im_frame_of(const MoKfEntry* en, int nE, int type
 }
 
 // (b) the arriving points in sorted order: into the other ping-pong buffer when the lane rebuilds, else into newPts.
-__global__ void __launch_bounds__(IM_TILE) im_gather_new_kernel(ImBatch b, MoDev m) {
+__global__ void __launch_bounds__(IM_THREADS) im_gather_new_kernel(ImBatch b, MoDev m) {
     const ImSeg& s = b.segs[blockIdx.y];
     const int lane = blockIdx.y >> 1;
     if (!m.active[lane]) return;
@@ -87,7 +90,7 @@ __global__ void __launch_bounds__(IM_TILE) im_gather_new_kernel(ImBatch b, MoDev
     const int nE = m.nEntries[lane];
     const float inv = PM_DIV(1.0f, s.leaf);
     const int next = s.state[0] ^ 1;
-    for (int j = blockIdx.x * IM_TILE + threadIdx.x; j < n; j += gridDim.x * IM_TILE) {
+    for (int j = blockIdx.x * IM_THREADS + threadIdx.x; j < n; j += gridDim.x * IM_THREADS) {
         const int src = (int)vals[j];
         const float4 p = s.raw[src];
         const int f = im_frame_of(en, nE, s.type, src);
@@ -102,30 +105,39 @@ __device__ __forceinline__ bool im_departed(const ImCtl& ctl, int f) {
     return d;
 }
 
-// (a) survivors per tile of the current sorted cloud
-__global__ void __launch_bounds__(IM_TILE) im_mark_kernel(ImBatch b, MoDev m) {
+// (a) survivors per tile of the current sorted cloud (reads only the frame ids)
+__global__ void __launch_bounds__(IM_THREADS) im_mark_kernel(ImBatch b, MoDev m) {
     const ImSeg& s = b.segs[blockIdx.y];
     const int lane = blockIdx.y >> 1;
     if (!m.active[lane]) return;
-    const ImCtl& ctl = m.imCtl[lane];
+    const ImCtl ctl = m.imCtl[lane];
     if (!ctl.changed || ctl.rebuild) return;
     __shared__ int ws[32];
     const int n = s.state[1];
-    const int* fr = s.frame[s.state[0]];
+    const int* __restrict__ fr = s.frame[s.state[0]];
+    int* tileKept = s.tileKept;
     for (int tile = blockIdx.x; tile * IM_TILE < n; tile += gridDim.x) {
-        const int i = tile * IM_TILE + threadIdx.x;
-        const int keep = (i < n && !im_departed(ctl, fr[i])) ? 1 : 0;
-        const int t = block_sum_1024(keep, ws);
-        if (threadIdx.x == 0) s.tileKept[tile] = t;
+        const int i0 = tile * IM_TILE + threadIdx.x * IM_PER;
+        int keep = 0;
+        if (i0 + IM_PER <= n) {
+            const int4 f = *reinterpret_cast<const int4*>(fr + i0);
+            keep = (im_departed(ctl, f.x) ? 0 : 1) + (im_departed(ctl, f.y) ? 0 : 1) + (im_departed(ctl, f.z) ? 0 : 1) + (im_departed(ctl, f.w) ? 0 : 1);
+        } else {
+            for (int e = 0; e < IM_PER; ++e) if (i0 + e < n && !im_departed(ctl, fr[i0 + e])) ++keep;
+        }
+        const int t = block_sum(keep, ws);
+        if (threadIdx.x == 0) tileKept[tile] = t;
     }
 }
 
-// (c) survivors move to rank + (arrivals with a smaller voxel); every point also records its rank for the arrivals' pass
-__global__ void __launch_bounds__(IM_TILE) im_merge_old_kernel(ImBatch b, MoDev m) {
+// (c) survivors move to rank + (arrivals with a smaller voxel).  A thread owns 4 consecutive points: one binary search
+// over the arrivals for the first, the others gallop on from there (voxels ascend, arrivals are ~30x sparser).  The rank of
+// every 32nd point is kept for the arrivals' pass.
+__global__ void __launch_bounds__(IM_THREADS) im_merge_old_kernel(ImBatch b, MoDev m) {
     const ImSeg& s = b.segs[blockIdx.y];
     const int lane = blockIdx.y >> 1;
     if (!m.active[lane]) return;
-    const ImCtl& ctl = m.imCtl[lane];
+    const ImCtl ctl = m.imCtl[lane];
     if (!ctl.changed || ctl.rebuild) return;
     __shared__ int ws[32];
     const int n = s.state[1], nNew = min(s.state[3], s.newCap);
@@ -133,26 +145,47 @@ __global__ void __launch_bounds__(IM_TILE) im_merge_old_kernel(ImBatch b, MoDev 
     const float4* __restrict__ src = s.pts[cur]; const int* __restrict__ fr = s.frame[cur];
     float4* __restrict__ dst = s.pts[cur ^ 1]; int* __restrict__ dfr = s.frame[cur ^ 1];
     const unsigned long long* __restrict__ nk = s.newKey;
+    const int* tileKept = s.tileKept; int* rank32 = s.rank; int* state = s.state;
     const float inv = PM_DIV(1.0f, s.leaf);
     for (int tile = blockIdx.x; tile * IM_TILE < n; tile += gridDim.x) {
         int pre = 0;
-        for (int k = threadIdx.x; k < tile; k += IM_TILE) pre += s.tileKept[k];
-        pre = block_sum_1024(pre, ws);
-        const int i = tile * IM_TILE + threadIdx.x;
-        float4 p = make_float4(0.f, 0.f, 0.f, 0.f); int f = -1, keep = 0;
-        if (i < n) { p = src[i]; f = fr[i]; keep = im_departed(ctl, f) ? 0 : 1; }
-        int total;
-        const int r = pre + block_excl_scan_1024(keep, ws, &total);
-        if (i < n) s.rank[i] = r;
-        if (keep) {
-            const unsigned long long key = im_key(p, inv);
-            int lo = 0, hi = nNew;            // arrivals with key < this point's key (equal voxels: old before new)
-            while (lo < hi) { const int mid = (lo + hi) >> 1; if (nk[mid] < key) lo = mid + 1; else hi = mid; }
-            dst[r + lo] = p; dfr[r + lo] = f;
+        for (int k = threadIdx.x; k < tile; k += IM_THREADS) pre += tileKept[k];
+        pre = block_sum(pre, ws);
+        const int i0 = tile * IM_TILE + threadIdx.x * IM_PER;
+        float4 p[IM_PER]; int f[IM_PER]; int keep[IM_PER]; int mine = 0;
+#pragma unroll
+        for (int e = 0; e < IM_PER; ++e) {
+            keep[e] = 0; f[e] = -1; p[e] = make_float4(0.f, 0.f, 0.f, 0.f);
+            if (i0 + e < n) { p[e] = src[i0 + e]; f[e] = fr[i0 + e]; keep[e] = im_departed(ctl, f[e]) ? 0 : 1; }
+            mine += keep[e];
         }
-        if (threadIdx.x == 0 && (tile + 1) * IM_TILE >= n) s.state[2] = pre + total;
+        int total;
+        int r = pre + block_excl_scan(mine, ws, &total);
+        if ((threadIdx.x & 7) == 0 && i0 < n) rank32[i0 >> 5] = r;
+        int lo = -1;
+#pragma unroll
+        for (int e = 0; e < IM_PER; ++e) {
+            if (!keep[e]) continue;
+            const unsigned long long key = im_key(p[e], inv);
+            if (lo < 0) {                     // arrivals with key < this point's key (equal voxels: old before new)
+                int a = 0, z = nNew;
+                while (a < z) { const int mid = (a + z) >> 1; if (nk[mid] < key) a = mid + 1; else z = mid; }
+                lo = a;
+            } else {
+                int step = 0;
+                while (lo < nNew && nk[lo] < key && step < 8) { ++lo; ++step; }
+                if (lo < nNew && nk[lo] < key) {   // a long stretch of arrivals in between: search the rest
+                    int a = lo, z = nNew;
+                    while (a < z) { const int mid = (a + z) >> 1; if (nk[mid] < key) a = mid + 1; else z = mid; }
+                    lo = a;
+                }
+            }
+            dst[r + lo] = p[e]; dfr[r + lo] = f[e];
+            ++r;
+        }
+        if (threadIdx.x == 0 && (tile + 1) * IM_TILE >= n) state[2] = pre + total;
     }
-    if (n == 0 && blockIdx.x == 0 && threadIdx.x == 0) s.state[2] = 0;
+    if (n == 0 && blockIdx.x == 0 && threadIdx.x == 0) state[2] = 0;
 }
 
 // (c) arrivals move to their index + (survivors with a voxel <= theirs)
@@ -160,19 +193,24 @@ __global__ void __launch_bounds__(256) im_merge_new_kernel(ImBatch b, MoDev m) {
     const ImSeg& s = b.segs[blockIdx.y];
     const int lane = blockIdx.y >> 1;
     if (!m.active[lane]) return;
-    const ImCtl& ctl = m.imCtl[lane];
+    const ImCtl ctl = m.imCtl[lane];
     if (!ctl.changed || ctl.rebuild) return;
     const int n = s.state[1], nNew = min(s.state[3], s.newCap), kept = s.state[2];
     const int cur = s.state[0];
-    const float4* __restrict__ old = s.pts[cur];
+    const float4* __restrict__ old = s.pts[cur]; const int* __restrict__ fr = s.frame[cur];
+    float4* __restrict__ dst = s.pts[cur ^ 1]; int* __restrict__ dfr = s.frame[cur ^ 1];
     const float inv = PM_DIV(1.0f, s.leaf);
     for (int j = blockIdx.x * blockDim.x + threadIdx.x; j < nNew; j += gridDim.x * blockDim.x) {
         const unsigned long long key = s.newKey[j];
         int lo = 0, hi = n;                   // first old point with a larger voxel
         while (lo < hi) { const int mid = (lo + hi) >> 1; if (im_key(old[mid], inv) <= key) lo = mid + 1; else hi = mid; }
-        const int before = lo < n ? s.rank[lo] : kept;
-        s.pts[cur ^ 1][j + before] = s.newPts[j];
-        s.frame[cur ^ 1][j + before] = s.newFrame[j];
+        int before = kept;
+        if (lo < n) {                         // survivors in front of old[lo]: the recorded rank of its group of 32 + the group's head
+            before = s.rank[lo >> 5];
+            for (int q = lo & ~31; q < lo; ++q) before += im_departed(ctl, fr[q]) ? 0 : 1;
+        }
+        dst[j + before] = s.newPts[j];
+        dfr[j + before] = s.newFrame[j];
     }
 }
 
@@ -190,55 +228,88 @@ __global__ void im_commit_kernel(ImBatch b, MoDev m) {
     *s.nTotal = n;
 }
 
-// (d) voxel runs of the merged cloud: heads per tile, then one thread per head averages its run front to back
-__global__ void __launch_bounds__(IM_TILE) im_heads_kernel(ImBatch b, MoDev m) {
+// (d) voxel runs of the merged cloud.  A tile's points are staged in shared memory (one coalesced read); the thread that
+// owns the first point of a run folds the run front to back -- the float32 sums of pcl::VoxelGrid: members in input order,
+// starting from 0 -- continuing in global memory when the run leaves the tile.  Results go to tile-local slots of the idle
+// ping-pong buffer; im_compact_kernel moves them to their final positions once every tile's count is known.
+__global__ void __launch_bounds__(IM_THREADS) im_reduce_kernel(ImBatch b, MoDev m) {
     const ImSeg& s = b.segs[blockIdx.y];
     const int lane = blockIdx.y >> 1;
     if (!m.active[lane] || !m.imCtl[lane].changed) return;
     __shared__ int ws[32];
+    __shared__ float4 sp[IM_TILE];
+    __shared__ unsigned long long sk[IM_TILE];
     const int n = s.state[1];
     const float4* __restrict__ pts = s.pts[s.state[0]];
+    float4* __restrict__ stage = s.pts[s.state[0] ^ 1];
+    int* tileHeads = s.tileHeads;
     const float inv = PM_DIV(1.0f, s.leaf);
     for (int tile = blockIdx.x; tile * IM_TILE < n; tile += gridDim.x) {
-        const int i = tile * IM_TILE + threadIdx.x;
-        int head = 0;
-        if (i < n) head = (i == 0 || im_key(pts[i - 1], inv) != im_key(pts[i], inv)) ? 1 : 0;
-        const int t = block_sum_1024(head, ws);
-        if (threadIdx.x == 0) s.tileHeads[tile] = t;
+        const int t0 = tile * IM_TILE, t1 = min(t0 + IM_TILE, n);
+        __syncthreads();
+        for (int k = threadIdx.x; k < t1 - t0; k += IM_THREADS) { const float4 p = pts[t0 + k]; sp[k] = p; sk[k] = im_key(p, inv); }
+        __syncthreads();
+        const int l0 = threadIdx.x * IM_PER;
+        unsigned long long prev = 0ull; bool hasPrev = false;
+        if (t0 + l0 < t1 && t0 + l0 > 0) { prev = l0 > 0 ? sk[l0 - 1] : im_key(pts[t0 - 1], inv); hasPrev = true; }
+        int head[IM_PER]; int mine = 0;
+#pragma unroll
+        for (int e = 0; e < IM_PER; ++e) {
+            head[e] = 0;
+            if (t0 + l0 + e < t1) {
+                const unsigned long long k = sk[l0 + e];
+                head[e] = (!hasPrev || k != prev) ? 1 : 0;
+                prev = k; hasPrev = true;
+            }
+            mine += head[e];
+        }
+        int total;
+        int off = block_excl_scan(mine, ws, &total);
+#pragma unroll
+        for (int e = 0; e < IM_PER; ++e) {
+            if (!head[e]) continue;
+            const int l = l0 + e;
+            const unsigned long long key = sk[l];
+            const float4 p = sp[l];
+            float sx = PM_ADD(0.f, p.x), sy = PM_ADD(0.f, p.y), sz = PM_ADD(0.f, p.z), sw = PM_ADD(0.f, p.w); int cnt = 1;
+            int q = l + 1;
+            for (; q < t1 - t0 && sk[q] == key; ++q) {
+                const float4 a = sp[q];
+                sx = PM_ADD(sx, a.x); sy = PM_ADD(sy, a.y); sz = PM_ADD(sz, a.z); sw = PM_ADD(sw, a.w); ++cnt;
+            }
+            if (q == t1 - t0) {               // the run may go on in the next tiles
+                for (int g = t1; g < n; ++g) {
+                    const float4 a = pts[g];
+                    if (im_key(a, inv) != key) break;
+                    sx = PM_ADD(sx, a.x); sy = PM_ADD(sy, a.y); sz = PM_ADD(sz, a.z); sw = PM_ADD(sw, a.w); ++cnt;
+                }
+            }
+            const float fc = (float)cnt;
+            stage[t0 + off] = make_float4(PM_DIV(sx, fc), PM_DIV(sy, fc), PM_DIV(sz, fc), PM_DIV(sw, fc));
+            ++off;
+        }
+        if (threadIdx.x == 0) tileHeads[tile] = total;
     }
 }
 
-__global__ void __launch_bounds__(IM_TILE) im_reduce_kernel(ImBatch b, MoDev m) {
+__global__ void __launch_bounds__(IM_THREADS) im_compact_kernel(ImBatch b, MoDev m) {
     const ImSeg& s = b.segs[blockIdx.y];
     const int lane = blockIdx.y >> 1;
     if (!m.active[lane] || !m.imCtl[lane].changed) return;
     __shared__ int ws[32];
     const int n = s.state[1];
     if (n == 0) { if (blockIdx.x == 0 && threadIdx.x == 0) *s.nOut = 0; return; }
-    const float4* __restrict__ pts = s.pts[s.state[0]];
-    const float inv = PM_DIV(1.0f, s.leaf);
+    const float4* __restrict__ stage = s.pts[s.state[0] ^ 1];
+    float4* __restrict__ out = s.out;
+    const int* tileHeads = s.tileHeads;
     for (int tile = blockIdx.x; tile * IM_TILE < n; tile += gridDim.x) {
         int pre = 0;
-        for (int k = threadIdx.x; k < tile; k += IM_TILE) pre += s.tileHeads[k];
-        pre = block_sum_1024(pre, ws);
-        const int i = tile * IM_TILE + threadIdx.x;
-        unsigned long long key = 0ull; int head = 0; float4 p = make_float4(0.f, 0.f, 0.f, 0.f);
-        if (i < n) { p = pts[i]; key = im_key(p, inv); head = (i == 0 || im_key(pts[i - 1], inv) != key) ? 1 : 0; }
-        int total;
-        const int off = pre + block_excl_scan_1024(head, ws, &total);
-        if (head) {
-            // the float32 sums of pcl::VoxelGrid: members in input order, starting from 0
-            float sx = PM_ADD(0.f, p.x), sy = PM_ADD(0.f, p.y), sz = PM_ADD(0.f, p.z), sw = PM_ADD(0.f, p.w); int cnt = 1;
-            for (int q = i + 1; q < n; ++q) {
-                const float4 a = pts[q];
-                if (im_key(a, inv) != key) break;
-                sx = PM_ADD(sx, a.x); sy = PM_ADD(sy, a.y); sz = PM_ADD(sz, a.z); sw = PM_ADD(sw, a.w); ++cnt;
-            }
-            const float fc = (float)cnt;
-            if (off < s.outCap) s.out[off] = make_float4(PM_DIV(sx, fc), PM_DIV(sy, fc), PM_DIV(sz, fc), PM_DIV(sw, fc));
-        }
+        for (int k = threadIdx.x; k < tile; k += IM_THREADS) pre += tileHeads[k];
+        pre = block_sum(pre, ws);
+        const int cnt = tileHeads[tile];
+        for (int k = threadIdx.x; k < cnt; k += IM_THREADS) if (pre + k < s.outCap) out[pre + k] = stage[tile * IM_TILE + k];
         if (threadIdx.x == 0 && (tile + 1) * IM_TILE >= n) {
-            int t = pre + total;
+            int t = pre + cnt;
             if (t > s.outCap) { t = s.outCap; atomicOr(s.errors, 4); }
             *s.nOut = t;
         }
@@ -266,7 +337,7 @@ void Engine::allocIncrementalMap(const std::vector<VgSeg>& mapSegs) {
             ImSeg& g = segs[2 * l + t];
             const int cap = t == 0 ? mo.cornerRawCap : mo.surfRawCap;
             for (int k = 0; k < 2; ++k) { g.pts[k] = alloc<float4>(cap, false); g.frame[k] = alloc<int>(cap, false); }
-            g.rank = alloc<int>(cap, false);
+            g.rank = alloc<int>(cap / 32 + 2, false);
             g.newPts = alloc<float4>(newCap, false); g.newFrame = alloc<int>(newCap, false); g.newKey = alloc<unsigned long long>(newCap, false);
             g.raw = t == 0 ? mo.cornerFromMap + l * mo.cornerRawCap : mo.surfFromMap + l * mo.surfRawCap;
             g.nRaw = mo.imNewCounts + l * 4 + t;
@@ -335,15 +406,14 @@ __global__ void mo_assemble_map_kernel(MoDev m);
 int Engine::incrementalLocalMap() {
     int n = 0;
     { ProfScope ps(this, "im_sort_arrivals"); n += vg_sort_keys(vgMapNew, stream); }
-    ProfScope ps(this, "im_merge_reduce");
-    dim3 gNew(std::min(im.maxTiles, 16), im.nSeg), gOld(std::min(im.maxTiles, 32), im.nSeg), gB(std::min(im.maxNewTiles * 4, 16), im.nSeg);
-    im_gather_new_kernel<<<gNew, IM_TILE, 0, stream>>>(im, mo);
-    im_mark_kernel<<<gOld, IM_TILE, 0, stream>>>(im, mo);
-    im_merge_old_kernel<<<gOld, IM_TILE, 0, stream>>>(im, mo);
-    im_merge_new_kernel<<<gB, 256, 0, stream>>>(im, mo);
-    im_commit_kernel<<<(im.nSeg + 127) / 128, 128, 0, stream>>>(im, mo);
-    im_heads_kernel<<<gOld, IM_TILE, 0, stream>>>(im, mo);
-    im_reduce_kernel<<<gOld, IM_TILE, 0, stream>>>(im, mo);
+    dim3 gNew(std::min(im.maxTiles * 4, 32), im.nSeg), gOld(std::min(im.maxTiles, 32), im.nSeg), gB(std::min(im.maxNewTiles * 4, 16), im.nSeg);
+    { ProfScope ps(this, "im_gather_new_kernel"); im_gather_new_kernel<<<gNew, IM_THREADS, 0, stream>>>(im, mo); }
+    { ProfScope ps(this, "im_mark_kernel"); im_mark_kernel<<<gOld, IM_THREADS, 0, stream>>>(im, mo); }
+    { ProfScope ps(this, "im_merge_old_kernel"); im_merge_old_kernel<<<gOld, IM_THREADS, 0, stream>>>(im, mo); }
+    { ProfScope ps(this, "im_merge_new_kernel"); im_merge_new_kernel<<<gB, 256, 0, stream>>>(im, mo); }
+    { ProfScope ps(this, "im_commit_kernel"); im_commit_kernel<<<(im.nSeg + 127) / 128, 128, 0, stream>>>(im, mo); }
+    { ProfScope ps(this, "im_reduce_kernel"); im_reduce_kernel<<<gOld, IM_THREADS, 0, stream>>>(im, mo); }
+    { ProfScope ps(this, "im_compact_kernel"); im_compact_kernel<<<gOld, IM_THREADS, 0, stream>>>(im, mo); }
     return n + 7;
 }
 
