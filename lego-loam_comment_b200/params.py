@@ -42,12 +42,15 @@ _SENSORS = {
     "hdl32": (32, 1800, 360.0 / _f32(1800), 41.333 / _f32(31), 30.666666, 20, 1),      # README.md:73-82
     "hdl64": (64, 2083, 360.0 / _f32(2083), 26.9 / _f32(63), 24.9, 50, 1),             # SURVEY.md 8c (not in reference)
     "vls128": (128, 1800, 0.2, 0.3, 25.0, 10, 1),                                      # utility.h:79-84
+    "os1_16": (16, 1024, 360.0 / _f32(1024), 33.2 / _f32(15), 16.6 + 0.1, 7, 1),       # utility.h:88-94
+    "os1_64": (64, 1024, 360.0 / _f32(1024), 33.2 / _f32(63), 16.6 + 0.1, 15, 1),      # utility.h:96-102
 }
 
 # beam geometry used only by the synthetic generator: (elev_bottom_deg, elev_step_deg, sensor_height)
 SENSOR_GEOMETRY = {
     "vlp16": (-15.0, 2.0, 0.7), "vlp16_noring": (-15.0, 2.0, 0.7),
     "hdl32": (-30.67, 41.33 / 31.0, 1.2), "hdl64": (-24.9, 26.9 / 63.0, 1.73), "vls128": (-25.0, 0.3, 1.8),
+    "os1_16": (-16.6, 33.2 / 15.0, 0.9), "os1_64": (-16.6, 33.2 / 63.0, 1.5),
 }
 
 

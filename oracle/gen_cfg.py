@@ -25,6 +25,9 @@ CONFIGS = {
     "hdl64": ("64", "2083", "360.0/float(Horizon_SCAN)", "26.9/float(N_SCAN-1)", "24.9", "50", "true"),
     # utility.h:79-84
     "vls128": ("128", "1800", "0.2", "0.3", "25.0", "10", "true"),
+    # utility.h:88-102 (Ouster OS1-16 / OS1-64: 1024-column images)
+    "os1_16": ("16", "1024", "360.0/float(Horizon_SCAN)", "33.2/float(N_SCAN-1)", "16.6+0.1", "7", "true"),
+    "os1_64": ("64", "1024", "360.0/float(Horizon_SCAN)", "33.2/float(N_SCAN-1)", "16.6+0.1", "15", "true"),
     # VLP-16 with loop closure switched on (utility.h:104 = true), SURVEY.md section 8f n2 / BASELINE config 5
     "vlp16_loop": ("16", "1800", "0.2", "2.0", "15.0+0.1", "7", "true", "true"),
 }

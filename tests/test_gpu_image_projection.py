@@ -51,6 +51,8 @@ def _compare_ip(pl, ref, lane=0):
     ("hdl32", "street", {}),
     ("hdl64", "street", {}),
     ("vls128", "street", {"dropout": 0.02}),
+    ("os1_16", "street", {}),                       # utility.h:88-94: 1024-column images
+    ("os1_64", "street", {"dropout": 0.02}),        # utility.h:96-102
 ])
 def test_image_projection_bit_exact(sensor, scene, kw):
     import refpy

@@ -37,6 +37,8 @@ def _cloud_close(g, r, what):
     ("hdl32", "street", {}, 18),
     ("hdl64", "street", {}, 14),
     ("vls128", "street", {}, 10),
+    ("os1_16", "street", {}, 22),
+    ("os1_64", "street", {}, 14),
 ])
 def test_scan_to_map_matches_reference(sensor, scene, kw, nscans):
     import refpy
