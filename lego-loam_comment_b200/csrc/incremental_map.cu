@@ -239,6 +239,7 @@ __global__ void __launch_bounds__(IM_THREADS) im_reduce_kernel(ImBatch b, MoDev 
     __shared__ int ws[32];
     __shared__ float4 sp[IM_TILE];
     __shared__ unsigned long long sk[IM_TILE];
+    __shared__ unsigned short sh[IM_TILE];
     const int n = s.state[1];
     const float4* __restrict__ pts = s.pts[s.state[0]];
     float4* __restrict__ stage = s.pts[s.state[0] ^ 1];
@@ -265,10 +266,13 @@ __global__ void __launch_bounds__(IM_THREADS) im_reduce_kernel(ImBatch b, MoDev 
         }
         int total;
         int off = block_excl_scan(mine, ws, &total);
+        // the tile's run heads, compacted: afterwards thread h folds run h, so every active thread has exactly one run
+        // (one thread walking its up-to-4 heads one after the other ran with 12 of 32 threads active)
 #pragma unroll
-        for (int e = 0; e < IM_PER; ++e) {
-            if (!head[e]) continue;
-            const int l = l0 + e;
+        for (int e = 0; e < IM_PER; ++e) if (head[e]) sh[off++] = (unsigned short)(l0 + e);
+        __syncthreads();
+        for (int h = threadIdx.x; h < total; h += IM_THREADS) {
+            const int l = sh[h];
             const unsigned long long key = sk[l];
             const float4 p = sp[l];
             float sx = PM_ADD(0.f, p.x), sy = PM_ADD(0.f, p.y), sz = PM_ADD(0.f, p.z), sw = PM_ADD(0.f, p.w); int cnt = 1;
@@ -285,8 +289,7 @@ __global__ void __launch_bounds__(IM_THREADS) im_reduce_kernel(ImBatch b, MoDev 
                 }
             }
             const float fc = (float)cnt;
-            stage[t0 + off] = make_float4(PM_DIV(sx, fc), PM_DIV(sy, fc), PM_DIV(sz, fc), PM_DIV(sw, fc));
-            ++off;
+            stage[t0 + h] = make_float4(PM_DIV(sx, fc), PM_DIV(sy, fc), PM_DIV(sz, fc), PM_DIV(sw, fc));
         }
         if (threadIdx.x == 0) tileHeads[tile] = total;
     }

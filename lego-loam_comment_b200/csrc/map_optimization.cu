@@ -222,12 +222,17 @@ __global__ void __launch_bounds__(256, 4) mo_search_kernel(MoDev m, int iter) {
     const float4* qC = m.cornerLastDS + (size_t)lane * m.scanCornerCap;
     const float4* qS = m.surfTotalLastDS + (size_t)lane * (m.scanSurfCap + m.scanOutlierCap);
     const size_t slotBase = (size_t)lane * m.resBlocks * MO_RES_THREADS;
+    __shared__ int cellList[VH_LIST_CELLS * 256];   // per thread: the non-empty cells around its query (column tid: no bank conflicts)
     for (int i = blockIdx.x * 256 + tid; i < n; i += gridDim.x * 256) {
         const int q = iter == 0 ? i : m.knnMissList[slotBase + i];
         const bool corner = q < nCorner;
         const float4 ps = map_transform(sc, corner ? qC[q] : qS[q - nCorner]);
         float d2[5]; int idx[5]; int cand[VH_CACHE_K]; float rc2;
+#ifdef LEGO_KNN_NESTED
         const int found = vh_knn5_fill(corner ? vhC : vhS, ps.x, ps.y, ps.z, 1.0f, d2, idx, cand, &rc2);
+#else
+        const int found = vh_knn5_fill_flat(corner ? vhC : vhS, ps.x, ps.y, ps.z, 1.0f, d2, idx, cand, &rc2, cellList + tid, 256);
+#endif
 #pragma unroll
         for (int j = 0; j < VH_CACHE_K / 4; ++j)
             m.knnCand[(slotBase + q) * (VH_CACHE_K / 4) + j] = make_int4(cand[4 * j], cand[4 * j + 1], cand[4 * j + 2], cand[4 * j + 3]);

@@ -313,6 +313,98 @@ __device__ inline int vh_knn5_fill(const VhLane& v, float x, float y, float z, f
     return found5;
 }
 
+// ---- flat form of vh_knn5_fill --------------------------------------------------------------------------------
+// Same result as vh_knn5_fill (the top list is the K smallest (distance, index) pairs inside the widened bound, whatever
+// order the points are met in), shaped for SIMT execution: ncu showed the nested version running with 9.75 of 32 threads
+// active (profiles/r02_ncu_full_top7_vlp16_l296.txt) -- every lane sits in a different cell / point of its own nested loops.
+// Here a thread (1) scans its own cell, (2) walks the other 26 cells in ONE uniform loop that only prunes by box distance
+// and probes the hash, noting the non-empty cells in a per-thread list in shared memory, (3) runs ONE flat loop over all
+// listed points; switching to the next cell costs two loads and a re-check of the (tighter) bound, no probe.
+// (distance, index) travel as one 64-bit key -- float bits of a non-negative distance order like the float -- so an
+// insertion slot is a min / max pair.  `list` = VH_LIST_CELLS ints of shared memory owned by this thread, stride `stride`.
+constexpr int VH_LIST_CELLS = 26;
+__device__ __forceinline__ unsigned long long vh_key64(float d, int i) { return ((unsigned long long)__float_as_uint(d) << 32) | (unsigned)i; }
+
+__device__ inline int vh_knn5_fill_flat(const VhLane& v, float x, float y, float z, float bound, float* d2, int* idx, int* cand, float* rc2,
+                                        int* list, int stride) {
+    const float ux = x * v.invCell, uy = y * v.invCell, uz = z * v.invCell;
+    const float flx = floorf(ux), fly = floorf(uy), flz = floorf(uz);
+    const int cx = (int)flx, cy = (int)fly, cz = (int)flz;
+    const float cell = 1.0f / v.invCell;
+    const float lo[3] = {(ux - flx) * cell, (uy - fly) * cell, (uz - flz) * cell};
+    const float hi[3] = {cell - lo[0], cell - lo[1], cell - lo[2]};
+    const float wideR = sqrtf(bound) + VH_CACHE_MARGIN, wide = wideR * wideR;
+    unsigned long long e[VH_CACHE_K];
+#pragma unroll
+    for (int k = 0; k < VH_CACHE_K; ++k) e[k] = vh_key64(wide, 0x7fffffff);
+    auto offer = [&](const float4& a) {
+        unsigned long long key = vh_key64(vh_dist2(a, x, y, z), __float_as_int(a.w));
+        if (key > e[VH_CACHE_K - 1]) return;
+#pragma unroll
+        for (int k = 0; k < VH_CACHE_K; ++k) { const unsigned long long t = e[k]; e[k] = key < t ? key : t; key = key < t ? t : key; }
+    };
+    // (1) the query's own cell
+    {
+        const int s = vh_find(v.keys, v.H, vh_pack(cx, cy, cz));
+        if (s >= 0) {
+            const int en = v.start[s];
+            for (int t = en - v.count[s]; t < en; ++t) offer(v.sorted[t]);
+        }
+    }
+    // (2) the 26 neighbours, nearest boxes first: prune by box distance against the bound so far, probe, note
+    int nList = 0;
+    for (int o = 1; o < 27; ++o) {
+        const int code = VH_ORDER27[o];
+        const int dx = (code & 3) - 1, dy = ((code >> 2) & 3) - 1, dz = ((code >> 4) & 3) - 1;
+        const float gx = dx < 0 ? lo[0] : (dx > 0 ? hi[0] : 0.f);
+        const float gy = dy < 0 ? lo[1] : (dy > 0 ? hi[1] : 0.f);
+        const float gz = dz < 0 ? lo[2] : (dz > 0 ? hi[2] : 0.f);
+        const float boxD2 = gx * gx + gy * gy + gz * gz;
+        if (boxD2 > __uint_as_float((unsigned)(e[VH_CACHE_K - 1] >> 32)) * 1.0001f + 1e-5f) continue;
+        const int s = vh_find(v.keys, v.H, vh_pack(cx + dx, cy + dy, cz + dz));
+        if (s < 0) continue;
+        list[nList * stride] = s | (o << 26);      // H <= 2^26 slots
+        ++nList;
+    }
+    // (3) every listed point in one loop
+    int li = 0, t = 0, en = 0;
+    while (true) {
+        if (t == en) {
+            bool got = false;
+            while (li < nList) {
+                const int packed = list[li * stride]; ++li;
+                const int code = VH_ORDER27[packed >> 26];
+                const int dx = (code & 3) - 1, dy = ((code >> 2) & 3) - 1, dz = ((code >> 4) & 3) - 1;
+                const float gx = dx < 0 ? lo[0] : (dx > 0 ? hi[0] : 0.f);
+                const float gy = dy < 0 ? lo[1] : (dy > 0 ? hi[1] : 0.f);
+                const float gz = dz < 0 ? lo[2] : (dz > 0 ? hi[2] : 0.f);
+                if (gx * gx + gy * gy + gz * gz > __uint_as_float((unsigned)(e[VH_CACHE_K - 1] >> 32)) * 1.0001f + 1e-5f) continue;
+                const int s = packed & ((1 << 26) - 1);
+                en = v.start[s]; t = en - v.count[s];
+                if (t < en) { got = true; break; }
+            }
+            if (!got) break;
+        }
+        offer(v.sorted[t]); ++t;
+    }
+    int found5 = 0;
+#pragma unroll
+    for (int k = 0; k < 5; ++k) {
+        const float dk = __uint_as_float((unsigned)(e[k] >> 32)); const int ik = (int)(unsigned)e[k];
+        const bool in = ik != 0x7fffffff && dk <= bound;
+        d2[k] = in ? dk : bound; idx[k] = in ? ik : 0x7fffffff;
+        found5 += in ? 1 : 0;
+    }
+#pragma unroll
+    for (int k = 0; k < VH_CACHE_K; ++k) { const int ik = (int)(unsigned)e[k]; cand[k] = ik == 0x7fffffff ? -1 : ik; }
+    // everything nearer than `reach` lies inside the 27 visited cells
+    const float reach = cell + fminf(fminf(fminf(lo[0], hi[0]), fminf(lo[1], hi[1])), fminf(lo[2], hi[2]));
+    const bool full = (int)(unsigned)e[VH_CACHE_K - 1] != 0x7fffffff;    // K points inside the widened bound exist
+    const float rc = fminf(full ? sqrtf(__uint_as_float((unsigned)(e[VH_CACHE_K - 1] >> 32))) : wideR, reach);
+    *rc2 = rc * rc;
+    return found5;
+}
+
 // Re-ranks the cached candidates at the new query position.  Returns true when the outcome is proven to be what
 // vh_knn5(bound) returns there: d2 / idx hold it and *found5 = min(neighbours inside the bound, 5).
 __device__ inline bool vh_knn5_cached(const float4* __restrict__ cloud, const int* cand, float ox, float oy, float oz, float rc2,
