@@ -12,7 +12,10 @@
 
 namespace lego {
 
-constexpr int ODO_THREADS = 512;
+#ifndef LEGO_ODO_THREADS
+#define LEGO_ODO_THREADS 512
+#endif
+constexpr int ODO_THREADS = LEGO_ODO_THREADS;
 constexpr int ODO_WARPS = ODO_THREADS / 32;
 constexpr int ODO_TE_BLOCKS = 24;
 #ifndef LEGO_ODO_CORNER_CELL
@@ -25,7 +28,8 @@ struct OdoShared {
     float matP[9];
     int isDegenerate;
     int keepGoing;
-    int ringOff[132];
+    int ringOff[136];          // firstGE of build_ring_offsets
+    int ringLast[136];         // lastLE
     int nextQuery;             // dynamic distribution of the correspondence searches over the warps
     float trig[6];             // sin / cos of transformCur's three angles for the current iteration (srx crx sry cry srz crz)
     double red[ODO_WARPS][10];
@@ -80,14 +84,30 @@ __device__ inline int nearest_brute_warp(const float4* __restrict__ cloud, int M
     return bestI == 0x7fffffff ? -1 : bestI;
 }
 
-// Start offset of every ring inside a ring-ordered cloud (intensity = ring after TransformToEnd).
-__device__ inline void build_ring_offsets(const float4* __restrict__ cloud, int M, int R, int* off) {
-    for (int r = threadIdx.x; r <= R + 2; r += blockDim.x) off[r] = M;
+// Bounds of the reference's adjacent-ring scans (featureAssociation.cpp:1062-1110, 1173-1226).  A scan walks up from
+// closest + 1 until the first point whose label int(intensity) exceeds closestPointScan + 2.5, and down from closest - 1
+// until the first label below closestPointScan - 2.5.  The label is NOT always the ring: adjustDistortion stores
+// ring + 0.1 * relTime, and a slightly negative relTime (common at high yaw rates) makes int() give ring - 1, so inside a
+// ring's stretch the labels r - 1 and r interleave.  Only "label(j) in {ring(j) - 1, ring(j)}, rings ascending" holds,
+// which is enough for the break positions to be independent of where the scan starts:
+//   firstGE[v] = min { j : label(j) >= v }   (upward scans stop there),   lastLE[v] = max { j : label(j) <= v }   (downward).
+// An earlier version took "the index where the label steps up to v" with plain stores, which is the same thing only for
+// sorted labels -- with interleaved labels several threads stored different indices (a race, visible as run-to-run
+// differences of transformCur) and the bounds could cut a scan short.
+__device__ inline void build_ring_offsets(const float4* __restrict__ cloud, int M, int R, int* firstGE, int* lastLE) {
+    for (int r = threadIdx.x; r <= R + 3; r += blockDim.x) { firstGE[r] = M; lastLE[r] = -1; }
     __syncthreads();
     for (int j = threadIdx.x; j < M; j += blockDim.x) {
-        const int r = (int)cloud[j].w;
-        const int rp = j > 0 ? (int)cloud[j - 1].w : -1;
-        if (r != rp) for (int rr = max(rp + 1, 0); rr <= min(r, R + 2); ++rr) off[rr] = j;
+        const int v = min(max((int)cloud[j].w, 0), R + 2);
+        const int vp = j > 0 ? min(max((int)cloud[j - 1].w, 0), R + 2) : -1;
+        const int vn = j + 1 < M ? min(max((int)cloud[j + 1].w, 0), R + 2) : -1;
+        if (v != vp) atomicMin(&firstGE[v], j);      // first / last point of every stretch of equal labels
+        if (v != vn) atomicMax(&lastLE[v], j);
+    }
+    __syncthreads();
+    if (threadIdx.x == 0) {
+        for (int r = R + 2; r >= 0; --r) firstGE[r] = min(firstGE[r], firstGE[r + 1]);
+        for (int r = 1; r <= R + 3; ++r) lastLE[r] = max(lastLE[r], lastLE[r - 1]);
     }
     __syncthreads();
 }
@@ -110,7 +130,7 @@ __device__ int odo_phase(OdoShared& sh, float4* sel, const float4* __restrict__ 
 #ifdef LEGO_ODO_PROF
     long long t0_ = clock64();
 #endif
-    build_ring_offsets(last, M, c.R, sh.ringOff);
+    build_ring_offsets(last, M, c.R, sh.ringOff, sh.ringLast);
     ODO_T(0)
     int itersDone = 0;
     for (int iter = 0; iter < 25; ++iter) {
@@ -144,7 +164,7 @@ __device__ int odo_phase(OdoShared& sh, float4* sel, const float4* __restrict__ 
                     const float4 p = sel[q];
                     const int scan = (int)last[closest].w;
                     // forward scan: the reference bounds it by the CURRENT feature count (quirk Q13)
-                    const int hiF = min(min(Q, M), sh.ringOff[min(scan + 3, c.R + 2)]);
+                    const int hiF = min(min(Q, M), sh.ringOff[min(scan + 3, c.R + 3)]);
                     const int nF = max(hiF - (closest + 1), 0);
                     auto offerF = [&](const float4& a, int j) {
                         const float d = vh_dist2(a, p.x, p.y, p.z);
@@ -166,7 +186,7 @@ __device__ int odo_phase(OdoShared& sh, float4* sel, const float4* __restrict__ 
                         offerF(a0, j); offerF(a1, j + 32); offerF(a2, j + 64); offerF(a3, j + 96);
                     }
                     for (; j < hiF; j += 32) offerF(last[j], j);
-                    const int loB = sh.ringOff[max(scan - 2, 0)];
+                    const int loB = scan >= 3 ? sh.ringLast[min(scan - 3, c.R + 3)] + 1 : 0;
                     j = closest - 1 - lid;
                     for (; j - 96 >= loB; j -= 128) {
                         const float4 a0 = last[j], a1 = last[j - 32], a2 = last[j - 64], a3 = last[j - 96];

@@ -80,3 +80,40 @@ def test_features_bit_exact_and_odometry(sensor, scene, kw, nscans):
         assert g.shape == r.shape and np.allclose(g, r, rtol=1e-5, atol=1e-6), tag + "laserCloudSurfLast"
     assert np.abs(ref.get("transformSum")).max() > 0.05, "trajectory did not move: the odometry check would be vacuous"
     pl.close(); ref.close()
+
+
+def test_interleaved_ring_labels_at_high_yaw_rate():
+    """featureAssociation.cpp:522-523 stores ring + 0.1 * relTime; on a tight circle (0.5 rad/s yaw) relTime is often slightly
+    negative, so int(intensity) -- the "ring" of the adjacent-ring scans, featureAssociation.cpp:1062-1110, 1173-1226 -- labels
+    a ring-r point r - 1 and the labels interleave inside a ring's stretch.  The odometry must follow the reference's linear
+    scans there (break at the first label beyond +-2.5) and must be deterministic: a version that assumed sorted labels had a
+    write race in its offset table and gave two different transformCur from identical inputs (scan 326 of this sequence)."""
+    import refpy
+    sensor = "vlp16"
+    require_ref(sensor)
+    seq = SynthSequence(sensor, seed=1, scene="room", speed=4.0, n_scans=340, circle_radius=8.0)
+    ref = refpy.RefPipeline(sensor)
+    pls = [Pipeline(make_params(sensor), lanes=1, max_points=seq.cap) for _ in range(3)]
+    interleaved = 0
+    worst = 0.0
+    for k in range(334):
+        xyzi, ring = seq.scan(k)
+        ref.feed(xyzi, ring, seq.stamp(k), stages=3)
+        x = np.zeros((1, seq.cap, 4), np.float32); x[0, :len(xyzi)] = xyzi
+        r = np.zeros((1, seq.cap), np.uint16); r[0, :len(ring)] = ring
+        for pl in pls:
+            pl.step(x, r, [len(xyzi)], [seq.stamp(k)], stage_mask=3)
+        tc = [pl.download("transformCur") for pl in pls]
+        assert all(np.array_equal(_bits(t), _bits(tc[0])) for t in tc), "scan %d: pipelines fed the same scans disagree: %s" % (k, tc)
+        labels = ref.cloud("laserCloudSurfLast")[:, 3].astype(np.int32)
+        interleaved += int((np.diff(labels) < 0).any())
+        if k % 4 == 0 or k > 300:
+            for name in ("transformCur", "transformSum"):
+                d = float(np.max(np.abs(pls[0].download(name) - ref.get(name))))
+                worst = max(worst, d)
+                assert d < POSE_TOL, "scan %d %s: %g" % (k, name, d)
+    assert interleaved >= 1, "the sequence did not produce interleaved ring labels (scan 325 does on the reference)"
+    print("interleaved-label scans checked:", interleaved, "worst pose difference", worst)
+    for pl in pls:
+        pl.close()
+    ref.close()
