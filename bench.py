@@ -61,6 +61,8 @@ def parse_args():
     ap.add_argument("--distinct", type=int, default=0, help="distinct generated sequences per GPU the lanes replay (0 = auto)")
     ap.add_argument("--input", default="xyz", choices=["xyz", "xyzi"], help="point format on the wire: xyz = 12 B + ring, xyzi = 16 B + ring")
     ap.add_argument("--secondary", default="auto", help="second sensor measured inside the same line at N=1 ('auto' = hdl64 when --sensor vlp16, 'none')")
+    ap.add_argument("--threads", type=int, default=-1, help="host threads submitting the handles' steps (-1 = one per handle for --workload loop, whose mapping "
+                    "calls end with a stream synchronisation, else 1; ctypes releases the GIL inside the C ABI)")
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-e2e", action="store_true")
     ap.add_argument("--no-latency", action="store_true")
@@ -418,10 +420,27 @@ def run_b200(args, sensor, lanes, workload):
     dev_scan, seq = make_scan_fn(d_x.data_ptr(), d_r.data_ptr(), True)
     group = make_group()
 
+    n_threads = args.threads if args.threads >= 0 else (H if workload == "loop" else 1)
+    pool = None
+    if n_threads > 1:
+        from concurrent.futures import ThreadPoolExecutor
+        pool = ThreadPoolExecutor(max_workers=min(n_threads, H))
+
     def run_scans(scan_fn, s0, s1):
-        for s in range(s0, s1):
-            for h, pl in enumerate(group):
+        """scans s0 .. s1-1 for every handle.  With a thread pool every handle is driven by its own host thread (one handle = one
+        host thread is the C ABI's rule), so a handle that blocks -- loop-closure mode synchronises its stream in every mapping
+        call -- does not keep the others from submitting."""
+        if pool is None:
+            for s in range(s0, s1):
+                for h, pl in enumerate(group):
+                    scan_fn(h, pl, s + phase[h])
+            return
+
+        def drive(h, pl):
+            for s in range(s0, s1):
                 scan_fn(h, pl, s + phase[h])
+        for f in [pool.submit(drive, h, pl) for h, pl in enumerate(group)]:
+            f.result()
 
     for h, pl in enumerate(group):           # handle h runs phase[h] scans ahead
         for s in range(phase[h]):
@@ -457,10 +476,14 @@ def run_b200(args, sensor, lanes, workload):
         pl.timer_record(0)
     t_host0 = time.perf_counter()
     submit_scan_ms = []      # host time to enqueue one scan of every handle; the first ones find the launch queues empty
-    for s in range(win.first_timed, win.T):
-        t_s = time.perf_counter()
-        run_scans(dev_scan, s, s + 1)
-        submit_scan_ms.append((time.perf_counter() - t_s) * 1e3)
+    if pool is None:
+        for s in range(win.first_timed, win.T):
+            t_s = time.perf_counter()
+            run_scans(dev_scan, s, s + 1)
+            submit_scan_ms.append((time.perf_counter() - t_s) * 1e3)
+    else:
+        run_scans(dev_scan, win.first_timed, win.T)       # every handle's thread runs through the whole timed window on its own
+        submit_scan_ms.append((time.perf_counter() - t_host0) * 1e3 / max(win.T - win.first_timed, 1))
     host_submit_s = time.perf_counter() - t_host0
     for pl in group:
         pl.timer_record(1)
@@ -502,9 +525,15 @@ def run_b200(args, sensor, lanes, workload):
         DEPTH = 5   # scans in flight per handle: the poses of scan k are collected after scan k+4 was submitted
 
         def submit(s):
-            for h, pl in enumerate(group):
+            def one(h, pl):
                 host_scan(h, pl, s + phase[h])
                 pl.poses_async(s % 8)
+            if pool is None:
+                for h, pl in enumerate(group):
+                    one(h, pl)
+            else:
+                for f in [pool.submit(one, h, pl) for h, pl in enumerate(group)]:
+                    f.result()
 
         def collect(s):
             return np.concatenate([pl.poses_wait(s % 8)[0] for pl in group])
@@ -568,7 +597,7 @@ def run_b200(args, sensor, lanes, workload):
     return dict(rank=rank, world=world, ms=ms, L=L, K=K, W=W, S=S, win=win, e2e=e2e, clocks=clocks, launches=launches,
                 prof_all=prof_all, prof_sum=prof_sum, counts_all=counts_all, roofline=roofline, cap=cap, params=params, D=D,
                 host_submit_ms=host_submit_s * 1e3 / K, submit_scan_ms=submit_scan_ms, local_map=local_map, gen_s=inp.gen_s, fpp=fpp, H=H,
-                mean_points=float(inp.npts[win.first_timed:win.T].mean()), inputs=inp)
+                mean_points=float(inp.npts[win.first_timed:win.T].mean()), inputs=inp, threads=(min(n_threads, H) if pool else 1))
 
 
 def measure_latency(args, sensor, workload, inp, win, device):
@@ -715,7 +744,7 @@ def result_block(args, r, sensor, workload):
     L, K, S, world = r["L"], r["K"], r["S"], r["world"]
     win = r["win"]
     cfg = {"workload": workload_name(args, sensor, workload, win), "sensor": sensor, "lanes_per_gpu": L, "handles_per_gpu": r["H"],
-           "handle_stagger_scans": args.stagger, "stages": args.stages,
+           "handle_stagger_scans": args.stagger, "host_threads": r["threads"], "stages": args.stages,
            "distinct_sequences_per_gpu": r["D"],
            "lane_inputs": "lane l replays generated sequence l %% %d of its GPU (own state per lane; own H2D copy per lane in the e2e arm)" % r["D"],
            "points_per_scan": round(r["mean_points"], 1), "input_format": "xyz+ring (14 B/point)" if r["fpp"] == 3 else "xyzi+ring (18 B/point)",
