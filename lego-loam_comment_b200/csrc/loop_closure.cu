@@ -16,6 +16,8 @@
 #include <climits>
 #include <cmath>
 #include <cstring>
+#include <atomic>
+#include <thread>
 #include "engine.h"
 #include "map_kernels.cuh"
 
@@ -344,6 +346,18 @@ static void estimate_to_floats(const pg::Pose& p, float* pose6D, float* aft) {
 
 // saveKeyFramesAndFactor (mapOptmization.cpp:1353-1440) on the host for the lanes whose graph holds a loop factor; the
 // other lanes keep the device-only path (their estimate is the inserted value).
+// Runs body(i) for i in [0, n) on up to hardware_concurrency host threads.  Used for the per-lane pose-graph updates: every
+// lane owns its graph, key-frame list and override slot, and a Gauss-Newton step over a few hundred poses takes
+// milliseconds to tenths of a second, so lanes are worth running side by side (the reference's iSAM2 is host code too).
+template <class F> static void parallel_lanes(int n, F body) {
+    const int nt = std::min<int>(n, std::max(1u, std::thread::hardware_concurrency()));
+    if (nt <= 1) { for (int i = 0; i < n; ++i) body(i); return; }
+    std::atomic<int> next(0);
+    std::vector<std::thread> pool;
+    for (int t = 0; t < nt; ++t) pool.emplace_back([&]() { for (int i = next.fetch_add(1); i < n; i = next.fetch_add(1)) body(i); });
+    for (auto& th : pool) th.join();
+}
+
 void Engine::saveKeyFramesHostGraph(const std::vector<int>& active) {
     bool any = false;
     for (int l = 0; l < c.L; ++l) { moOverridesHost[l].use = 0; moOverridesHost[l].save = 0; if (active[l] && moHost[l].graph.hasLoop) any = true; }
@@ -351,21 +365,21 @@ void Engine::saveKeyFramesHostGraph(const std::vector<int>& active) {
         cuda_check(cudaMemcpyAsync(moAftHost, mo.transformAftMapped, sizeof(float) * 6 * c.L, cudaMemcpyDeviceToHost, stream), "aft");
         cuda_check(cudaMemcpyAsync(moScanCountsHost, mo.scanCounts, sizeof(int) * 8 * c.L, cudaMemcpyDeviceToHost, stream), "scanCounts");
         cuda_check(cudaStreamSynchronize(stream), "graph sync");
-        for (int l = 0; l < c.L; ++l) {
+        parallel_lanes(c.L, [&](int l) {
             MoLaneHost& H = moHost[l];
-            if (!active[l] || !H.graph.hasLoop) continue;
+            if (!active[l] || !H.graph.hasLoop) return;
             MoOverride& ov = moOverridesHost[l];
             ov.use = 1;
             const float* Aft = moAftHost + l * 6;
             const float cx = Aft[3], cy = Aft[4], cz = Aft[5];
             const float dist = sqrtf((H.prevRobotPos[0] - cx) * (H.prevRobotPos[0] - cx) + (H.prevRobotPos[1] - cy) * (H.prevRobotPos[1] - cy) +
                                      (H.prevRobotPos[2] - cz) * (H.prevRobotPos[2] - cz));
-            if ((double)dist < 0.3) continue;
+            if ((double)dist < 0.3) return;
             const int n = (int)H.keyFrames.size();
             const MoKeyFrame& last = H.keyFrames.back();
             const int used = last.poolOff + last.nC + last.nS + last.nO;
             const int* sc = moScanCountsHost + l * 8;
-            if (n >= mo.maxKeyFrames || used + sc[0] + sc[1] + sc[2] > mo.poolCap) { H.lastError |= 1; continue; }
+            if (n >= mo.maxKeyFrames || used + sc[0] + sc[1] + sc[2] > mo.poolCap) { H.lastError |= 1; return; }
             H.prevRobotPos[0] = cx; H.prevRobotPos[1] = cy; H.prevRobotPos[2] = cz;
             const pg::Pose from = pose_from_transform(H.transformLast), to = pose_from_transform(Aft);
             H.graph.addBetween(n - 1, n, pg::between(from, to), kOdometryVariances);
@@ -375,7 +389,7 @@ void Engine::saveKeyFramesHostGraph(const std::vector<int>& active) {
             estimate_to_floats(H.graph.x[n], ov.pose6D, ov.aft);
             for (int i = 0; i < 6; ++i) H.transformLast[i] = ov.aft[i];
             ov.save = 1;
-        }
+        });
     }
     cuda_check(cudaMemcpyAsync(mo.overrides, moOverridesHost, sizeof(MoOverride) * c.L, cudaMemcpyHostToDevice, stream), "overrides");
 }
@@ -506,8 +520,8 @@ void Engine::runIcpBatch(const std::vector<int>& lanes, const std::vector<int>& 
         cuda_check(cudaMemcpyAsync(hRes, lc.results, sizeof(LcResult) * S, cudaMemcpyDeviceToHost, stream), "lc results");
         cuda_check(cudaMemcpyAsync(hCounts, lc.counts, sizeof(int) * 4 * S, cudaMemcpyDeviceToHost, stream), "lc counts back");
         cuda_check(cudaStreamSynchronize(stream), "icp sync");
-        for (int s = 0; s < nb; ++s) {
-            if (!hActive[s]) continue;
+        parallel_lanes(nb, [&](int s) {   // (the slots of one batch belong to different lanes)
+            if (!hActive[s]) return;
             const int l = lanes[base + s];
             MoLaneHost& H = moHost[l];
             const LcResult& r = hRes[s];
@@ -515,10 +529,10 @@ void Engine::runIcpBatch(const std::vector<int>& lanes, const std::vector<int>& 
             H.lastLoop[5] = r.converged; H.lastLoop[6] = r.iterations; H.lastLoop[7] = r.nSrc; H.lastLoop[8] = hCounts[4 * s + 2];
             std::memcpy(H.lastIcpT, r.T, sizeof(r.T)); H.lastIcpFitness = r.fitness;
             // icp.hasConverged() == false || icp.getFitnessScore() > historyKeyframeFitnessScore -> no constraint
-            if (!r.converged || r.fitness > (double)params.historyKeyframeFitnessScore) continue;
+            if (!r.converged || r.fitness > (double)params.historyKeyframeFitnessScore) return;
             addLoopConstraint(l, closest[base + s], latest[base + s], r);
             H.lastLoop[2] = 1;
-        }
+        });
     }
 }
 

@@ -7,8 +7,7 @@
 // whitened by 1/sqrt(variance).  While the graph is a pure chain every factor was computed from the inserted values,
 // the residuals are zero and the estimate IS the inserted values, so no arithmetic happens (pass-through).  From the
 // first loop factor on, every update() is one Gauss-Newton step over the whole graph relinearised at the current
-// estimate, solved by an envelope (skyline) Cholesky: the chain gives a 12-wide band and a loop factor only widens
-// the six rows of its newer key frame.  Jacobians are closed-form (right perturbations):
+// estimate, solved by an envelope (skyline) Cholesky in reverse Cuthill-McKee order of the poses (rcmOrder).  Jacobians are closed-form (right perturbations):
 //   d e / d xi_j = [ Jr^-1(phi)  0 ; 0  Rd ]                 d e / d xi_i = [ -Jr^-1(phi) Rh^T  0 ; Rz^T [th]x  -Rz^T ]
 // with h = Ti^-1 Tj = (Rh, th), z = (Rz, tz) the measurement, d = (Rd, td) = z^-1 h, phi = Log(Rd).
 #pragma once
@@ -131,13 +130,41 @@ private:
         }
     }
 
+    // Reverse Cuthill-McKee order of the key frames (block graph: one node per pose, one edge per between factor).  In key-
+    // frame order a loop factor stretches the envelope of its newer pose back to the older one and the Cholesky fills it
+    // (a 2000-scan circle: ~500 poses, rows 2000+ wide, ~1 s per update); ordered by breadth-first levels from the newest pose
+    // the profile is a few poses per lap wide.  pos[k] = position of pose k in the elimination order.
+    void rcmOrder(std::vector<int>& pos) const {
+        const int n = (int)x.size();
+        std::vector<std::vector<int> > adj(n);
+        for (const Factor& F : factors) if (F.i >= 0 && F.i != F.j) { adj[F.i].push_back(F.j); adj[F.j].push_back(F.i); }
+        for (auto& a : adj) { std::sort(a.begin(), a.end()); a.erase(std::unique(a.begin(), a.end()), a.end()); }
+        std::vector<int> order; order.reserve(n);
+        std::vector<char> seen(n, 0);
+        for (int root = n - 1; root >= 0; --root) {          // (the graph is connected through the chain; the loop covers any other case)
+            if (seen[root]) continue;
+            size_t head = order.size();
+            order.push_back(root); seen[root] = 1;
+            while (head < order.size()) {
+                const int u = order[head++];
+                std::vector<int> nb;
+                for (int v : adj[u]) if (!seen[v]) { nb.push_back(v); seen[v] = 1; }
+                std::sort(nb.begin(), nb.end(), [&](int a, int b) { return adj[a].size() != adj[b].size() ? adj[a].size() < adj[b].size() : a < b; });
+                order.insert(order.end(), nb.begin(), nb.end());
+            }
+        }
+        pos.assign(n, 0);
+        for (int k = 0; k < n; ++k) pos[order[n - 1 - k]] = k;
+    }
+
     void gaussNewtonStep() {
         const int n = (int)x.size(), D = 6 * n;
         if (n == 0) return;
+        std::vector<int> pos; rcmOrder(pos);
         std::vector<int> first(D);
         for (int r = 0; r < D; ++r) first[r] = r - r % 6;
         for (const Factor& F : factors)
-            if (F.i >= 0) { const int lo = std::min(F.i, F.j), hi = std::max(F.i, F.j); for (int a = 0; a < 6; ++a) first[6 * hi + a] = std::min(first[6 * hi + a], 6 * lo); }
+            if (F.i >= 0) { const int lo = std::min(pos[F.i], pos[F.j]), hi = std::max(pos[F.i], pos[F.j]); for (int a = 0; a < 6; ++a) first[6 * hi + a] = std::min(first[6 * hi + a], 6 * lo); }
         std::vector<size_t> off(D + 1, 0);
         for (int r = 0; r < D; ++r) off[r + 1] = off[r] + (size_t)(r - first[r] + 1);
         std::vector<double> H(off[D], 0.0), g(D, 0.0);
@@ -146,7 +173,7 @@ private:
             double e[6], Ji[36], Jj[36];
             linearize(F, F.i >= 0 ? &x[F.i] : nullptr, x[F.j], e, Ji, Jj);
             const double* J[2] = {F.i >= 0 ? Ji : Jj, Jj};
-            const int var[2] = {F.i >= 0 ? F.i : F.j, F.j};
+            const int var[2] = {pos[F.i >= 0 ? F.i : F.j], pos[F.j]};    // rows / columns in elimination order
             const int nv = F.i >= 0 ? 2 : 1;
             for (int v = 0; v < nv; ++v)
                 for (int a = 0; a < 6; ++a) {
@@ -155,7 +182,7 @@ private:
                     for (int w = 0; w < nv; ++w)
                         for (int b = 0; b < 6; ++b) {
                             const int rr = 6 * var[v] + a, cc = 6 * var[w] + b;
-                            if (cc > rr) continue;
+                            if (cc > rr) continue;       // lower triangle; the mirrored block comes with (w, v)
                             double q = 0; for (int r = 0; r < 6; ++r) q += J[v][6 * r + a] * J[w][6 * r + b];
                             at(rr, cc) += q;
                         }
@@ -169,7 +196,7 @@ private:
             }
         for (int r = 0; r < D; ++r) { double s = g[r]; for (int k = first[r]; k < r; ++k) s -= at(r, k) * g[k]; g[r] = s / at(r, r); }
         for (int r = D - 1; r >= 0; --r) { g[r] /= at(r, r); for (int k = first[r]; k < r; ++k) g[k] -= at(r, k) * g[r]; }
-        for (int i = 0; i < n; ++i) x[i] = retract(x[i], &g[6 * i]);
+        for (int i = 0; i < n; ++i) x[i] = retract(x[i], &g[6 * pos[i]]);
     }
 };
 

@@ -14,8 +14,10 @@
 // (R <- R Exp(omega), t <- t + R v), factor error = [Log(dR), dt] of  d = measured^-1 * (Ti^-1 Tj)  (prior: measured^-1 * T),
 // whitened by 1/sqrt(variance).  Jacobians here are central differences in double (the product uses closed forms).
 #pragma once
+#include <algorithm>
 #include <cmath>
 #include <cstring>
+#include <utility>
 #include <vector>
 
 namespace tp {
@@ -75,13 +77,37 @@ struct PoseGraph {
         for (int a = 0; a < 6; ++a) e[a] /= F.sigma[a];
     }
 
+    // Elimination order: breadth-first levels from the newest pose, reversed (reverse Cuthill-McKee).  Only the cost
+    // depends on it (in key-frame order every loop factor stretches the envelope across the chain); the Gauss-Newton step is
+    // the same linear solve in exact arithmetic.
+    std::vector<int> eliminationOrder() const {
+        const int n = (int)x.size();
+        std::vector<std::vector<int> > nbr(n);
+        for (const PgFactor& F : f) if (F.i >= 0 && F.i != F.j) { nbr[F.i].push_back(F.j); nbr[F.j].push_back(F.i); }
+        std::vector<int> seq; std::vector<char> done(n, 0);
+        for (int start = n - 1; start >= 0; --start) {
+            if (done[start]) continue;
+            size_t q = seq.size(); seq.push_back(start); done[start] = 1;
+            for (; q < seq.size(); ++q) {
+                std::vector<std::pair<size_t, int> > next;
+                for (int v : nbr[seq[q]]) if (!done[v]) { done[v] = 1; next.push_back(std::make_pair(nbr[v].size(), v)); }
+                std::sort(next.begin(), next.end());
+                for (size_t k = 0; k < next.size(); ++k) seq.push_back(next[k].second);
+            }
+        }
+        std::vector<int> where(n);
+        for (int k = 0; k < n; ++k) where[seq[n - 1 - k]] = k;
+        return where;
+    }
+
     // one Gauss-Newton step: envelope (skyline) Cholesky of the normal equations
     void gaussNewtonStep() {
         const int n = (int)x.size(), D = 6 * n;
         if (n == 0) return;
+        const std::vector<int> where = eliminationOrder();
         std::vector<int> first(D);
         for (int r = 0; r < D; ++r) first[r] = r - (r % 6);
-        for (const PgFactor& F : f) if (F.i >= 0) { const int lo = std::min(F.i, F.j), hi = std::max(F.i, F.j); for (int a = 0; a < 6; ++a) first[6 * hi + a] = std::min(first[6 * hi + a], 6 * lo); }
+        for (const PgFactor& F : f) if (F.i >= 0) { const int lo = std::min(where[F.i], where[F.j]), hi = std::max(where[F.i], where[F.j]); for (int a = 0; a < 6; ++a) first[6 * hi + a] = std::min(first[6 * hi + a], 6 * lo); }
         std::vector<size_t> off(D + 1, 0);
         for (int r = 0; r < D; ++r) off[r + 1] = off[r] + (size_t)(r - first[r] + 1);
         std::vector<double> H(off[D], 0.0), g(D, 0.0);
@@ -89,7 +115,7 @@ struct PoseGraph {
         const double h = 1e-6;
         for (const PgFactor& F : f) {
             const int nv = F.i < 0 ? 1 : 2;
-            const int var[2] = {F.i < 0 ? F.j : F.i, F.j};
+            const int var[2] = {where[F.i < 0 ? F.j : F.i], where[F.j]};
             double e0[6]; error(F, F.i < 0 ? x[F.j] : x[F.i], x[F.j], e0);
             double J[2][6][6];
             for (int v = 0; v < nv; ++v)
@@ -125,7 +151,7 @@ struct PoseGraph {
         }
         for (int r = 0; r < D; ++r) { double s = g[r]; for (int k = first[r]; k < r; ++k) s -= at(r, k) * g[k]; g[r] = s / at(r, r); }
         for (int r = D - 1; r >= 0; --r) { g[r] /= at(r, r); for (int k = first[r]; k < r; ++k) g[k] -= at(r, k) * g[r]; }
-        for (int i = 0; i < n; ++i) x[i] = pg_retract(x[i], &g[6 * i]);
+        for (int i = 0; i < n; ++i) x[i] = pg_retract(x[i], &g[6 * where[i]]);
     }
 };
 
