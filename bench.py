@@ -63,6 +63,7 @@ def parse_args():
     ap.add_argument("--secondary", default="auto", help="second sensor measured inside the same line at N=1 ('auto' = hdl64 when --sensor vlp16, 'none')")
     ap.add_argument("--threads", type=int, default=-1, help="host threads submitting the handles' steps (-1 = one per handle for --workload loop, whose mapping "
                     "calls end with a stream synchronisation, else 1; ctypes releases the GIL inside the C ABI)")
+    ap.add_argument("--host-copies", type=int, default=0, help="e2e arm: 0 = one cudaMemcpyAsync per lane (ring channel directly behind the points), 2 = packing kernel over page-locked memory")
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-e2e", action="store_true")
     ap.add_argument("--no-latency", action="store_true")
@@ -198,8 +199,9 @@ def make_sequence(sensor, seed, workload, speed, n_scans):
 
 
 class Inputs:
-    """Pinned host copy of D sequences x T scans, layout [scan][sequence][cap] so that one scan of all sequences is
-    contiguous: xyz float32[T, D, cap, fpp] (fpp 3 or 4), ring uint16[T, D, cap], npts int32[T, D]."""
+    """Pinned host copy of D sequences x T scans, one slot of cap * (4 fpp + 2) bytes per (scan, sequence) so that one scan of
+    all sequences is contiguous: a slot holds the scan's npts points (fpp floats each) and, directly behind them, its ring
+    channel (npts uint16) -- the layout with which lego_pipeline_step_lanes moves a lane with one copy."""
 
     def __init__(self, sensor, seeds, T, workload, speed, fpp, pinned=True):
         import torch
@@ -207,24 +209,35 @@ class Inputs:
         self.D, self.T, self.fpp = len(seeds), T, fpp
         self.cap = cap = seqs[0].cap
         D = self.D
+        self.slot = slot = cap * (4 * fpp + 2)
         t0 = time.perf_counter()
-        xs = torch.zeros((T, D, cap, fpp), dtype=torch.float32, pin_memory=pinned)
-        rs = torch.zeros((T, D, cap), dtype=torch.int16, pin_memory=pinned)
-        self._keep = (xs, rs)
-        self.xyz = xs.numpy()
-        self.ring = rs.numpy().view(np.uint16)
+        blob = torch.zeros((T, D, slot), dtype=torch.uint8, pin_memory=pinned)
+        self._keep = blob
+        self.blob = blob.numpy()
         self.npts = np.zeros((T, D), np.int32)
+        # generate into scratch (points | ring at the END of the slot), then slide every scan's ring channel up behind its points
+        xyz = self.blob[:, :, :cap * 4 * fpp].view(np.float32)
+        ring = self.blob[:, :, cap * 4 * fpp:].view(np.uint16)
         for d, s in enumerate(seqs):
-            s.batch_into(0, T, self.xyz[0, d], self.ring[0, d], self.npts[0, d:], fpp, D * cap, D)
+            s.batch_into(0, T, xyz[0, d], ring[0, d], self.npts[0, d:], fpp, D * slot // 4, D, ring_stride=D * slot // 2)
+        for t in range(T):
+            for d in range(D):
+                n = int(self.npts[t, d])
+                self.blob[t, d, n * 4 * fpp:n * (4 * fpp + 2)] = self.blob[t, d, cap * 4 * fpp:cap * 4 * fpp + 2 * n].copy()
         self.gen_s = time.perf_counter() - t0
         self.stamps = np.arange(T, dtype=np.float64) * 0.1
-        self.scan_bytes_xyz = D * cap * fpp * 4
-        self.scan_bytes_ring = D * cap * 2
+        self.scan_bytes = D * slot
 
-    def tables(self, base_xyz, base_ring, lanes):
-        """per-lane address tables of scan 0 (uint64); scan t adds t * scan_bytes_*"""
+    def scan_xyz(self, t, d):
+        """(npts, fpp) float32 view of one scan's points"""
+        n = int(self.npts[t, d])
+        return self.blob[t, d, :n * 4 * self.fpp].view(np.float32).reshape(n, self.fpp)
+
+    def tables(self, base, lanes):
+        """per-lane slot addresses of scan 0 (uint64) and the sequence every lane replays; scan t adds t * scan_bytes, the ring
+        channel of a lane sits npts * 4 * fpp bytes behind its points"""
         seq = np.arange(lanes, dtype=np.uint64) % np.uint64(self.D)
-        return (np.uint64(base_xyz) + seq * np.uint64(self.cap * self.fpp * 4), np.uint64(base_ring) + seq * np.uint64(self.cap * 2), seq.astype(np.int64))
+        return np.uint64(base) + seq * np.uint64(self.slot), seq.astype(np.int64)
 
 
 # ------------------------------------------------------------------------------------------------ roofline
@@ -401,23 +414,24 @@ def run_b200(args, sensor, lanes, workload):
         for pl in group:
             pl.close()
 
-    def make_scan_fn(base_xyz, base_ring, on_device):
-        xt, rt, seq = inp.tables(base_xyz, base_ring, L)
+    def make_scan_fn(base, on_device):
+        xt, seq = inp.tables(base, L)
+        psz = np.uint64(4 * fpp)
 
         def scan(h, pl, s):
             l0, l1 = bounds[h], bounds[h + 1]
-            pl.step_lanes(xt[l0:l1] + np.uint64(s * inp.scan_bytes_xyz), rt[l0:l1] + np.uint64(s * inp.scan_bytes_ring),
-                          inp.npts[s][seq[l0:l1]], np.full(l1 - l0, inp.stamps[s]), floats_per_point=fpp,
+            n = inp.npts[s][seq[l0:l1]]
+            px = xt[l0:l1] + np.uint64(s * inp.scan_bytes)
+            pl.step_lanes(px, px + n.astype(np.uint64) * psz, n, np.full(l1 - l0, inp.stamps[s]), floats_per_point=fpp,
                           stage_mask=args.stages, on_device=on_device)
         return scan, seq
 
     # ---- device-resident inputs (value) -------------------------------------------------------------
     # The lanes are split over `handles` pipeline handles = CUDA streams: while one handle sits in its latency-bound LM
     # kernels (one CTA per lane) the others' streaming kernels fill the rest of the GPU.
-    d_x = torch.from_numpy(inp.xyz).cuda()
-    d_r = torch.from_numpy(inp.ring.view(np.int16)).cuda()
+    d_x = torch.from_numpy(inp.blob).cuda()
     torch.cuda.synchronize()
-    dev_scan, seq = make_scan_fn(d_x.data_ptr(), d_r.data_ptr(), True)
+    dev_scan, seq = make_scan_fn(d_x.data_ptr(), True)
     group = make_group()
 
     n_threads = args.threads if args.threads >= 0 else (H if workload == "loop" else 1)
@@ -509,14 +523,17 @@ def run_b200(args, sensor, lanes, workload):
             kf_in_map.append(len(pl.download("surroundingExistingKeyPosesID", l)))
     poses_dev = np.concatenate([pl.poses()[0] for pl in group])
     close_group(group)
-    del d_x, d_r
+    del d_x
     torch.cuda.empty_cache()
     ms = max_over_ranks(ms, world, "cuda")
     # ---- host buffers through the C ABI (e2e) --------------------------------------------------------
     e2e = None
     if not args.no_e2e:
         group = make_group()
-        host_scan, _ = make_scan_fn(inp.xyz.ctypes.data, inp.ring.ctypes.data, False)
+        # the scans sit in page-locked host memory, every lane's ring channel directly behind its points: one cudaMemcpyAsync per
+        # lane (input mode 0).  --host-copies 2 = input mode 2, one packing kernel per scan pulls the lanes over PCIe (measured
+        # slower: SM-initiated PCIe reads reach ~23 GB/s on this box, the copy engine ~2x that with one copy per lane)
+        host_scan, _ = make_scan_fn(inp.blob.ctypes.data, 2 if args.host_copies == 2 else 0)
         # Streaming use of the C ABI: scan t is submitted from pinned host memory (one H2D copy per lane of exactly its
         # points on the handle's copy stream), its pose read-back is enqueued behind it, and the result of scan t-4 is
         # collected while scans t-3 .. t are in flight (a mapping scan lasts as long as several uploads, so less slack
@@ -564,16 +581,16 @@ def run_b200(args, sensor, lanes, workload):
         assert same, "host-buffer and device-buffer runs disagree"
         # what the PCIe link of this box gives a plain pinned->device copy (context for E: the streaming loop cannot beat
         # h2d_bytes_per_step / this rate)
-        n_probe = max(1, min(inp.T, int(256e6 // max(inp.scan_bytes_xyz, 1))))
-        src = torch.from_numpy(inp.xyz[:n_probe])
-        probe = torch.empty(src.shape, dtype=torch.float32, device="cuda")
+        n_probe = max(1, min(inp.T, int(256e6 // max(inp.scan_bytes, 1))))
+        src = torch.from_numpy(inp.blob[:n_probe])
+        probe = torch.empty(src.shape, dtype=torch.uint8, device="cuda")
         ev0, ev1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
         probe.copy_(src, non_blocking=True); torch.cuda.synchronize()
         ev0.record()
         for _ in range(3):
             probe.copy_(src, non_blocking=True)
         ev1.record(); torch.cuda.synchronize()
-        h2d_gbs = 3 * src.numel() * 4 / (ev0.elapsed_time(ev1) * 1e-3) / 1e9
+        h2d_gbs = 3 * src.numel() / (ev0.elapsed_time(ev1) * 1e-3) / 1e9
         del probe
         pts_timed = int(sum(int(inp.npts[s][seq].sum()) for s in range(win.first_timed, win.T)))
         e2e = {"value": L * K * S * world / e2e_s, "unit": UNIT,
@@ -582,6 +599,9 @@ def run_b200(args, sensor, lanes, workload):
                "h2d_bytes_per_scan": round(pts_timed * (fpp * 4 + 2) / float(K * S * L), 1),
                "input_format": "x y z float32 + ring uint16 (14 B/point), only the npts points of each lane" if fpp == 3 else
                                "x y z intensity float32 + ring uint16 (18 B/point), only the npts points of each lane",
+               "h2d_path": "packing kernel reading page-locked host memory (lego_pipeline_step_lanes, src_on_device = 2)" if args.host_copies == 2 else
+                           "one cudaMemcpyAsync per lane: the ring channel sits directly behind the lane's points (lego_pipeline_step_lanes, src_on_device = 0)",
+               "h2d_gbs_achieved": round(pts_timed * (fpp * 4 + 2) / e2e_s / 1e9, 1),
                "seconds": e2e_s, "pcie_h2d_gbs_plain_copy": round(h2d_gbs, 1), "poses_equal_device_arm": same,
                "mode": "streaming: up to 5 scans in flight per handle, the poses of scan k are collected after scan k+4 was submitted"}
 
@@ -608,12 +628,13 @@ def measure_latency(args, sensor, workload, inp, win, device):
     from lego_loam_b200.params import make_params
     params = make_params(sensor, device=device, loop_closure=(workload == "loop"), max_keyframes=max(640, win.T // 3 + 64))
     pl = Pipeline(params, lanes=1, max_points=inp.cap)
-    xt, rt, _ = inp.tables(inp.xyz.ctypes.data, inp.ring.ctypes.data, 1)
+    xt, _ = inp.tables(inp.blob.ctypes.data, 1)
     n_timed = min(200, win.T - win.first_timed)
     lat, mapped = [], []
     for s in range(win.first_timed + n_timed):
         t0 = time.perf_counter()
-        pl.step_lanes(xt + np.uint64(s * inp.scan_bytes_xyz), rt + np.uint64(s * inp.scan_bytes_ring), inp.npts[s][:1],
+        px = xt + np.uint64(s * inp.scan_bytes)
+        pl.step_lanes(px, px + np.uint64(int(inp.npts[s][0]) * 4 * inp.fpp), inp.npts[s][:1],
                       inp.stamps[s:s + 1], floats_per_point=inp.fpp, stage_mask=args.stages)
         _, flags = pl.poses()
         dt = (time.perf_counter() - t0) * 1e3

@@ -174,8 +174,14 @@ int lego_pipeline_step(lego_pipeline* h, const float* xyzi, const uint16_t* ring
 /* Same step with ONE POINTER PER LANE and no padding on the wire: xyz[l] points at npts[l] points of lane l,
  * floats_per_point = 4 (x y z intensity, like lego_pipeline_step) or 3 (x y z packed -- ImageProjection never reads the
  * input intensity, imageProjection.cpp:248-255 overwrites it); ring[l] at npts[l] uint16 (ring may be NULL without
- * useCloudRing).  The pointer TABLES are host memory; with src_on_device = 1 the pointers in them are device pointers.
- * Host sources: exactly npts[l] * (4 * floats_per_point + 2) bytes per lane cross PCIe.
+ * useCloudRing).  The pointer TABLES are host memory.  src_on_device: 0 = the pointers in them are ordinary host memory
+ * (one cudaMemcpyAsync per lane and channel), 1 = device memory (read in place), 2 = PAGE-LOCKED host memory that the
+ * device can address (cudaMallocHost / cudaHostAlloc / cudaHostRegister, e.g. torch pin_memory): one packing kernel pulls
+ * every lane's points over PCIe, which is what keeps the link busy with hundreds of lanes.  Passing pageable memory with
+ * 2 is an error the call cannot detect (the kernel faults).
+ * Host sources: exactly npts[l] * (4 * floats_per_point + 2) bytes per lane cross PCIe.  With src_on_device = 0, a lane whose
+ * ring channel starts exactly where its points end (ring[l] == (char*)xyz[l] + npts[l] * 4 * floats_per_point) is moved
+ * with ONE copy instead of two, which matters at hundreds of lanes (the copy engine spends 2-3 us per copy).
  *
  * Input lifetime (both step forms): host buffers are copied asynchronously on the handle's copy stream -- they must
  * stay valid and unmodified until lego_pipeline_input_wait() returns (or any later synchronising call on the handle:

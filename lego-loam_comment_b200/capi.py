@@ -195,15 +195,16 @@ class Pipeline:
                                            1 if on_device else 0, stage_mask), "lego_pipeline_step")
 
     def step_lanes(self, xyz_ptrs, ring_ptrs, npts, stamps, floats_per_point=4, stage_mask=7, on_device=False):
-        """lego_pipeline_step_lanes: xyz_ptrs / ring_ptrs = uint64[lanes] tables of per-lane addresses (host memory, or device
-        memory when on_device); only npts[l] points of lane l are read."""
+        """lego_pipeline_step_lanes: xyz_ptrs / ring_ptrs = uint64[lanes] tables of per-lane addresses; on_device False / 0 =
+        host memory, True / 1 = device memory, 2 = page-locked device-mapped host memory (packing kernel).  Only npts[l]
+        points of lane l are read."""
         npts = np.ascontiguousarray(npts, np.int32)
         stamps = np.ascontiguousarray(stamps, np.float64)
         xp = np.ascontiguousarray(xyz_ptrs, np.uint64)
         rp = None if ring_ptrs is None else np.ascontiguousarray(ring_ptrs, np.uint64)
         assert xp.shape == (self.lanes,) and npts.shape == (self.lanes,) and stamps.shape == (self.lanes,)
         _check(self.lib.lego_pipeline_step_lanes(self.h, xp.ctypes.data, None if rp is None else rp.ctypes.data, npts.ctypes.data,
-                                                 int(floats_per_point), stamps.ctypes.data, 1 if on_device else 0, stage_mask),
+                                                 int(floats_per_point), stamps.ctypes.data, int(on_device), stage_mask),
                "lego_pipeline_step_lanes")
 
     def input_wait(self):

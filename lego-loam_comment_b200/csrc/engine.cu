@@ -45,10 +45,12 @@ Engine::Engine(const lego_params& p, int lanes, int max_points) : params(p) {
     const size_t tbl = sizeof(void*) * L;
     for (int b = 0; b < IN_SLOTS; ++b) {
         d_in_xyzi[b] = alloc<float4>(L * c.Pcap); d_in_ring[b] = alloc<uint16_t>(L * c.Pcap); d_npts[b] = alloc<int>(L);
+        d_in_blob[b] = alloc<char>(L * c.Pcap * 18, false);     // lanes that arrive as one block: points, then the ring channel right behind them
         d_ptr_xyzi[b] = alloc<const float4*>(L); d_ptr_ring[b] = alloc<const uint16_t*>(L);
         cuda_check(cudaEventCreateWithFlags(&evCopied[b], cudaEventDisableTiming), "event");
         cuda_check(cudaEventCreateWithFlags(&evConsumed[b], cudaEventDisableTiming), "event");
-        cuda_check(cudaMallocHost(reinterpret_cast<void**>(&h_pin[b]), 2 * tbl + sizeof(int) * L), "cudaMallocHost");
+        cuda_check(cudaMallocHost(reinterpret_cast<void**>(&h_pin[b]), 4 * tbl + sizeof(int) * L + 16), "cudaMallocHost");   // 2 pointer tables | npts | 2 source tables
+        d_src_xyz[b] = alloc<const float*>(L); d_src_ring[b] = alloc<const uint16_t*>(L);
     }
     ip.in_xyzi = d_ptr_xyzi[0]; ip.in_ring = d_ptr_ring[0]; ip.npts = d_npts[0]; ip.in_floats = 4;
     ip.owner = alloc<int>(L * N); ip.rangeMat = alloc<float>(L * N); ip.fullCloud = alloc<float4>(L * N);
@@ -138,6 +140,42 @@ float Engine::timerElapsed(int a, int b) {
 
 void Engine::sync() { cuda_check(cudaStreamSynchronize(stream), "stream sync"); }
 
+// Packing kernel of the page-locked input mode: every lane's points and ring channel are pulled out of device-mapped host
+// memory (cudaMallocHost / cudaHostRegister: under unified addressing the host pointer is valid on the device) into the
+// staging slot, one launch for all lanes.  One cudaMemcpyAsync per lane and channel -- 1184 calls per 592-lane scan -- left
+// the PCIe link at 25 GB/s; the kernel's coalesced reads keep it busy (bench.py e2e).  16-byte loads when the source allows.
+__global__ void __launch_bounds__(256) ip_stage_pinned_kernel(const float* const* __restrict__ src_xyz, const uint16_t* const* __restrict__ src_ring,
+                                                              const int* __restrict__ npts, float4* dst_xyz, uint16_t* dst_ring, int Pcap, int fpp) {
+    const int lane = blockIdx.y;
+    const int n = npts[lane];
+    const int gtid = blockIdx.x * blockDim.x + threadIdx.x, gsz = gridDim.x * blockDim.x;
+    {
+        const float* s = src_xyz[lane];
+        float* d = reinterpret_cast<float*>(dst_xyz + (size_t)lane * Pcap);
+        const int words = n * fpp;
+        if ((reinterpret_cast<uintptr_t>(s) & 15) == 0) {
+            const int quads = words >> 2;
+            const float4* s4 = reinterpret_cast<const float4*>(s); float4* d4 = reinterpret_cast<float4*>(d);
+            for (int i = gtid; i < quads; i += gsz) d4[i] = s4[i];
+            for (int i = (quads << 2) + gtid; i < words; i += gsz) d[i] = s[i];
+        } else {
+            for (int i = gtid; i < words; i += gsz) d[i] = s[i];
+        }
+    }
+    if (src_ring) {
+        const uint16_t* s = src_ring[lane];
+        uint16_t* d = dst_ring + (size_t)lane * Pcap;
+        if ((reinterpret_cast<uintptr_t>(s) & 3) == 0) {
+            const int pairs = n >> 1;
+            const uint32_t* s2 = reinterpret_cast<const uint32_t*>(s); uint32_t* d2 = reinterpret_cast<uint32_t*>(d);
+            for (int i = gtid; i < pairs; i += gsz) d2[i] = s2[i];
+            if ((n & 1) && gtid == 0) d[n - 1] = s[n - 1];
+        } else {
+            for (int i = gtid; i < n; i += gsz) d[i] = s[i];
+        }
+    }
+}
+
 // copyPointCloud (imageProjection.cpp:163-179): the host message becomes device arrays.  Host sources are copied into
 // one of IN_SLOTS staging buffers on a separate copy stream, so the uploads of the next scans overlap the processing of
 // this one; device sources are used in place through the per-lane pointer table (no copy at all).
@@ -198,10 +236,30 @@ void Engine::uploadScan(const float* xyzi, const uint16_t* ring, const int* npts
 
 // One pointer per lane, floats_per_point = 4 (x y z intensity) or 3 (x y z packed: the reference never reads the input
 // intensity, imageProjection.cpp:248-255 overwrites it).  Host sources: npts[l] points of lane l cross PCIe, nothing else.
-void Engine::uploadScanLanes(const float* const* xyz, const uint16_t* const* ring, const int* npts, int floats_per_point, bool src_on_device) {
+void Engine::uploadScanLanes(const float* const* xyz, const uint16_t* const* ring, const int* npts, int floats_per_point, bool src_on_device,
+                             bool host_is_pinned) {
     if (floats_per_point != 3 && floats_per_point != 4) throw std::invalid_argument("floats_per_point must be 3 or 4");
     for (int l = 0; l < c.L; ++l) if (!xyz[l] || (c.useRing && (!ring || !ring[l]))) throw std::invalid_argument("null lane pointer");
     const int b = beginUpload(npts, src_on_device);
+    if (!src_on_device && host_is_pinned) {
+        // page-locked, device-mapped host memory: one packing kernel on the copy stream instead of 2 L copies
+        const size_t tblBytes = sizeof(void*) * (size_t)c.L;
+        const float** sx = reinterpret_cast<const float**>(h_pin[b] + 2 * tblBytes + ((sizeof(int) * (size_t)c.L + 15) & ~(size_t)15));
+        const uint16_t** sr = reinterpret_cast<const uint16_t**>(reinterpret_cast<char*>(sx) + tblBytes);
+        int* hn = reinterpret_cast<int*>(h_pin[b] + 2 * tblBytes);
+        for (int l = 0; l < c.L; ++l) { sx[l] = xyz[l]; sr[l] = ring ? ring[l] : nullptr; hn[l] = npts[l]; }
+        cuda_check(cudaMemcpyAsync(d_src_xyz[b], sx, tblBytes, cudaMemcpyHostToDevice, copyStream), "upload source table");
+        if (ring) cuda_check(cudaMemcpyAsync(d_src_ring[b], sr, tblBytes, cudaMemcpyHostToDevice, copyStream), "upload source table");
+        cuda_check(cudaMemcpyAsync(d_npts[b], hn, sizeof(int) * c.L, cudaMemcpyHostToDevice, copyStream), "upload npts");
+        dim3 g(24, c.L);
+        ip_stage_pinned_kernel<<<g, 256, 0, copyStream>>>(d_src_xyz[b], ring ? d_src_ring[b] : nullptr, d_npts[b], d_in_xyzi[b], d_in_ring[b], c.Pcap, floats_per_point);
+        launches += 1;
+        const float4** hx = reinterpret_cast<const float4**>(h_pin[b]);
+        const uint16_t** hr = reinterpret_cast<const uint16_t**>(h_pin[b] + tblBytes);
+        for (int l = 0; l < c.L; ++l) { hx[l] = d_in_xyzi[b] + (size_t)l * c.Pcap; hr[l] = d_in_ring[b] + (size_t)l * c.Pcap; }
+        finishUpload(b, npts, floats_per_point);
+        return;
+    }
     const size_t tbl = sizeof(void*) * (size_t)c.L;
     const float4** hx = reinterpret_cast<const float4**>(h_pin[b]);
     const uint16_t** hr = reinterpret_cast<const uint16_t**>(h_pin[b] + tbl);
@@ -210,6 +268,13 @@ void Engine::uploadScanLanes(const float* const* xyz, const uint16_t* const* rin
         if (src_on_device) {
             hx[l] = reinterpret_cast<const float4*>(xyz[l]);
             hr[l] = ring ? ring[l] : nullptr;
+        } else if (ring && reinterpret_cast<const char*>(ring[l]) == reinterpret_cast<const char*>(xyz[l]) + psz * npts[l]) {
+            // the ring channel directly follows the points in the caller's buffer: ONE copy moves the lane (a copy carries
+            // 2-3 us of fixed cost on the copy engine, which at 592 lanes x 2 channels halves the PCIe rate)
+            char* blob = d_in_blob[b] + (size_t)l * c.Pcap * 18;
+            hx[l] = reinterpret_cast<const float4*>(blob);
+            hr[l] = reinterpret_cast<const uint16_t*>(blob + psz * npts[l]);
+            if (npts[l] > 0) cuda_check(cudaMemcpyAsync(blob, xyz[l], (psz + sizeof(uint16_t)) * npts[l], cudaMemcpyHostToDevice, copyStream), "upload lane");
         } else {
             hx[l] = d_in_xyzi[b] + (size_t)l * c.Pcap;
             hr[l] = d_in_ring[b] + (size_t)l * c.Pcap;

@@ -283,7 +283,8 @@ public:
 
     // ---- ImageProjection (names follow imageProjection.cpp) ----
     void uploadScan(const float* xyzi, const uint16_t* ring, const int* npts, int stride_points, bool src_on_device);
-    void uploadScanLanes(const float* const* xyz, const uint16_t* const* ring, const int* npts, int floats_per_point, bool src_on_device);
+    void uploadScanLanes(const float* const* xyz, const uint16_t* const* ring, const int* npts, int floats_per_point, bool src_on_device,
+                         bool host_is_pinned = false);
     void inputWait();             // input buffers of the last step may be refilled once this returns
     void inputConsumed();         // marks the point after which the current input buffers may be overwritten
     void projectPointCloud();     // + findStartEndAngle
@@ -416,7 +417,9 @@ private:
     // double-buffered input staging: the H2D copy of scan k+1 runs on copyStream while scan k is still being processed
     static constexpr int IN_SLOTS = 5;   // staging slots: the uploads of scans k+1 .. k+4 may run while scan k is processed (a mapping scan lasts ~3 uploads)
     float4* d_in_xyzi[IN_SLOTS] = {}; uint16_t* d_in_ring[IN_SLOTS] = {}; int* d_npts[IN_SLOTS] = {};
+    char* d_in_blob[IN_SLOTS] = {};
     const float4** d_ptr_xyzi[IN_SLOTS] = {}; const uint16_t** d_ptr_ring[IN_SLOTS] = {};
+    const float** d_src_xyz[IN_SLOTS] = {}; const uint16_t** d_src_ring[IN_SLOTS] = {};   // page-locked input mode: the callers' host pointers
     cudaStream_t copyStream = nullptr;
     cudaEvent_t evCopied[IN_SLOTS] = {}, evConsumed[IN_SLOTS] = {};
     int inBuf = 0, curIn = 0;

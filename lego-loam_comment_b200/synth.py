@@ -46,6 +46,8 @@ def _load():
                                          ctypes.c_void_p, ctypes.c_int, ctypes.c_int]
         lib.lego_synth_batch_fmt.argtypes = [ctypes.c_void_p, ctypes.c_int, ctypes.c_int, ctypes.c_void_p, ctypes.c_void_p, ctypes.c_void_p,
                                              ctypes.c_int, ctypes.c_int, ctypes.c_int, ctypes.c_long, ctypes.c_int]
+        lib.lego_synth_batch_strided.argtypes = [ctypes.c_void_p, ctypes.c_int, ctypes.c_int, ctypes.c_void_p, ctypes.c_void_p, ctypes.c_void_p,
+                                                 ctypes.c_int, ctypes.c_int, ctypes.c_int, ctypes.c_long, ctypes.c_long, ctypes.c_int]
         lib.lego_synth_pose.argtypes = [ctypes.POINTER(SynthCfg), ctypes.c_double, ctypes.c_void_p]
         _lib = lib
     return _lib
@@ -93,12 +95,18 @@ class SynthSequence:
         _load().lego_synth_batch(self._h, k0, count, xyzi.ctypes.data, ring.ctypes.data, npts.ctypes.data, self.cap, threads)
         return xyzi, ring, npts
 
-    def batch_into(self, k0, count, xyz, ring, npts, floats_per_point, scan_stride_points, npts_stride=1, threads=None):
+    def batch_into(self, k0, count, xyz, ring, npts, floats_per_point, scan_stride_points, npts_stride=1, threads=None, ring_stride=None):
         """scans k0 .. k0+count-1 written straight into caller memory (e.g. one sequence's slots of a pinned
-        [scan][sequence][cap] buffer): xyz / ring / npts are numpy views whose first element is scan k0's slot."""
+        [scan][sequence][cap] buffer): xyz / ring / npts are numpy views whose first element is scan k0's slot.  Scan s goes
+        to xyz + s * scan_stride_points * floats_per_point floats and ring + s * scan_stride_points uint16 -- or, with
+        ring_stride given, scan_stride_points counts FLOATS of the xyz channel and ring_stride uint16 of the ring channel."""
         threads = threads or min(32, os.cpu_count() or 1)
-        _load().lego_synth_batch_fmt(self._h, k0, count, xyz.ctypes.data, ring.ctypes.data, npts.ctypes.data, self.cap, threads,
-                                     int(floats_per_point), int(scan_stride_points), int(npts_stride))
+        if ring_stride is None:
+            _load().lego_synth_batch_fmt(self._h, k0, count, xyz.ctypes.data, ring.ctypes.data, npts.ctypes.data, self.cap, threads,
+                                         int(floats_per_point), int(scan_stride_points), int(npts_stride))
+        else:
+            _load().lego_synth_batch_strided(self._h, k0, count, xyz.ctypes.data, ring.ctypes.data, npts.ctypes.data, self.cap, threads,
+                                             int(floats_per_point), int(scan_stride_points), int(ring_stride), int(npts_stride))
 
     def pose(self, t):
         out = np.zeros(6)

@@ -79,6 +79,64 @@ def test_step_lanes_from_device_memory():
     a.close(); b.close()
 
 
+def test_step_lanes_one_block_per_lane():
+    """A lane whose ring channel starts exactly where its points end is uploaded with one copy (include/lego_b200.h); the
+    results equal the two-copy path's.  Mixed in one step: lane 0 adjacent, lane 1 separate buffers."""
+    sensor = "vlp16"
+    seqs, scans = _scans(sensor, (61, 62), 7)
+    cap = seqs[0].cap
+    a = Pipeline(make_params(sensor), lanes=2, max_points=cap)
+    b = Pipeline(make_params(sensor), lanes=2, max_points=cap)
+    for k, pair in enumerate(scans):
+        n = np.array([len(p[0]) for p in pair], np.int32)
+        x3 = [np.ascontiguousarray(p[0][:, :3]) for p in pair]
+        rg = [np.ascontiguousarray(p[1]) for p in pair]
+        blob = np.zeros(n[0] * 14, np.uint8)
+        blob[:n[0] * 12] = x3[0].view(np.uint8).reshape(-1); blob[n[0] * 12:] = rg[0].view(np.uint8)
+        st = [k * 0.1] * 2
+        a.step_lanes(np.array([x.ctypes.data for x in x3], np.uint64), np.array([r.ctypes.data for r in rg], np.uint64), n, st, floats_per_point=3)
+        b.step_lanes(np.array([blob.ctypes.data, x3[1].ctypes.data], np.uint64), np.array([blob.ctypes.data + int(n[0]) * 12, rg[1].ctypes.data], np.uint64),
+                     n, st, floats_per_point=3)
+        a.input_wait(); b.input_wait()
+        assert np.array_equal(a.poses()[0], b.poses()[0]), "scan %d" % k
+        for lane in range(2):
+            for name in NAMES:
+                assert _same(a.download(name, lane), b.download(name, lane)), "%s lane %d scan %d" % (name, lane, k)
+    a.close(); b.close()
+
+
+def test_step_lanes_from_page_locked_memory():
+    """src_on_device = 2: the lanes' scans sit in page-locked host memory and one packing kernel gathers them (no per-lane
+    copies).  Same results as ordinary host memory, with odd point counts and unaligned lane pointers."""
+    import torch
+    sensor = "vlp16"
+    seqs, scans = _scans(sensor, (51, 52, 53), 7)
+    cap = seqs[0].cap
+    a = Pipeline(make_params(sensor), lanes=3, max_points=cap)
+    b = Pipeline(make_params(sensor), lanes=3, max_points=cap)
+    pin_x = torch.zeros((3, cap * 3 + 8), dtype=torch.float32).pin_memory()
+    pin_r = torch.zeros((3, cap + 8), dtype=torch.int16).pin_memory()
+    for k, trio in enumerate(scans):
+        n = np.array([len(p[0]) - (l + k) % 2 for l, p in enumerate(trio)], np.int32)       # odd and even counts
+        xs, rs, xp, rp = [], [], [], []
+        for l, (xyzi, ring) in enumerate(trio):
+            x3 = np.ascontiguousarray(xyzi[:n[l], :3]); rg = np.ascontiguousarray(ring[:n[l]])
+            xs.append(x3); rs.append(rg)
+            off = l                                         # lane l starts l floats / l uint16 into its row: 4- and 2-byte aligned only
+            pin_x[l, off:off + 3 * n[l]] = torch.from_numpy(x3.reshape(-1))
+            pin_r[l, off:off + n[l]] = torch.from_numpy(rg.view(np.int16))
+            xp.append(pin_x[l].data_ptr() + 4 * off); rp.append(pin_r[l].data_ptr() + 2 * off)
+        st = [k * 0.1] * 3
+        a.step_lanes(np.array([x.ctypes.data for x in xs], np.uint64), np.array([r.ctypes.data for r in rs], np.uint64), n, st, floats_per_point=3)
+        b.step_lanes(np.array(xp, np.uint64), np.array(rp, np.uint64), n, st, floats_per_point=3, on_device=2)
+        a.input_wait(); b.input_wait()
+        assert np.array_equal(a.poses()[0], b.poses()[0]), "scan %d" % k
+        for lane in range(3):
+            for name in NAMES:
+                assert _same(a.download(name, lane), b.download(name, lane)), "%s lane %d scan %d" % (name, lane, k)
+    a.close(); b.close()
+
+
 def test_step_argument_and_capacity_errors():
     sensor = "vlp16"
     seq = SynthSequence(sensor, seed=3)

@@ -26,11 +26,17 @@ def _worker(rank, world, port, q):
         r, w, l = bench.dist_env()
         # same synthetic generator, different seeds -> different scans on every rank
         inp = bench.Inputs("vlp16", seeds[:2], 3, "drive", 3.0, 3, pinned=False)
-        assert inp.xyz.shape == (3, 2, inp.cap, 3) and inp.npts.shape == (3, 2)
-        digest = float(inp.xyz[0, 0, :inp.npts[0, 0]].sum())
-        # lane l replays sequence l % D: the per-lane address tables point into the [scan][sequence][cap] buffer
-        xt, rt, seq = inp.tables(inp.xyz.ctypes.data, inp.ring.ctypes.data, 5)
-        assert list(seq) == [0, 1, 0, 1, 0] and int(xt[1] - xt[0]) == inp.cap * 12 and int(rt[3] - rt[2]) == inp.cap * 2
+        assert inp.blob.shape == (3, 2, inp.cap * 14) and inp.npts.shape == (3, 2)
+        digest = float(inp.scan_xyz(0, 0).sum())
+        # one slot per (scan, sequence): the scan's points and, directly behind them, its ring channel
+        from lego_loam_b200.synth import SynthSequence
+        xyzi, ring = SynthSequence("vlp16", seed=seeds[1], scene="street", speed=3.0, n_scans=64).scan(2)
+        n = int(inp.npts[2, 1])
+        assert n == len(xyzi) and np.array_equal(inp.scan_xyz(2, 1), xyzi[:, :3])
+        assert np.array_equal(inp.blob[2, 1, n * 12:n * 14].view(np.uint16), ring)
+        # lane l replays sequence l % D: the per-lane address table points at the slots of scan 0
+        xt, seq = inp.tables(inp.blob.ctypes.data, 5)
+        assert list(seq) == [0, 1, 0, 1, 0] and int(xt[1] - xt[0]) == inp.cap * 14 and inp.scan_bytes == 2 * inp.cap * 14
         digests = [None] * world
         dist.all_gather_object(digests, digest)
         class A: sensor = "vlp16"; steps = 1; warmup = 0; speed = 3.0; stages = 3; gpus = world; workload = "drive"; scans_per_step = 0

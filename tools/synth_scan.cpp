@@ -280,6 +280,20 @@ void lego_synth_batch_fmt(void* h, int scan0, int count, float* xyz, uint16_t* r
     for (auto& th : pool) th.join();
 }
 
+// The same with independent strides for the two channels (in floats and in uint16 elements): lets a caller keep a scan's ring
+// channel in the same slot as its points.
+void lego_synth_batch_strided(void* h, int scan0, int count, float* xyz, uint16_t* ring, int* npts, int cap, int threads, int fpp,
+                              long xyz_stride_floats, long ring_stride_elems, int npts_stride) {
+    if (threads < 1) threads = 1;
+    std::vector<std::thread> pool;
+    for (int t = 0; t < threads; ++t)
+        pool.emplace_back([=]() {
+            for (int s = t; s < count; s += threads)
+                npts[(size_t)s * npts_stride] = lego_synth_scan_fmt(h, scan0 + s, xyz + (size_t)s * xyz_stride_floats, ring + (size_t)s * ring_stride_elems, cap, fpp);
+        });
+    for (auto& th : pool) th.join();
+}
+
 // count scans starting at scan0, multi-threaded. xyzi: count*cap*4, ring: count*cap, npts: count.
 void lego_synth_batch(void* h, int scan0, int count, float* xyzi, uint16_t* ring, int* npts, int cap, int threads) {
     if (threads < 1) threads = 1;
