@@ -301,10 +301,21 @@ def gather_counts(pl, params, lanes):
         # the queries whose cache could not prove the answer are not counted (lower bound)
         search += 176 * (int(s_[0]) + int(s_[4]))
         rerank += max(int(st[3]) - 1, 0) * 224 * (int(s_[0]) + int(s_[4]))
+    arr, n_map, n_ds = int(sc[0] + sc[1] + sc[2]), int(mc[0] + mc[1]), int(mc[2] + mc[3])
     c["mo_bytes"] = {
         "mo_begin_kernel": 200 * lanes,
-        "mo_assemble_map_kernel": 32 * int(mc[0] + mc[1]),
-        "vg_filter(localMap)": 16 * int(mc.sum()),
+        # incremental local map (csrc/incremental_map.cu): n = points of the sorted local map, arr = points of the key frames that
+        # arrived in this call (about one key frame = this scan's down-sampled clouds), nDS = points of the down-sampled map
+        "mo_assemble_map_kernel": 32 * arr,
+        "im_sort_arrivals": 20 * arr,
+        "im_gather_new_kernel": 48 * arr,
+        "im_mark_kernel": 4 * n_map,
+        "im_merge_old_kernel": 40 * n_map,
+        "im_merge_new_kernel": 48 * arr,
+        "im_commit_kernel": 0.0,
+        "im_reduce_kernel": 16 * n_map + 16 * n_ds,
+        "im_compact_kernel": 32 * n_ds,
+        "vg_filter(localMap)": 16 * int(mc.sum()),        # only with LEGO_INCR_MAP=0 (whole map assembled and filtered per call)
         "vg_filter(currentScan)": 16 * (c["Fl"] + c["Flf"] + c["O"] + int(sc[0] + sc[1] + sc[2])),
         "mo_concat_kernel": 32 * int(sc[3]),
         "vg_filter(surfTotal)": 16 * int(sc[3] + sc[4]),
