@@ -65,6 +65,8 @@ void operator delete[](void* p, std::size_t) noexcept { std::free(p); }
 #undef main
 #undef private
 
+#include "topic_dump.h"
+
 namespace {
 
 typedef std::chrono::steady_clock Clock;
@@ -393,6 +395,13 @@ int ref_feed_scan(void* h, const float* xyzi, const uint16_t* ring, int P, int i
     }
     return out;
 }
+
+// The last message the reference's nodes published on `topic`, flattened (oracle/topic_dump.h).  viz topics only exist when
+// ref_subscribe_all(1) made getNumSubscribers() non-zero before the scan.
+long ref_topic_dump(const char* topic, double* out, long cap, long nvalid, double* stamp, char* frame, char* child, int str_cap, long* count) {
+    return topic_dump::dump(topic, out, cap, nvalid, stamp, frame, child, str_cap, count);
+}
+void ref_subscribe_all(int on) { ros::ShimState::get().all_subscribed = on != 0; }
 
 // One sensor_msgs/Imu message, delivered to the two subscribers the reference has for /imu/data
 // (featureAssociation.cpp:193, mapOptmization.cpp:242).

@@ -182,3 +182,74 @@ def pose_graph(poses, factors, meas, variances, steps):
     lib.oracle_pose_graph.argtypes = [ctypes.c_void_p, ctypes.c_int, ctypes.c_void_p, ctypes.c_void_p, ctypes.c_void_p, ctypes.c_int, ctypes.c_int, ctypes.c_void_p]
     lib.oracle_pose_graph(poses.ctypes.data, len(poses), factors.ctypes.data, meas.ctypes.data, variances.ctypes.data, len(factors), steps, out.ctypes.data)
     return out
+
+
+# ---------------------------------------------------------------- topics (reference nodes and B200 node shells)
+TOPICS_CLOUD = ["/segmented_cloud", "/outlier_cloud", "/laser_cloud_sharp", "/laser_cloud_less_sharp", "/laser_cloud_flat", "/laser_cloud_less_flat",
+                "/laser_cloud_corner_last", "/laser_cloud_surf_last", "/outlier_cloud_last"]
+TOPICS_ODOMETRY = ["/laser_odom_to_init", "/aft_mapped_to_init", "/integrated_to_init"]
+TOPIC_INFO = "/segmented_cloud_info"
+
+
+def _topic_dump(fn, topic, nvalid=0):
+    """-> dict(values float64[n], stamp, frame_id, child_frame_id, count) of the last message on `topic`, or None"""
+    fn.restype = ctypes.c_long
+    fn.argtypes = [ctypes.c_char_p, ctypes.c_void_p, ctypes.c_long, ctypes.c_long, ctypes.POINTER(ctypes.c_double), ctypes.c_char_p,
+                   ctypes.c_char_p, ctypes.c_int, ctypes.POINTER(ctypes.c_long)]
+    stamp, count = ctypes.c_double(0), ctypes.c_long(0)
+    frame, child = ctypes.create_string_buffer(64), ctypes.create_string_buffer(64)
+    n = fn(topic.encode(), None, 0, nvalid, ctypes.byref(stamp), frame, child, 64, ctypes.byref(count))
+    if n < 0:
+        return None
+    out = np.zeros(max(n, 1), np.float64)
+    fn(topic.encode(), out.ctypes.data, n, nvalid, ctypes.byref(stamp), frame, child, 64, ctypes.byref(count))
+    return {"values": out[:n], "stamp": stamp.value, "frame_id": frame.value.decode(), "child_frame_id": child.value.decode(), "count": count.value}
+
+
+def ref_topic(ref, topic, nvalid=0):
+    """last message the REFERENCE's nodes published on `topic` (ref: RefPipeline)"""
+    return _topic_dump(ref.lib.ref_topic_dump, topic, nvalid)
+
+
+def ref_subscribe_all(ref, on=True):
+    ref.lib.ref_subscribe_all.argtypes = [ctypes.c_int]
+    ref.lib.ref_subscribe_all(1 if on else 0)
+
+
+def shells_so(cfg):
+    return os.path.join(HERE, "_ref", "liblego_shells_%s.so" % cfg)
+
+
+class ShellPipeline:
+    """The four B200 ROS node shells (ros/lego_loam_b200/src) compiled against oracle/shim and linked to liblego_b200.so,
+    driven synchronously (oracle/shell_harness.cpp).  Needs a CUDA device: the shells call the C ABI."""
+
+    def __init__(self, cfg="vlp16", subscribe_all=True):
+        self.lib = lib = ctypes.CDLL(shells_so(cfg))
+        lib.shell_create.restype = ctypes.c_void_p
+        lib.shell_create.argtypes = [ctypes.c_int]
+        lib.shell_destroy.argtypes = [ctypes.c_void_p]
+        lib.shell_feed_scan.restype = ctypes.c_int
+        lib.shell_feed_scan.argtypes = [ctypes.c_void_p, ctypes.c_void_p, ctypes.c_void_p, ctypes.c_int, ctypes.c_int, ctypes.c_double]
+        self.h = lib.shell_create(1 if subscribe_all else 0)
+        if not self.h:
+            raise RuntimeError("node shells could not be created (no CUDA device?)")
+
+    def feed(self, xyzi, ring, stamp, is_dense=True):
+        xyzi = np.ascontiguousarray(xyzi, np.float32)
+        ring = None if ring is None else np.ascontiguousarray(ring, np.uint16)
+        return self.lib.shell_feed_scan(self.h, xyzi.ctypes.data, None if ring is None else ring.ctypes.data, int(xyzi.shape[0]),
+                                        1 if is_dense else 0, float(stamp))
+
+    def topic(self, topic, nvalid=0):
+        return _topic_dump(self.lib.shell_topic_dump, topic, nvalid)
+
+    def errors(self):
+        return self.lib.shell_errors()
+
+    def close(self):
+        if self.h:
+            self.lib.shell_destroy(self.h)
+            self.h = None
+
+    __del__ = close

@@ -10,6 +10,7 @@
 #include <cstdint>
 #include <cstdio>
 #include <cstdarg>
+#include <functional>
 #include <map>
 #include <set>
 #include <memory>
@@ -18,6 +19,7 @@
 
 namespace ros {
 
+struct Duration { double sec_ = 0.0; double toSec() const { return sec_; } };
 struct Time {
     double sec_ = 0.0;
     Time() {}
@@ -25,6 +27,7 @@ struct Time {
     double toSec() const { return sec_; }
     Time& fromSec(double s) { sec_ = s; return *this; }
     static Time now() { return Time(0.0); }
+    Duration operator-(const Time& o) const { Duration d; d.sec_ = sec_ - o.sec_; return d; }
 };
 
 struct Rate {
@@ -40,6 +43,9 @@ struct ShimState {
     bool all_subscribed = false;
     bool shutdown_requested = false;
     int errors = 0;
+    // callbacks registered through NodeHandle::subscribe, per topic; shim_deliver() hands them a message synchronously (the
+    // harness of the B200 node shells drives its nodes that way; the reference harness calls the handlers itself)
+    std::map<std::string, std::vector<std::function<void(const std::shared_ptr<void>&)> > > callbacks;
     static ShimState& get() { static ShimState s; return s; }
 };
 
@@ -62,7 +68,13 @@ struct NodeHandle {
     explicit NodeHandle(const std::string& = "") {}
     template <class M> Publisher advertise(const std::string& topic, int) { Publisher p; p.topic = topic; return p; }
     template <class M, class T, class A>
-    Subscriber subscribe(const std::string&, int, void (T::*)(A), T*) { return Subscriber(); }
+    Subscriber subscribe(const std::string& topic, int, void (T::*fn)(A), T* obj) {
+        ShimState::get().callbacks[topic].push_back([fn, obj](const std::shared_ptr<void>& p) {
+            std::shared_ptr<const M> m = std::static_pointer_cast<const M>(p);
+            (obj->*fn)(m);
+        });
+        return Subscriber();
+    }
 };
 
 inline void init(int, char**, const std::string&) {}
@@ -78,11 +90,26 @@ template <class M> std::shared_ptr<const M> shim_last(const std::string& topic) 
     return std::static_pointer_cast<const M>(it->second);
 }
 inline long shim_count(const std::string& topic) { return ShimState::get().count[topic]; }
+// hands `msg` to every callback subscribed to `topic`; returns how many there were
+inline int shim_deliver(const std::string& topic, const std::shared_ptr<void>& msg) {
+    ShimState& s = ShimState::get();
+    auto it = s.callbacks.find(topic);
+    if (it == s.callbacks.end()) return 0;
+    for (auto& cb : it->second) cb(msg);
+    return (int)it->second.size();
+}
+// the last message published on `topic`, type-erased (for shim_deliver)
+inline std::shared_ptr<void> shim_last_raw(const std::string& topic) {
+    ShimState& s = ShimState::get();
+    auto it = s.last.find(topic);
+    return it == s.last.end() ? std::shared_ptr<void>() : it->second;
+}
 
 }  // namespace ros
 
 #define ROS_INFO(...)  do { } while (0)
 #define ROS_ERROR(...) do { ros::ShimState::get().errors += 1; } while (0)
+#define ROS_FATAL(...) do { ros::ShimState::get().errors += 1; } while (0)
 
 namespace std_msgs {
 struct Header { ros::Time stamp; std::string frame_id; unsigned seq = 0; };
@@ -140,6 +167,10 @@ template <class T> struct GuardedVec {
     GuardedVec() : v(GUARD, static_cast<T>(0x40000000)) {}
     void assign(size_t n, T x) { v.assign(GUARD + n, x); for (int g = 0; g < GUARD; ++g) v[g] = static_cast<T>(0x40000000); }
     size_t size() const { return v.size() - GUARD; }
+    typename std::vector<T>::iterator begin() { return v.begin() + GUARD; }
+    typename std::vector<T>::iterator end() { return v.end(); }
+    typename std::vector<T>::const_iterator begin() const { return v.begin() + GUARD; }
+    typename std::vector<T>::const_iterator end() const { return v.end(); }
     T& operator[](long i) { return v[GUARD + i]; }
     const T& operator[](long i) const { return v[GUARD + i]; }
 };

@@ -1,7 +1,9 @@
 // Shared helpers of the four ROS1 node shells.  The shells keep the reference's topic contract (names,
 // types, queue sizes, frame ids: SURVEY.md 8b) and hand the numerical work to liblego_b200.so through include/lego_b200.h.
-// NOT COMPILED OR TESTED IN THIS REPOSITORY'S ENVIRONMENT: ROS1 / catkin / PCL are absent from the build image.  The calls
-// into the C ABI are the ones tests/test_gpu_stage_api.py exercises through ctypes.
+// ROS1 / catkin / PCL are absent from this repository's build image, so a catkin build has never run.  The sources ARE compiled
+// here, unmodified, against the stand-in ROS / PCL headers the reference's own nodes are compiled with (oracle/shim,
+// oracle/shell_harness.cpp -> oracle/_ref/liblego_shells_<cfg>.so) and driven message by message next to the reference's nodes:
+// tests/test_gpu_ros_shells.py compares every topic (messages published, frame ids, stamps, payloads).
 #pragma once
 #include <ros/ros.h>
 #include <nav_msgs/Odometry.h>

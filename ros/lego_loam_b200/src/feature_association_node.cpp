@@ -1,5 +1,5 @@
 // featureAssociation node shell (reference featureAssociation.cpp:186-206 topic wiring, 461-489 handlers, 1817-1860
-// runFeatureAssociation, 1727-1744 publishOdometry, 1796-1813 cloud publication).  Uncompiled here, see common.h.
+// runFeatureAssociation, 1727-1744 publishOdometry, 1796-1813 cloud publication).  Compiled and driven through oracle/shim here, see common.h.
 #include "common.h"
 
 class FeatureAssociationNode {

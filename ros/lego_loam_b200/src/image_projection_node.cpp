@@ -1,9 +1,8 @@
 // imageProjection node shell: /velodyne_points -> /segmented_cloud, /segmented_cloud_info, /outlier_cloud
-// (reference imageProjection.cpp:86-107 topic wiring, 181-197 cloudHandler, 463-478 publishCloud).  Uncompiled here, see common.h.
+// (reference imageProjection.cpp:86-107 topic wiring, 181-197 cloudHandler, 463-478 publishCloud).  Compiled and driven through oracle/shim here, see common.h.
 #include "common.h"
 
-struct PointXYZIR { PCL_ADD_POINT4D; PCL_ADD_INTENSITY; uint16_t ring; EIGEN_MAKE_ALIGNED_OPERATOR_NEW } EIGEN_ALIGN16;
-POINT_CLOUD_REGISTER_POINT_STRUCT(PointXYZIR, (float, x, x)(float, y, y)(float, z, z)(float, intensity, intensity)(uint16_t, ring, ring))
+// PointXYZIR (x y z intensity + uint16 ring) comes from the reference's utility.h:153-165, which common.h includes.
 
 class ImageProjectionNode {
 public:

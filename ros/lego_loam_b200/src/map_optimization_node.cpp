@@ -3,7 +3,7 @@
 // thread).  The global map the reference serves from visualizeGlobalMapThread is served from the node's own loop (a
 // lego_mo handle belongs to one thread): /laser_cloud_surround every 5 s while someone listens, and the four PCD files
 // of mapOptmization.cpp:729-755 at shutdown, all through lego_mo_global_map / lego_write_pcd_ascii.
-// Uncompiled here, see common.h.
+// Compiled and driven through oracle/shim here, see common.h.
 #include "common.h"
 
 class MapOptimizationNode {

@@ -1,4 +1,4 @@
-// transformFusion node shell (reference transformFusion.cpp:66-76 topic wiring, 181-241 handlers).  Uncompiled here, see common.h.
+// transformFusion node shell (reference transformFusion.cpp:66-76 topic wiring, 181-241 handlers).  Compiled and driven through oracle/shim here, see common.h.
 #include "common.h"
 
 class TransformFusionNode {

@@ -1,0 +1,72 @@
+"""The four ROS1 node shells of the port (ros/lego_loam_b200/src/*.cpp) against the reference's own nodes, topic by topic.
+ROS, catkin and PCL do not exist in this image, so both sides are compiled against the same stand-in headers (oracle/shim): the
+reference's node sources unmodified (oracle/ref_harness.cpp, its own cloudHandler / runFeatureAssociation / run methods), the
+shells unmodified (oracle/shell_harness.cpp) and linked to liblego_b200.so.  Both receive the same /velodyne_points messages;
+every topic of SURVEY.md section 8b is compared: name published at all, number of messages, frame_id, child_frame_id, stamp,
+payload (clouds and cloud_info bit for bit where the stage is bit-exact, poses within 1e-4)."""
+import os
+
+import numpy as np
+import pytest
+
+import lego_loam_b200  # noqa: F401
+from conftest import require_ref
+from lego_loam_b200.synth import SynthSequence
+
+pytestmark = pytest.mark.gpu
+
+BIT_EXACT = ["/segmented_cloud", "/outlier_cloud", "/laser_cloud_sharp", "/laser_cloud_less_sharp", "/laser_cloud_flat"]
+CLOSE = ["/laser_cloud_less_flat", "/laser_cloud_corner_last", "/laser_cloud_surf_last", "/outlier_cloud_last"]
+
+
+def test_node_shells_publish_what_the_reference_nodes_publish():
+    import refpy
+    sensor = "vlp16"
+    require_ref(sensor)
+    if not os.path.exists(refpy.shells_so(sensor)):
+        pytest.skip("oracle/_ref/liblego_shells_%s.so not built" % sensor)
+    seq = SynthSequence(sensor, seed=21, scene="street", speed=4.0)
+    ref = refpy.RefPipeline(sensor, snapshots=False)
+    ref.set_verbatim(True)                      # the reference's own driver methods, publishers included
+    refpy.ref_subscribe_all(ref, True)          # getNumSubscribers() != 0: the "if subscribed" topics are published too
+    sh = refpy.ShellPipeline(sensor, subscribe_all=True)
+    mapped = 0
+    for k in range(30):
+        xyzi, ring = seq.scan(k)
+        rf = ref.feed(xyzi, ring, seq.stamp(k), stages=15)
+        sf = sh.feed(xyzi, ring, seq.stamp(k))
+        assert sf >= 0 and sh.errors() == 0, "scan %d: a node shell reported an error" % k
+        assert bool(sf & 8) == bool(rf & 8), "scan %d: mapping ran in one pipeline only (%d vs %d)" % (k, sf, rf)
+        mapped += bool(rf & 8)
+        tag = "scan %d " % k
+        S = 0
+        for topic in BIT_EXACT + CLOSE:
+            a, b = sh.topic(topic), refpy.ref_topic(ref, topic)
+            assert (a is None) == (b is None), tag + topic + ": published by one side only"
+            if a is None:
+                continue
+            assert a["count"] == b["count"], tag + topic + ": %d vs %d messages" % (a["count"], b["count"])
+            assert a["frame_id"] == b["frame_id"] and a["stamp"] == b["stamp"], tag + topic + ": header %r %r vs %r %r" % (a["frame_id"], a["stamp"], b["frame_id"], b["stamp"])
+            assert a["values"].shape == b["values"].shape, tag + topic + ": %d vs %d values" % (len(a["values"]), len(b["values"]))
+            if topic in BIT_EXACT:
+                assert np.array_equal(a["values"], b["values"]), tag + topic
+            else:
+                assert np.allclose(a["values"], b["values"], rtol=1e-5, atol=2e-4), tag + topic
+            if topic == "/segmented_cloud":
+                S = len(a["values"]) // 4
+        a, b = sh.topic(refpy.TOPIC_INFO, S), refpy.ref_topic(ref, refpy.TOPIC_INFO, S)
+        assert a is not None and b is not None and a["count"] == b["count"] and a["stamp"] == b["stamp"], tag + "cloud_info header"
+        assert np.array_equal(a["values"], b["values"]), tag + "cloud_info payload"
+        for topic in refpy.TOPICS_ODOMETRY:
+            a, b = sh.topic(topic), refpy.ref_topic(ref, topic)
+            assert (a is None) == (b is None), tag + topic + ": published by one side only"
+            if a is None:
+                continue
+            assert a["count"] == b["count"], tag + topic + ": %d vs %d messages" % (a["count"], b["count"])
+            assert (a["frame_id"], a["child_frame_id"], a["stamp"]) == (b["frame_id"], b["child_frame_id"], b["stamp"]), \
+                tag + topic + ": header %r vs %r" % ((a["frame_id"], a["child_frame_id"], a["stamp"]), (b["frame_id"], b["child_frame_id"], b["stamp"]))
+            assert np.max(np.abs(a["values"] - b["values"])) < 1e-4, tag + topic + ": %s vs %s" % (a["values"], b["values"])
+    assert mapped >= 6
+    final = sh.topic("/integrated_to_init")
+    assert final is not None and np.abs(final["values"][4:7]).max() > 0.5, "the fused pose did not move"
+    sh.close(); ref.close()
