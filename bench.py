@@ -63,7 +63,8 @@ def parse_args():
     ap.add_argument("--secondary", default="auto", help="second sensor measured inside the same line at N=1 ('auto' = hdl64 when --sensor vlp16, 'none')")
     ap.add_argument("--threads", type=int, default=-1, help="host threads submitting the handles' steps (-1 = one per handle for --workload loop, whose mapping "
                     "calls end with a stream synchronisation, else 1; ctypes releases the GIL inside the C ABI)")
-    ap.add_argument("--host-copies", type=int, default=0, help="e2e arm: 0 = one cudaMemcpyAsync per lane (ring channel directly behind the points), 2 = packing kernel over page-locked memory")
+    ap.add_argument("--host-copies", type=int, default=3, help="e2e arm: 3 = the scans are slots of one host arena, neighbouring lanes share a cudaMemcpyAsync (src_on_device 3); "
+                    "0 = one cudaMemcpyAsync per lane (ring channel directly behind the points); 2 = packing kernel over page-locked memory")
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-e2e", action="store_true")
     ap.add_argument("--no-latency", action="store_true")
@@ -326,6 +327,7 @@ def gather_counts(pl, params, lanes):
         "mo_search_kernel": search / 10.0,
         "mo_residual_kernel": s2m / 10.0,
         "mo_solve_kernel": 0.0,
+        "mo_lm_persistent_kernel": rerank + search + s2m,   # one launch = all iterations of a mapping call
         "mo_save_keyframe_kernel": 32 * int(sc[0] + sc[1] + sc[2]),
     }
     c["map"] = {"cornerFromMap": int(mc[0]), "surfFromMap": int(mc[1]), "cornerFromMapDS": int(mc[2]), "surfFromMapDS": int(mc[3]),
@@ -544,7 +546,10 @@ def run_b200(args, sensor, lanes, workload):
         # the scans sit in page-locked host memory, every lane's ring channel directly behind its points: one cudaMemcpyAsync per
         # lane (input mode 0).  --host-copies 2 = input mode 2, one packing kernel per scan pulls the lanes over PCIe (measured
         # slower: SM-initiated PCIe reads reach ~23 GB/s on this box, the copy engine ~2x that with one copy per lane)
-        host_scan, _ = make_scan_fn(inp.blob.ctypes.data, 2 if args.host_copies == 2 else 0)
+        # at 2-3 us of copy-engine time per copy, 592 copies per scan cap the link at ~34 GB/s).  --host-copies 3 (default) = input
+        # mode 3: the caller declares the lane blocks slots of one arena, lanes in neighbouring slots travel in one copy with the
+        # unused tail of each slot (counted in h2d_bytes_per_step)
+        host_scan, _ = make_scan_fn(inp.blob.ctypes.data, args.host_copies if args.host_copies in (2, 3) else 0)
         # Streaming use of the C ABI: scan t is submitted from pinned host memory (one H2D copy per lane of exactly its
         # points on the handle's copy stream), its pose read-back is enqueued behind it, and the result of scan t-4 is
         # collected while scans t-3 .. t are in flight (a mapping scan lasts as long as several uploads, so less slack
@@ -604,15 +609,29 @@ def run_b200(args, sensor, lanes, workload):
         h2d_gbs = 3 * src.numel() / (ev0.elapsed_time(ev1) * 1e-3) / 1e9
         del probe
         pts_timed = int(sum(int(inp.npts[s][seq].sum()) for s in range(win.first_timed, win.T)))
+        moved = pts_timed * (fpp * 4 + 2)
+        copies_per_scan = L
+        if args.host_copies == 3:
+            # a run = lanes of one handle in consecutive slots; it moves whole slots except for its last lane
+            last = np.ones(L, bool)
+            last[:-1] = seq[1:] != seq[:-1] + 1
+            last[np.asarray(bounds[1:], np.int64) - 1] = True
+            copies_per_scan = int(last.sum())
+            moved = int(sum(int(inp.npts[s][seq[last]].sum()) for s in range(win.first_timed, win.T))) * (fpp * 4 + 2) \
+                + int((~last).sum()) * inp.slot * (win.T - win.first_timed)
         e2e = {"value": L * K * S * world / e2e_s, "unit": UNIT,
-               "h2d_bytes_per_step": int(pts_timed * (fpp * 4 + 2) / K + S * L * (16 + 4)),
+               "h2d_bytes_per_step": int(moved / K + S * L * (16 + 4)),
+               "h2d_copies_per_scan": copies_per_scan,
                "d2h_bytes_per_step": int(S * L * 19 * 4),
-               "h2d_bytes_per_scan": round(pts_timed * (fpp * 4 + 2) / float(K * S * L), 1),
+               "h2d_bytes_per_scan": round(moved / float(K * S * L), 1),
                "input_format": "x y z float32 + ring uint16 (14 B/point), only the npts points of each lane" if fpp == 3 else
                                "x y z intensity float32 + ring uint16 (18 B/point), only the npts points of each lane",
                "h2d_path": "packing kernel reading page-locked host memory (lego_pipeline_step_lanes, src_on_device = 2)" if args.host_copies == 2 else
+                           "the lanes' scans are fixed-size slots of one pinned arena, ring channel directly behind the points: lanes in neighbouring slots "
+                           "share one cudaMemcpyAsync, unused slot tails included in the byte count (lego_pipeline_step_lanes, src_on_device = 3)"
+                           if args.host_copies == 3 else
                            "one cudaMemcpyAsync per lane: the ring channel sits directly behind the lane's points (lego_pipeline_step_lanes, src_on_device = 0)",
-               "h2d_gbs_achieved": round(pts_timed * (fpp * 4 + 2) / e2e_s / 1e9, 1),
+               "h2d_gbs_achieved": round(moved / e2e_s / 1e9, 1),
                "seconds": e2e_s, "pcie_h2d_gbs_plain_copy": round(h2d_gbs, 1), "poses_equal_device_arm": same,
                "mode": "streaming: up to 5 scans in flight per handle, the poses of scan k are collected after scan k+4 was submitted"}
 

@@ -181,7 +181,11 @@ int lego_pipeline_step(lego_pipeline* h, const float* xyzi, const uint16_t* ring
  * 2 is an error the call cannot detect (the kernel faults).
  * Host sources: exactly npts[l] * (4 * floats_per_point + 2) bytes per lane cross PCIe.  With src_on_device = 0, a lane whose
  * ring channel starts exactly where its points end (ring[l] == (char*)xyz[l] + npts[l] * 4 * floats_per_point) is moved
- * with ONE copy instead of two, which matters at hundreds of lanes (the copy engine spends 2-3 us per copy).
+ * with ONE copy instead of two, which matters at hundreds of lanes (the copy engine spends 2-3 us per copy), and lanes
+ * whose blocks touch exactly (xyz[l+1] starts where ring[l] ends) share one copy.  3 = host memory like 0, and the caller
+ * states that all lane blocks are slots of ONE allocation (a receive arena): consecutive lanes that lie less than 96 KB
+ * apart are then moved by one copy TOGETHER WITH THE BYTES BETWEEN THEM (those bytes must be readable, which only the
+ * caller can know; they are never used).  With slots of a fixed size this turns hundreds of copies per scan into a few.
  *
  * Input lifetime (both step forms): host buffers are copied asynchronously on the handle's copy stream -- they must
  * stay valid and unmodified until lego_pipeline_input_wait() returns (or any later synchronising call on the handle:

@@ -196,8 +196,9 @@ class Pipeline:
 
     def step_lanes(self, xyz_ptrs, ring_ptrs, npts, stamps, floats_per_point=4, stage_mask=7, on_device=False):
         """lego_pipeline_step_lanes: xyz_ptrs / ring_ptrs = uint64[lanes] tables of per-lane addresses; on_device False / 0 =
-        host memory, True / 1 = device memory, 2 = page-locked device-mapped host memory (packing kernel).  Only npts[l]
-        points of lane l are read."""
+        host memory, True / 1 = device memory, 2 = page-locked device-mapped host memory (packing kernel), 3 = host memory whose
+        lane blocks are slots of one allocation (neighbouring lanes share a copy, the bytes between them are read too).
+        Otherwise only npts[l] points of lane l are read."""
         npts = np.ascontiguousarray(npts, np.int32)
         stamps = np.ascontiguousarray(stamps, np.float64)
         xp = np.ascontiguousarray(xyz_ptrs, np.uint64)

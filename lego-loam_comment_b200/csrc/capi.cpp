@@ -98,8 +98,8 @@ int lego_pipeline_step_lanes(lego_pipeline* h, const float* const* xyz, const ui
     if (e.c.useRing && !ring) return LEGO_ERR_ARG;
     LEGO_TRY
     h->stamps.assign(stamps, stamps + e.c.L);
-    if (src_on_device < 0 || src_on_device > 2) { lego::set_last_error("src_on_device must be 0, 1 or 2"); return LEGO_ERR_ARG; }
-    if (stage_mask & 1) e.uploadScanLanes(xyz, ring, npts, floats_per_point, src_on_device == 1, src_on_device == 2);
+    if (src_on_device < 0 || src_on_device > 3) { lego::set_last_error("src_on_device must be 0, 1, 2 or 3"); return LEGO_ERR_ARG; }
+    if (stage_mask & 1) e.uploadScanLanes(xyz, ring, npts, floats_per_point, src_on_device == 1, src_on_device == 2, src_on_device == 3);
     return run_stages(h, stage_mask);
     LEGO_CATCH
 }

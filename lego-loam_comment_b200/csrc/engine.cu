@@ -237,7 +237,7 @@ void Engine::uploadScan(const float* xyzi, const uint16_t* ring, const int* npts
 // One pointer per lane, floats_per_point = 4 (x y z intensity) or 3 (x y z packed: the reference never reads the input
 // intensity, imageProjection.cpp:248-255 overwrites it).  Host sources: npts[l] points of lane l cross PCIe, nothing else.
 void Engine::uploadScanLanes(const float* const* xyz, const uint16_t* const* ring, const int* npts, int floats_per_point, bool src_on_device,
-                             bool host_is_pinned) {
+                             bool host_is_pinned, bool host_is_arena) {
     if (floats_per_point != 3 && floats_per_point != 4) throw std::invalid_argument("floats_per_point must be 3 or 4");
     for (int l = 0; l < c.L; ++l) if (!xyz[l] || (c.useRing && (!ring || !ring[l]))) throw std::invalid_argument("null lane pointer");
     const int b = beginUpload(npts, src_on_device);
@@ -264,17 +264,38 @@ void Engine::uploadScanLanes(const float* const* xyz, const uint16_t* const* rin
     const float4** hx = reinterpret_cast<const float4**>(h_pin[b]);
     const uint16_t** hr = reinterpret_cast<const uint16_t**>(h_pin[b] + tbl);
     const size_t psz = sizeof(float) * (size_t)floats_per_point;
+    const size_t slot = (size_t)c.Pcap * 18;               // bytes of d_in_blob per lane
+    // A copy carries 2-3 us of fixed cost on the copy engine whatever its size (at 592 lanes x 2 channels that halves the
+    // PCIe rate).  So (1) a lane whose ring channel directly follows its points moves with ONE copy, and (2) lanes whose
+    // blocks follow one another in the caller's memory move TOGETHER, as long as the run stays inside the device slots
+    // of its own lanes: the device image of a run is the host image, so lane l sits at run base + (host address of l -
+    // host address of the run's first lane).  Without the caller's word that the lanes are slots of ONE allocation
+    // (host_is_arena) only lanes that touch exactly are joined: the bytes between two blocks may not be readable.
+    const size_t maxGap = host_is_arena ? 96 * 1024 : 0;   // break-even of one more copy at ~50 GB/s
+    const bool blobOk = slot % (floats_per_point == 4 ? 16 : 4) == 0;
+    const size_t align = floats_per_point == 4 ? 16 : 4;   // float4 loads of x y z i
+    int run0 = -1; const char* runHost = nullptr; size_t runLen = 0;
+    auto flush = [&]() {
+        if (run0 >= 0 && runLen > 0)
+            cuda_check(cudaMemcpyAsync(d_in_blob[b] + (size_t)run0 * slot, runHost, runLen, cudaMemcpyHostToDevice, copyStream), "upload lanes");
+        run0 = -1; runLen = 0;
+    };
     for (int l = 0; l < c.L; ++l) {
         if (src_on_device) {
             hx[l] = reinterpret_cast<const float4*>(xyz[l]);
             hr[l] = ring ? ring[l] : nullptr;
-        } else if (ring && reinterpret_cast<const char*>(ring[l]) == reinterpret_cast<const char*>(xyz[l]) + psz * npts[l]) {
-            // the ring channel directly follows the points in the caller's buffer: ONE copy moves the lane (a copy carries
-            // 2-3 us of fixed cost on the copy engine, which at 592 lanes x 2 channels halves the PCIe rate)
-            char* blob = d_in_blob[b] + (size_t)l * c.Pcap * 18;
+        } else if (ring && blobOk && reinterpret_cast<const char*>(ring[l]) == reinterpret_cast<const char*>(xyz[l]) + psz * npts[l]) {
+            const char* p = reinterpret_cast<const char*>(xyz[l]);
+            const size_t len = (psz + sizeof(uint16_t)) * (size_t)npts[l];
+            bool joined = false;
+            if (run0 >= 0 && p >= runHost + runLen) {
+                const size_t off = (size_t)(p - runHost);
+                if (off - runLen <= maxGap && off % align == 0 && off + len <= (size_t)(l - run0 + 1) * slot) { runLen = off + len; joined = true; }
+            }
+            if (!joined) { flush(); run0 = l; runHost = p; runLen = len; }
+            char* blob = d_in_blob[b] + (size_t)run0 * slot + (size_t)(p - runHost);
             hx[l] = reinterpret_cast<const float4*>(blob);
             hr[l] = reinterpret_cast<const uint16_t*>(blob + psz * npts[l]);
-            if (npts[l] > 0) cuda_check(cudaMemcpyAsync(blob, xyz[l], (psz + sizeof(uint16_t)) * npts[l], cudaMemcpyHostToDevice, copyStream), "upload lane");
         } else {
             hx[l] = d_in_xyzi[b] + (size_t)l * c.Pcap;
             hr[l] = d_in_ring[b] + (size_t)l * c.Pcap;
@@ -284,6 +305,7 @@ void Engine::uploadScanLanes(const float* const* xyz, const uint16_t* const* rin
             }
         }
     }
+    flush();
     finishUpload(b, npts, floats_per_point);
 }
 

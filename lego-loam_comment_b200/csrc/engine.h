@@ -284,7 +284,7 @@ public:
     // ---- ImageProjection (names follow imageProjection.cpp) ----
     void uploadScan(const float* xyzi, const uint16_t* ring, const int* npts, int stride_points, bool src_on_device);
     void uploadScanLanes(const float* const* xyz, const uint16_t* const* ring, const int* npts, int floats_per_point, bool src_on_device,
-                         bool host_is_pinned = false);
+                         bool host_is_pinned = false, bool host_is_arena = false);
     void inputWait();             // input buffers of the last step may be refilled once this returns
     void inputConsumed();         // marks the point after which the current input buffers may be overwritten
     void projectPointCloud();     // + findStartEndAngle
@@ -397,6 +397,8 @@ public:
     cudaEvent_t moStaged[2] = {nullptr, nullptr};
     MoRecord* moRecordsHost = nullptr;   // pinned [L]
     cudaEvent_t moRecordsReady = nullptr;
+    bool moPersistentLm = true;      // LEGO_LM_PERSISTENT=0: ten launches of {re-rank, search, fit, solve} over all lanes instead of one persistent CTA per lane
+    int moLmThreads = 512;
     bool moKnnCache = true;          // LEGO_KNN_CACHE=0 searches the voxel hash in every LM iteration (parity check of the cache)
     bool moRecordsPending = false;
     bool moLastAny = false;

@@ -21,6 +21,10 @@ __global__ void mo_search_kernel(MoDev m, int iter);
 __global__ void mo_residual_kernel(MoDev m);
 __global__ void mo_solve_kernel(MoDev m, int iter);
 __global__ void mo_save_keyframe_kernel(MoDev m);
+__global__ void mo_lm_persistent_kernel(MoDev m, int useCache);
+
+int mo_lm_threads();                 // map_optimization.cu: block size the persistent LM kernel was compiled for
+cudaError_t mo_lm_set_smem(size_t bytes);
 
 static int env_int(const char* name, int dflt) {
     const char* v = std::getenv(name);
@@ -49,6 +53,15 @@ void Engine::allocMapOptimization() {
     const size_t L = c.L, N = c.N, R = c.R;
     mo.maxKeyFrames = params.maxKeyFrames > 0 ? params.maxKeyFrames : env_int("LEGO_MAX_KEYFRAMES", 640);
     moKnnCache = env_int("LEGO_KNN_CACHE", 1) != 0;
+    // One persistent block per lane needs lanes to fill the GPU: measured equal to the launch loop at 592 lanes (with 39 launches
+    // fewer per mapping call and no empty tail iterations), 1.7x slower at one lane, where the loop spreads a lane's queries
+    // over 16 blocks.  LEGO_LM_PERSISTENT = 0 / 1 forces either.
+    const int persist = env_int("LEGO_LM_PERSISTENT", -1);
+    moPersistentLm = persist < 0 ? c.L >= 148 : persist != 0;
+    if (moPersistentLm) {
+        moLmThreads = mo_lm_threads();
+        cuda_check(mo_lm_set_smem(sizeof(int) * (size_t)VH_LIST_CELLS * moLmThreads), "smem attr");
+    }
     const size_t perKf = std::min<size_t>(N / 4, 16384);
     mo.poolCap = (int)std::min<size_t>((size_t)mo.maxKeyFrames * perKf, (size_t)INT_MAX / 2);
     mo.maxSel = 256;
@@ -382,6 +395,14 @@ void Engine::mapOptimizationBody(const std::vector<int>& active) {
     { ProfScope ps(this, "vh_build(surfMap)"); launches += vh_build(mo.hashSurfMap, c.L, mo.surfFromMapDS, (size_t)mo.surfDSCap, stream); }
     {   // scan2MapOptimization: <= 10 x {residuals, solve}; a converged lane makes its share of later launches a no-op
         { ProfScope ps(this, "mo_lm_begin_kernel"); mo_lm_begin_kernel<<<(c.L + 63) / 64, 64, 0, stream>>>(mo, c.L); }
+        if (moPersistentLm) {
+            // one persistent CTA per lane runs all iterations (map_optimization.cu: mo_lm_persistent_kernel)
+            const int threads = moLmThreads;
+            const size_t smem = sizeof(int) * (size_t)VH_LIST_CELLS * threads;
+            ProfScope ps(this, "mo_lm_persistent_kernel");
+            mo_lm_persistent_kernel<<<c.L, threads, smem, stream>>>(mo, moKnnCache ? 1 : 0);
+            launches += 2;
+        } else {
         dim3 g(std::min(mo.resBlocks, MO_RES_INFLIGHT), c.L);   // 16 x 256 queries per lane in flight; larger scans loop
 #ifndef LEGO_MO_GRID_LATER
 #define LEGO_MO_GRID_LATER 8
@@ -405,7 +426,8 @@ void Engine::mapOptimizationBody(const std::vector<int>& active) {
             }
             { ProfScope ps(this, "mo_solve_kernel"); mo_solve_kernel<<<c.L, 32, 0, stream>>>(mo, iter); }
         }
-        launches += 40;
+        launches += 41;
+        }
     }
     if (loopMode()) saveKeyFramesHostGraph(active);   // lanes whose graph holds a loop factor: gate + iSAM update on the host
     { ProfScope ps(this, "mo_save_keyframe_kernel"); mo_save_keyframe_kernel<<<c.L, 256, 0, stream>>>(mo); }

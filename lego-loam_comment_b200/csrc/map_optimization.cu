@@ -282,20 +282,9 @@ __global__ void __launch_bounds__(MO_RES_THREADS, 4) mo_residual_kernel(MoDev m)
 }
 
 // LMOptimization (mapOptmization.cpp:1229-1327) + the loop control of scan2MapOptimization + transformUpdate (463-496)
-__global__ void __launch_bounds__(32) mo_solve_kernel(MoDev m, int iter) {
-    const int lane = blockIdx.x, lid = threadIdx.x;
-    if (!m.state[lane * 16 + 6]) return;
-    __shared__ double s[MO_ACC];
-    const int nQ = m.scanCounts[lane * 8 + 0] + m.scanCounts[lane * 8 + 4];
-    const int nb = (nQ + MO_RES_THREADS - 1) / MO_RES_THREADS;
-    if (lid < MO_ACC) {
-        double t = 0.0;
-        const double* p = m.partials + (size_t)lane * m.resBlocks * (MO_RES_THREADS / 32) * MO_ACC + lid;
-        for (int b = 0; b < nb * (MO_RES_THREADS / 32); ++b) t += p[(size_t)b * MO_ACC];
-        s[lid] = t;
-    }
-    __syncwarp();
-    if (lid != 0) return;
+// The solve of one LM iteration for one lane from the 28 summed accumulators s (LMOptimization, loop control of
+// scan2MapOptimization, transformUpdate).  One thread.  Returns 1 when the lane is finished.
+__device__ inline int mo_solve_lane(MoDev& m, int lane, int iter, const double* s) {
     float* T = m.transformTobeMapped + lane * 6;
     float* matP = m.matP + lane * 36;
     const int rows = (int)s[27];
@@ -327,7 +316,8 @@ __global__ void __launch_bounds__(32) mo_solve_kernel(MoDev m, int iter) {
     }
     m.knnMissCount[lane] = 0;
     m.state[lane * 16 + 3] = iter + 1; m.state[lane * 16 + 4] = rows;
-    if (done || iter == 9) {
+    const int finished = (done || iter == 9) ? 1 : 0;
+    if (finished) {
         m.state[lane * 16 + 6] = 0;
         m.records[lane].iters = iter + 1;
         // transformUpdate (mapOptmization.cpp:463-496); the host interpolated the IMU roll / pitch at the end of the sweep
@@ -338,7 +328,154 @@ __global__ void __launch_bounds__(32) mo_solve_kernel(MoDev m, int iter) {
         }
         for (int i = 0; i < 6; ++i) { m.transformBefMapped[lane * 6 + i] = m.transformSum[lane * 6 + i]; m.transformAftMapped[lane * 6 + i] = T[i]; }
     }
+    return finished;
 }
+
+__global__ void __launch_bounds__(32) mo_solve_kernel(MoDev m, int iter) {
+    const int lane = blockIdx.x, lid = threadIdx.x;
+    if (!m.state[lane * 16 + 6]) return;
+    __shared__ double s[MO_ACC];
+    const int nQ = m.scanCounts[lane * 8 + 0] + m.scanCounts[lane * 8 + 4];
+    const int nb = (nQ + MO_RES_THREADS - 1) / MO_RES_THREADS;
+    if (lid < MO_ACC) {
+        double t = 0.0;
+        const double* p = m.partials + (size_t)lane * m.resBlocks * (MO_RES_THREADS / 32) * MO_ACC + lid;
+        for (int b = 0; b < nb * (MO_RES_THREADS / 32); ++b) t += p[(size_t)b * MO_ACC];
+        s[lid] = t;
+    }
+    __syncwarp();
+    if (lid != 0) return;
+    mo_solve_lane(m, lane, iter, s);
+}
+
+// scan2MapOptimization (mapOptmization.cpp:1329-1350) as ONE persistent CTA per lane: all <= 10 LM iterations -- re-rank the
+// cached neighbours, search the misses, fit the rows, solve -- run back to back with block barriers instead of kernel
+// boundaries.  The per-iteration kernels above sweep over every lane in every launch: each lane's map (hash + points,
+// ~1.6 MB) is evicted between a lane's iterations and fetched from DRAM again (ncu: iteration 1 reads as many bytes as
+// iteration 0), and a mapping call costs 40 launches of which the tail is empty.  Here a lane's iterations touch its map while it
+// is still in L2 / L1, a converged lane frees its SM at once, and the call is two launches.  Same device functions, and the
+// rows are summed over the same 32-query slices in the same order as mo_residual_kernel / mo_solve_kernel do
+// (partials[slice] by the same shuffle butterfly, slices added up in index order), so the poses are bit-identical.
+#ifndef LEGO_MO_LM_THREADS
+#define LEGO_MO_LM_THREADS 512
+#endif
+#ifndef LEGO_MO_LM_MINBLOCKS
+#define LEGO_MO_LM_MINBLOCKS (1024 / LEGO_MO_LM_THREADS)
+#endif
+constexpr int MO_LM_THREADS = LEGO_MO_LM_THREADS;
+__global__ void __launch_bounds__(MO_LM_THREADS, LEGO_MO_LM_MINBLOCKS) mo_lm_persistent_kernel(MoDev m, int useCache) {
+    extern __shared__ int cellList[];   // [VH_LIST_CELLS][MO_LM_THREADS]: per thread, the non-empty cells around its query
+    __shared__ float sTrig[6];
+    __shared__ int sDone, sMiss, sNext;
+    __shared__ double sSum[MO_ACC];
+    const int lane = blockIdx.x, tid = threadIdx.x, lid = tid & 31, warp = tid >> 5;
+    if (!m.state[lane * 16 + 6]) return;
+    const int nCorner = m.scanCounts[lane * 8 + 0], nSurf = m.scanCounts[lane * 8 + 4], nQ = nCorner + nSurf;
+    const float* T = m.transformTobeMapped + lane * 6;
+    const VhLane vhC = vh_lane(m.hashCornerMap, lane), vhS = vh_lane(m.hashSurfMap, lane);
+    const float4* mapC = m.cornerFromMapDS + (size_t)lane * m.cornerDSCap;
+    const float4* mapS = m.surfFromMapDS + (size_t)lane * m.surfDSCap;
+    const float4* qC = m.cornerLastDS + (size_t)lane * m.scanCornerCap;
+    const float4* qS = m.surfTotalLastDS + (size_t)lane * (m.scanSurfCap + m.scanOutlierCap);
+    const size_t slotBase = (size_t)lane * m.resBlocks * MO_RES_THREADS;
+    const int nSlices = (nQ + 31) / 32;
+    for (int iter = 0; iter < 10; ++iter) {
+        if (tid < 6) sTrig[tid] = pm::sincosf_glibc(T[tid >> 1], (tid & 1) ^ 1);   // cos, sin, cos, sin, ... of the pose of this iteration
+        if (tid == 0) { sMiss = 0; sNext = 0; }
+        __syncthreads();
+        MapSinCos sc;
+        sc.cRoll = sTrig[0]; sc.sRoll = sTrig[1]; sc.cPitch = sTrig[2]; sc.sPitch = sTrig[3]; sc.cYaw = sTrig[4]; sc.sYaw = sTrig[5];
+        sc.tX = T[3]; sc.tY = T[4]; sc.tZ = T[5];
+        const bool all = iter == 0 || !useCache;
+        if (!all) {   // re-rank the cached candidates; a query whose cache cannot prove the answer goes onto the miss list
+            for (int base = 0; base < nQ; base += MO_LM_THREADS) {
+                const int q = base + tid;
+                bool miss = false;
+                if (q < nQ) {
+                    const bool corner = q < nCorner;
+                    const float4 ps = map_transform(sc, corner ? qC[q] : qS[q - nCorner]);
+                    const float4 meta = m.knnMeta[slotBase + q];
+                    int cand[VH_CACHE_K];
+#pragma unroll
+                    for (int j = 0; j < VH_CACHE_K / 4; ++j) {
+                        const int4 c4 = m.knnCand[(slotBase + q) * (VH_CACHE_K / 4) + j];
+                        cand[4 * j] = c4.x; cand[4 * j + 1] = c4.y; cand[4 * j + 2] = c4.z; cand[4 * j + 3] = c4.w;
+                    }
+                    float d2[5]; int idx[5]; int found;
+                    if (vh_knn5_cached(corner ? mapC : mapS, cand, meta.x, meta.y, meta.z, meta.w, ps.x, ps.y, ps.z, 1.0f, d2, idx, &found))
+                        mo_store_result(m, slotBase + q, found, d2[4], idx);
+                    else miss = true;
+                }
+                const unsigned bal = __ballot_sync(0xffffffffu, miss);
+                if (bal) {
+                    int pos = 0;
+                    if (lid == 0) pos = atomicAdd(&sMiss, __popc(bal));
+                    pos = __shfl_sync(0xffffffffu, pos, 0);
+                    if (miss) m.knnMissList[slotBase + pos + __popc(bal & ((1u << lid) - 1))] = q;
+                }
+            }
+            __syncthreads();
+        }
+        // searches, handed out one at a time: they differ a lot in length
+        const int nSearch = all ? nQ : sMiss;
+        for (int i = atomicAdd(&sNext, 1); i < nSearch; i = atomicAdd(&sNext, 1)) {
+            const int q = all ? i : m.knnMissList[slotBase + i];
+            const bool corner = q < nCorner;
+            const float4 ps = map_transform(sc, corner ? qC[q] : qS[q - nCorner]);
+            float d2[5]; int idx[5]; int cand[VH_CACHE_K]; float rc2;
+            const int found = vh_knn5_fill_flat(corner ? vhC : vhS, ps.x, ps.y, ps.z, 1.0f, d2, idx, cand, &rc2, cellList + tid, MO_LM_THREADS);
+#pragma unroll
+            for (int j = 0; j < VH_CACHE_K / 4; ++j)
+                m.knnCand[(slotBase + q) * (VH_CACHE_K / 4) + j] = make_int4(cand[4 * j], cand[4 * j + 1], cand[4 * j + 2], cand[4 * j + 3]);
+            m.knnMeta[slotBase + q] = make_float4(ps.x, ps.y, ps.z, rc2);
+            mo_store_result(m, slotBase + q, found, d2[4], idx);
+        }
+        __syncthreads();
+        // rows: one warp per 32-query slice, the slice's sums exactly as mo_residual_kernel forms them
+        for (int sl = warp; sl < nSlices; sl += MO_LM_THREADS / 32) {
+            const int q = sl * 32 + lid;
+            double acc[MO_ACC];
+#pragma unroll
+            for (int k = 0; k < MO_ACC; ++k) acc[k] = 0.0;
+            if (q < nQ) {
+                const bool corner = q < nCorner;
+                const float4 o = corner ? qC[q] : qS[q - nCorner];
+                const float4 ps = map_transform(sc, o);
+                const int4 r0 = m.knnRes[(slotBase + q) * 2], r1 = m.knnRes[(slotBase + q) * 2 + 1];
+                const int idx[5] = {r0.x, r0.y, r0.z, r0.w, r1.x};
+                float cx, cy, cz, cd;
+                const bool ok = corner ? mo_corner_residual(mapC, ps, r1.z, __int_as_float(r1.y), idx, &cx, &cy, &cz, &cd)
+                                       : mo_surf_residual(mapS, ps, r1.z, __int_as_float(r1.y), idx, &cx, &cy, &cz, &cd);
+                if (ok) mo_accumulate(acc, sc, o, cx, cy, cz, cd);
+            }
+            double mine = 0.0;
+#pragma unroll
+            for (int k = 0; k < MO_ACC; ++k) {
+                double v = acc[k];
+#pragma unroll
+                for (int o2 = 16; o2 > 0; o2 >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o2);
+                if (lid == k) mine = v;
+            }
+            if (lid < MO_ACC) m.partials[((size_t)lane * m.resBlocks * (MO_RES_THREADS / 32) + sl) * MO_ACC + lid] = mine;
+        }
+        __syncthreads();
+        if (warp == 0) {
+            if (lid < MO_ACC) {   // (the per-iteration kernels also add the all-zero slices that pad the last 256-query block: x + 0.0 = x)
+                double t = 0.0;
+                const double* p = m.partials + (size_t)lane * m.resBlocks * (MO_RES_THREADS / 32) * MO_ACC + lid;
+                for (int b = 0; b < nSlices; ++b) t += p[(size_t)b * MO_ACC];
+                sSum[lid] = t;
+            }
+            __syncwarp();
+            if (lid == 0) sDone = mo_solve_lane(m, lane, iter, sSum);
+        }
+        __syncthreads();
+        if (sDone) break;
+    }
+}
+
+int mo_lm_threads() { return MO_LM_THREADS; }
+cudaError_t mo_lm_set_smem(size_t bytes) { return cudaFuncSetAttribute(mo_lm_persistent_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)bytes); }
 
 // Rot3::RzRyRx(x, y, z) then .roll() / .pitch() / .yaw() (the GTSAM calls of mapOptmization.cpp:1376-1440), in double.
 __device__ inline void rzryrx_round_trip(double x, double y, double z, double* roll, double* pitch, double* yaw) {

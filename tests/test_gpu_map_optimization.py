@@ -141,6 +141,42 @@ def test_neighbour_cache_changes_nothing(monkeypatch):
     plain.close(); cached.close()
 
 
+def test_persistent_lm_kernel_changes_nothing(monkeypatch):
+    """scan2MapOptimization runs as one persistent block per lane (csrc/map_optimization.cu: mo_lm_persistent_kernel); with
+    LEGO_LM_PERSISTENT=0 the same device functions run as ten launches of {re-rank, search, fit, solve} over all lanes.
+    Poses, iteration counts, row counts and the neighbour results must be bit-identical, with lanes of different scan
+    sizes (dropout) and different iteration counts in one step."""
+    sensor = "hdl32"
+    seqs = [SynthSequence(sensor, seed=17, scene="street", speed=6.0, dropout=0.01), SynthSequence(sensor, seed=18, scene="street", speed=2.0),
+            SynthSequence(sensor, seed=19, scene="street", speed=9.0, dropout=0.2)]
+    cap = seqs[0].cap
+    monkeypatch.setenv("LEGO_LM_PERSISTENT", "0")
+    loop = Pipeline(make_params(sensor), lanes=3, max_points=cap)
+    monkeypatch.setenv("LEGO_LM_PERSISTENT", "1")
+    pers = Pipeline(make_params(sensor), lanes=3, max_points=cap)
+    mapped = 0; iters = set()
+    for k in range(30):
+        x = np.zeros((3, cap, 4), np.float32); r = np.zeros((3, cap), np.uint16); n = []
+        for l, q in enumerate(seqs):
+            xyzi, ring = q.scan(k)
+            x[l, :len(xyzi)] = xyzi; r[l, :len(ring)] = ring; n.append(len(xyzi))
+        out = []
+        for pl in (loop, pers):
+            pl.step(x, r, n, [seqs[0].stamp(k)] * 3, stage_mask=7)
+            poses, flags = pl.poses()
+            out.append((poses.copy(), flags.copy(), [pl.download("moState", l).copy() for l in range(3)],
+                        [pl.download("transformTobeMapped", l).copy() for l in range(3)]))
+        assert np.array_equal(out[0][1], out[1][1])
+        assert np.array_equal(out[0][0].view(np.uint32), out[1][0].view(np.uint32)), "scan %d: poses differ" % k
+        for l in range(3):
+            assert np.array_equal(out[0][2][l], out[1][2][l]), "scan %d lane %d: moState %s vs %s" % (k, l, out[0][2][l], out[1][2][l])
+            assert np.array_equal(out[0][3][l].view(np.uint32), out[1][3][l].view(np.uint32))
+            if out[0][1][l] & 8:
+                mapped += 1; iters.add(int(out[0][2][l][3]))
+    assert mapped >= 15 and len(iters) >= 2, "want mapping calls with different iteration counts, got %d calls, iterations %s" % (mapped, sorted(iters))
+    loop.close(); pers.close()
+
+
 def test_incremental_local_map_changes_nothing(monkeypatch):
     """The local map of extractSurroundingKeyFrames is kept sorted on the device and updated per call (key frames that left
     are deleted, the new ones merged in: csrc/incremental_map.cu).  With LEGO_INCR_MAP=0 every call assembles and filters

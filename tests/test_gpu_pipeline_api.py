@@ -105,6 +105,52 @@ def test_step_lanes_one_block_per_lane():
     a.close(); b.close()
 
 
+def test_step_lanes_runs_of_lanes_share_a_copy():
+    """Lanes whose blocks follow one another in host memory travel in one copy (include/lego_b200.h): with src_on_device = 3 the
+    slots of one arena (fixed slot size, unused tails between the lanes), with src_on_device = 0 only blocks that touch
+    exactly -- here with even and odd point counts, so that some joints are 4-byte aligned and some are not.  Same results as
+    separate buffers, x y z and x y z intensity."""
+    sensor = "vlp16"
+    seqs, scans = _scans(sensor, (71, 72, 73, 74), 6)
+    cap = seqs[0].cap
+    for fpp in (3, 4):
+        bpp = 4 * fpp + 2
+        a = Pipeline(make_params(sensor), lanes=4, max_points=cap)
+        b = Pipeline(make_params(sensor), lanes=4, max_points=cap)
+        c = Pipeline(make_params(sensor), lanes=4, max_points=cap)
+        slot = cap * bpp
+        arena = np.zeros(4 * slot + 64, np.uint8)
+        a0 = (-arena.ctypes.data) % 16                   # slot 0 starts 16-byte aligned
+        tight = np.zeros(4 * slot + 64, np.uint8)
+        t0 = (-tight.ctypes.data) % 16
+        for k, four in enumerate(scans):
+            n = np.array([len(p[0]) - (l + k) % 2 for l, p in enumerate(four)], np.int32)
+            xs = [np.ascontiguousarray(p[0][:n[l], :fpp]) for l, p in enumerate(four)]
+            rs = [np.ascontiguousarray(p[1][:n[l]]) for l, p in enumerate(four)]
+            xa, ra, xt, rt = [], [], [], []
+            cur = t0
+            for l in range(4):
+                raw = np.concatenate([xs[l].view(np.uint8).reshape(-1), rs[l].view(np.uint8).reshape(-1)])
+                o = a0 + l * slot
+                arena[o:o + len(raw)] = raw
+                arena[o + len(raw):o + slot] = 0xAB                      # the tail of a slot is never interpreted
+                xa.append(arena.ctypes.data + o); ra.append(arena.ctypes.data + o + int(n[l]) * 4 * fpp)
+                tight[cur:cur + len(raw)] = raw
+                xt.append(tight.ctypes.data + cur); rt.append(tight.ctypes.data + cur + int(n[l]) * 4 * fpp)
+                cur += len(raw)                                          # the next lane touches this one
+            st = [k * 0.1] * 4
+            a.step_lanes(np.array([x.ctypes.data for x in xs], np.uint64), np.array([r.ctypes.data for r in rs], np.uint64), n, st, floats_per_point=fpp)
+            b.step_lanes(np.array(xa, np.uint64), np.array(ra, np.uint64), n, st, floats_per_point=fpp, on_device=3)
+            c.step_lanes(np.array(xt, np.uint64), np.array(rt, np.uint64), n, st, floats_per_point=fpp, on_device=0)
+            a.input_wait(); b.input_wait(); c.input_wait()
+            for other, what in ((b, "arena"), (c, "touching")):
+                assert np.array_equal(a.poses()[0], other.poses()[0]), "%s fpp %d scan %d" % (what, fpp, k)
+                for lane in range(4):
+                    for name in NAMES:
+                        assert _same(a.download(name, lane), other.download(name, lane)), "%s %s lane %d scan %d" % (what, name, lane, k)
+        a.close(); b.close(); c.close()
+
+
 def test_step_lanes_from_page_locked_memory():
     """src_on_device = 2: the lanes' scans sit in page-locked host memory and one packing kernel gathers them (no per-lane
     copies).  Same results as ordinary host memory, with odd point counts and unaligned lane pointers."""
