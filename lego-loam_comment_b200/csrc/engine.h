@@ -397,6 +397,7 @@ public:
     cudaEvent_t moStaged[2] = {nullptr, nullptr};
     MoRecord* moRecordsHost = nullptr;   // pinned [L]
     cudaEvent_t moRecordsReady = nullptr;
+    int odoCluster = 1;              // CTAs (one thread-block cluster) per lane in fa_odometry_cluster_kernel; 1 = fa_odometry_kernel
     bool moPersistentLm = true;      // LEGO_LM_PERSISTENT=0: ten launches of {re-rank, search, fit, solve} over all lanes instead of one persistent CTA per lane
     int moLmThreads = 512;
     bool moKnnCache = true;          // LEGO_KNN_CACHE=0 searches the voxel hash in every LM iteration (parity check of the cache)

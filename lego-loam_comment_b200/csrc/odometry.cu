@@ -28,6 +28,16 @@ VoxelHash Engine::allocHash(int cap, float cell, const int* n, int nStride, int 
 
 void Engine::allocOdometry() {
     const size_t L = c.L, N = c.N, R = c.R;
+    // CTAs per lane of the scan-to-scan LM kernel: a cluster of up to 8 while that still leaves every lane its own SMs (the B200
+    // has 148); LEGO_ODO_CLUSTER = 1 / 2 / 4 / 8 forces a size
+    {
+        int sms = 148;
+        cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, params.device);
+        const char* e = std::getenv("LEGO_ODO_CLUSTER");
+        int want = e && *e ? std::atoi(e) : 0;
+        if (want != 1 && want != 2 && want != 4 && want != 8) { want = 8; while (want > 1 && (int)L * want > sms) want >>= 1; }
+        odoCluster = want;
+    }
     for (int b = 0; b < 2; ++b) { fa.cornerLast[b] = alloc<float4>(L * R * 120); fa.surfLast[b] = alloc<float4>(L * N); }
     fa.lastCounts = alloc<int>(L * 4);
     fa.transformCur = alloc<float>(L * 6); fa.transformSum = alloc<float>(L * 6); fa.matP = alloc<float>(L * 9);
@@ -61,11 +71,12 @@ bool Engine::lookupOdometry(int lane, const std::string& n, void** ptr, int* ele
 }
 
 // ------------------------------------------------------------------------------------------------------------
-__global__ void __launch_bounds__(ODO_THREADS) fa_odometry_kernel(IpDev d, FaDev f, Consts c, int buf) {
+template <bool CL>
+__device__ __forceinline__ void odometry_body(IpDev& d, FaDev& f, Consts& c, int buf, int lane, bool leader) {
     extern __shared__ __align__(16) unsigned char odo_smem[];
     __shared__ OdoShared sh;
     float4* sel = reinterpret_cast<float4*>(odo_smem);
-    const int lane = blockIdx.x, tid = threadIdx.x;
+    const int tid = threadIdx.x;
     if (!f.lmState[lane * 8 + 0]) return;                       // first scan: checkSystemInitialization only
     const int nCornerLast = f.lastCounts[lane * 4 + 0], nSurfLast = f.lastCounts[lane * 4 + 1];
     if (nCornerLast < 10 || nSurfLast < 100) return;            // featureAssociation.cpp:1668-1669
@@ -77,17 +88,30 @@ __global__ void __launch_bounds__(ODO_THREADS) fa_odometry_kernel(IpDev d, FaDev
     int itS = 0, itC = 0;
     {
         const VhLane vh = vh_lane(f.hashSurf, lane);
-        itS = odo_phase<true>(sh, sel, f.flat + lane * R * 24, f.featCounts[lane * 4 + 2], f.surfLast[buf] + lane * N, nSurfLast, vh,
+        itS = odo_phase<true, CL>(sh, sel, f.flat + lane * R * 24, f.featCounts[lane * 4 + 2], f.surfLast[buf] + lane * N, nSurfLast, vh,
                         f.surfInd + lane * R * 24 * 3, c);
     }
     {
         const VhLane vh = vh_lane(f.hashCorner, lane);
-        itC = odo_phase<false>(sh, sel, f.sharp + lane * R * 12, f.featCounts[lane * 4 + 0], f.cornerLast[buf] + lane * R * 120, nCornerLast, vh,
+        itC = odo_phase<false, CL>(sh, sel, f.sharp + lane * R * 12, f.featCounts[lane * 4 + 0], f.cornerLast[buf] + lane * R * 120, nCornerLast, vh,
                          f.cornerInd + lane * R * 12 * 2, c);
     }
+    if (!leader) return;        // every CTA of a cluster ends with the same state; the first one stores it
     if (tid < 6) f.transformCur[lane * 6 + tid] = sh.T[tid];
     if (tid < 9) f.matP[lane * 9 + tid] = sh.matP[tid];
     if (tid == 0) { f.lmState[lane * 8 + 1] = sh.isDegenerate; f.lmState[lane * 8 + 6] = itS; f.lmState[lane * 8 + 7] = itC; }
+}
+
+__global__ void __launch_bounds__(ODO_THREADS) fa_odometry_kernel(IpDev d, FaDev f, Consts c, int buf) {
+    odometry_body<false>(d, f, c, buf, blockIdx.x, true);
+}
+
+// The same kernel for few lanes: one thread-block cluster (2, 4 or 8 CTAs on neighbouring SMs, launch attribute) per lane.
+// One CTA per lane leaves a GPU with fewer lanes than SMs mostly idle while each lane's ~130 searches per refresh queue up
+// behind 16 warps.
+__global__ void __launch_bounds__(ODO_THREADS) fa_odometry_cluster_kernel(IpDev d, FaDev f, Consts c, int buf) {
+    cooperative_groups::cluster_group cluster = cooperative_groups::this_cluster();
+    odometry_body<true>(d, f, c, buf, blockIdx.x / cluster.num_blocks(), cluster.block_rank() == 0);
 }
 
 // publishCloudsLast (featureAssociation.cpp:1759-1789) / checkSystemInitialization (featureAssociation.cpp:1605-1637):
@@ -165,8 +189,23 @@ void Engine::updateTransformation() {
     if (anyImu) { ProfScope ps(this, "fa_imu_initial_guess_kernel"); fa_imu_initial_guess_kernel<<<(c.L + 63) / 64, 64, 0, stream>>>(fa, c); launches += 1; }
     const size_t smem = sizeof(float4) * 24 * (size_t)c.R;
     static bool attr_set = false;
-    if (!attr_set) { cuda_check(cudaFuncSetAttribute(fa_odometry_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 64 * 1024), "smem attr"); attr_set = true; }
-    { ProfScope ps(this, "fa_odometry_kernel"); fa_odometry_kernel<<<c.L, ODO_THREADS, smem, stream>>>(ip, fa, c, faBuf); }
+    if (!attr_set) {
+        cuda_check(cudaFuncSetAttribute(fa_odometry_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 64 * 1024), "smem attr");
+        cuda_check(cudaFuncSetAttribute(fa_odometry_cluster_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 64 * 1024), "smem attr");
+        attr_set = true;
+    }
+    if (odoCluster > 1) {
+        cudaLaunchConfig_t cfg = {};
+        cfg.gridDim = dim3((unsigned)(c.L * odoCluster)); cfg.blockDim = dim3(ODO_THREADS); cfg.dynamicSmemBytes = smem; cfg.stream = stream;
+        cudaLaunchAttribute at[1];
+        at[0].id = cudaLaunchAttributeClusterDimension;
+        at[0].val.clusterDim.x = (unsigned)odoCluster; at[0].val.clusterDim.y = 1; at[0].val.clusterDim.z = 1;
+        cfg.attrs = at; cfg.numAttrs = 1;
+        ProfScope ps(this, "fa_odometry_kernel");
+        cuda_check(cudaLaunchKernelEx(&cfg, fa_odometry_cluster_kernel, ip, fa, c, faBuf), "cluster launch");
+    } else {
+        ProfScope ps(this, "fa_odometry_kernel"); fa_odometry_kernel<<<c.L, ODO_THREADS, smem, stream>>>(ip, fa, c, faBuf);
+    }
     launches += 1;
 }
 

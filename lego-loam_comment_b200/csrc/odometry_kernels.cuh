@@ -4,6 +4,7 @@
 // and the convergence test -- all without leaving the kernel.
 #pragma once
 #include <cfloat>
+#include <cooperative_groups.h>
 #include "engine.h"
 #include "kernel_utils.cuh"
 #include "pose_math.cuh"
@@ -121,11 +122,24 @@ static __device__ unsigned long long g_odo_prof[8];   // ring offsets, transform
 #else
 #define ODO_T(i)
 #endif
-template <bool SURF>
+// CL: the lane is run by a thread-block CLUSTER.  Every CTA of the cluster carries the whole LM state and repeats the cheap parts
+// (TransformToStart of the features, rows, reduction, solve: same instructions on the same data, so all copies of T agree bit
+// for bit), and the correspondence searches -- 3/4 of the kernel's cycles -- are handed out over the warps of ALL its CTAs
+// through one counter in the shared memory of CTA 0 (distributed shared memory).  Results go to `ind` in global memory; the
+// cluster barrier behind the searches orders them before the reads of the other CTAs.
+template <bool CL> __device__ __forceinline__ int odo_ind(const int* ind, int i) { return CL ? __ldcg(ind + i) : ind[i]; }
+template <bool SURF, bool CL>
 __device__ int odo_phase(OdoShared& sh, float4* sel, const float4* __restrict__ feats, int Q,
                           const float4* __restrict__ last, int M, const VhLane& vh, int* ind, const Consts& c) {
     constexpr int K = SURF ? 3 : 2;
     const int tid = threadIdx.x, lid = tid & 31, warp = tid >> 5;
+    int* nextQuery = &sh.nextQuery;
+    bool leader = true;
+    if (CL) {
+        cooperative_groups::cluster_group cluster = cooperative_groups::this_cluster();
+        nextQuery = cluster.map_shared_rank(&sh.nextQuery, 0);
+        leader = cluster.block_rank() == 0;
+    }
     const float maxD2 = c.nearestFeatureSearchSqDist;
 #ifdef LEGO_ODO_PROF
     long long t0_ = clock64();
@@ -136,16 +150,16 @@ __device__ int odo_phase(OdoShared& sh, float4* sel, const float4* __restrict__ 
     for (int iter = 0; iter < 25; ++iter) {
         itersDone = iter + 1;
         for (int q = tid; q < Q; q += ODO_THREADS) sel[q] = pose::transform_to_start(feats[q], sh.T);
-        if (tid == 0) sh.nextQuery = 0;
+        if (tid == 0 && leader) sh.nextQuery = 0;
         // six otherwise idle threads evaluate the iteration's sin / cos (double-precision restatements of glibc) once for the CTA
         if (tid >= ODO_THREADS - 6) { const int k = tid - (ODO_THREADS - 6); sh.trig[k] = pm::sincosf_glibc(sh.T[k >> 1], k & 1); }
-        __syncthreads();
+        if (CL && iter % 5 == 0) cooperative_groups::this_cluster().sync(); else __syncthreads();
         ODO_T(1)
         if (iter % 5 == 0) {
             // one query per warp at a time, handed out dynamically: the searches differ a lot in length
             while (true) {
                 int q = 0;
-                if (lid == 0) q = atomicAdd(&sh.nextQuery, 1);
+                if (lid == 0) q = atomicAdd(nextQuery, 1);
                 q = __shfl_sync(0xffffffffu, q, 0);
                 if (q >= Q) break;
                 float d2near;
@@ -201,7 +215,7 @@ __device__ int odo_phase(OdoShared& sh, float4* sel, const float4* __restrict__ 
                 if (lid == 0) { const long long w2_ = clock64(); atomicAdd(&g_odo_prof2[SURF ? 4 : 0], (unsigned long long)(w1_ - w0_)); atomicAdd(&g_odo_prof2[SURF ? 5 : 1], (unsigned long long)(w2_ - w1_)); atomicAdd(&g_odo_prof2[SURF ? 6 : 2], 1ull); if (closest < 0) atomicAdd(&g_odo_prof2[3], 1ull); }
 #endif
             }
-            __syncthreads();
+            if (CL) cooperative_groups::this_cluster().sync(); else __syncthreads();
             ODO_T(2)
 #ifdef LEGO_ODO_PROF
             if (threadIdx.x == 0) atomicAdd(&g_odo_prof[5], 1ull);
@@ -218,7 +232,7 @@ __device__ int odo_phase(OdoShared& sh, float4* sel, const float4* __restrict__ 
             const float4 o = feats[q];
             float cx, cy, cz, cd; bool ok = false;
             if (SURF) {
-                const int i1 = ind[q * 3], i2 = ind[q * 3 + 1], i3 = ind[q * 3 + 2];
+                const int i1 = odo_ind<CL>(ind, q * 3), i2 = odo_ind<CL>(ind, q * 3 + 1), i3 = odo_ind<CL>(ind, q * 3 + 2);
                 if (i2 >= 0 && i3 >= 0) {
                     const float4 t1 = last[i1], t2 = last[i2], t3 = last[i3];
                     float pa = (t2.y - t1.y) * (t3.z - t1.z) - (t3.y - t1.y) * (t2.z - t1.z);
@@ -233,7 +247,7 @@ __device__ int odo_phase(OdoShared& sh, float4* sel, const float4* __restrict__ 
                     if ((double)s > 0.1 && pd2 != 0.f) { cx = s * pa; cy = s * pb; cz = s * pc; cd = s * pd2; ok = true; }
                 }
             } else {
-                const int i1 = ind[q * 2], i2 = ind[q * 2 + 1];
+                const int i1 = odo_ind<CL>(ind, q * 2), i2 = odo_ind<CL>(ind, q * 2 + 1);
                 if (i2 >= 0) {
                     const float4 t1 = last[i1], t2 = last[i2];
                     const float x0 = p.x, y0 = p.y, z0 = p.z, x1 = t1.x, y1 = t1.y, z1 = t1.z, x2 = t2.x, y2 = t2.y, z2 = t2.z;

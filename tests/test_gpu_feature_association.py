@@ -117,3 +117,37 @@ def test_interleaved_ring_labels_at_high_yaw_rate():
     for pl in pls:
         pl.close()
     ref.close()
+
+
+def test_odometry_cluster_sizes_change_nothing(monkeypatch):
+    """The scan-to-scan LM kernel runs a lane on a thread-block cluster of 1, 2, 4 or 8 CTAs (csrc/odometry.cu:
+    fa_odometry_cluster_kernel) that share the correspondence searches; transformCur, the iteration counts and the
+    correspondences' effect on every later scan must not depend on the cluster size.  Two lanes with different feature counts."""
+    sensor = "hdl32"
+    seqs = [SynthSequence(sensor, seed=23, scene="street", speed=7.0), SynthSequence(sensor, seed=24, scene="street", speed=3.0, dropout=0.15)]
+    cap = seqs[0].cap
+    pls = []
+    for cl in (1, 2, 4, 8):
+        monkeypatch.setenv("LEGO_ODO_CLUSTER", str(cl))
+        pls.append(Pipeline(make_params(sensor), lanes=2, max_points=cap))
+    monkeypatch.delenv("LEGO_ODO_CLUSTER")
+    pls.append(Pipeline(make_params(sensor), lanes=2, max_points=cap))       # the default for two lanes (8)
+    moved = 0.0
+    for k in range(16):
+        x = np.zeros((2, cap, 4), np.float32); r = np.zeros((2, cap), np.uint16); n = []
+        for l, q in enumerate(seqs):
+            xyzi, ring = q.scan(k)
+            x[l, :len(xyzi)] = xyzi; r[l, :len(ring)] = ring; n.append(len(xyzi))
+        outs = []
+        for pl in pls:
+            pl.step(x, r, n, [k * 0.1] * 2, stage_mask=3)
+            outs.append([(pl.download("transformCur", l).copy(), pl.download("lmState", l).copy(), pl.download("transformSum", l).copy()) for l in range(2)])
+        for o in outs[1:]:
+            for l in range(2):
+                assert np.array_equal(o[l][0].view(np.uint32), outs[0][l][0].view(np.uint32)), "scan %d lane %d transformCur" % (k, l)
+                assert np.array_equal(o[l][1], outs[0][l][1]), "scan %d lane %d lmState %s vs %s" % (k, l, o[l][1], outs[0][l][1])
+                assert np.array_equal(o[l][2].view(np.uint32), outs[0][l][2].view(np.uint32))
+        moved = max(moved, float(np.abs(outs[0][0][0]).max()))
+    assert moved > 0.05
+    for pl in pls:
+        pl.close()
