@@ -164,11 +164,17 @@ __global__ void __launch_bounds__(256) ip_ccl_runs_kernel(IpDev d, Consts c) {
     const int cell = blockIdx.x * blockDim.x + tid;
     const size_t base = (size_t)lane * c.N;
     const bool valid = cell < c.N;
-    const bool seg = valid && seg_cell(d, base + cell);
     const int col = valid ? cell % c.C : 0;
+    // loads first, decisions after: one DRAM round trip instead of three dependent ones (the left neighbour's values sit in the
+    // same lines as this thread's)
+    const size_t g = base + (valid ? cell : 0), gl = valid && cell > 0 ? g - 1 : g;
+    const int own = d.owner[g], ownL = d.owner[gl];
+    const unsigned char gm = d.groundMat[g], gmL = d.groundMat[gl];
+    const float r = d.rangeMat[g], rL = d.rangeMat[gl];
+    const bool seg = valid && own >= 0 && gm != 1;
     bool leftConn = false;
-    if (seg && tid > 0 && col > 0 && seg_cell(d, base + cell - 1))
-        leftConn = seg_edge(d.rangeMat[base + cell], d.rangeMat[base + cell - 1], c.sinAlphaX, c.cosAlphaX, c.segmentTheta);
+    if (seg && tid > 0 && col > 0 && ownL >= 0 && gmL != 1)
+        leftConn = seg_edge(r, rL, c.sinAlphaX, c.cosAlphaX, c.segmentTheta);
     const bool brk = !leftConn;
     __shared__ int s_lastBrk[8];
     __shared__ unsigned char s_brk[257];
@@ -193,20 +199,26 @@ __global__ void __launch_bounds__(256) ip_ccl_union_kernel(IpDev d, Consts c) {
     const int lane = blockIdx.y, tid = threadIdx.x;
     const int cell = blockIdx.x * blockDim.x + tid;
     const size_t base = (size_t)lane * c.N;
-    const bool seg = cell < c.N && seg_cell(d, base + cell);
-    const int row = cell < c.N ? cell / c.C : 0, col = cell - row * c.C;
-    const float r = seg ? d.rangeMat[base + cell] : 0.f;
+    const bool in = cell < c.N;
+    const int row = in ? cell / c.C : 0, col = cell - row * c.C;
+    // Everything the vertical edge needs is loaded up front and unconditionally: the kernel is a chain of dependent DRAM
+    // round trips otherwise (cell class -> class of the cell below -> its range -> the run bits; L1 hit rate 1 %), and with all
+    // loads in flight at once it is one.
+    const bool below = in && row + 1 < c.R;
+    const size_t g = base + (in ? cell : 0), gd = below ? g + c.C : g;
+    const int own = d.owner[g], ownD = d.owner[gd];
+    const unsigned char gm = d.groundMat[g], gmD = d.groundMat[gd];
+    const float r = d.rangeMat[g], rD = d.rangeMat[gd];
+    const int rl = d.runLen[g], rlD = d.runLen[gd];
+    const bool seg = in && own >= 0 && gm != 1;
     int* parent = d.parent + base;
     // vertical neighbour, rows do not wrap (imageProjection.cpp:400-401)
     bool vert = false, hang = false;
-    if (seg && row + 1 < c.R) {
-        const int dc = cell + c.C;
-        if (seg_cell(d, base + dc)) {
-            vert = seg_edge(r, d.rangeMat[base + dc], c.sinAlphaY, c.cosAlphaY, c.segmentTheta);
-            // both this cell and the one below hang on their left neighbours: if the left pair is joined
-            // vertically too, this edge joins the same two runs again
-            hang = (d.runLen[base + cell] & RUN_LEFT_BIT) && (d.runLen[base + dc] & RUN_LEFT_BIT);
-        }
+    if (seg && below && ownD >= 0 && gmD != 1) {
+        vert = seg_edge(r, rD, c.sinAlphaY, c.cosAlphaY, c.segmentTheta);
+        // both this cell and the one below hang on their left neighbours: if the left pair is joined
+        // vertically too, this edge joins the same two runs again
+        hang = (rl & RUN_LEFT_BIT) && (rlD & RUN_LEFT_BIT);
     }
     __shared__ unsigned char s_vert[256];
     s_vert[tid] = vert ? 1 : 0;
@@ -233,11 +245,16 @@ __global__ void __launch_bounds__(256) ip_ccl_stats_kernel(IpDev d, Consts c) {
     const int cell = blockIdx.x * blockDim.x + threadIdx.x;
     if (cell >= c.N) return;
     const size_t base = (size_t)lane * c.N;
-    if (!seg_cell(d, base + cell)) return;
     int* parent = d.parent + base;
-    const int root = uf_find(parent, cell);
+    // independent loads first (see ip_ccl_union_kernel); any value on a cell's parent chain leads to its root
+    const int own = d.owner[base + cell];
+    const unsigned char gm = d.groundMat[base + cell];
+    const int p0 = parent[cell];
+    const int rl = d.runLen[base + cell];
+    if (!(own >= 0 && gm != 1)) return;
+    const int root = p0 == cell ? cell : uf_find(parent, p0);
     if (root != cell) parent[cell] = root;
-    const int len = d.runLen[base + cell] & ~RUN_LEFT_BIT;
+    const int len = rl & ~RUN_LEFT_BIT;
     if (len > 0) {
         const int leader = cell - len + 1;
         const int n = len - (leader == root ? 1 : 0);
@@ -260,17 +277,22 @@ __device__ __forceinline__ bool comp_valid(const IpDev& d, const Consts& c, size
 }
 
 // Per-cell classification shared by the counting and the writing pass (imageProjection.cpp:326-351).
-// returns bit0 = cell heads a valid segment, bit1 = cell goes to segmentedCloud, bit2 = cell goes to outlierCloud
+// returns bit0 = cell heads a valid segment, bit1 = cell goes to segmentedCloud, bit2 = cell goes to outlierCloud,
+// bit3 = cell heads a segment that is NOT valid (its label becomes 999999), bit4 = ground cell
 __device__ __forceinline__ int classify_cell(const IpDev& d, const Consts& c, size_t base, int row, int col) {
     const int cell = row * c.C + col;
     const size_t g = base + cell;
+    const int own = d.owner[g];
     const bool ground = d.groundMat[g] == 1;
-    int f = 0;
-    if (d.owner[g] >= 0 && !ground) {
-        const int root = d.parent[g];
+    const int root = d.parent[g];          // loaded with the other two, used only for segmentation cells
+    int f = ground ? 16 : 0;
+    if (own >= 0 && !ground) {
         const bool valid = comp_valid(d, c, base, root);
         if (valid) { if (root == cell) f |= 1; f |= 2; }
-        else if (row > c.G && col % 5 == 0) f |= 4;
+        else {
+            if (root == cell) f |= 8;
+            if (row > c.G && col % 5 == 0) f |= 4;
+        }
     } else if (ground) {
         if (!(col % 5 != 0 && col > 5 && col < c.C - 5)) f |= 2;
     }
@@ -351,11 +373,11 @@ __global__ void __launch_bounds__(256) ip_compact_kernel(IpDev d, Consts c) {
         if (col < c.C) {
             const size_t g = base + row * c.C + col;
             if (f & 1) d.labelMat[g] = off[0] + 1;
-            else if (d.owner[g] >= 0 && d.groundMat[g] != 1 && d.parent[g] == row * c.C + col) d.labelMat[g] = 999999;
+            else if (f & 8) d.labelMat[g] = 999999;
             if (f & 2) {
                 const size_t o = base + off[1];
                 d.segCloud[o] = d.fullCloud[g];
-                d.segGround[o] = d.groundMat[g] == 1 ? 1 : 0;
+                d.segGround[o] = (f & 16) ? 1 : 0;
                 d.segCol[o] = col;
                 d.segRange[o] = d.rangeMat[g];
             }
