@@ -125,7 +125,7 @@ void ref_params(float* out8) {
 
 void* ref_create(int viz_subscribed) {
     ros::ShimState& s = ros::ShimState::get();
-    s.last.clear(); s.count.clear(); s.subscribed.clear(); s.errors = 0; s.shutdown_requested = false;
+    s.last.clear(); s.count.clear(); s.subscribed.clear(); s.callbacks.clear(); s.errors = 0; s.shutdown_requested = false;
     s.all_subscribed = false;
     if (viz_subscribed) {   // makes FeatureAssociation::publishCloud (featureAssociation.cpp:786-817) emit the 4 feature clouds
         s.subscribed.insert("/laser_cloud_sharp"); s.subscribed.insert("/laser_cloud_less_sharp");

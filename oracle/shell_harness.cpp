@@ -6,6 +6,10 @@
 // handler -> mapOptimization -> TransformFusion's mapping handler).  tests/test_gpu_ros_shells.py compares the topics with the
 // reference nodes' (name, frame_id, stamp, payload).  ROS itself is absent from this image, so this is as close to "the
 // shells run" as the environment allows; the shells' sources are compiled unmodified.
+#include <execinfo.h>
+#include <signal.h>
+#include <unistd.h>
+
 #include <algorithm>
 #include <cmath>
 #include <cstdint>
@@ -62,16 +66,32 @@ void pump(Shells& S, const char* const* topics, int n) {
 
 }  // namespace
 
+// a crash inside the shells or the library under them prints the native frames (module + offset, for addr2line) before the
+// interpreter's own handler reports the Python ones
+void shell_segv_handler(int sig) {
+    void* frames[48];
+    const int n = backtrace(frames, 48);
+    static const char msg[] = "shell_harness: SIGSEGV, native frames:\n";
+    if (write(2, msg, sizeof(msg) - 1) < 0) {}
+    backtrace_symbols_fd(frames, n, 2);
+    signal(sig, SIG_DFL);
+    raise(sig);
+}
+
 extern "C" {
 
 void* shell_create(int subscribe_all) {
+    if (std::getenv("LEGO_SHELL_BACKTRACE")) signal(SIGSEGV, shell_segv_handler);
+    // one set of shells per process at a time: the subscriber table of the stand-in ROS is global to this library, and the
+    // callbacks of an earlier, destroyed set would dangle
+    ros::ShimState::get() = ros::ShimState();
     ros::ShimState::get().all_subscribed = subscribe_all != 0;
     ros::ShimState::get().errors = 0;
     Shells* s = new Shells();
     if (ros::ShimState::get().shutdown_requested || ros::ShimState::get().errors) { delete s; return nullptr; }
     return s;
 }
-void shell_destroy(void* h) { delete static_cast<Shells*>(h); }
+void shell_destroy(void* h) { delete static_cast<Shells*>(h); ros::ShimState::get().callbacks.clear(); }
 int shell_errors() { return ros::ShimState::get().errors; }
 
 // One lidar scan as the driver's /velodyne_points message.  Returns bit0 = delivered, bit3 = /aft_mapped_to_init was published

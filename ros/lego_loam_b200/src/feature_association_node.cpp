@@ -67,10 +67,12 @@ public:
             t.setRotation(tf::Quaternion(-g.y, -g.z, g.x, g.w)); t.setOrigin(tf::Vector3(sum[3], sum[4], sum[5]));
             broadcaster_.sendTransform(t);
         }
-        if (out.published) {
+        // publishCloudsLast forwards the three clouds every second scan (featureAssociation.cpp:1790-1813); the initialisation scan
+        // publishes corner and surf once from checkSystemInitialization (featureAssociation.cpp:1620-1630), no outliers, no odometry
+        if (out.published) { lego_ros::unpack(out.outlierCloudLast, c); lego_ros::publish_cloud(pubOutlierLast_, c, header_.stamp, "/camera"); }
+        if (out.published || !out.odometry_valid) {
             lego_ros::unpack(out.laserCloudCornerLast, c); lego_ros::publish_cloud(pubCornerLast_, c, header_.stamp, "/camera");
             lego_ros::unpack(out.laserCloudSurfLast, c); lego_ros::publish_cloud(pubSurfLast_, c, header_.stamp, "/camera");
-            if (out.odometry_valid) { lego_ros::unpack(out.outlierCloudLast, c); lego_ros::publish_cloud(pubOutlierLast_, c, header_.stamp, "/camera"); }
         }
     }
 
