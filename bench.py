@@ -671,11 +671,15 @@ def measure_latency(args, sensor, workload, inp, win, device):
         if s >= win.first_timed:
             lat.append(dt); mapped.append(bool(flags[0] & 8))
     launches = pl.launch_count()
+    graph_launches = pl.graph_launch_count()
     pl.close()
     lat = np.array(lat); mapped = np.array(mapped)
     out = {"lanes": 1, "scans": int(len(lat)), "scan_range": [win.first_timed, win.first_timed + n_timed - 1],
            "ms_per_scan": {"mean": float(lat.mean()), "p50": float(np.percentile(lat, 50)), "p99": float(np.percentile(lat, 99)), "max": float(lat.max())},
            "launches_per_scan": launches / float(win.first_timed + n_timed),
+           "graph_launches_per_scan": graph_launches / float(win.first_timed + n_timed),
+           "submission": ("CUDA graphs: the front end and the mapping body of a scan are one cudaGraphLaunch each (csrc/engine.cu runGraphed; "
+                          "launches_per_scan counts the kernels inside them)") if graph_launches else "plain kernel launches (LEGO_GRAPH=0)",
            "what": "wall time of lego_pipeline_step_lanes (pinned host scan in) + lego_pipeline_get_poses (poses on the host), one scan at a time"}
     if mapped.any() and (~mapped).any():
         out["ms_per_scan"]["p50_mapping_scan"] = float(np.percentile(lat[mapped], 50))

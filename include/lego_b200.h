@@ -213,6 +213,11 @@ int lego_pipeline_poses_wait(lego_pipeline* h, int slot, float* poses_out, int* 
 int lego_pipeline_sync(lego_pipeline* h);
 /* number of kernel launches issued by the handle so far (bench.py's gpu_launches) */
 long lego_pipeline_launch_count(lego_pipeline* h);
+/* number of cudaGraphLaunch submissions so far.  The per-scan launch sequences are replayed from CUDA graphs when the
+ * handle has fewer than 148 lanes (a scan is then launch-latency bound; LEGO_GRAPH=0 / 1 in the environment forces
+ * either), except while profiling, with IMU data and in loop-closure mode.  Kernels inside a graph still count in
+ * lego_pipeline_launch_count.  No counterpart in the reference (its nodes are plain CPU callbacks). */
+long lego_pipeline_graph_launch_count(lego_pipeline* h);
 /* Timing on the handle's own stream (CUDA events; a caller's torch.cuda.Event cannot see this stream).
  * timer_record(slot) records event `slot` (0..7); timer_elapsed waits for slot_b and returns the device time between
  * the two.  profile(mode): 0 off, 1 bracket every kernel launch with events, 2 only kernels whose name contains

@@ -17,7 +17,7 @@ EXPORTED = [
     "lego_fa_create", "lego_fa_destroy", "lego_fa_process",
     "lego_mo_create", "lego_mo_destroy", "lego_mo_process",
     "lego_pipeline_create", "lego_pipeline_destroy", "lego_pipeline_step", "lego_pipeline_step_lanes", "lego_pipeline_input_wait", "lego_pipeline_get_poses", "lego_pipeline_poses_async", "lego_pipeline_poses_wait",
-    "lego_pipeline_sync", "lego_pipeline_launch_count", "lego_pipeline_download", "lego_pipeline_upload",
+    "lego_pipeline_sync", "lego_pipeline_launch_count", "lego_pipeline_graph_launch_count", "lego_pipeline_download", "lego_pipeline_upload",
     "lego_pipeline_timer_record", "lego_pipeline_timer_elapsed", "lego_pipeline_timer_elapsed_between", "lego_pipeline_profile", "lego_pipeline_profile_read",
     "lego_tf_create", "lego_tf_destroy", "lego_tf_laser_odometry", "lego_tf_aft_mapped",
     "lego_selftest_atan2f", "lego_selftest_std_sort", "lego_selftest_warp_sort", "lego_selftest_voxel_grid",
@@ -52,6 +52,8 @@ def load():
         lib.lego_pipeline_sync.argtypes = [ctypes.c_void_p]
         lib.lego_pipeline_launch_count.argtypes = [ctypes.c_void_p]
         lib.lego_pipeline_launch_count.restype = ctypes.c_long
+        lib.lego_pipeline_graph_launch_count.argtypes = [ctypes.c_void_p]
+        lib.lego_pipeline_graph_launch_count.restype = ctypes.c_long
         lib.lego_pipeline_download.argtypes = [ctypes.c_void_p, ctypes.c_int, ctypes.c_char_p, ctypes.c_void_p, ctypes.c_long,
                                                ctypes.POINTER(ctypes.c_int)]
         lib.lego_pipeline_download.restype = ctypes.c_long
@@ -229,6 +231,9 @@ class Pipeline:
 
     def launch_count(self):
         return self.lib.lego_pipeline_launch_count(self.h)
+
+    def graph_launch_count(self):
+        return self.lib.lego_pipeline_graph_launch_count(self.h)
 
     def timer_record(self, slot):
         _check(self.lib.lego_pipeline_timer_record(self.h, slot), "lego_pipeline_timer_record")

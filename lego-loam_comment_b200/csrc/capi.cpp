@@ -47,12 +47,12 @@ int lego_pipeline_destroy(lego_pipeline* h) {
 // the stages of one scan for every lane, after the input was handed to the engine
 static int run_stages(lego_pipeline* h, int stage_mask) {
     Engine& e = *h->e;
-    if (stage_mask & 1) {
+    if ((stage_mask & 3) == 3) e.frontEnd(h->stamps.data());
+    else if (stage_mask & 1) {
         e.projectPointCloud();
         e.groundRemoval();
         e.cloudSegmentation();
-    }
-    if (stage_mask & 2) {
+    } else if (stage_mask & 2) {
         e.adjustDistortionCalculateSmoothnessMarkOccluded(h->stamps.data());
         e.extractFeatures();
         e.updateTransformation();
@@ -129,6 +129,7 @@ int lego_pipeline_poses_wait(lego_pipeline* h, int slot, float* poses_out, int* 
     LEGO_TRY h->e->posesWait(slot, poses_out, flags_out); return LEGO_OK; LEGO_CATCH
 }
 long lego_pipeline_launch_count(lego_pipeline* h) { return h ? h->e->launches : 0; }
+long lego_pipeline_graph_launch_count(lego_pipeline* h) { return h ? h->e->graphLaunches : 0; }
 int lego_pipeline_profile(lego_pipeline* h, int mode, const char* filter) {
     if (!h || mode < 0 || mode > 2) return LEGO_ERR_ARG;
     LEGO_TRY

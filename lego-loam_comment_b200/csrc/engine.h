@@ -8,6 +8,8 @@
 #include <deque>
 #include <string>
 #include <vector>
+#include <unordered_map>
+#include <functional>
 #include "../../include/lego_b200.h"
 #include "pose_graph.h"
 #include "voxel_grid.cuh"
@@ -288,6 +290,7 @@ public:
     void inputWait();             // input buffers of the last step may be refilled once this returns
     void inputConsumed();         // marks the point after which the current input buffers may be overwritten
     void projectPointCloud();     // + findStartEndAngle
+    void projectPointCloudLaunch();   // the launches alone (no event record: capturable into a CUDA graph)
     void groundRemoval();
     void cloudSegmentation();
     void finalizeLabelMat();      // numeric labels for every cell (only needed for parity / visualisation)
@@ -296,6 +299,8 @@ public:
     void extractFeatures();
     void updateTransformation();
     void integrateTransformationPublishCloudsLast();
+    void integrateTransformationPublishCloudsLastLaunch();   // the launches alone; the caller flips faBuf
+    void frontEnd(const double* stamps);   // ImageProjection + FeatureAssociation of one scan, replayed from a CUDA graph when allowed
 
     // ---- mapOptimization (names follow mapOptmization.cpp) ----
     void allocMapOptimization();
@@ -371,6 +376,18 @@ public:
     lego_params params;
     cudaStream_t stream = nullptr;
     long launches = 0;
+    // ---- CUDA graphs (engine.cu): the per-scan launch sequences never change shape (all sizes live in device counters), so
+    // the front end (27 launches) and the mapping body (<= 70) are captured once per value of the few host-side indices
+    // that select buffers and replayed with one cudaGraphLaunch.  LEGO_GRAPH = 0 / 1 forces either; default: below 148 lanes,
+    // where a scan is launch-latency bound.  Off while profiling, with IMU data (host uploads inside the sequence) and in
+    // loop-closure mode (host pose graph inside the mapping body).
+    struct GraphEntry { cudaGraphExec_t exec = nullptr; long launches = 0; int seen = 0; };
+    std::unordered_map<unsigned long long, GraphEntry> graphs;
+    int graphMode = 0;
+    bool graphBroken = false;          // a capture failed once: stay eager
+    long graphLaunches = 0;            // cudaGraphLaunch calls so far
+    bool graphsUsable() const { return graphMode != 0 && !graphBroken && profMode == 0 && !anyImu && !loopMode(); }
+    void runGraphed(unsigned long long key, const std::function<void()>& body);
     int faBuf = 0;             // which of the double-buffered "last" clouds is current (same for every lane)
     IpDev ip;
     FaDev fa;

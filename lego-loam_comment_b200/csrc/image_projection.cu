@@ -409,12 +409,16 @@ __global__ void __launch_bounds__(256) ip_label_finalize_kernel(IpDev d, Consts 
 
 // ------------------------------------------------------------------------------------------------------------
 void Engine::projectPointCloud() {
+    projectPointCloudLaunch();
+    inputConsumed();
+}
+
+void Engine::projectPointCloudLaunch() {
     { ProfScope ps(this, "memset_owner"); cuda_check(cudaMemsetAsync(ip.owner, 0xFF, sizeof(int) * (size_t)c.L * c.N, stream), "memset owner"); }
     dim3 g1((c.Pcap + 255) / 256, c.L);
     { ProfScope ps(this, "ip_project_kernel"); ip_project_kernel<<<g1, 256, 0, stream>>>(ip, c); }
     dim3 g2((c.N + 255) / 256, c.L);
     { ProfScope ps(this, "ip_gather_kernel"); ip_gather_kernel<<<g2, 256, 0, stream>>>(ip, c); }
-    inputConsumed();
     launches += 3;
 }
 

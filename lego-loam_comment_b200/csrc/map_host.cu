@@ -375,6 +375,9 @@ void Engine::mapOptimizationBody(const std::vector<int>& active) {
 
     mapOptimizationImuBlend(active);
     // ---- the mapping body ----
+    // One fixed launch sequence; the host enters it only through the parity of the "last" clouds and the grid of the assemble
+    // kernel, so it is replayed from a CUDA graph where graphs are in use (engine.h: runGraphed).
+    const std::function<void()> body = [this, maxEntries, &active]() {
     { ProfScope ps(this, "mo_begin_kernel"); mo_begin_kernel<<<(c.L + 63) / 64, 64, 0, stream>>>(fa, mo, c.L); }
     if (maxEntries > 0) {
         dim3 g(std::min(maxEntries, 64), c.L);
@@ -432,6 +435,11 @@ void Engine::mapOptimizationBody(const std::vector<int>& active) {
     if (loopMode()) saveKeyFramesHostGraph(active);   // lanes whose graph holds a loop factor: gate + iSAM update on the host
     { ProfScope ps(this, "mo_save_keyframe_kernel"); mo_save_keyframe_kernel<<<c.L, 256, 0, stream>>>(mo); }
     launches += 3;
+    };
+    if (graphsUsable())
+        runGraphed(2ull | ((unsigned long long)faBuf << 8) | ((unsigned long long)std::min(maxEntries, 64) << 16) |
+                   ((unsigned long long)(moPersistentLm ? 1 : 0) << 32) | ((unsigned long long)(imEnabled ? 1 : 0) << 33), body);
+    else body();
     cuda_check(cudaMemcpyAsync(moRecordsHost, mo.records, sizeof(MoRecord) * c.L, cudaMemcpyDeviceToHost, stream), "records");
     cuda_check(cudaEventRecord(moRecordsReady, stream), "event record");
     moRecordsPending = true;

@@ -210,11 +210,15 @@ void Engine::updateTransformation() {
 }
 
 void Engine::integrateTransformationPublishCloudsLast() {
+    integrateTransformationPublishCloudsLastLaunch();
+    faBuf ^= 1;
+}
+
+void Engine::integrateTransformationPublishCloudsLastLaunch() {
     const int nb = faBuf ^ 1;
     dim3 g(ODO_TE_BLOCKS, c.L);
     { ProfScope ps(this, "fa_clouds_last_kernel"); fa_clouds_last_kernel<<<g, 256, 0, stream>>>(ip, fa, c, nb); }
     { ProfScope ps(this, "fa_finish_scan_kernel"); fa_finish_scan_kernel<<<(c.L + 63) / 64, 64, 0, stream>>>(ip, fa, c); }
-    faBuf = nb;
     // the two kd-tree rebuilds of featureAssociation.cpp:1786-1787 become two voxel-hash builds
     launches += 2;
     { ProfScope ps(this, "vh_build(cornerLast)"); launches += vh_build(fa.hashCorner, c.L, fa.cornerLast[nb], (size_t)c.R * 120, stream); }

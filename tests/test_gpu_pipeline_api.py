@@ -230,3 +230,43 @@ def test_keyframe_pool_overflow_is_reported():
     assert failed_at is not None and failed_at <= 22, failed_at
     assert int(pl.download("moState")[1]) == 3
     pl.close()
+
+
+def test_cuda_graph_replay_changes_nothing(monkeypatch):
+    """Below 148 lanes the per-scan launch sequences (front end, mapping body) are replayed from CUDA graphs
+    (csrc/engine.cu: runGraphed; LEGO_GRAPH=0 keeps plain launches).  Same scans through both: images, features, poses,
+    LM state and the key-frame count must be bit-identical, the graph handle must really have replayed graphs and both
+    must have run the same number of kernels."""
+    sensor = "vlp16"
+    seqs = [SynthSequence(sensor, seed=41, scene="street", speed=4.0), SynthSequence(sensor, seed=42, scene="street", speed=9.0, dropout=0.1)]
+    cap = seqs[0].cap
+    monkeypatch.setenv("LEGO_GRAPH", "0")
+    eager = Pipeline(make_params(sensor), lanes=2, max_points=cap)
+    monkeypatch.setenv("LEGO_GRAPH", "1")
+    graph = Pipeline(make_params(sensor), lanes=2, max_points=cap)
+    mapped = 0
+    for k in range(64):
+        x = np.zeros((2, cap, 4), np.float32); r = np.zeros((2, cap), np.uint16); n = []
+        for l, q in enumerate(seqs):
+            xyzi, ring = q.scan(k)
+            x[l, :len(xyzi)] = xyzi; r[l, :len(ring)] = ring; n.append(len(xyzi))
+        out = []
+        for pl in (eager, graph):
+            pl.step(x, r, n, [seqs[0].stamp(k)] * 2, stage_mask=7)
+            poses, flags = pl.poses()
+            rec = [poses.copy(), flags.copy()]
+            if k % 8 == 7 or k < 4:
+                for l in range(2):
+                    rec += [pl.download(nm, l).copy() for nm in NAMES]
+                    rec += [pl.download("moState", l).copy(), pl.download("transformTobeMapped", l).copy()]
+            out.append(rec)
+        assert len(out[0]) == len(out[1])
+        for a, b in zip(out[0], out[1]):
+            assert _same(np.asarray(a), np.asarray(b)), "scan %d: graph replay differs from plain launches" % k
+        mapped += int(np.count_nonzero(out[0][1] & 8))
+    assert mapped >= 20
+    assert eager.graph_launch_count() == 0
+    # 10 front-end keys (5 input slots x 2 parities) seen twice before the first replay; mapping graphs on top
+    assert graph.graph_launch_count() >= 64 - 20
+    assert graph.launch_count() == eager.launch_count()
+    eager.close(); graph.close()
