@@ -251,11 +251,14 @@ def algorithmic_bytes(name, c):
     t = {
         "memset_owner": 4 * N,
         "ip_project_kernel": 18 * P + 4 * P,
-        "ip_gather_kernel": 4 * N + 16 * P + 20 * N,
+        "ip_gather_kernel": 4 * N + 16 * P + 21 * N,   # owner in, the winners' points in; fullCloud, rangeMat, groundMat out
         "ip_ground_kernel": 16 * (c["G"] + 1) * c["C"] * L + N,
         "ip_ccl_runs_kernel": 17 * N,       # rangeMat, owner, groundMat in; parent, runLen out
         "ip_ccl_union_kernel": 13 * N,      # rangeMat, owner, groundMat, runLen in; parent updated in place at the roots
         "ip_ccl_stats_kernel": 17 * N,      # parent in/out, runLen, owner, groundMat in
+        "ip_ccl_tile_kernel": 14 * N,       # rangeMat, owner, groundMat in; parent, marker out (statistics only at tile roots)
+        "ip_ccl_border_kernel": 0,          # a few hundred cells per image
+        "ip_ccl_finish_kernel": 9 * N,      # marker, parent in; parent out
         "ip_row_count_kernel": 10 * N,      # owner, groundMat, parent in; cellClass out
         "ip_compact_kernel": 10 * N + 41 * S + 16 * O + 8 * c["R"] * L,
         "fa_prepare_kernel": 20 * S,

@@ -7,6 +7,10 @@
 
 namespace lego {
 
+int ccl_tile_width(int R);                              // image_projection.cu
+size_t ccl_tile_smem(int R, int tw, int rowWords);
+cudaError_t ccl_tile_set_smem(size_t bytes);
+
 static thread_local std::string g_last_error;
 void set_last_error(const std::string& s) { g_last_error = s; }
 const std::string& last_error() { return g_last_error; }
@@ -32,6 +36,12 @@ Engine::Engine(const lego_params& p, int lanes, int max_points) : params(p) {
     c.useRing = p.useCloudRing;
     c.ang_res_x = p.ang_res_x; c.ang_res_y = p.ang_res_y; c.ang_bottom = p.ang_bottom;
     c.sensorMinimumRange = p.sensorMinimumRange; c.sensorMountAngle = p.sensorMountAngle; c.segmentTheta = p.segmentTheta;
+    {
+        const char* e = std::getenv("LEGO_SEG_EDGE_EXACT");
+        const double th = (double)p.segmentTheta, t = std::tan(th);
+        const bool on = !(e && e[0] == '1') && th > 0.05 && th < 1.5;
+        c.segTanLo = on ? (float)(t * (1.0 - 1e-4)) : 0.0f; c.segTanHi = on ? (float)(t * (1.0 + 1e-4)) : 0.0f;
+    }
     // sin(alpha)/cos(alpha) in labelComponents are float overloads on a float constant (imageProjection.cpp:421);
     // computing them here with the host C library keeps them bit-identical to the reference's values.
     c.sinAlphaX = sinf(p.segmentAlphaX); c.cosAlphaX = cosf(p.segmentAlphaX);
@@ -60,6 +70,9 @@ Engine::Engine(const lego_params& p, int lanes, int max_points) : params(p) {
     ip.segCloud = alloc<float4>(L * N); ip.segGround = alloc<uint8_t>(L * N); ip.segCol = alloc<int>(L * N);
     ip.segRange = alloc<float>(L * N); ip.startRing = alloc<int>(L * R); ip.endRing = alloc<int>(L * R);
     ip.orient = alloc<float>(L * 4); ip.outlier = alloc<float4>(L * c.Ocap); ip.counts = alloc<int>(L * 8);
+
+    cclTileW = ccl_tile_width(c.R);
+    if (cclTileW > 0) cuda_check(ccl_tile_set_smem(ccl_tile_smem(c.R, cclTileW, c.rowWords)), "smem attr");
 
     allocFeatureAssociation();
     allocMapOptimization();

@@ -29,6 +29,7 @@ struct Consts {
     int useRing;
     float ang_res_x, ang_res_y, ang_bottom;
     float sensorMinimumRange, sensorMountAngle, segmentTheta;
+    float segTanLo, segTanHi;  // tan(segmentTheta) * (1 -+ 1e-4): bounds of the band in which seg_edge evaluates atan2f (0 = always)
     float sinAlphaX, cosAlphaX, sinAlphaY, cosAlphaY;   // sinf/cosf of segmentAlphaX/Y computed on the host (glibc)
     int segmentValidPointNum, segmentValidLineNum;
     float scanPeriod, edgeThreshold, surfThreshold, nearestFeatureSearchSqDist;
@@ -414,6 +415,7 @@ public:
     cudaEvent_t moStaged[2] = {nullptr, nullptr};
     MoRecord* moRecordsHost = nullptr;   // pinned [L]
     cudaEvent_t moRecordsReady = nullptr;
+    int cclTileW = 0;                // tile width of the shared-memory connected components (image_projection.cu), 0 = three-pass form
     int odoCluster = 1;              // CTAs (one thread-block cluster) per lane in fa_odometry_cluster_kernel; 1 = fa_odometry_kernel
     bool moPersistentLm = true;      // LEGO_LM_PERSISTENT=0: ten launches of {re-rank, search, fit, solve} over all lanes instead of one persistent CTA per lane
     int moLmThreads = 512;

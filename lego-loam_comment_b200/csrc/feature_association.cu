@@ -84,46 +84,65 @@ __device__ __forceinline__ float ori_branch_b(float4 p, float endOri) {
     return ori;
 }
 
-// occlusion rule of one loop iteration k of markOccludedPoints (featureAssociation.cpp:647-670):
-// 1 = marks k-5..k, 2 = marks k+1..k+6, 0 = nothing.  Valid loop range is [5, S-6).
-__device__ __forceinline__ int occl_type(const float* r, const int* col, int k, int S) {
-    if (k < 5 || k >= S - 6) return 0;
-    const int cd = abs(col[k + 1] - col[k]);
-    if (cd >= 10) return 0;
-    if ((double)PM_SUB(r[k], r[k + 1]) > 0.3) return 1;
-    if ((double)PM_SUB(r[k + 1], r[k]) > 0.3) return 2;
-    return 0;
-}
+// Occlusion rule of one loop iteration k of markOccludedPoints (featureAssociation.cpp:647-670), valid for k in [5, S-6):
+// column gap < 10 and r[k] - r[k+1] > 0.3 -> type 1 (marks k-5..k); r[k+1] - r[k] > 0.3 -> type 2 (marks k+1..k+6); else 0.
 
 // calculateSmoothness + markOccludedPoints as one gather stencil per point, plus the halfPassed search of
 // adjustDistortion.  The reference's scatter writes (picked[i-5..i] = 1 ...) are all "set to 1", so gathering the
 // union of the rules that can reach index i is order-free and exact.  Entries the reference does not reset
 // (i < 5, i >= S-5) keep their previous value OR-ed with this scan's marks, exactly as its persistent arrays do.
 __global__ void __launch_bounds__(256) fa_prepare_kernel(IpDev d, FaDev f, Consts c) {
+    // The block's 256 points plus a halo of 6 + 7 slots are staged once; the occlusion rule of every k in reach is then
+    // evaluated ONCE per block (it was evaluated by each of the 12 points it can reach) and read back as a byte.
+    constexpr int HB = 6, HA = 7, W = 256 + HB + HA;
+    __shared__ float sr[W];
+    __shared__ int scol[W];
+    __shared__ unsigned char socc[W];
     const int lane = blockIdx.y;
-    const int i = blockIdx.x * blockDim.x + threadIdx.x;
+    const int i0 = blockIdx.x * blockDim.x, tid = threadIdx.x, i = i0 + tid;
     const int S = d.counts[lane * 8 + 0];
-    if (i >= S) return;
+    if (i0 >= S) return;
     const size_t base = (size_t)lane * c.N;
     const float* r = d.segRange + base;
     const int* col = d.segCol + base;
+    for (int q = tid; q < W; q += 256) {
+        const int k = i0 - HB + q;
+        const bool in = k >= 0 && k < S;
+        sr[q] = in ? r[k] : 0.0f;
+        scol[q] = in ? col[k] : 0;
+    }
+    __syncthreads();
+    for (int q = tid; q < W - 1; q += 256) {      // rule of loop iteration k = i0 - 6 + q (reads k and k + 1)
+        const int k = i0 - HB + q;
+        int t = 0;
+        if (k >= 5 && k < S - 6 && abs(scol[q + 1] - scol[q]) < 10) {
+            if ((double)PM_SUB(sr[q], sr[q + 1]) > 0.3) t = 1;
+            else if ((double)PM_SUB(sr[q + 1], sr[q]) > 0.3) t = 2;
+        }
+        socc[q] = (unsigned char)t;
+    }
+    __syncthreads();
+    if (i >= S) return;
+    const int q = tid + HB;                        // this point's slot in the staged arrays
     int pk;
     if (i >= 5 && i < S - 5) {
-        float s = PM_ADD(r[i - 5], r[i - 4]);
-        s = PM_ADD(s, r[i - 3]); s = PM_ADD(s, r[i - 2]); s = PM_ADD(s, r[i - 1]);
-        s = PM_SUB(s, PM_MUL(r[i], 10.0f));
-        s = PM_ADD(s, r[i + 1]); s = PM_ADD(s, r[i + 2]); s = PM_ADD(s, r[i + 3]); s = PM_ADD(s, r[i + 4]); s = PM_ADD(s, r[i + 5]);
+        float s = PM_ADD(sr[q - 5], sr[q - 4]);
+        s = PM_ADD(s, sr[q - 3]); s = PM_ADD(s, sr[q - 2]); s = PM_ADD(s, sr[q - 1]);
+        s = PM_SUB(s, PM_MUL(sr[q], 10.0f));
+        s = PM_ADD(s, sr[q + 1]); s = PM_ADD(s, sr[q + 2]); s = PM_ADD(s, sr[q + 3]); s = PM_ADD(s, sr[q + 4]); s = PM_ADD(s, sr[q + 5]);
         f.curv[base + i] = PM_MUL(s, s);
         f.label[base + i] = 0;
         pk = 0;
     } else {
         pk = f.picked[base + i];
     }
-    for (int k = i; k <= i + 5; ++k) if (occl_type(r, col, k, S) == 1) pk = 1;
-    for (int k = i - 6; k <= i - 1; ++k) if (occl_type(r, col, k, S) == 2) pk = 1;
+#pragma unroll
+    for (int k = 0; k <= 5; ++k) if (socc[q + k] == 1) pk = 1;       // iterations i .. i+5 mark k-5 .. k
+#pragma unroll
+    for (int k = 1; k <= 6; ++k) if (socc[q - k] == 2) pk = 1;       // iterations i-6 .. i-1 mark k+1 .. k+6
     if (i >= 5 && i < S - 6) {
-        const float d1 = fabsf(PM_SUB(r[i - 1], r[i])), d2 = fabsf(PM_SUB(r[i + 1], r[i]));
-        if ((double)d1 > 0.02 * (double)r[i] && (double)d2 > 0.02 * (double)r[i]) pk = 1;
+        const float d1 = fabsf(PM_SUB(sr[q - 1], sr[q])), d2 = fabsf(PM_SUB(sr[q + 1], sr[q]));
+        if ((double)d1 > 0.02 * (double)sr[q] && (double)d2 > 0.02 * (double)sr[q]) pk = 1;
     }
     f.picked[base + i] = pk;
     // halfPassed: first index whose branch-A orientation is more than pi past the start (quirk Q9)

@@ -89,3 +89,35 @@ def test_image_projection_lanes_independent():
             assert np.array_equal(pl4.download(name, i).view(np.uint8), pl1.download(name, 0).view(np.uint8)), (i, name)
         pl1.close()
     pl4.close()
+
+
+@pytest.mark.parametrize("sensor", ["vlp16", "hdl64", "vls128"])
+def test_tiled_connected_components_change_nothing(sensor, monkeypatch):
+    """labelComponents as shared-memory tiles (csrc/image_projection.cu: ip_ccl_tile / border / finish) with the tan-ratio
+    shortcut of the edge test, against the three-pass form on the global forest with atan2f in every edge test
+    (LEGO_CCL_TILE=0, LEGO_SEG_EDGE_EXACT=1): roots, labels, segmented and outlier clouds, ring indices bit-identical, on
+    scans with dropouts (ragged components) and for tile widths 256 / 64 / 32."""
+    from lego_loam_b200.capi import Pipeline
+    from lego_loam_b200.params import make_params
+    from lego_loam_b200.synth import SynthSequence
+    seq = SynthSequence(sensor, seed=5, scene="street", speed=5.0, dropout=0.15)
+    monkeypatch.setenv("LEGO_CCL_TILE", "0"); monkeypatch.setenv("LEGO_SEG_EDGE_EXACT", "1")
+    old = Pipeline(make_params(sensor), lanes=1, max_points=seq.cap)
+    monkeypatch.setenv("LEGO_CCL_TILE", "1"); monkeypatch.setenv("LEGO_SEG_EDGE_EXACT", "0")
+    new = Pipeline(make_params(sensor), lanes=1, max_points=seq.cap)
+    names = ("labelMat", "segmentedCloud", "outlierCloud", "startRingIndex", "endRingIndex", "segGroundFlag",
+             "segColInd", "segRange", "ipCounts")
+    segments = 0
+    for k in range(4):
+        xyzi, ring = seq.scan(k)
+        x = np.zeros((1, seq.cap, 4), np.float32); x[0, :len(xyzi)] = xyzi
+        r = np.zeros((1, seq.cap), np.uint16); r[0, :len(ring)] = ring
+        for pl in (old, new):
+            pl.step(x, r, [len(xyzi)], [seq.stamp(k)], stage_mask=1)
+        for nm in names:
+            a, b = old.download(nm), new.download(nm)
+            assert a.shape == b.shape and np.array_equal(a.view(np.uint8), b.view(np.uint8)), "scan %d: %s differs" % (k, nm)
+        lab = old.download("labelMat")
+        segments += int(lab[(lab > 0) & (lab < 999999)].max(initial=0))
+    assert segments > 20
+    old.close(); new.close()
