@@ -8,7 +8,8 @@ import numpy as np
 from .params import LegoParams
 
 _HERE = os.path.dirname(os.path.abspath(__file__))
-LIB_PATH = os.path.join(_HERE, "liblego_b200.so")
+# LEGO_B200_LIB: a differently compiled build of the same library (compile-time knob experiments under tools/)
+LIB_PATH = os.environ.get("LEGO_B200_LIB") or os.path.join(_HERE, "liblego_b200.so")
 
 # every extern "C" symbol declared in include/lego_b200.h (checked by tests/test_abi.py)
 EXPORTED = [

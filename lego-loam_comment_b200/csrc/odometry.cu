@@ -102,7 +102,14 @@ __device__ __forceinline__ void odometry_body(IpDev& d, FaDev& f, Consts& c, int
     if (tid == 0) { f.lmState[lane * 8 + 1] = sh.isDegenerate; f.lmState[lane * 8 + 6] = itS; f.lmState[lane * 8 + 7] = itC; }
 }
 
-__global__ void __launch_bounds__(ODO_THREADS) fa_odometry_kernel(IpDev d, FaDev f, Consts c, int buf) {
+// 256 threads with registers left for 5 CTAs per SM: 740 resident CTAs hold all 592 lanes of the default bench in ONE wave
+// (512 threads x 2 per SM = 296 ran two), 15.9 -> 13.8 ms per 25-scan step although the kernel spills ~1 KB per thread;
+// 512 x 1 (114 registers, no spills) 19.6 ms, 512 x 3 16.2 ms, 384 x 2 16.6 ms, 256 x 6 14.2 ms (profiles/README.md)
+#ifndef LEGO_ODO_MINBLOCKS
+#define LEGO_ODO_MINBLOCKS 5
+#endif
+#define ODO_BOUNDS __launch_bounds__(ODO_THREADS, LEGO_ODO_MINBLOCKS)
+__global__ void ODO_BOUNDS fa_odometry_kernel(IpDev d, FaDev f, Consts c, int buf) {
     odometry_body<false>(d, f, c, buf, blockIdx.x, true);
 }
 

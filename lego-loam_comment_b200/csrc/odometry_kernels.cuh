@@ -14,7 +14,7 @@
 namespace lego {
 
 #ifndef LEGO_ODO_THREADS
-#define LEGO_ODO_THREADS 512
+#define LEGO_ODO_THREADS 256
 #endif
 constexpr int ODO_THREADS = LEGO_ODO_THREADS;
 constexpr int ODO_WARPS = ODO_THREADS / 32;

@@ -129,7 +129,12 @@ __global__ void __launch_bounds__(256) rs_scan_kernel(VgBatch b) {
     if (d == 0) { s.state[8] = skip; s.state[7] = skip ? 0 : 1; }
 }
 
-__global__ void __launch_bounds__(VG_THREADS) rs_scatter_kernel(VgBatch b, int shift) {
+#ifdef LEGO_RS_MINBLOCKS
+#define RS_BOUNDS __launch_bounds__(VG_THREADS, LEGO_RS_MINBLOCKS)
+#else
+#define RS_BOUNDS __launch_bounds__(VG_THREADS)
+#endif
+__global__ void RS_BOUNDS rs_scatter_kernel(VgBatch b, int shift) {
     const VgSeg& s = b.segs[blockIdx.y];
     const int n = s.state[9];
     if (s.state[8]) return;
