@@ -28,14 +28,14 @@ VoxelHash Engine::allocHash(int cap, float cell, const int* n, int nStride, int 
 
 void Engine::allocOdometry() {
     const size_t L = c.L, N = c.N, R = c.R;
-    // CTAs per lane of the scan-to-scan LM kernel: a cluster of up to 8 while that still leaves every lane its own SMs (the B200
-    // has 148); LEGO_ODO_CLUSTER = 1 / 2 / 4 / 8 forces a size
+    // CTAs per lane of the scan-to-scan LM kernel: a cluster of up to 16 (beyond the portable 8: opt-in attribute) while that
+    // still leaves every lane its own SMs (the B200 has 148); LEGO_ODO_CLUSTER = 1 / 2 / 4 / 8 / 16 forces a size
     {
         int sms = 148;
         cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, params.device);
         const char* e = std::getenv("LEGO_ODO_CLUSTER");
         int want = e && *e ? std::atoi(e) : 0;
-        if (want != 1 && want != 2 && want != 4 && want != 8) { want = 8; while (want > 1 && (int)L * want > sms) want >>= 1; }
+        if (want != 1 && want != 2 && want != 4 && want != 8 && want != 16) { want = 16; while (want > 1 && (int)L * want > sms) want >>= 1; }
         odoCluster = want;
     }
     for (int b = 0; b < 2; ++b) { fa.cornerLast[b] = alloc<float4>(L * R * 120); fa.surfLast[b] = alloc<float4>(L * N); }
@@ -199,6 +199,7 @@ void Engine::updateTransformation() {
     if (!attr_set) {
         cuda_check(cudaFuncSetAttribute(fa_odometry_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 64 * 1024), "smem attr");
         cuda_check(cudaFuncSetAttribute(fa_odometry_cluster_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 64 * 1024), "smem attr");
+        cuda_check(cudaFuncSetAttribute(fa_odometry_cluster_kernel, cudaFuncAttributeNonPortableClusterSizeAllowed, 1), "cluster attr");
         attr_set = true;
     }
     if (odoCluster > 1) {

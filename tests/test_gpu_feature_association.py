@@ -127,11 +127,11 @@ def test_odometry_cluster_sizes_change_nothing(monkeypatch):
     seqs = [SynthSequence(sensor, seed=23, scene="street", speed=7.0), SynthSequence(sensor, seed=24, scene="street", speed=3.0, dropout=0.15)]
     cap = seqs[0].cap
     pls = []
-    for cl in (1, 2, 4, 8):
+    for cl in (1, 2, 4, 8, 16):
         monkeypatch.setenv("LEGO_ODO_CLUSTER", str(cl))
         pls.append(Pipeline(make_params(sensor), lanes=2, max_points=cap))
     monkeypatch.delenv("LEGO_ODO_CLUSTER")
-    pls.append(Pipeline(make_params(sensor), lanes=2, max_points=cap))       # the default for two lanes (8)
+    pls.append(Pipeline(make_params(sensor), lanes=2, max_points=cap))       # the default for two lanes (16)
     moved = 0.0
     for k in range(16):
         x = np.zeros((2, cap, 4), np.float32); r = np.zeros((2, cap), np.uint16); n = []
