@@ -199,6 +199,68 @@ def make_sequence(sensor, seed, workload, speed, n_scans):
     return SynthSequence(sensor, seed=seed, scene="street", speed=speed, n_scans=max(n_scans, 64))
 
 
+# ------------------------------------------------------------------------------------------------ host memory placement
+_NUMA = {"node": None, "note": "not tried"}
+
+
+def numa_place_near_gpu(device_index):
+    """Page-locked input buffers should live in the DRAM of the socket the GPU hangs on: with one rank per GPU on a two-socket
+    box, round 1's 8-GPU end-to-end run moved ~25 GB/s per GPU where one GPU alone moves 55 (every rank's buffers on one
+    socket).  Reads the GPU's NUMA node from sysfs, makes it the preferred node of this thread's allocations
+    (set_mempolicy(MPOL_PREFERRED): falls back to other nodes by itself) and moves the thread onto that node's cores when its
+    affinity mask allows.  Anything missing (one node, a VM without topology, no permission) leaves the defaults in place.
+    Returns what was done, for the bench line."""
+    import ctypes
+    import platform
+    info = {"node": None, "note": ""}
+    try:
+        import torch
+        pr = torch.cuda.get_device_properties(device_index)
+        dom, bus, dev = getattr(pr, "pci_domain_id", 0), getattr(pr, "pci_bus_id", None), getattr(pr, "pci_device_id", 0)
+        if bus is None:
+            info["note"] = "no PCI id from torch"; return info
+        path = "/sys/bus/pci/devices/%04x:%02x:%02x.0/numa_node" % (dom, bus, dev)
+        with open(path) as f:
+            node = int(f.read().strip())
+        with open("/sys/devices/system/node/online") as f:
+            online = f.read().strip()
+        if node < 0 or online in ("0", ""):
+            info["note"] = "single NUMA node (gpu node %d, online %s)" % (node, online); return info
+        info["node"] = node
+        nr = {"x86_64": 238, "aarch64": 237}.get(platform.machine())
+        if nr is not None and node < 64:
+            libc = ctypes.CDLL(None, use_errno=True)
+            mask = ctypes.c_ulong(1 << node)
+            rc = libc.syscall(nr, 1, ctypes.byref(mask), 65)    # MPOL_PREFERRED
+            info["mempolicy"] = "preferred node %d" % node if rc == 0 else "set_mempolicy errno %d" % ctypes.get_errno()
+        cpus = set()
+        with open("/sys/devices/system/node/node%d/cpulist" % node) as f:
+            for part in f.read().strip().split(","):
+                if part:
+                    a, _, b = part.partition("-")
+                    cpus.update(range(int(a), int(b or a) + 1))
+        mine = os.sched_getaffinity(0) & cpus
+        if mine:
+            os.sched_setaffinity(0, mine); info["cpus"] = len(mine)
+        else:
+            info["cpus"] = 0
+        info["note"] = "gpu %d on NUMA node %d" % (device_index, node)
+    except Exception as e:   # placement is an optimisation: never fail the bench over it
+        info["note"] = "left alone: %s" % str(e)[:120]
+    return info
+
+
+def numa_reset():
+    import ctypes
+    import platform
+    nr = {"x86_64": 238, "aarch64": 237}.get(platform.machine())
+    if nr is not None and _NUMA.get("mempolicy", "").startswith("preferred"):
+        try:
+            ctypes.CDLL(None).syscall(nr, 0, None, 0)             # MPOL_DEFAULT
+        except OSError:
+            pass
+
+
 class Inputs:
     """Pinned host copy of D sequences x T scans, one slot of cap * (4 fpp + 2) bytes per (scan, sequence) so that one scan of
     all sequences is contiguous: a slot holds the scan's npts points (fpp floats each) and, directly behind them, its ring
@@ -413,7 +475,9 @@ def run_b200(args, sensor, lanes, workload):
     Ttot = win.T + max(phase)
     cap0 = params.N_SCAN * params.Horizon_SCAN
     D = args.distinct if args.distinct > 0 else default_distinct(sensor, world, L, Ttot, cap0)
+    _NUMA.update(numa_place_near_gpu(local))
     inp = Inputs(sensor, rank_seeds(rank, world, D), Ttot, workload, args.speed, fpp)
+    numa_reset()
     cap = inp.cap
     bounds = [(h * L) // H for h in range(H + 1)]
 
@@ -636,6 +700,7 @@ def run_b200(args, sensor, lanes, workload):
                            "one cudaMemcpyAsync per lane: the ring channel sits directly behind the lane's points (lego_pipeline_step_lanes, src_on_device = 0)",
                "h2d_gbs_achieved": round(moved / e2e_s / 1e9, 1),
                "seconds": e2e_s, "pcie_h2d_gbs_plain_copy": round(h2d_gbs, 1), "poses_equal_device_arm": same,
+               "host_memory": dict(_NUMA),
                "mode": "streaming: up to 5 scans in flight per handle, the poses of scan k are collected after scan k+4 was submitted"}
 
     prof_h0 = prof_all[0]
