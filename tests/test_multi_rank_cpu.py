@@ -83,3 +83,39 @@ def test_window_is_the_same_for_both_arms():
     assert w.first_timed == 125 and w.prime == 100 and w.T == 175
     assert bench.default_distinct("vlp16", 1, 592, 625, 28800) == 32
     assert bench.default_distinct("vlp16", 8, 592, 625, 28800) == 4
+
+
+def test_reference_arm_prints_the_contract_line():
+    """`bench.py --impl reference` as the driver launches it (no GPU involved): one JSON line with the arm's own metric, the
+    window both arms time, a cpu_baseline describing the run and an e2e block that repeats the value with zero copy bytes."""
+    import json
+    import subprocess
+    from conftest import require_ref
+    require_ref("vlp16")
+    out = subprocess.run([sys.executable, os.path.join(ROOT, "bench.py"), "--impl", "reference", "--steps", "1", "--warmup", "3"],
+                         capture_output=True, text=True, timeout=600, cwd=ROOT)
+    assert out.returncode == 0, out.stderr[-2000:]
+    lines = [ln for ln in out.stdout.strip().splitlines() if ln.startswith("{")]
+    assert len(lines) == 1
+    d = json.loads(lines[0])
+    assert d["impl"] == "reference" and d["metric"] == "scans_per_sec" and d["unit"] == "scans/s" and d["higher_is_better"] is True
+    assert d["value"] > 0 and d["n_gpus"] == 1 and d["steps"] == 1 and d["warmup"] == 3 and d["vs_baseline"] is None
+    lo, hi = d["config"]["timed_scan_range"]
+    assert lo >= 125 and hi - lo + 1 == d["config"]["timed_scans_per_lane"] == 25      # steady-state window, one 25-scan step
+    cb = d["cpu_baseline"]
+    assert cb["kind"] == "reference" and cb["cores"] >= 1 and cb["value"] == d["value"] and "sample" in cb
+    assert d["e2e"] == {"value": d["value"], "unit": "scans/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0}
+    assert d["gpu_launches"] == 0
+
+
+def test_numa_placement_never_fails_the_bench():
+    """The page-locked input arena is placed near the GPU when the box has several NUMA nodes; without a driver, without
+    topology or on one node the helper must report why it did nothing and leave the process untouched."""
+    sys.path.insert(0, ROOT)
+    import bench
+    before = os.sched_getaffinity(0)
+    info = bench.numa_place_near_gpu(0)
+    bench.numa_reset()
+    assert isinstance(info, dict) and "note" in info and info["note"]
+    if info["node"] is None:
+        assert os.sched_getaffinity(0) == before
