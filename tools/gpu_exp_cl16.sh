@@ -1,3 +1,4 @@
+# 16-CTA odometry clusters: cluster-size equality test + pipeline API tests, then one-lane latency with clusters of 8 and 16
 mkdir -p gpurun_out
 timeout 600 python -m pytest tests/test_gpu_feature_association.py tests/test_gpu_pipeline_api.py -x -q -m gpu 2>&1 | tail -4
 for CL in 8 16; do

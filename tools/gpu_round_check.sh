@@ -1,3 +1,4 @@
+# what the driver runs at the end of a round, in one gpurun call: the no-alloc test alone, the GPU suite, the default bench (+ event profile), the reference arm
 mkdir -p gpurun_out
 nvidia-smi --query-gpu=name,memory.total --format=csv,noheader > gpurun_out/r1_gpu.txt; nproc >> gpurun_out/r1_gpu.txt; free -g | head -2 >> gpurun_out/r1_gpu.txt
 timeout 600 python -m pytest tests/test_zz_no_alloc.py -x -q -m gpu > gpurun_out/r1_noalloc_alone.log 2>&1; echo "noalloc alone rc=$?"
