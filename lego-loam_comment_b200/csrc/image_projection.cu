@@ -280,10 +280,12 @@ __global__ void __launch_bounds__(256) ip_ccl_stats_kernel(IpDev d, Consts c) {
 // ---- tiled connected components ------------------------------------------------------------------------------------------
 // The three passes above send every vertical edge through an atomicMin chain in L2 (ip_ccl_union_kernel: L1 hit rate 1 %).
 // Here a CTA owns a tile of ALL rows x TW columns (<= 4096 cells) and resolves it in shared memory:
-//   ip_ccl_tile_kernel    ranges staged in shared memory, both edge tests per cell, lock-free min-index union-find on a
-//                         shared-memory forest, then per tile component (rooted at its smallest cell) the number of members
-//                         besides that root and the row bits of those members.  Row-major order inside a tile is the order of
-//                         the image, so "smallest local index" = "smallest cell index".
+//   ip_ccl_tile_kernel    ranges staged in shared memory, both edge tests per cell kept as ballot words, horizontal runs get
+//                         their first cell as parent from those words (no atomics), vertical edges are lock-free min-index
+//                         unions on the shared-memory forest of run heads (both ends pointed at the surviving root), then per
+//                         tile component (rooted at its smallest cell) the number of members besides that root and the row
+//                         bits of those members.  Row-major order inside a tile is the order of the image, so "smallest local
+//                         index" = "smallest cell index".
 //   ip_ccl_border_kernel  the edges between neighbouring tiles and the column wrap (R per border) joined on the global forest
 //                         the tile roots form: a few hundred unions per image instead of one per run.
 //   ip_ccl_finish_kernel  every cell is pointed at its final root; every tile root that is not the final root hands over its
